@@ -1,0 +1,202 @@
+/* b200jpeg.h -- C ABI of the B200-native scan-to-pixels path.
+ *
+ * Drop-in boundary for aswanthabam/JPEG_Decoder's hot path.  The reference has no FFI; its
+ * path is four private member functions run by Image::process_image_data() (jpeg.cpp:755-789),
+ * called once from readJPEG() at the SOS marker (jpeg.cpp:858-863).  Everything the reference
+ * holds at that seam is mirrored here as plain structs (no C++ or torch types):
+ *
+ *   b200jpeg_huffman_table  <- HuffmanTable            include/huffman.hpp:8-15
+ *   b200jpeg_quant_table    <- QuantizationTable       include/types.hpp:79-96
+ *   b200jpeg_component      <- ColorComponent          include/types.hpp:69-77
+ *   b200jpeg_image_desc     <- Image's private state   jpeg.cpp:21-34, 792-795
+ *   b200jpeg_mcu            <- MCU                     include/types.hpp:32-67
+ *
+ * and the stages map as
+ *
+ *   b200jpeg_parse_header() <- Image::Image + readJPEG up to SOS   jpeg.cpp:797-807, 826-867
+ *                              (read_sof :67, read_huffman_table :148, read_quantization_table :197,
+ *                               read_sos :233, read_dri :289; Marker::Marker file.hpp:192-258)
+ *   b200jpeg_decode_batch() <- process_image_data()                jpeg.cpp:755-789
+ *                              = readImageData file.hpp:59-104 + decodeHuffman :405-446
+ *                              + dequantize :572-590 + inverseDCT :735-753 + YCbCrToRGB :544-561
+ *                              + the RGB gather of display.hpp:19-34
+ *
+ * Error convention: the reference logs and calls exit(1); this library never exits and never
+ * throws across the boundary.  Calls return 0 or a negative B200JPEG_E_* code; per-image
+ * problems come back in status[] (bit mask, 0 = decoded).
+ *
+ * There is no CPU fallback: every decode entry point fails with B200JPEG_E_CUDA if no
+ * sm_100-class device is usable.
+ */
+#ifndef B200JPEG_H
+#define B200JPEG_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200JPEG_ABI_VERSION 1
+
+/* ---- return codes (calls) ---- */
+enum {
+  B200JPEG_OK = 0,
+  B200JPEG_E_ARG = -1,            /* null/invalid argument */
+  B200JPEG_E_CUDA = -2,           /* CUDA error or no device (see b200jpeg_last_error) */
+  B200JPEG_E_NOMEM = -3,
+  B200JPEG_E_STATE = -4,          /* run/fetch without a prepared batch */
+  /* header parser: one code per exit(1) of the reference */
+  B200JPEG_E_NOT_JPEG = -10,      /* jpeg.cpp:800-805 */
+  B200JPEG_E_PROGRESSIVE = -11,   /* jpeg.cpp:69-73 */
+  B200JPEG_E_COMPONENTS = -12,    /* jpeg.cpp:83-87, 236-240 */
+  B200JPEG_E_SAMPLING = -13,      /* jpeg.cpp:110-136 */
+  B200JPEG_E_TABLE_ID = -14,      /* jpeg.cpp:156-160, 205-209 */
+  B200JPEG_E_DHT = -15,           /* jpeg.cpp:177-181, 190-194 */
+  B200JPEG_E_SOS = -16,           /* jpeg.cpp:255-264, 282-286 */
+  B200JPEG_E_DRI = -17,           /* jpeg.cpp:292-296 */
+  B200JPEG_E_NO_SOS = -18,        /* readJPEG returned before SOS, jpeg.cpp:878-903 */
+  B200JPEG_E_TABLE_MISSING = -19, /* jpeg.cpp:757-774 */
+  B200JPEG_E_TRUNCATED = -20,     /* header runs past the end of the buffer */
+  B200JPEG_E_COMPONENT_ID = -21,  /* jpeg.cpp:95-104 */
+  B200JPEG_E_UNSUPPORTED = -22    /* accepted by the reference's parser but outside the kernels:
+                                     the subsampled component is not the first one */
+};
+
+/* ---- per-image status bits written by the kernels (status[i] == 0: decoded) ---- */
+enum {
+  B200JPEG_ST_BAD_MARKER = 1 << 0,     /* file.hpp:91-95 */
+  B200JPEG_ST_NO_EOI = 1 << 1,         /* file.hpp:59-104 would never return */
+  B200JPEG_ST_BAD_RST_COUNT = 1 << 2,  /* RSTn markers != ceil(MCUs/RI)-1 */
+  B200JPEG_ST_BAD_CODE = 1 << 3,       /* jpeg.cpp:300-320 */
+  B200JPEG_ST_BAD_DC_LEN = 1 << 4,     /* jpeg.cpp:330-334 */
+  B200JPEG_ST_BAD_RUN = 1 << 5,        /* jpeg.cpp:372-376 */
+  B200JPEG_ST_BAD_AC_LEN = 1 << 6,     /* jpeg.cpp:381-385 */
+  B200JPEG_ST_OVERRUN = 1 << 7,        /* file.hpp:36-40 */
+  B200JPEG_ST_BLOCK_COUNT = 1 << 8,
+  B200JPEG_ST_DC_RANGE = 1 << 9,
+  B200JPEG_ST_NOT_CONVERGED = 1 << 10,
+  B200JPEG_ST_UNSUPPORTED = 1 << 11
+};
+
+/* parser flags */
+enum {
+  B200JPEG_PARSE_REFERENCE = 0, /* accept exactly what the reference accepts */
+  B200JPEG_PARSE_SPEC = 1       /* superset: 1-component grey, COM/unknown
+                                   segments skipped, fill bytes before markers */
+};
+
+/* HuffmanTable, include/huffman.hpp:8-15.  offset[] are cumulative counts (jpeg.cpp:170-176),
+ * codes[] what generateCodes() assigns (huffman.hpp:17-29). */
+typedef struct {
+  uint8_t offset[17];
+  uint8_t symbols[176];   /* `char symbols[162]` in the reference; jpeg.cpp:177 admits up to 176 */
+  uint32_t codes[176];
+  uint8_t set;
+} b200jpeg_huffman_table;
+
+/* QuantizationTable, include/types.hpp:79-96: de-zig-zagged at construction (natural order). */
+typedef struct {
+  int32_t table[64];
+  uint8_t set;
+} b200jpeg_quant_table;
+
+/* ColorComponent, include/types.hpp:69-77 */
+typedef struct {
+  int32_t horizontal_sampling_factor;
+  int32_t vertical_sampling_factor;
+  int32_t quantizationTableID;
+  int32_t huffmanDCTTableID;
+  int32_t huffmanACTableID;
+} b200jpeg_component;
+
+/* MCU, include/types.hpp:32-67: one 8x8 block position; y/cb/cr before YCbCrToRGB, r/g/b after. */
+typedef struct {
+  int32_t y[64], cb[64], cr[64];
+} b200jpeg_mcu;
+
+/* The state Image holds when process_image_data() is entered (jpeg.cpp:21-34, 792-795). */
+typedef struct {
+  int32_t image_width, image_height;          /* jpeg.cpp:792-793 */
+  int32_t mcuWidth, mcuHeight;                /* ceil(/8), jpeg.cpp:30-31, 77-78 */
+  int32_t mcuWidthReal, mcuHeightReal;        /* jpeg.cpp:794-795, 118-125 */
+  int32_t horizontalSamplingFactor;           /* jpeg.cpp:32, 126 */
+  int32_t verticalSamplingFactor;             /* jpeg.cpp:33, 127 */
+  int32_t numComponents;                      /* jpeg.cpp:29 */
+  int32_t restartInterval;                    /* jpeg.cpp:27, 291 */
+  int32_t zeroBased;                          /* jpeg.cpp:28 */
+  b200jpeg_component color_components[3];     /* jpeg.cpp:23 */
+  b200jpeg_quant_table quantization_tables[4];/* jpeg.cpp:22 */
+  b200jpeg_huffman_table huffmanDCTTable[4];  /* jpeg.cpp:24 */
+  b200jpeg_huffman_table huffmanACTable[4];   /* jpeg.cpp:25 */
+  int64_t scan_offset;   /* offset of the first entropy-coded byte in the file; where
+                            Marker::Marker starts readImageData(), file.hpp:214-219 */
+  int64_t scan_length;   /* bytes from scan_offset to the end of the file (stuffed, markers and
+                            EOI included; the kernels find FF D9 themselves) */
+} b200jpeg_image_desc;
+
+typedef struct b200jpeg_ctx b200jpeg_ctx;
+
+/* Host-side header parse (no GPU needed).  Mirrors readJPEG()'s marker loop up to and including
+ * read_sos(), returning a code where the reference calls exit(1). */
+int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags, b200jpeg_image_desc *desc);
+
+/* One context per GPU: owns a stream, device arenas and pinned staging.  Use from one host
+ * thread at a time. */
+int b200jpeg_create(int device, b200jpeg_ctx **ctx);
+void b200jpeg_destroy(b200jpeg_ctx *ctx);
+const char *b200jpeg_last_error(const b200jpeg_ctx *ctx);
+
+/* Whole path, HOST buffers in and out (the reference-facing call):
+ *   file_bytes[i]/file_sizes[i]  the complete JPEG file i (pageable or pinned host memory)
+ *   rgb_out[i]   host buffer of 3*W*H bytes: row-major, top-down, interleaved R,G,B, pitch 3*W
+ *                (the display.hpp:27-34 gather flattened); may be NULL to skip the copy
+ *   coef_out[i]  optional (array or entry may be NULL): host buffer of
+ *                mcuWidthReal*mcuHeightReal b200jpeg_mcu-shaped int16 triples, i.e.
+ *                int16 [pos][3][64] natural order -- the MCU array after decodeHuffman()
+ *   status[i]    per-image status bits
+ * Equivalent to prepare + run + fetch below. */
+int b200jpeg_decode_batch(b200jpeg_ctx *ctx, const b200jpeg_image_desc *descs, int n,
+                          const uint8_t *const *file_bytes, const size_t *file_sizes,
+                          uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status);
+
+/* The same in three steps, so that a caller can keep a batch resident in HBM:
+ *   prepare: plan the batch, copy the scans (and the small descriptors) host -> device
+ *   run    : launch every kernel of the path on the context's stream (asynchronous)
+ *   fetch  : wait, then copy RGB / coefficients / status device -> host */
+int b200jpeg_batch_prepare(b200jpeg_ctx *ctx, const b200jpeg_image_desc *descs, int n,
+                           const uint8_t *const *file_bytes, const size_t *file_sizes);
+int b200jpeg_batch_run(b200jpeg_ctx *ctx);
+int b200jpeg_batch_fetch(b200jpeg_ctx *ctx, uint8_t *const *rgb_out, int16_t *const *coef_out,
+                         int32_t *status);
+int b200jpeg_sync(b200jpeg_ctx *ctx);
+
+/* Device-resident results of the current batch (valid until the next prepare). */
+int b200jpeg_device_rgb(b200jpeg_ctx *ctx, int i, void **dev_ptr, size_t *pitch_bytes);
+void *b200jpeg_stream(b200jpeg_ctx *ctx);   /* cudaStream_t */
+
+/* Counters of the current batch. */
+typedef struct {
+  int64_t images, pixels, scan_bytes, coded_blocks, rgb_bytes;
+  int64_t h2d_bytes, d2h_bytes;
+  int32_t kernel_launches;      /* kernels launched by the last b200jpeg_batch_run */
+  int32_t sync_rounds;          /* fix launches the last run needed */
+} b200jpeg_batch_stats;
+int b200jpeg_batch_get_stats(const b200jpeg_ctx *ctx, b200jpeg_batch_stats *stats);
+
+/* Per-stage CUDA-event times of the last b200jpeg_batch_run (milliseconds): unstuff, entropy
+ * sync, entropy write, pixel, total.  Only recorded when enabled (adds event records). */
+enum { B200JPEG_T_UNSTUFF = 0, B200JPEG_T_SYNC = 1, B200JPEG_T_WRITE = 2, B200JPEG_T_PIXEL = 3,
+       B200JPEG_T_TOTAL = 4, B200JPEG_T_COUNT = 5 };
+int b200jpeg_set_timing(b200jpeg_ctx *ctx, int enabled);
+int b200jpeg_last_timing(b200jpeg_ctx *ctx, float *ms, int count);
+
+/* Pinned host memory helpers (cudaHostAlloc / cudaFreeHost) for zero-staging copies. */
+void *b200jpeg_host_alloc(size_t bytes);
+void b200jpeg_host_free(void *p);
+
+int b200jpeg_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
