@@ -1,0 +1,187 @@
+// host_parse.cpp -- host-side marker reader / header parser behind b200jpeg_parse_header().
+//
+// Mirrors, on one contiguous buffer instead of a per-byte ifstream, what the reference does
+// between Image::Image (jpeg.cpp:797-807) and the call of process_image_data() (jpeg.cpp:861):
+//   Marker::Marker          include/file.hpp:192-258   marker classification + length + payload
+//   Image::readJPEG         jpeg.cpp:826-907           dispatch loop
+//   read_sof                jpeg.cpp:67-146
+//   read_huffman_table      jpeg.cpp:148-196  (+ HuffmanTable::generateCodes, huffman.hpp:17-29)
+//   read_quantization_table jpeg.cpp:197-231  (+ QuantizationTable ctor, types.hpp:86-92)
+//   read_sos                jpeg.cpp:233-287
+//   read_dri                jpeg.cpp:289-298
+//   table checks            jpeg.cpp:757-774
+// Every exit(1) of the reference becomes a negative return code.  The scan itself is NOT
+// touched here: readImageData (file.hpp:59-104) is replaced by the unstuff kernels.
+#include "../../include/b200jpeg.h"
+#include <string.h>
+
+namespace {
+
+const int kZigZag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                         41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                         30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+inline int be16(const uint8_t *p) { return (p[0] << 8) | p[1]; }
+
+int parse_sof(b200jpeg_image_desc *d, int marker, const uint8_t *p, int len, bool spec) {
+  if (marker == 0xc2) return B200JPEG_E_PROGRESSIVE;
+  if (len < 6) return B200JPEG_E_TRUNCATED;
+  d->image_height = be16(p + 1);
+  d->image_width = be16(p + 3);
+  d->mcuWidth = (d->image_width + 7) / 8;
+  d->mcuHeight = (d->image_height + 7) / 8;
+  d->mcuWidthReal = d->mcuWidth;
+  d->mcuHeightReal = d->mcuHeight;
+  const int nc = p[5];
+  d->numComponents = nc;
+  if (nc != 3 && !(spec && nc == 1)) return B200JPEG_E_COMPONENTS;
+  if (len < 6 + 3 * nc) return B200JPEG_E_TRUNCATED;
+  for (int i = 0; i < nc; ++i) {
+    const int id = p[6 + 3 * i];
+    if (id == 0) d->zeroBased = 1;
+    if (!d->zeroBased && id > 3) return B200JPEG_E_COMPONENT_ID;
+    if (d->zeroBased && id > 2) return B200JPEG_E_COMPONENT_ID;
+    b200jpeg_component *c = &d->color_components[i];
+    c->horizontal_sampling_factor = p[7 + 3 * i] >> 4;
+    c->vertical_sampling_factor = p[7 + 3 * i] & 15;
+    c->quantizationTableID = p[8 + 3 * i];
+    if (nc == 1) {  // T.81 A.2.2: a one-component scan has one block per MCU whatever Hi,Vi say
+      c->horizontal_sampling_factor = c->vertical_sampling_factor = 1;
+      d->horizontalSamplingFactor = d->verticalSamplingFactor = 1;
+      continue;
+    }
+    if (id == 1) {
+      const int h = c->horizontal_sampling_factor, v = c->vertical_sampling_factor;
+      if ((h != 1 && h != 2) || (v != 1 && v != 2)) return B200JPEG_E_SAMPLING;
+      if (h == 2 && d->mcuWidth % 2 == 1) d->mcuWidthReal += 1;
+      if (v == 2 && d->mcuHeight % 2 == 1) d->mcuHeightReal += 1;
+      d->horizontalSamplingFactor = h;
+      d->verticalSamplingFactor = v;
+      if (i != 0 && (h != 1 || v != 1)) return B200JPEG_E_UNSUPPORTED;
+    } else if (c->horizontal_sampling_factor != 1 || c->vertical_sampling_factor != 1) {
+      return B200JPEG_E_SAMPLING;
+    }
+  }
+  return 0;
+}
+
+int parse_dht(b200jpeg_image_desc *d, const uint8_t *p, int len) {
+  while (len > 0) {
+    if (len < 17) return B200JPEG_E_DHT;
+    const int id = p[0] & 15, is_ac = p[0] >> 4;
+    if (id > 3) return B200JPEG_E_TABLE_ID;
+    b200jpeg_huffman_table *t = is_ac ? &d->huffmanACTable[id] : &d->huffmanDCTTable[id];
+    t->offset[0] = 0;
+    int all = 0;
+    for (int i = 1; i <= 16; ++i) { all += p[i]; t->offset[i] = (uint8_t)all; }
+    if (all > 176) return B200JPEG_E_DHT;
+    if (len < 17 + all) return B200JPEG_E_DHT;
+    memset(t->symbols, 0, sizeof t->symbols);
+    for (int i = 0; i < all; ++i) t->symbols[i] = p[17 + i];
+    t->set = 1;
+    uint32_t code = 0;  // generateCodes(), huffman.hpp:17-29
+    memset(t->codes, 0, sizeof t->codes);
+    for (int i = 0; i < 16; ++i) {
+      for (int j = t->offset[i]; j < t->offset[i + 1]; ++j) t->codes[j] = code++;
+      code <<= 1;
+    }
+    p += 17 + all;
+    len -= 17 + all;
+  }
+  return len != 0 ? B200JPEG_E_DHT : 0;
+}
+
+int parse_dqt(b200jpeg_image_desc *d, const uint8_t *p, int len) {
+  while (len > 0) {
+    const int id = p[0] & 15, wide = p[0] >> 4;
+    ++p; --len;
+    if (id > 3) return B200JPEG_E_TABLE_ID;
+    uint8_t raw[64];
+    if (wide) {
+      if (len < 128) return B200JPEG_E_TRUNCATED;
+      for (int i = 0; i < 64; ++i) raw[i] = p[2 * i + 1];  // jpeg.cpp:216 keeps the low byte only
+      p += 128; len -= 128;
+    } else {
+      if (len < 64) return B200JPEG_E_TRUNCATED;
+      memcpy(raw, p, 64);
+      p += 64; len -= 64;
+    }
+    b200jpeg_quant_table *q = &d->quantization_tables[id];
+    for (int i = 0; i < 64; ++i) q->table[kZigZag[i]] = raw[i];  // types.hpp:86-92
+    q->set = 1;
+  }
+  return 0;
+}
+
+int parse_sos(b200jpeg_image_desc *d, const uint8_t *p, int len) {
+  if (len < 1) return B200JPEG_E_SOS;
+  const int nc = p[0];
+  if (nc != d->numComponents || (nc != 3 && nc != 1)) return B200JPEG_E_COMPONENTS;
+  if (len < 1 + 2 * nc + 3) return B200JPEG_E_SOS;
+  for (int i = 0; i < nc; ++i) {  // bound by position, the id byte is ignored (jpeg.cpp:241-247)
+    d->color_components[i].huffmanDCTTableID = p[2 + 2 * i] >> 4;
+    d->color_components[i].huffmanACTableID = p[2 + 2 * i] & 15;
+  }
+  const uint8_t *q = p + 1 + 2 * nc;
+  if (q[0] != 0 || q[1] != 63) return B200JPEG_E_SOS;
+  if (q[2] != 0) return B200JPEG_E_SOS;
+  if (len + 2 - 6 - 2 * nc != 0) return B200JPEG_E_SOS;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags, b200jpeg_image_desc *d) {
+  if (!file || !d) return B200JPEG_E_ARG;
+  memset(d, 0, sizeof *d);
+  const bool spec = (flags & B200JPEG_PARSE_SPEC) != 0;
+  if (len < 2 || file[0] != 0xff || file[1] != 0xd8) return B200JPEG_E_NOT_JPEG;
+  size_t pos = 2;
+  bool got_sos = false;
+  while (!got_sos) {
+    if (pos >= len) return B200JPEG_E_NO_SOS;
+    if (file[pos++] != 0xff) return B200JPEG_E_NO_SOS;       // jpeg.cpp:899-903
+    if (pos >= len) return B200JPEG_E_TRUNCATED;
+    const int m = file[pos++];
+    if (m == 0x00) continue;                                 // PAD, file.hpp:196-200
+    if (m >= 0xd0 && m < 0xd8) continue;                     // DRM, file.hpp:208-213
+    if (spec && m == 0xff) { --pos; continue; }              // fill byte, T.81 B.1.1.2
+    if (pos + 2 > len) return B200JPEG_E_TRUNCATED;
+    const int seglen = be16(file + pos);
+    const uint8_t *p = file + pos + 2;
+    const int plen = seglen - 2;
+    if (plen < 0 || pos + (size_t)seglen > len) return B200JPEG_E_TRUNCATED;
+    pos += (size_t)seglen;
+    if (m >= 0xe0 && m < 0xf0) continue;                     // META, file.hpp:201-207
+    int rc = 0;
+    switch (m) {
+      case 0xc0: case 0xc2: rc = parse_sof(d, m, p, plen, spec); break;
+      case 0xc4: rc = parse_dht(d, p, plen); break;
+      case 0xdb: rc = parse_dqt(d, p, plen); break;
+      case 0xdd:
+        if (plen != 2) rc = B200JPEG_E_DRI; else d->restartInterval = be16(p);
+        break;
+      case 0xda: rc = parse_sos(d, p, plen); got_sos = true; break;
+      case 0xd8: break;                                      // SOI is only logged, jpeg.cpp:838-841
+      default:
+        if (spec && m != 0xd9 && !(m >= 0xc1 && m <= 0xcf)) break;   // COM and friends
+        if (spec && m != 0xd9) { rc = B200JPEG_E_PROGRESSIVE; break; }
+        rc = B200JPEG_E_NO_SOS;                              // EOI / INVALID, jpeg.cpp:878-887
+    }
+    if (rc) return rc;
+  }
+  if (d->numComponents == 0 || d->horizontalSamplingFactor == 0 || d->verticalSamplingFactor == 0)
+    return B200JPEG_E_SAMPLING;
+  for (int i = 0; i < d->numComponents; ++i) {               // jpeg.cpp:757-774
+    const b200jpeg_component &c = d->color_components[i];
+    if (c.quantizationTableID > 3 || c.huffmanDCTTableID > 3 || c.huffmanACTableID > 3) return B200JPEG_E_TABLE_ID;
+    if (!d->quantization_tables[c.quantizationTableID].set || !d->huffmanDCTTable[c.huffmanDCTTableID].set ||
+        !d->huffmanACTable[c.huffmanACTableID].set)
+      return B200JPEG_E_TABLE_MISSING;
+  }
+  d->scan_offset = (int64_t)pos;
+  d->scan_length = (int64_t)(len - pos);
+  return B200JPEG_OK;
+}
+
+extern "C" int b200jpeg_abi_version(void) { return B200JPEG_ABI_VERSION; }

@@ -122,8 +122,8 @@ struct BitReader {
   uint64_t buf;
   int avail;
   uint32_t widx;
-  B2_DEVICE uint32_t ld(uint32_t i) const { return PADDED ? base[i + (i >> 5)] : base[i]; }
-  B2_DEVICE void seek(uint32_t bit) {       // bit position relative to `base`
+  B2_MEMBER uint32_t ld(uint32_t i) const { return PADDED ? base[i + (i >> 5)] : base[i]; }
+  B2_MEMBER void seek(uint32_t bit) {       // bit position relative to `base`
     widx = bit >> 5;
     const uint32_t o = bit & 31;
     const uint64_t w0 = ld(widx), w1 = ld(widx + 1);
@@ -131,12 +131,12 @@ struct BitReader {
     avail = 64 - (int)o;
     widx += 2;
   }
-  B2_DEVICE void refill() {
+  B2_MEMBER void refill() {
     if (avail <= 32) { buf |= (uint64_t)ld(widx) << (32 - avail); avail += 32; ++widx; }
   }
-  B2_DEVICE uint32_t peek() const { return (uint32_t)(buf >> 32); }
-  B2_DEVICE void skip(uint32_t n) { buf <<= n; avail -= (int)n; }
-  B2_DEVICE uint32_t pos() const { return (widx << 5) - (uint32_t)avail; }
+  B2_MEMBER uint32_t peek() const { return (uint32_t)(buf >> 32); }
+  B2_MEMBER void skip(uint32_t n) { buf <<= n; avail -= (int)n; }
+  B2_MEMBER uint32_t pos() const { return (widx << 5) - (uint32_t)avail; }
 };
 
 B2_DEVICE int extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:335-343, 388-397

@@ -175,4 +175,15 @@ B2_GLOBAL void k_unstuff_finish(const ImageDev *__restrict__ imgs, int nimg, uin
   out[i] = o;
 }
 
+// ImageOut arrives memset to 0xFF (end_pos = err_pos = kNone); clear the counters and status.
+B2_GLOBAL void k_reset_out(ImageOut *__restrict__ out, int nimg) {
+  const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+  if (i >= nimg) return;
+  out[i].us_len = 0; out[i].nrst = 0; out[i].status = 0;
+}
+B2_GLOBAL void k_raise_status(ImageOut *__restrict__ out, int nimg, uint32_t bits) {
+  const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+  if (i < nimg) out[i].status |= bits;
+}
+
 }  // namespace b2

@@ -1,0 +1,215 @@
+// pipeline.h -- batch planner and kernel launch sequence of the scan-to-pixels path.
+//
+// This is what stands where Image::process_image_data() (jpeg.cpp:755-789) stands in the
+// reference: it takes the parsed state of n images (b200jpeg_image_desc, the mirror of Image's
+// private members) plus their file bytes and runs
+//     U  unstuff + segment discovery      (file.hpp:59-104)
+//     E  entropy decode                   (jpeg.cpp:300-446)
+//     P  dequant + IDCT + upsample + RGB  (jpeg.cpp:511-753, display.hpp:19-34)
+// Compiled twice from the same source: by nvcc into libb200jpeg.so (device memory, CUDA
+// launches) and, with -DB200JPEG_EMU, by g++ into the test-only emulation library.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/b200jpeg.h"
+#include "platform.h"
+#include "dev_types.h"
+#include "kernels_unstuff.cuh"
+#include "kernels_entropy.cuh"
+#include "kernels_pixel.cuh"
+
+namespace b2 {
+
+// ---------------------------------------------------------------- memory backend
+#ifdef B200JPEG_EMU
+struct Backend {
+  std::string err;
+  bool ok() const { return err.empty(); }
+  void *alloc(size_t n) { return calloc(n ? n : 1, 1); }
+  void release(void *p) { free(p); }
+  void h2d(void *d, const void *s, size_t n) { memcpy(d, s, n); }
+  void d2h(void *d, const void *s, size_t n) { memcpy(d, s, n); }
+  void d2h_2d(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h) {
+    for (size_t y = 0; y < h; ++y) memcpy((char *)d + y * dp, (const char *)s + y * sp, w);
+  }
+  void fill(void *d, int v, size_t n) { memset(d, v, n); }
+  void sync() {}
+  void check(const char *) {}
+  cudaStream_t stream = nullptr;
+};
+#else
+struct Backend {
+  std::string err;
+  cudaStream_t stream = nullptr;
+  bool ok() const { return err.empty(); }
+  void fail(const char *what, cudaError_t e) {
+    if (err.empty()) err = std::string(what) + ": " + cudaGetErrorString(e);
+  }
+  void *alloc(size_t n) {
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, n ? n : 1);
+    if (e != cudaSuccess) { fail("cudaMalloc", e); return nullptr; }
+    return p;
+  }
+  void release(void *p) { if (p) cudaFree(p); }
+  void h2d(void *d, const void *s, size_t n) {
+    if (!n) return;
+    cudaError_t e = cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) fail("cudaMemcpyAsync H2D", e);
+  }
+  void d2h(void *d, const void *s, size_t n) {
+    if (!n) return;
+    cudaError_t e = cudaMemcpyAsync(d, s, n, cudaMemcpyDeviceToHost, stream);
+    if (e != cudaSuccess) fail("cudaMemcpyAsync D2H", e);
+  }
+  void d2h_2d(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h) {
+    cudaError_t e = cudaMemcpy2DAsync(d, dp, s, sp, w, h, cudaMemcpyDeviceToHost, stream);
+    if (e != cudaSuccess) fail("cudaMemcpy2DAsync D2H", e);
+  }
+  void fill(void *d, int v, size_t n) {
+    if (!n) return;
+    cudaError_t e = cudaMemsetAsync(d, v, n, stream);
+    if (e != cudaSuccess) fail("cudaMemsetAsync", e);
+  }
+  void sync() {
+    cudaError_t e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess) fail("cudaStreamSynchronize", e);
+  }
+  void check(const char *what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) fail(what, e);
+  }
+};
+#endif
+
+// A device buffer that only ever grows (arena reused across batches).
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  bool reserve(Backend &be, size_t n) {
+    if (n <= cap) return true;
+    be.release(p);
+    cap = n + n / 8 + 4096;
+    p = be.alloc(cap);
+    if (!p) { cap = 0; return false; }
+    return true;
+  }
+  void destroy(Backend &be) { be.release(p); p = nullptr; cap = 0; }
+  template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Sampling formats the pixel kernel is instantiated for.
+enum PixFormat { PF_444 = 0, PF_422 = 1, PF_440 = 2, PF_420 = 3, PF_GRAY = 4, PF_COUNT = 5 };
+inline int pix_tm(int f) {   // MCUs per pixel tile, PixCfg::kTM
+  switch (f) { case PF_444: return 32; case PF_422: case PF_440: return 24; case PF_420: return 16; default: return 96; }
+}
+
+struct BatchPlan {
+  int n = 0;
+  std::vector<ImageDev> imgs;
+  std::vector<TableSet> tsets;
+  std::vector<int32_t> tile_base, cta_base;           // n+1 exclusive prefixes
+  std::vector<int32_t> grp_img[PF_COUNT], grp_pre[PF_COUNT];
+  std::vector<int> bwr, bhr;                          // reference block grid (coef export)
+  size_t raw_bytes = 0, rgb_bytes = 0;
+  int64_t nblocks = 0, pixels = 0, scan_bytes = 0;
+  int ntiles = 0, nsubs = 0, nctas = 0, nsegs = 0, nslots_max = 2;
+};
+
+// Build the plan.  Returns 0 or a B200JPEG_E_* code.
+inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file_sizes, BatchPlan &P) {
+  P = BatchPlan();
+  P.n = n;
+  P.imgs.resize(n);
+  P.tile_base.assign(n + 1, 0);
+  P.cta_base.assign(n + 1, 0);
+  P.bwr.resize(n); P.bhr.resize(n);
+  int64_t coef_base = 0;
+  size_t raw_off = 0, rgb_off = 0;
+  int seg_base = 0, sub_base = 0;
+  for (int i = 0; i < n; ++i) {
+    const b200jpeg_image_desc &d = descs[i];
+    ImageDev &im = P.imgs[i];
+    memset(&im, 0, sizeof im);
+    const int nc = d.numComponents, hs = d.horizontalSamplingFactor, vs = d.verticalSamplingFactor;
+    if ((nc != 1 && nc != 3) || hs < 1 || hs > 2 || vs < 1 || vs > 2) return B200JPEG_E_ARG;
+    if (d.image_width <= 0 || d.image_height <= 0) return B200JPEG_E_ARG;
+    if (nc == 3) {   // the kernels take the subsampled component first (jpeg.cpp:110 allows id==1 anywhere)
+      if (d.color_components[0].horizontal_sampling_factor != hs || d.color_components[0].vertical_sampling_factor != vs)
+        return B200JPEG_E_UNSUPPORTED;
+      for (int c = 1; c < 3; ++c)
+        if (d.color_components[c].horizontal_sampling_factor != 1 || d.color_components[c].vertical_sampling_factor != 1)
+          return B200JPEG_E_UNSUPPORTED;
+    }
+    if (d.scan_offset < 0 || d.scan_length < 0 || (size_t)(d.scan_offset + d.scan_length) > file_sizes[i]) return B200JPEG_E_ARG;
+    if (d.scan_length >= (int64_t)1 << 28) return B200JPEG_E_UNSUPPORTED;   // bit positions are 32-bit
+    im.width = d.image_width; im.height = d.image_height;
+    im.hs = nc == 1 ? 1 : hs; im.vs = nc == 1 ? 1 : vs; im.ncomp = nc;
+    im.bpm = nc == 1 ? 1 : hs * vs + 2;
+    im.mcux = (d.mcuWidth + im.hs - 1) / im.hs;      // the x/y loops of jpeg.cpp:415-417
+    im.mcuy = (d.mcuHeight + im.vs - 1) / im.vs;
+    im.restart_interval = d.restartInterval;
+    for (int c = 0; c < nc; ++c) {
+      im.tq[c] = (int8_t)d.color_components[c].quantizationTableID;
+      im.td[c] = (int8_t)d.color_components[c].huffmanDCTTableID;
+      im.ta[c] = (int8_t)d.color_components[c].huffmanACTableID;
+    }
+    // table set, shared with earlier images when byte-identical
+    TableSet ts; memset(&ts, 0, sizeof ts);
+    for (int t = 0; t < 4; ++t) {
+      if (d.quantization_tables[t].set) for (int k = 0; k < 64; ++k) ts.q[t][k] = (uint8_t)d.quantization_tables[t].table[k];
+      const b200jpeg_huffman_table *src[2] = {&d.huffmanDCTTable[t], &d.huffmanACTable[t]};
+      HuffSpec *dst[2] = {&ts.dc[t], &ts.ac[t]};
+      for (int k = 0; k < 2; ++k) if (src[k]->set) {
+        memcpy(dst[k]->offset, src[k]->offset, 17); memcpy(dst[k]->symbols, src[k]->symbols, 176); dst[k]->set = 1;
+      }
+    }
+    int found = -1;
+    for (int t = (int)P.tsets.size() - 1; t >= 0 && t >= (int)P.tsets.size() - 4; --t)
+      if (!memcmp(&P.tsets[t], &ts, sizeof ts)) { found = t; break; }
+    if (found < 0) { P.tsets.push_back(ts); found = (int)P.tsets.size() - 1; }
+    im.tset = found;
+    {
+      int nslots = 0; bool dcu[4] = {false, false, false, false}, acu[4] = {false, false, false, false};
+      for (int c = 0; c < nc; ++c) {
+        if (!dcu[im.td[c] & 3]) { dcu[im.td[c] & 3] = true; ++nslots; }
+        if (!acu[im.ta[c] & 3]) { acu[im.ta[c] & 3] = true; ++nslots; }
+      }
+      if (nslots > P.nslots_max) P.nslots_max = nslots;
+    }
+    im.raw_len = (uint32_t)d.scan_length;
+    im.raw_off = raw_off;
+    raw_off += align_up((size_t)d.scan_length + 64, 256);
+    const int64_t mcus = (int64_t)im.mcux * im.mcuy;
+    im.nseg = d.restartInterval > 0 ? (int)((mcus + d.restartInterval - 1) / d.restartInterval) : 1;
+    im.seg_base = seg_base; seg_base += im.nseg + 1;
+    im.ntiles = (int)((d.scan_length + kUTile - 1) / kUTile);
+    im.tile_base = P.tile_base[i]; P.tile_base[i + 1] = im.tile_base + im.ntiles;
+    im.nsub_max = (int)(((int64_t)d.scan_length * 8 + kSubBits - 1) / kSubBits);
+    im.ncta = (im.nsub_max + kCT - 1) / kCT;
+    im.sub_base = sub_base; sub_base += im.ncta * kCT;
+    im.cta_base = P.cta_base[i]; P.cta_base[i + 1] = im.cta_base + im.ncta;
+    im.nblocks = (int32_t)(mcus * im.bpm);
+    im.coef_base = coef_base; coef_base += im.nblocks;
+    im.rgb_pitch = (uint32_t)align_up((size_t)3 * im.width, 16);
+    im.rgb_off = rgb_off; rgb_off += align_up((size_t)im.rgb_pitch * im.height, 256);
+    P.bwr[i] = d.mcuWidthReal; P.bhr[i] = d.mcuHeightReal;
+    P.pixels += (int64_t)im.width * im.height;
+    P.scan_bytes += d.scan_length;
+    const int f = nc == 1 ? PF_GRAY : (hs == 2 ? (vs == 2 ? PF_420 : PF_422) : (vs == 2 ? PF_440 : PF_444));
+    if (P.grp_pre[f].empty()) P.grp_pre[f].push_back(0);
+    const int tiles = im.mcuy * ((im.mcux + pix_tm(f) - 1) / pix_tm(f));
+    P.grp_img[f].push_back(i);
+    P.grp_pre[f].push_back(P.grp_pre[f].back() + tiles);
+  }
+  P.raw_bytes = raw_off; P.rgb_bytes = rgb_off; P.nblocks = coef_base;
+  P.ntiles = P.tile_base[n]; P.nctas = P.cta_base[n]; P.nsubs = sub_base; P.nsegs = seg_base;
+  return 0;
+}
+
+}  // namespace b2

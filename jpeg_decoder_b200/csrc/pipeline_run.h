@@ -1,0 +1,255 @@
+// pipeline_run.h -- device arenas, upload, the launch sequence, download.  See pipeline.h.
+#pragma once
+#include <stdlib.h>
+#include "pipeline.h"
+
+namespace b2 {
+
+constexpr int kFixLaunches = 2;       // cross-CTA repair launches issued per run
+constexpr int kMaxExtraFix = 64;      // further repair rounds if the last launch still moved state
+
+struct Pipeline {
+  Backend be;
+  BatchPlan plan;
+  bool prepared = false, ran = false;
+  // arenas
+  DevBuf d_raw, d_us, d_imgs, d_tsets, d_out, d_tile_base, d_cta_base, d_tile_cnt, d_tile_pre, d_seg;
+  DevBuf d_sub_e, d_sub_used, d_sub_info, d_cta_tot, d_cta_pre, d_bnd[2], d_flags, d_coef, d_rgb, d_export;
+  DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
+  std::vector<ImageOut> h_out;
+  std::vector<uint32_t> h_flags;
+  int launches = 0, sync_rounds = 0;
+  int64_t h2d_bytes = 0, d2h_bytes = 0;
+  bool timing = false;
+  float last_ms[B200JPEG_T_COUNT] = {0, 0, 0, 0, 0};
+#ifndef B200JPEG_EMU
+  cudaEvent_t ev[B200JPEG_T_COUNT + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+#endif
+
+  void destroy() {
+    DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_cta_base, &d_tile_cnt, &d_tile_pre,
+                     &d_seg, &d_sub_e, &d_sub_used, &d_sub_info, &d_cta_tot, &d_cta_pre, &d_bnd[0], &d_bnd[1],
+                     &d_flags, &d_coef, &d_rgb, &d_export};
+    for (DevBuf *b : all) b->destroy(be);
+    for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
+  }
+
+  // plan + H2D of the scans and descriptors
+  int prepare(const b200jpeg_image_desc *descs, int n, const uint8_t *const *files, const size_t *sizes) {
+    prepared = ran = false;
+    if (n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
+    const int rc = make_plan(descs, n, sizes, plan);
+    if (rc) return rc;
+    const BatchPlan &P = plan;
+    bool ok = true;
+    ok &= d_raw.reserve(be, P.raw_bytes + 1024);
+    ok &= d_us.reserve(be, P.raw_bytes + (size_t)kChunkWords * 4 + 1024);
+    ok &= d_imgs.reserve(be, sizeof(ImageDev) * n);
+    ok &= d_tsets.reserve(be, sizeof(TableSet) * P.tsets.size());
+    ok &= d_out.reserve(be, sizeof(ImageOut) * n);
+    ok &= d_tile_base.reserve(be, 4 * (size_t)(n + 1));
+    ok &= d_cta_base.reserve(be, 4 * (size_t)(n + 1));
+    ok &= d_tile_cnt.reserve(be, 4 * (size_t)P.ntiles);
+    ok &= d_tile_pre.reserve(be, 8 * (size_t)P.ntiles);
+    ok &= d_seg.reserve(be, 4 * (size_t)P.nsegs);
+    ok &= d_sub_e.reserve(be, sizeof(SubState) * (size_t)P.nsubs);
+    ok &= d_sub_used.reserve(be, sizeof(SubState) * (size_t)P.nsubs);
+    ok &= d_sub_info.reserve(be, sizeof(SubInfo) * (size_t)P.nsubs);
+    ok &= d_cta_tot.reserve(be, sizeof(SubInfo) * (size_t)P.nctas);
+    ok &= d_cta_pre.reserve(be, sizeof(SubInfo) * (size_t)P.nctas);
+    ok &= d_bnd[0].reserve(be, sizeof(SubState) * (size_t)P.nctas);
+    ok &= d_bnd[1].reserve(be, sizeof(SubState) * (size_t)P.nctas);
+    ok &= d_flags.reserve(be, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
+    ok &= d_coef.reserve(be, 128 * (size_t)P.nblocks);
+    ok &= d_rgb.reserve(be, P.rgb_bytes);
+    for (int f = 0; f < PF_COUNT; ++f) if (!P.grp_img[f].empty()) {
+      ok &= d_grp_img[f].reserve(be, 4 * P.grp_img[f].size());
+      ok &= d_grp_pre[f].reserve(be, 4 * P.grp_pre[f].size());
+    }
+    if (!ok) return be.ok() ? B200JPEG_E_NOMEM : B200JPEG_E_CUDA;
+    h2d_bytes = 0;
+    // scans: one copy per image, adjacent source ranges merged into one
+    for (int i = 0; i < n;) {
+      const uint8_t *src = files[i] + descs[i].scan_offset;
+      size_t len = (size_t)descs[i].scan_length;
+      int j = i + 1;
+      // merge when the next image's scan sits exactly where the device layout expects it
+      while (j < n && files[j] + descs[j].scan_offset == src + (P.imgs[j].raw_off - P.imgs[i].raw_off)) {
+        len = (size_t)(P.imgs[j].raw_off - P.imgs[i].raw_off) + (size_t)descs[j].scan_length;
+        ++j;
+      }
+      be.h2d(d_raw.as<uint8_t>() + P.imgs[i].raw_off, src, len);
+      h2d_bytes += (int64_t)len;
+      i = j;
+    }
+    be.h2d(d_imgs.p, P.imgs.data(), sizeof(ImageDev) * n);
+    be.h2d(d_tsets.p, P.tsets.data(), sizeof(TableSet) * P.tsets.size());
+    be.h2d(d_tile_base.p, P.tile_base.data(), 4 * (size_t)(n + 1));
+    be.h2d(d_cta_base.p, P.cta_base.data(), 4 * (size_t)(n + 1));
+    h2d_bytes += (int64_t)(sizeof(ImageDev) * n + sizeof(TableSet) * P.tsets.size() + 8 * (size_t)(n + 1));
+    for (int f = 0; f < PF_COUNT; ++f) if (!P.grp_img[f].empty()) {
+      be.h2d(d_grp_img[f].p, P.grp_img[f].data(), 4 * P.grp_img[f].size());
+      be.h2d(d_grp_pre[f].p, P.grp_pre[f].data(), 4 * P.grp_pre[f].size());
+      h2d_bytes += (int64_t)(4 * (P.grp_img[f].size() + P.grp_pre[f].size()));
+    }
+    if (!be.ok()) return B200JPEG_E_CUDA;
+    prepared = true;
+    return 0;
+  }
+
+  void mark(int k) {
+#ifndef B200JPEG_EMU
+    if (timing) cudaEventRecord(ev[k], be.stream);
+#else
+    (void)k;
+#endif
+  }
+
+  template <int HS, int VS, int NC>
+  void launch_pixel(int f) {
+    const BatchPlan &P = plan;
+    if (P.grp_img[f].empty()) return;
+    const int ngrp = (int)P.grp_img[f].size();
+    const int tiles = P.grp_pre[f].back();
+    const size_t smem = sizeof(float) * PixCfg<HS, VS, NC>::kSmemFloats;
+    B2_LAUNCH((k_pixel<HS, VS, NC>), tiles, kPixThreads, smem, be.stream, d_imgs.as<ImageDev>(),
+              d_grp_img[f].as<int32_t>(), d_grp_pre[f].as<int32_t>(), ngrp, d_tsets.as<TableSet>(),
+              d_out.as<ImageOut>(), d_coef.as<int16_t>(), d_rgb.as<uint8_t>());
+    ++launches;
+  }
+
+  void launch_fix(int k) {   // k-th repair launch: reads boundary states k-1, writes k
+    const BatchPlan &P = plan;
+    const size_t smem = entropy_smem_bytes(P.nslots_max, false);
+    B2_LAUNCH((k_entropy_sync<false>), P.nctas, kCT, smem, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(),
+              P.n, d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
+              d_sub_e.as<SubState>(), d_sub_used.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_tot.as<SubInfo>(),
+              d_bnd[(k + 1) & 1].as<SubState>(), d_bnd[k & 1].as<SubState>(), d_flags.as<uint32_t>() + k, P.nslots_max);
+    ++launches; ++sync_rounds;
+  }
+
+  void launch_tail(int last_fix) {   // scan + write + pixel
+    const BatchPlan &P = plan;
+    (void)last_fix;
+    B2_LAUNCH(k_entropy_scan, (P.n + 7) / 8, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n, d_cta_tot.as<SubInfo>(),
+              d_cta_pre.as<SubInfo>());
+    ++launches;
+    mark(2);
+    const size_t smem_w = entropy_smem_bytes(P.nslots_max, true);
+    B2_LAUNCH(k_entropy_write, P.nctas, kCT, smem_w, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(), P.n,
+              d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
+              d_sub_e.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_pre.as<SubInfo>(), d_coef.as<int16_t>(),
+              P.nslots_max);
+    ++launches;
+    mark(3);
+    launch_pixel<1, 1, 3>(PF_444);
+    launch_pixel<2, 1, 3>(PF_422);
+    launch_pixel<1, 2, 3>(PF_440);
+    launch_pixel<2, 2, 3>(PF_420);
+    launch_pixel<1, 1, 1>(PF_GRAY);
+    mark(4);
+  }
+
+  // every kernel of the path, asynchronously on be.stream
+  int run() {
+    if (!prepared) return B200JPEG_E_STATE;
+    const BatchPlan &P = plan;
+    launches = 0; sync_rounds = 0;
+    mark(0);
+    // ImageOut: end_pos/err_pos = kNone, the rest 0
+    be.fill(d_out.p, 0xff, sizeof(ImageOut) * P.n);
+    be.fill(d_flags.p, 0, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
+    B2_LAUNCH(k_reset_out, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n);
+    ++launches;
+    if (P.ntiles > 0) {
+      B2_LAUNCH(k_unstuff_count, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
+                P.n, d_raw.as<uint8_t>(), d_tile_cnt.as<uint32_t>(), d_out.as<ImageOut>());
+      B2_LAUNCH(k_unstuff_scan, (P.n + 7) / 8, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n,
+                d_tile_cnt.as<uint32_t>(), d_tile_pre.as<uint2>());
+      B2_LAUNCH(k_unstuff_scatter, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(),
+                d_tile_base.as<int32_t>(), P.n, d_raw.as<uint8_t>(), d_tile_pre.as<uint2>(), d_us.as<uint8_t>(),
+                d_seg.as<uint32_t>(), d_out.as<ImageOut>());
+      launches += 3;
+    }
+    B2_LAUNCH(k_unstuff_finish, (P.n + 255) / 256, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n, d_seg.as<uint32_t>(),
+              d_out.as<ImageOut>());
+    ++launches;
+    mark(1);
+    if (P.nctas > 0) {
+      const size_t smem = entropy_smem_bytes(P.nslots_max, false);
+      B2_LAUNCH((k_entropy_sync<true>), P.nctas, kCT, smem, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(),
+                P.n, d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
+                d_sub_e.as<SubState>(), d_sub_used.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_tot.as<SubInfo>(),
+                (const SubState *)nullptr, d_bnd[1].as<SubState>(), d_flags.as<uint32_t>(), P.nslots_max);
+      ++launches;
+      for (int k = 0; k < kFixLaunches; ++k) launch_fix(k);   // launch k reads d_bnd[(k+1)&1], writes d_bnd[k&1]
+      launch_tail(kFixLaunches - 1);
+    } else { mark(2); mark(3); mark(4); }
+    mark(5);
+    be.check("kernel launch");
+    ran = true;
+    return be.ok() ? 0 : B200JPEG_E_CUDA;
+  }
+
+  // wait; if self-synchronisation had not settled, keep repairing and redo the tail
+  int finish() {
+    if (!ran) return B200JPEG_E_STATE;
+    const BatchPlan &P = plan;
+    h_flags.assign(kFixLaunches + kMaxExtraFix + 2, 0);
+    h_out.resize(P.n);
+    int k = kFixLaunches - 1;
+    for (;;) {
+      be.d2h(h_flags.data(), d_flags.p, 4 * h_flags.size());
+      be.sync();
+      if (!be.ok()) return B200JPEG_E_CUDA;
+      if (P.nctas == 0 || h_flags[k] == 0) break;
+      if (k + 1 >= kFixLaunches + kMaxExtraFix) {
+        B2_LAUNCH(k_raise_status, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n, (uint32_t)ST_NOT_CONVERGED);
+        break;
+      }
+      ++k;
+      launch_fix(k);
+      launch_tail(k);
+    }
+    be.d2h(h_out.data(), d_out.p, sizeof(ImageOut) * P.n);
+    be.sync();
+#ifndef B200JPEG_EMU
+    if (timing) {
+      for (int s = 0; s < 4; ++s) cudaEventElapsedTime(&last_ms[s], ev[s], ev[s + 1]);
+      cudaEventElapsedTime(&last_ms[B200JPEG_T_TOTAL], ev[0], ev[5]);
+    }
+#endif
+    return be.ok() ? 0 : B200JPEG_E_CUDA;
+  }
+
+  int fetch(uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+    const int rc = finish();
+    if (rc) return rc;
+    const BatchPlan &P = plan;
+    d2h_bytes = 0;
+    if (status) for (int i = 0; i < P.n; ++i) status[i] = (int32_t)h_out[i].status;
+    if (rgb_out) for (int i = 0; i < P.n; ++i) if (rgb_out[i]) {
+      const ImageDev &im = P.imgs[i];
+      const uint8_t *src = d_rgb.as<uint8_t>() + im.rgb_off;
+      const size_t row = (size_t)3 * im.width;
+      if (im.rgb_pitch == row) be.d2h(rgb_out[i], src, row * im.height);
+      else be.d2h_2d(rgb_out[i], row, src, im.rgb_pitch, row, im.height);
+      d2h_bytes += (int64_t)(row * im.height);
+    }
+    if (coef_out) for (int i = 0; i < P.n; ++i) if (coef_out[i]) {
+      const ImageDev &im = P.imgs[i];
+      const size_t bytes = (size_t)P.bwr[i] * P.bhr[i] * 3 * 64 * sizeof(int16_t);
+      if (!d_export.reserve(be, bytes)) return B200JPEG_E_NOMEM;
+      be.fill(d_export.p, 0, bytes);   // MCU[] is value-initialised, jpeg.cpp:407
+      B2_LAUNCH(k_export_coef, (im.nblocks + 3) / 4, 256, 0, be.stream, im, P.bwr[i], d_coef.as<int16_t>(),
+                d_export.as<int16_t>());
+      be.d2h(coef_out[i], d_export.p, bytes);
+      be.sync();
+      d2h_bytes += (int64_t)bytes;
+    }
+    be.sync();
+    return be.ok() ? 0 : B200JPEG_E_CUDA;
+  }
+};
+
+}  // namespace b2

@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #define B2_DEVICE __device__ __forceinline__
 #define B2_HD __host__ __device__ __forceinline__
+#define B2_MEMBER __device__ __forceinline__
 #define B2_GLOBAL __global__
 #define B2_SHARED __shared__
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
