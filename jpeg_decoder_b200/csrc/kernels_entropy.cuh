@@ -184,6 +184,18 @@ B2_DEVICE void decode_block(Reader &r, const uint32_t *__restrict__ dcl, const u
   }
 }
 
+// True when a block that ended at bit `pe` was the last one of the segment ending at `B`:
+// it reached/passed B, or only the 1-bit padding of the last byte is left (T.81 F.1.2.3; a
+// complete Huffman code is never all ones, so padding cannot be taken for another block).
+template <class Reader>
+B2_DEVICE bool segment_done(Reader &r, uint32_t pe, uint32_t B) {
+  if (pe >= B) return true;
+  const uint32_t n = B - pe;
+  if (n > 7) return false;
+  r.refill();
+  return (r.peek() >> (32 - n)) == ((1u << n) - 1u);
+}
+
 // largest k in [lo,hi] with seg[k] <= p
 B2_DEVICE int seg_find(const uint32_t *__restrict__ seg, int lo, int hi, uint32_t p) {
   while (lo < hi) {
@@ -217,7 +229,7 @@ B2_DEVICE SubResult decode_sub_sync(const EntropyShared &S, const uint32_t *__re
     if (c == 0) R.d0 += diff; else if (c == 1) R.d1 += diff; else R.d2 += diff;
     ++R.nb;
     const uint32_t pe = chunk_bit0 + r.pos();
-    if (pe + 7 >= B) {            // the block ends in (or past) the last byte of its segment
+    if (segment_done(r, pe, B)) {   // last block of its segment
       p = B; blk = 0;
       R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 1;
       if (B >= S.us_bits) break;
@@ -534,7 +546,7 @@ k_entropy_write(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ c
       for (int q = 0; q < 8; ++q) stage4[q * kCT + tid] = make_uint4(0, 0, 0, 0);
       ++bidx;
       const uint32_t pe = chunk_bit0 + rd.pos();
-      if (pe + 7 >= B) {
+      if (segment_done(rd, pe, B)) {
         if (pe > B) err |= ST_OVERRUN;
         if (bidx < limit) err |= ST_BLOCK_COUNT;
         if (bidx > limit && k + 1 < im.nseg) err |= ST_BLOCK_COUNT;

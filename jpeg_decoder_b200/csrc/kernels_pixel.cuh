@@ -25,7 +25,7 @@ namespace b2 {
 
 constexpr int kPixThreads = 96;
 
-B2_HD float f32_bits(uint32_t u) {
+B2_DEVICE float f32_bits(uint32_t u) {
 #ifdef B200JPEG_EMU
   float f; memcpy(&f, &u, 4); return f;
 #else

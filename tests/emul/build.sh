@@ -1,0 +1,7 @@
+#!/bin/sh
+# Builds the test-only emulation library (see cuda_emul.h).  Usage: tests/emul/build.sh
+set -e
+cd "$(dirname "$0")/../.."
+mkdir -p tests/emul/_build
+g++ -std=c++20 -O1 -g -pthread -fPIC -shared -Wall -Wno-unused-function -Wno-unknown-pragmas -ffp-contract=off \
+    -o tests/emul/_build/libb200jpeg_emul.so tests/emul/emul_lib.cpp jpeg_decoder_b200/csrc/host_parse.cpp

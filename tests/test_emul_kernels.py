@@ -1,0 +1,57 @@
+"""CPU tier: the product's kernel SOURCES (unstuff, entropy sync/fix/scan/write, fused pixel) and
+launch sequence, compiled against the SIMT emulation in tests/emul, checked against the oracle.
+This checks logic only; the same comparisons run on the real GPU in test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+from tests.conftest import fixture_bytes
+
+
+def check(emul, oracle_mod, datas, flags=0):
+    st, rgbs, coefs, info = emul.decode(datas, flags=flags)
+    for i, d in enumerate(datas):
+        rc, _, oc, orgb = oracle_mod.port_decode(d, flags=flags)
+        assert rc == 0 and st[i] == 0, (i, rc, st[i])
+        assert np.array_equal(coefs[i].astype(np.int32), oc), "coefficients differ, image %d" % i   # bit-exact
+        assert np.array_equal(rgbs[i], orgb), "RGB differs, image %d" % i                              # 0 differing samples
+    return info
+
+
+def test_fixture_no_restart(emul, oracle_mod):
+    check(emul, oracle_mod, [fixture_bytes("img2.jpg")])          # 4:2:0, optimised tables, self-sync path
+
+
+def test_fixture_restart_444(emul, oracle_mod):
+    check(emul, oracle_mod, [fixture_bytes("img4.jpg")])          # 4:4:4, DRI=100, 49 RSTn
+
+
+def test_mixed_batch_all_formats(emul, oracle_mod, harness):
+    cases = [(64, 64, 90, 2, 2, 0, 0), (200, 120, 90, 2, 2, 0, -1), (200, 120, 90, 2, 1, 0, 7),
+             (200, 120, 75, 1, 2, 0, 3), (123, 77, 95, 1, 1, 0, 0), (8, 8, 50, 2, 2, 0, 0), (1, 1, 90, 1, 1, 0, 0),
+             (17, 9, 90, 2, 2, 0, 1), (300, 200, 50, 1, 1, 1, 0), (300, 200, 90, 1, 1, 1, 5)]
+    datas = [harness.synth_jpeg(100 + i, *c) for i, c in enumerate(cases)]
+    check(emul, oracle_mod, datas, flags=1)
+
+
+def test_multi_cta_scan_without_restart(emul, oracle_mod, harness):
+    # > 16 KiB of scan: several entropy CTAs whose start states are only known after the fix launches
+    d = harness.synth_jpeg(31, 640, 480, 92, 2, 2, False, 0)
+    assert len(d) > 5 * 16384
+    info = check(emul, oracle_mod, [d])
+    assert info["sync_rounds"] == 2
+
+
+def test_corrupt_streams_are_flagged_not_fatal(emul, harness):
+    from jpeg_decoder_b200 import abi
+    good = bytearray(harness.synth_jpeg(41, 160, 96, 85, 2, 2, False, -1))
+    sos = good.find(b"\xff\xda")
+    body = sos + 14
+    a = bytearray(good); a[-2:] = b"\x00\x00"                 # EOI removed
+    b = bytearray(good); b[body + 40:body + 42] = b"\xff\xc4"  # illegal marker inside the scan
+    c = bytearray(good)
+    k = c.find(b"\xff\xd1", body); c[k:k + 2] = b"\x12\x34"    # one RSTn destroyed
+    st, _, _, _ = emul.decode([bytes(good), bytes(a), bytes(b), bytes(c)])
+    assert st[0] == 0
+    assert st[1] & abi.ST_NO_EOI
+    assert st[2] & abi.ST_BAD_MARKER
+    assert st[3] & abi.ST_BAD_RST_COUNT

@@ -1,0 +1,116 @@
+"""GPU tier (-m gpu): parity of the CUDA path with the oracle, through the C ABI.
+
+Bars (BASELINE.json north_star): quantised coefficients BIT-EXACT with the reference's MCU decode;
+RGB within +-1 LSB per channel of the reference's float IDCT + colour (the kernels replicate the
+operation order, so the expected number of differing samples is 0 -- asserted where noted)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from tests.conftest import fixture_bytes
+
+pytestmark = pytest.mark.gpu
+FIXTURES = ["img.jpg", "img2.jpg", "img3.jpg", "img4.jpg", "img5.jpg", "img6.jpg"]
+RGB_TOL = 1   # LSB per channel, north_star
+
+
+@pytest.fixture(scope="module")
+def dec(lib_so):
+    import jpeg_decoder_b200 as jd
+    d = jd.Decoder(0)
+    yield d
+    d.close()
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def compare(dec, oracle_mod, datas, flags=0, exact_rgb=True):
+    st, rgbs, coefs = dec.decode(datas, flags=flags, want_coef=True)
+    worst, ndiff = 0, 0
+    for i, d in enumerate(datas):
+        rc, _, oc, orgb = oracle_mod.port_decode(d, flags=flags)
+        assert rc == 0 and st[i] == 0, (i, rc, st[i])
+        assert np.array_equal(coefs[i].astype(np.int32), oc), "coefficients differ (image %d)" % i
+        err = np.abs(rgbs[i].astype(np.int16) - orgb.astype(np.int16))
+        worst = max(worst, int(err.max())); ndiff += int((err > 0).sum())
+    assert worst <= RGB_TOL
+    if exact_rgb:
+        assert ndiff == 0, "RGB within tolerance but %d samples differ (max %d)" % (ndiff, worst)
+    return worst, ndiff
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_reference_fixtures(dec, oracle_mod, golden, name):
+    data = fixture_bytes(name)
+    st, rgbs, coefs = dec.decode([data], want_coef=True)
+    assert st == [0]
+    g = golden["fixtures"][name]
+    # digests taken from the UNTOUCHED reference binary (tests/golden/make_golden.py)
+    assert sha(coefs[0].astype(np.int32)) == g["coef_sha256"]
+    assert sha(rgbs[0]) == g["rgb_sha256"]
+
+
+def test_golden_synthetic(dec, golden, harness):
+    for name, g in golden["synthetic"].items():
+        data = harness.synth_jpeg(**g["args"])
+        st, rgbs, coefs = dec.decode([data], want_coef=True)
+        assert st == [0], name
+        assert sha(coefs[0].astype(np.int32)) == g["coef_sha256"], name
+        assert sha(rgbs[0]) == g["rgb_sha256"], name
+
+
+def test_mixed_batch_all_sampling_formats(dec, oracle_mod, harness):
+    cases = [(64, 64, 90, 2, 2, 0, 0), (200, 120, 90, 2, 2, 0, -1), (200, 120, 90, 2, 1, 0, 7), (200, 120, 75, 1, 2, 0, 3),
+             (123, 77, 95, 1, 1, 0, 0), (8, 8, 50, 2, 2, 0, 0), (1, 1, 90, 1, 1, 0, 0), (17, 9, 90, 2, 2, 0, 1),
+             (300, 200, 50, 1, 1, 1, 0), (300, 200, 90, 1, 1, 1, 5), (679, 451, 30, 2, 2, 0, 0), (1000, 30, 99, 2, 1, 0, 0)]
+    datas = [harness.synth_jpeg(100 + i, *c) for i, c in enumerate(cases)]
+    compare(dec, oracle_mod, datas, flags=1)
+
+
+def test_fixtures_in_one_batch_and_repeatable(dec, oracle_mod):
+    datas = [fixture_bytes(n) for n in FIXTURES]
+    compare(dec, oracle_mod, datas)
+    a = dec.decode(datas)[1]
+    b = dec.decode(datas)[1]
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))     # idempotent / deterministic
+
+
+def test_sampling_coverage_c4_reduced(dec, oracle_mod, harness):
+    # BASELINE config 4 (sampling-factor coverage) at 1024^2 so the CPU oracle finishes in seconds
+    datas, flags = [], 1
+    for q in (50, 90):
+        datas += [harness.synth_jpeg(200 + q, 1024, 1024, q, 1, 1, True, 0), harness.synth_jpeg(300 + q, 1024, 1024, q, 2, 1, False, 0),
+                  harness.synth_jpeg(400 + q, 1024, 1024, q, 1, 1, False, 0), harness.synth_jpeg(500 + q, 1024, 1024, q, 2, 1, False, 16)]
+    compare(dec, oracle_mod, datas, flags=flags)
+
+
+def test_corrupt_streams_flagged(dec, harness):
+    from jpeg_decoder_b200 import abi
+    good = bytearray(harness.synth_jpeg(41, 160, 96, 85, 2, 2, False, -1))
+    body = good.find(b"\xff\xda") + 14
+    a = bytearray(good); a[-2:] = b"\x00\x00"
+    b = bytearray(good); b[body + 40:body + 42] = b"\xff\xc4"
+    c = bytearray(good); k = c.find(b"\xff\xd1", body); c[k:k + 2] = b"\x12\x34"
+    e = bytearray(good); e[body + 100:body + 140] = bytes(40)           # garbage bits: decode errors, no crash
+    st, rgbs, _ = dec.decode([bytes(good), bytes(a), bytes(b), bytes(c), bytes(e), bytes(good)])
+    assert st[0] == 0 and st[5] == 0
+    assert st[1] & abi.ST_NO_EOI and st[2] & abi.ST_BAD_MARKER and st[3] & abi.ST_BAD_RST_COUNT
+    assert np.array_equal(rgbs[0], rgbs[5])                              # neighbours in the batch unaffected
+
+
+def test_truncated_and_random_garbage_do_not_crash(dec, harness):
+    rng = np.random.default_rng(3)
+    good = harness.synth_jpeg(43, 256, 256, 80, 2, 2, False, 0)
+    body = good.find(b"\xff\xda") + 14
+    datas = [good]
+    for k in range(6):
+        m = bytearray(good)
+        pos = rng.integers(body, len(good) - 2, size=20)
+        for p in pos:
+            m[p] = int(rng.integers(0, 255))           # avoids 0xFF: stays a syntactically valid scan
+        datas.append(bytes(m))
+    st, rgbs, _ = dec.decode(datas)
+    assert st[0] == 0 and len(rgbs) == 7

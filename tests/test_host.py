@@ -1,0 +1,103 @@
+"""CPU tier: the host surface -- header parser vs the oracle, ABI exports, rejection codes,
+batch planner arithmetic.  No GPU compute calls."""
+import ctypes as C
+import re
+import os
+
+import numpy as np
+import pytest
+
+from tests.conftest import ROOT, fixture_bytes
+from jpeg_decoder_b200 import abi
+
+FIXTURES = ["img.jpg", "img2.jpg", "img3.jpg", "img4.jpg", "img5.jpg", "img6.jpg"]
+
+
+@pytest.fixture(scope="module")
+def lib(lib_so):
+    import jpeg_decoder_b200 as j
+    return j.load()
+
+
+def test_library_exports_every_declared_symbol(lib):
+    hdr = open(os.path.join(ROOT, "include", "b200jpeg.h")).read()
+    declared = set(re.findall(r"\b(b200jpeg_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(abi.EXPORTS)
+    for s in declared:
+        assert hasattr(lib, s), s
+    assert lib.b200jpeg_abi_version() == abi.ABI_VERSION
+
+
+def test_struct_sizes_match_header(lib_so):
+    # compile a tiny C probe against the header and compare sizeof with the ctypes mirror
+    import subprocess, tempfile
+    src = '#include "b200jpeg.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu\\n",sizeof(b200jpeg_huffman_table),sizeof(b200jpeg_quant_table),sizeof(b200jpeg_component),sizeof(b200jpeg_image_desc),sizeof(b200jpeg_batch_stats));return 0;}'
+    with tempfile.TemporaryDirectory() as td:
+        open(os.path.join(td, "p.c"), "w").write(src)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(td, "p"), os.path.join(td, "p.c")])
+        got = [int(x) for x in subprocess.check_output([os.path.join(td, "p")]).split()]
+    want = [C.sizeof(abi.HuffmanTable), C.sizeof(abi.QuantTable), C.sizeof(abi.Component), C.sizeof(abi.ImageDesc),
+            C.sizeof(abi.BatchStats)]
+    assert got == want
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_parse_header_matches_oracle(lib, oracle_mod, name):
+    import jpeg_decoder_b200 as j
+    data = fixture_bytes(name)
+    d = j.parse_header(data)
+    rc, info, _, _ = oracle_mod.port_decode(data, want_coef=False, want_rgb=False)
+    assert rc == 0
+    assert (d.image_width, d.image_height, d.mcuWidth, d.mcuHeight, d.mcuWidthReal, d.mcuHeightReal) == (
+        info["width"], info["height"], info["bw"], info["bh"], info["bwr"], info["bhr"])
+    assert (d.horizontalSamplingFactor, d.verticalSamplingFactor, d.restartInterval) == (
+        info["hs"], info["vs"], info["restart_interval"])
+    assert d.scan_offset == info["scan_offset"] and d.scan_offset + d.scan_length == len(data)
+    # canonical codes as HuffmanTable::generateCodes (huffman.hpp:17-29): strictly increasing per length
+    t = d.huffmanACTable[d.color_components[0].huffmanACTableID]
+    assert t.set == 1
+    for l in range(16):
+        codes = [t.codes[k] for k in range(t.offset[l], t.offset[l + 1])]
+        assert codes == list(range(codes[0], codes[0] + len(codes))) if codes else True
+        assert all(c < (1 << (l + 1)) for c in codes)
+
+
+def test_parse_header_rejections(lib, harness):
+    import jpeg_decoder_b200 as j
+    def code(data, flags=0):
+        try:
+            j.parse_header(data, flags)
+            return 0
+        except j.B200JpegError as e:
+            return e.code
+    assert code(fixture_bytes("prograssive-sample-2.jpg")) == abi.E_PROGRESSIVE   # jpeg.cpp:69-73
+    assert code(b"\x00\x01\x02\x03") == abi.E_NOT_JPEG                             # jpeg.cpp:800-805
+    gray = harness.synth_jpeg(5, 64, 48, 80, 1, 1, True, 0)
+    assert code(gray) == abi.E_COMPONENTS                                          # jpeg.cpp:83-87
+    assert code(gray, abi.PARSE_SPEC) == 0
+    good = bytearray(harness.synth_jpeg(6, 64, 48, 80, 2, 2, False, 0))
+    sof = good.find(b"\xff\xc0")
+    bad = bytearray(good); bad[sof + 11] = 0x31                                    # luma 3x1
+    assert code(bytes(bad)) == abi.E_SAMPLING                                      # jpeg.cpp:110-117
+    bad = bytearray(good); bad[sof + 14] = 0x21                                    # chroma 2x1
+    assert code(bytes(bad)) == abi.E_SAMPLING                                      # jpeg.cpp:129-136
+    sos = good.find(b"\xff\xda")
+    bad = bytearray(good); bad[sos + 12] = 62                                      # Se != 63
+    assert code(bytes(bad)) == abi.E_SOS                                           # jpeg.cpp:255-259
+    assert code(bytes(good[:sos])) in (abi.E_NO_SOS, abi.E_TRUNCATED)
+    dht = good.find(b"\xff\xc4")
+    bad = bytearray(good); bad[dht + 4] = 0x05                                     # table id 5
+    assert code(bytes(bad)) == abi.E_TABLE_ID                                      # jpeg.cpp:156-160
+    com = bytes(good[:2]) + b"\xff\xfe\x00\x04hi" + bytes(good[2:])
+    assert code(com) == abi.E_NO_SOS        # COM is INVALID to the reference (file.hpp:252-253)
+    assert code(com, abi.PARSE_SPEC) == 0
+
+
+def test_decoder_fails_loudly_without_gpu(lib):
+    import torch
+    import jpeg_decoder_b200 as j
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(j.B200JpegError) as e:
+        j.Decoder(0)
+    assert e.value.code == abi.E_CUDA     # no CPU fallback exists

@@ -1,0 +1,90 @@
+"""CPU tier: pin the oracle.  The C restatement (oracle/jpeg_oracle.c) must reproduce the golden
+digests that tests/golden/make_golden.py took from the UNTOUCHED reference binary, and, where that
+binary is present (this container), match it byte for byte when both are run now."""
+import hashlib
+
+import numpy as np
+import pytest
+
+from tests.conftest import fixture_bytes
+
+FIXTURES = ["img.jpg", "img2.jpg", "img3.jpg", "img4.jpg", "img5.jpg", "img6.jpg"]
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_port_matches_reference_golden_on_fixtures(oracle_mod, golden, name):
+    rc, info, coef, rgb = oracle_mod.port_decode(fixture_bytes(name))
+    g = golden["fixtures"][name]
+    assert rc == 0
+    assert (info["width"], info["height"], info["bwr"], info["bhr"], info["hs"], info["vs"]) == (
+        g["w"], g["h"], g["bwr"], g["bhr"], g["hs"], g["vs"])
+    assert info["restart_interval"] == g["ri"] and info["scan_unstuffed"] == g["scan_unstuffed"]
+    assert sha(coef) == g["coef_sha256"]      # MCU array after decodeHuffman(), bit-exact
+    assert sha(rgb) == g["rgb_sha256"]        # RGB gather, bit-exact
+
+
+def test_port_matches_reference_golden_on_synthetic(oracle_mod, golden, harness):
+    for name, g in golden["synthetic"].items():
+        data = harness.synth_jpeg(**g["args"])
+        assert hashlib.sha256(data).hexdigest() == g["jpeg_sha256"], "bundled encoder drifted: " + name
+        rc, info, coef, rgb = oracle_mod.port_decode(data)
+        assert rc == 0 and sha(coef) == g["coef_sha256"] and sha(rgb) == g["rgb_sha256"], name
+
+
+def test_port_matches_live_reference_binary(oracle_mod, harness):
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref/ref_decode not built (reference sources absent)")
+    datas = [fixture_bytes("img2.jpg"), harness.synth_jpeg(77, 160, 96, 80, 2, 1, False, 5),
+             harness.synth_jpeg(78, 97, 55, 92, 1, 1, False, 0)]
+    for d in datas:
+        info, coef, rgb = oracle_mod.ref_dump(d)
+        rc, pi, pc, pr = oracle_mod.port_decode(d)
+        assert rc == 0 and np.array_equal(coef, pc) and np.array_equal(rgb, pr)
+        assert info["sizeof_mcu"] == 768
+
+
+def test_idct_constants_bit_patterns(oracle_mod):
+    # m0,m1,m2,m3,m4,m5,s0..s7 as the reference's double->float initialisers give them
+    want = [0x3fec835e, 0x3fb504f3, 0x3f8a8bd4, 0x3fb504f3, 0x40273d74, 0x3f43ef15,
+            0x3eb504f3, 0x3efb14be, 0x3eec835e, 0x3ed4db31, 0x3eb504f3, 0x3e8e39da, 0x3e43ef15, 0x3dc7c5c2]
+    assert [int(x) for x in oracle_mod.port_idct_constants()] == want
+
+
+def test_unstuff_rules(oracle_mod):
+    # file.hpp:59-104: FF00->FF, RSTn dropped, FF FF fill collapses, FF D9 ends
+    scan = bytes([0x12, 0xff, 0x00, 0x34, 0xff, 0xd3, 0x56, 0xff, 0xff, 0x00, 0x78, 0xff, 0xd9, 0x99])
+    n, out, used = oracle_mod.port_unstuff(scan)
+    assert n == 6 and bytes(out) == bytes([0x12, 0xff, 0x34, 0x56, 0xff, 0x78]) and used == 13
+    n, _, _ = oracle_mod.port_unstuff(bytes([0x01, 0xff, 0xc0, 0xff, 0xd9]))
+    assert n == -11   # ORACLE_E_SCAN_MARKER, file.hpp:91-95
+    n, _, _ = oracle_mod.port_unstuff(bytes([0x01, 0x02, 0x03]))
+    assert n == -12   # no EOI
+
+
+def test_reference_rejections(oracle_mod, harness):
+    assert oracle_mod.port_decode(fixture_bytes("prograssive-sample-2.jpg"))[0] == -2   # jpeg.cpp:69-73
+    gray = harness.synth_jpeg(5, 64, 48, 80, 1, 1, True, 0)
+    assert oracle_mod.port_decode(gray)[0] == -3                                      # jpeg.cpp:83-87
+    assert oracle_mod.port_decode(gray, flags=oracle_mod.F_SPEC)[0] == 0
+    assert oracle_mod.port_decode(b"\x89PNG....")[0] == -1                             # jpeg.cpp:800-805
+    if oracle_mod.have_ref():
+        with pytest.raises(RuntimeError):
+            oracle_mod.ref_dump(gray)
+
+
+def test_gray_equals_444_with_zero_chroma(oracle_mod, harness):
+    # grey cross-check -- a grey picture coded as 3 components has the same Y
+    rgbsrc = harness.synth_rgb(9, 80, 56)
+    y = (0.299 * rgbsrc[..., 0] + 0.587 * rgbsrc[..., 1] + 0.114 * rgbsrc[..., 2] + 0.5).astype(np.uint8)
+    g3 = np.repeat(y[..., None], 3, axis=2)
+    d1 = harness.encode_rgb(g3, 88, 1, 1, True, 0)
+    d3 = harness.encode_rgb(g3, 88, 1, 1, False, 0)
+    rc1, _, c1, r1 = oracle_mod.port_decode(d1, flags=oracle_mod.F_SPEC)
+    rc3, _, c3, r3 = oracle_mod.port_decode(d3)
+    assert rc1 == 0 and rc3 == 0
+    assert np.array_equal(c1[:, 0], c3[:, 0])
+    assert np.abs(r1.astype(int) - r3.astype(int)).max() <= 1
