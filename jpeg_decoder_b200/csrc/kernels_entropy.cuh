@@ -7,11 +7,14 @@
 //
 //   sync  : each thread decodes the blocks that START inside its sub.  Its start state is
 //           (bit position, block-in-MCU index) of the first block start at/after its sub's
-//           beginning -- unknown at first, so it is guessed, and then corrected by Jacobi
-//           iteration: thread t re-decodes whenever thread t-1's end state changed.  Huffman
-//           codes self-synchronise, so this settles after one or two rounds.  Segment starts
-//           (RSTn) are known bit positions and re-synchronise every decoder that reaches them.
-//   fix   : the same across CTA boundaries (one more launch per hop; two are issued).
+//           beginning.  That state is unknown, so the thread starts kOverlapBits EARLIER from a
+//           guess (or from the last segment start, which is exact) and lets the Huffman code
+//           self-synchronise on the way: measured on 4:2:0 streams the state -- including the
+//           block-in-MCU phase -- is right after 4096 bits for 92 % of starts (4:4:4: > 99.9 %).
+//           Thread t then checks its start against thread t-1's end state; the few subs that
+//           disagree are re-decoded (Jacobi iteration, compacted so whole warps stay busy).
+//           Segment starts (RSTn) re-synchronise every decoder that reaches them.
+//   fix   : the same check across CTA boundaries (one more launch per hop; two are issued).
 //   scan  : segmented prefix sums over the per-sub block counts and DC-difference sums give
 //           every sub its first output block and its DC predictors (jpeg.cpp:344-345, 413).
 //   write : final decode from the settled states; each thread assembles whole blocks in shared
@@ -28,13 +31,19 @@
 
 namespace b2 {
 
-constexpr int kSubBits = 1024;
+#ifndef B2_SUB_BITS
+#define B2_SUB_BITS 4096
+#endif
+#ifndef B2_OVERLAP_BITS
+#define B2_OVERLAP_BITS 4096
+#endif
+constexpr int kSubBits = B2_SUB_BITS;
+constexpr int kOverlapBits = B2_OVERLAP_BITS;         // self-synchronisation run-in before a sub (see header)
 constexpr int kSubWords = kSubBits / 32;
 constexpr int kCT = 128;                    // subs (= threads) per entropy CTA
 constexpr int kLutBits = 10;
 constexpr int kLutSize = 1 << kLutBits;
-constexpr int kHaloWords = 64;              // a block is at most 64*(16+11) bits = 54 words, + look-ahead
-constexpr int kChunkWords = kCT * kSubWords + kHaloWords;
+constexpr int kChunkWords = 64 + 8;          // read-ahead slack past the end of a scan: one block (<= 54 words) + queue
 constexpr int kMaxSlots = 6;                // <= 3 DC + 3 AC tables per image
 
 // LUT entry: adv | zinc<<8 | len<<16 | run<<24 ; 0 = code longer than kLutBits (or invalid)
@@ -49,7 +58,7 @@ B2_HD uint32_t lut_entry(uint32_t adv, uint32_t zinc, uint32_t len, uint32_t run
 B2_HD uint32_t make_entry(uint32_t sym, uint32_t len, bool is_dc) {
   if (is_dc) {
     if (sym > 11) return lut_entry(len, 64, len, kRunBadSize);          // jpeg.cpp:330-334
-    return lut_entry(len + sym, 0, len, 0);
+    return lut_entry(len + sym, 1, len, 0);                             // z: 0 -> 1
   }
   const uint32_t run = sym >> 4, size = sym & 15;
   if (sym == 0x00) return lut_entry(len, 64, len, 0);                   // EOB, jpeg.cpp:356-363
@@ -72,11 +81,13 @@ struct SlowTab {
 struct EntropyShared {
   SlowTab slow[kMaxSlots];
   SubState e[kCT];                     // end state per sub
-  int8_t dc_slot[kMaxBpm], ac_slot[kMaxBpm], comp_of[kMaxBpm];
+  SubState used[kCT];                  // start state the end state was computed from
+  SubInfo info[kCT];                   // blocks / DC sums since the last segment start
+  int32_t list[kCT];                   // compacted indices of subs to re-decode
+  int32_t tab_of[kMaxBpm];             // per block-in-MCU: dc slot | ac slot << 8 | component << 16
   uint32_t us_bits;
-  int32_t bpm, seg_lo, seg_hi, nslots;
+  int32_t bpm, nslots, count;
   SubState cta_in;
-  int32_t cta_in_valid;
   int32_t img;
 };
 
@@ -114,29 +125,42 @@ B2_DEVICE void build_table(const HuffSpec &spec, bool is_dc, uint32_t *lut, Slow
   }
 }
 
-// MSB-first bit reader over a word array (shared-memory chunk with one pad word per 32, or
-// global memory); replaces BitStream (file.hpp:122-165).
-template <bool PADDED>
+// MSB-first bit reader over the (word-swapped) unstuffed scan in global memory; replaces
+// BitStream (file.hpp:122-165).  128-bit loads into a four-word register queue feed a 64-bit
+// left-aligned window: one LDG.128 per 128 bits consumed, each lane streaming through its own
+// cache lines (L1 keeps the line for the 7 following loads).
 struct BitReader {
-  const uint32_t *base;   // word 0 = chunk start
+  const uint4 *base;      // word 0 of the image's unstuffed scan (16-byte aligned)
+  const uint4 *ptr;       // next vector to load
+  uint4 q;
+  int qn;                 // words left in q
   uint64_t buf;
-  int avail;
-  uint32_t widx;
-  B2_MEMBER uint32_t ld(uint32_t i) const { return PADDED ? base[i + (i >> 5)] : base[i]; }
-  B2_MEMBER void seek(uint32_t bit) {       // bit position relative to `base`
-    widx = bit >> 5;
-    const uint32_t o = bit & 31;
-    const uint64_t w0 = ld(widx), w1 = ld(widx + 1);
+  int avail;              // valid bits in buf
+  uint32_t wpos;          // bit index of the next word that will leave the queue
+  B2_MEMBER uint32_t next_word() {
+    if (qn == 0) { q = b2_ld_nc_v4(ptr); ++ptr; qn = 4; }
+    const uint32_t w = q.x;
+    q.x = q.y; q.y = q.z; q.z = q.w; --qn;
+    wpos += 32;
+    return w;
+  }
+  B2_MEMBER void seek(uint32_t bit) {      // bit position relative to `base`
+    const uint32_t wi = bit >> 5;
+    ptr = base + (wi >> 2);
+    q = b2_ld_nc_v4(ptr); ++ptr; qn = 4;
+    for (uint32_t k = 0; k < (wi & 3u); ++k) { q.x = q.y; q.y = q.z; q.z = q.w; --qn; }
+    wpos = wi << 5;
+    const uint64_t w0 = next_word(), w1 = next_word();
+    const uint32_t o = bit & 31u;
     buf = ((w0 << 32) | w1) << o;
     avail = 64 - (int)o;
-    widx += 2;
   }
   B2_MEMBER void refill() {
-    if (avail <= 32) { buf |= (uint64_t)ld(widx) << (32 - avail); avail += 32; ++widx; }
+    if (avail <= 32) { const uint64_t w = next_word(); buf |= w << (32 - avail); avail += 32; }
   }
   B2_MEMBER uint32_t peek() const { return (uint32_t)(buf >> 32); }
   B2_MEMBER void skip(uint32_t n) { buf <<= n; avail -= (int)n; }
-  B2_MEMBER uint32_t pos() const { return (widx << 5) - (uint32_t)avail; }
+  B2_MEMBER uint32_t pos() const { return wpos - (uint32_t)avail; }
 };
 
 B2_DEVICE int extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:335-343, 388-397
@@ -144,51 +168,10 @@ B2_DEVICE int extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:3
   return (v >> (size - 1)) ? (int)v : (int)v - (int)((1u << size) - 1);
 }
 
-// Decode one block.  WRITE=false: lengths only (+ the DC difference).  WRITE=true: values go to
-// the thread's staging block `stage` (zig-zag order), errors are OR-ed into *err.
-template <bool WRITE, class Reader>
-B2_DEVICE void decode_block(Reader &r, const uint32_t *__restrict__ dcl, const uint32_t *__restrict__ acl,
-                            const SlowTab &dcs, const SlowTab &acs, int &dcdiff, uint16_t *stage, int stage_stride,
-                            uint32_t *err) {
-  r.refill();
-  uint32_t w = r.peek();
-  uint32_t e = dcl[w >> (32 - kLutBits)];
-  if (e == 0) e = slow_lookup(dcs, w, true);
-  {
-    const uint32_t adv = e & 0xff, len = (e >> 16) & 0xff, run = e >> 24;
-    dcdiff = adv > len ? extend(w, len, adv - len) : 0;
-    if (WRITE && run >= kRunBadCode) *err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_DC_LEN;
-    r.skip(adv);
-  }
-  uint32_t z = 1;
-  while (z < 64) {
-    r.refill();
-    w = r.peek();
-    e = acl[w >> (32 - kLutBits)];
-    if (e == 0) e = slow_lookup(acs, w, false);
-    const uint32_t adv = e & 0xff, zinc = (e >> 8) & 0xff;
-    if (WRITE) {
-      const uint32_t len = (e >> 16) & 0xff, run = e >> 24;
-      if (run >= kRunBadCode) { *err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_AC_LEN; }
-      else {
-        const uint32_t zr = z + run;
-        if (zr > 63) { *err |= ST_BAD_RUN; }                            // jpeg.cpp:372-376
-        else if (adv > len) {
-          // chunk (zr>>3) of this thread lives at ((zr>>3)*stride + tid) * 8 halfwords
-          stage[((zr >> 3) * stage_stride) * 8 + (zr & 7)] = (uint16_t)extend(w, len, adv - len);
-        }
-      }
-    }
-    r.skip(adv);
-    z += zinc;
-  }
-}
-
 // True when a block that ended at bit `pe` was the last one of the segment ending at `B`:
 // it reached/passed B, or only the 1-bit padding of the last byte is left (T.81 F.1.2.3; a
 // complete Huffman code is never all ones, so padding cannot be taken for another block).
-template <class Reader>
-B2_DEVICE bool segment_done(Reader &r, uint32_t pe, uint32_t B) {
+B2_DEVICE bool segment_done(BitReader &r, uint32_t pe, uint32_t B) {
   if (pe >= B) return true;
   const uint32_t n = B - pe;
   if (n > 7) return false;
@@ -205,47 +188,119 @@ B2_DEVICE int seg_find(const uint32_t *__restrict__ seg, int lo, int hi, uint32_
   return lo;
 }
 
-struct SubResult { SubState e; int nb, d0, d1, d2, flag; };
+struct SubResult { SubState start, e; int nb, d0, d1, d2, flag; };
 
-// Decode every block that starts in [start.p, hi) -- lengths only -- and return the state at the
-// first block start >= hi together with the block count and DC-difference sums accumulated
-// since the last segment start met on the way (flag = one was met).
-template <class Reader>
-B2_DEVICE SubResult decode_sub_sync(const EntropyShared &S, const uint32_t *__restrict__ luts, Reader r,
-                                    uint32_t chunk_bit0, const uint32_t *__restrict__ seg, SubState start,
-                                    uint32_t hi) {
-  SubResult R; R.e = start; R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 0;
-  uint32_t p = start.p, blk = start.blk;
+// What the write pass needs on top of the walk itself.
+struct WriteCtx {
+  uint4 *stage4;          // this thread's staging block: chunk k at stage4[k * kCT]
+  int16_t *obase;         // coefficient buffer of the image
+  int bidx, limit;        // next output block, first block past the current segment's quota
+  int seg_blocks, nseg, nblocks;
+  int pred[3];
+  uint32_t err;
+};
+
+// The one decode loop of stage E: a flat loop over SYMBOLS (DC and AC alike) so that the lanes of a
+// warp stay in step; block ends are handled inside it.  Walks the blocks that start in
+// [from.p, hi).  While `lo` has not been reached the walk is only the self-synchronising run-in;
+// at the first block start >= lo the counters restart and that state is reported as R.start.
+//   WRITE=false: counts blocks and sums DC differences (per component) since the last segment
+//                start met on the way (R.flag = one was met).
+//   WRITE=true : also extracts the values into the staging block and stores finished blocks.
+template <bool WRITE>
+B2_DEVICE void decode_span(const EntropyShared &S, const uint32_t *__restrict__ luts, BitReader &r,
+                           const uint32_t *__restrict__ seg, int nseg, SubState from, uint32_t lo, uint32_t hi,
+                           SubResult &R, WriteCtx *W) {
+  uint32_t p = from.p, blk = from.blk;
+  bool started = p >= lo;
+  R.start = from; R.e = from; R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 0;
   if (hi > S.us_bits) hi = S.us_bits;
-  if (p >= hi) return R;
-  int k = seg_find(seg, S.seg_lo, S.seg_hi, p);
+  if (p >= hi) return;
+  int k = seg_find(seg, 0, nseg - 1, p);
   uint32_t B = seg[k + 1];
-  r.seek(p - chunk_bit0);
-  while (p < hi) {
-    const int ds = S.dc_slot[blk], as = S.ac_slot[blk];
-    int diff;
-    decode_block<false>(r, luts + ds * kLutSize, luts + as * kLutSize, S.slow[ds], S.slow[as], diff, nullptr, 0, nullptr);
-    const int c = S.comp_of[blk];
-    if (c == 0) R.d0 += diff; else if (c == 1) R.d1 += diff; else R.d2 += diff;
+  r.seek(p);
+  int tab = S.tab_of[blk];
+  uint32_t z = 0;
+  uint16_t *stage = WRITE ? reinterpret_cast<uint16_t *>(W->stage4) : nullptr;
+  for (;;) {
+    r.refill();
+    const uint32_t w = r.peek();
+    const bool is_dc = z == 0;
+    const int slot = is_dc ? (tab & 0xff) : ((tab >> 8) & 0xff);
+    uint32_t e = luts[slot * kLutSize + (w >> (32 - kLutBits))];
+    if (e == 0) e = slow_lookup(S.slow[slot], w, is_dc);
+    const uint32_t adv = e & 0xff, zinc = (e >> 8) & 0xff, len = (e >> 16) & 0xff, run = e >> 24;
+    if (is_dc) {
+      const int diff = adv > len ? extend(w, len, adv - len) : 0;     // jpeg.cpp:335-345
+      const int c = tab >> 16;
+      if (WRITE) {
+        if (run >= kRunBadCode) W->err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_DC_LEN;
+        const int dc = (W->pred[c] += diff);
+        if (dc < -32768 || dc > 32767) W->err |= ST_DC_RANGE;
+        stage[0] = (uint16_t)dc;
+      } else {
+        if (c == 0) R.d0 += diff; else if (c == 1) R.d1 += diff; else R.d2 += diff;
+      }
+    } else if (WRITE) {
+      if (run >= kRunBadCode) W->err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_AC_LEN;
+      else {
+        const uint32_t zr = z + run;
+        if (zr > 63) W->err |= ST_BAD_RUN;                               // jpeg.cpp:372-376
+        else if (adv > len) stage[(zr >> 3) * (kCT * 8) + (zr & 7)] = (uint16_t)extend(w, len, adv - len);
+      }
+    }
+    r.skip(adv);
+    z += zinc;
+    if (z < 64) continue;
+    // ---- block end ----
+    const uint32_t pe = r.pos();
+    if (WRITE) {
+      if (W->bidx < W->limit) {                  // blocks past the segment's quota are trailing garbage
+        uint4 *o = reinterpret_cast<uint4 *>(W->obase + (int64_t)W->bidx * 64);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) o[q] = W->stage4[q * kCT];
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) W->stage4[q * kCT] = make_uint4(0, 0, 0, 0);
+      ++W->bidx;
+    }
     ++R.nb;
-    const uint32_t pe = chunk_bit0 + r.pos();
-    if (segment_done(r, pe, B)) {   // last block of its segment
+    if (segment_done(r, pe, B)) {                // last block of its segment (jpeg.cpp:419-425)
+      if (WRITE) {
+        if (pe > B) W->err |= ST_OVERRUN;
+        if (W->bidx < W->limit) W->err |= ST_BLOCK_COUNT;
+        if (W->bidx > W->limit && k + 1 < W->nseg) W->err |= ST_BLOCK_COUNT;
+      }
       p = B; blk = 0;
       R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 1;
-      if (B >= S.us_bits) break;
-      ++k; B = seg[k + 1];
-      r.seek(p - chunk_bit0);
+      if (B < S.us_bits) {
+        ++k; B = seg[k + 1];
+        r.seek(p);
+        if (WRITE) {
+          W->bidx = k * W->seg_blocks;
+          W->limit = (k + 1 < W->nseg) ? (k + 1) * W->seg_blocks : W->nblocks;
+          W->pred[0] = W->pred[1] = W->pred[2] = 0;
+        }
+      }
     } else {
       p = pe;
       blk = blk + 1 == (uint32_t)S.bpm ? 0 : blk + 1;
     }
+    if (!started && p >= lo) {                   // the run-in is over: this is the sub's start state
+      started = true;
+      R.start.p = p; R.start.blk = blk;
+      R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 0;
+    }
+    if (p >= hi) break;
+    tab = S.tab_of[blk];
+    z = 0;
   }
   R.e.p = p; R.e.blk = blk;
-  return R;
 }
 
 // Segmented-sum monoid over (flag, nb, d0, d1, d2): a flag restarts the sums.
 struct Seg5 { int nb, d0, d1, d2, flag; };
+B2_DEVICE Seg5 seg5_zero() { Seg5 z; z.nb = z.d0 = z.d1 = z.d2 = z.flag = 0; return z; }
 B2_DEVICE Seg5 seg5_combine(const Seg5 &a, const Seg5 &b) {
   if (b.flag) return b;
   Seg5 r; r.nb = a.nb + b.nb; r.d0 = a.d0 + b.d0; r.d1 = a.d1 + b.d1; r.d2 = a.d2 + b.d2; r.flag = a.flag;
@@ -281,6 +336,10 @@ B2_DEVICE SubInfo seg5_to(const Seg5 &s) {
   SubInfo i; i.nb_flag = (int32_t)((uint32_t)s.nb | ((uint32_t)s.flag << 31)); i.d0 = s.d0; i.d1 = s.d1; i.d2 = s.d2;
   return i;
 }
+B2_DEVICE SubInfo info_of(const SubResult &R) {
+  Seg5 s; s.nb = R.nb; s.d0 = R.d0; s.d1 = R.d1; s.d2 = R.d2; s.flag = R.flag;
+  return seg5_to(s);
+}
 // CTA-wide exclusive segmented scan; *total = combine of all threads' values.
 B2_DEVICE Seg5 seg5_cta_excl(const Seg5 &v, Seg5 *total) {
   B2_SHARED Seg5 wsum[kCT / 32];
@@ -288,23 +347,20 @@ B2_DEVICE Seg5 seg5_cta_excl(const Seg5 &v, Seg5 *total) {
   const Seg5 inc = seg5_warp_incl(v);
   if (lane == 31) wsum[wid] = inc;
   __syncthreads();
-  Seg5 base; base.nb = base.d0 = base.d1 = base.d2 = base.flag = 0;
-  Seg5 tot = base;
+  Seg5 base = seg5_zero(), tot = seg5_zero();
   for (int w = 0; w < kCT / 32; ++w) { if (w < wid) base = seg5_combine(base, wsum[w]); tot = seg5_combine(tot, wsum[w]); }
   __syncthreads();
   Seg5 prev = seg5_shfl_up(inc, 1);
-  if (lane == 0) { prev.nb = prev.d0 = prev.d1 = prev.d2 = prev.flag = 0; }
+  if (lane == 0) prev = seg5_zero();
   *total = tot;
   return seg5_combine(base, prev);
 }
 
-// Common CTA prologue: image lookup, table build, chunk staging.  Returns false (uniformly) when
-// the CTA has nothing to decode.
-B2_DEVICE bool entropy_prologue(EntropyShared &S, uint32_t *luts, uint32_t *chunk, const ImageDev *__restrict__ imgs,
+// Common CTA prologue: image lookup and table build.  Returns false (uniformly) when the CTA lies
+// past the end of its image's unstuffed scan.
+B2_DEVICE bool entropy_prologue(EntropyShared &S, uint32_t *luts, const ImageDev *__restrict__ imgs,
                                 const int32_t *__restrict__ cta_base, int nimg, const TableSet *__restrict__ tsets,
-                                const ImageOut *__restrict__ out, const uint8_t *__restrict__ d_us,
-                                const uint32_t *__restrict__ seg_start, bool stage_chunk, ImageDev &im,
-                                uint32_t &chunk_bit0) {
+                                const ImageOut *__restrict__ out, ImageDev &im, uint32_t &chunk_bit0) {
   if (threadIdx.x == 0) {
     const int i = find_owner(cta_base, nimg, (int)blockIdx.x);
     S.img = i;
@@ -319,55 +375,78 @@ B2_DEVICE bool entropy_prologue(EntropyShared &S, uint32_t *luts, uint32_t *chun
   if (threadIdx.x == 0) {
     // one LUT slot per distinct (class, id) used by the scan's components
     int nslots = 0; int slot_of_dc[4] = {-1, -1, -1, -1}, slot_of_ac[4] = {-1, -1, -1, -1};
-    int8_t cdc[3], cac[3];
+    int cdc[3] = {0, 0, 0}, cac[3] = {0, 0, 0};
     for (int c = 0; c < im.ncomp; ++c) {
       const int td = im.td[c] & 3, ta = im.ta[c] & 3;
       if (slot_of_dc[td] < 0) slot_of_dc[td] = nslots++;
       if (slot_of_ac[ta] < 0) slot_of_ac[ta] = nslots++;
-      cdc[c] = (int8_t)slot_of_dc[td]; cac[c] = (int8_t)slot_of_ac[ta];
+      cdc[c] = slot_of_dc[td]; cac[c] = slot_of_ac[ta];
     }
     S.nslots = nslots;
     const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
     for (int b = 0; b < im.bpm; ++b) {
       const int c = b < nluma ? 0 : b - nluma + 1;
-      S.comp_of[b] = (int8_t)c; S.dc_slot[b] = cdc[c]; S.ac_slot[b] = cac[c];
+      S.tab_of[b] = cdc[c] | (cac[c] << 8) | (c << 16);
     }
     S.bpm = im.bpm;
-    const uint32_t *seg = seg_start + im.seg_base;
-    S.seg_lo = seg_find(seg, 0, im.nseg - 1, chunk_bit0);
-    S.seg_hi = seg_find(seg, 0, im.nseg - 1, chunk_bit0 + (uint32_t)(kCT * kSubBits + kHaloWords * 32));
   }
   __syncthreads();
   {
     bool done_dc[4] = {false, false, false, false}, done_ac[4] = {false, false, false, false};
     for (int c = 0; c < im.ncomp; ++c) {
       const int td = im.td[c] & 3, ta = im.ta[c] & 3;
-      const int b = c == 0 ? 0 : im.bpm - im.ncomp + c;   // a block of component c
-      if (!done_dc[td]) { done_dc[td] = true; build_table(ts.dc[td], true, luts + S.dc_slot[b] * kLutSize, S.slow[S.dc_slot[b]]); }
-      if (!done_ac[ta]) { done_ac[ta] = true; build_table(ts.ac[ta], false, luts + S.ac_slot[b] * kLutSize, S.slow[S.ac_slot[b]]); }
-    }
-  }
-  if (stage_chunk) {
-    // coalesced 128-bit loads of the chunk (+halo) into shared memory, one pad word per 32
-    const uint4 *src = reinterpret_cast<const uint4 *>(d_us + im.raw_off + (uint64_t)local_cta * (kCT * kSubBits / 8));
-    for (int v = threadIdx.x; v < kChunkWords / 4; v += blockDim.x) {
-      const uint4 q = b2_ld_nc_v4(src + v);
-      const uint32_t i0 = (uint32_t)v * 4, a = i0 + (i0 >> 5);   // the 4 words never straddle a pad
-      chunk[a] = q.x; chunk[a + 1] = q.y; chunk[a + 2] = q.z; chunk[a + 3] = q.w;
+      const int t = S.tab_of[c == 0 ? 0 : im.bpm - im.ncomp + c];   // a block of component c
+      if (!done_dc[td]) { done_dc[td] = true; build_table(ts.dc[td], true, luts + (t & 0xff) * kLutSize, S.slow[t & 0xff]); }
+      if (!done_ac[ta]) { done_ac[ta] = true; build_table(ts.ac[ta], false, luts + ((t >> 8) & 0xff) * kLutSize, S.slow[(t >> 8) & 0xff]); }
     }
   }
   __syncthreads();
   return true;
 }
 
-constexpr int kChunkSmemWords = kChunkWords + kChunkWords / 32 + 2;
 B2_HD size_t entropy_smem_bytes(int nslots, bool staging) {
-  return sizeof(uint32_t) * ((size_t)nslots * kLutSize + kChunkSmemWords) + (staging ? (size_t)kCT * 128 : 0) + 16;
+  return sizeof(uint32_t) * (size_t)nslots * kLutSize + (staging ? (size_t)kCT * 128 : 0) + 16;
+}
+
+// Jacobi repair inside a CTA: re-decode every sub whose start state differs from its predecessor's
+// end state, the needy subs compacted onto the first threads so that whole warps stay busy.
+// S.e / S.used / S.info hold the current states; thread 0's predecessor is S.cta_in if have_in.
+B2_DEVICE void entropy_repair(EntropyShared &S, const uint32_t *luts, BitReader &rd, const uint32_t *seg, int nseg,
+                              uint32_t chunk_bit0, bool have_in) {
+  const int tid = threadIdx.x;
+  for (int round = 0; round <= kCT; ++round) {
+    SubState prev; bool need = false;
+    if (tid > 0 || have_in) {
+      prev = tid == 0 ? S.cta_in : S.e[tid - 1];
+      const SubState u = S.used[tid];
+      const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
+      need = lo < S.us_bits && (prev.p != u.p || prev.blk != u.blk);
+    }
+    if (tid == 0) S.count = 0;
+    __syncthreads();
+    if (need) S.list[atomicAdd(&S.count, 1)] = tid;
+    __syncthreads();
+    const int cnt = S.count;
+#ifdef B200JPEG_EMU
+    if (tid == 0 && getenv("B2_EMU_TRACE")) fprintf(stderr, "cta %u repair round %d: %d subs\n", blockIdx.x, round, cnt);
+#endif
+    if (cnt == 0) break;
+    SubResult R; int j = -1; SubState from;
+    if (tid < cnt) {
+      j = S.list[tid];
+      from = j == 0 ? S.cta_in : S.e[j - 1];
+      const uint32_t lo = chunk_bit0 + (uint32_t)j * kSubBits;
+      decode_span<false>(S, luts, rd, seg, nseg, from, lo, lo + kSubBits, R, nullptr);
+    }
+    __syncthreads();                               // every S.e read of this round precedes every write
+    if (j >= 0) { S.e[j] = R.e; S.used[j] = from; S.info[j] = info_of(R); }
+    __syncthreads();
+  }
 }
 
 // ---- sync / fix -----------------------------------------------------------------------------
-// FIRST=true : round 0 from guessed starts, then Jacobi rounds inside the CTA.
-// FIRST=false: take the previous CTA's settled end state (bnd_in) and repair, if it changed.
+// FIRST=true : run-in + own sub from a guess (or the last segment start), then repair in the CTA.
+// FIRST=false: take the previous CTA's settled end state (bnd_in) and repair, if it differs.
 template <bool FIRST>
 B2_GLOBAL void __launch_bounds__(kCT)
 k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ cta_base, int nimg,
@@ -376,11 +455,10 @@ k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ ct
                SubState *__restrict__ sub_e, SubState *__restrict__ sub_used, SubInfo *__restrict__ sub_info,
                SubInfo *__restrict__ cta_tot, const SubState *__restrict__ bnd_in, SubState *__restrict__ bnd_out,
                uint32_t *__restrict__ changed_flag, int nslots_max) {
-  B2_DYN_SMEM(uint32_t, smem);
+  B2_DYN_SMEM(uint32_t, luts);
   B2_SHARED EntropyShared S;
-  uint32_t *luts = smem;
-  uint32_t *chunk = smem + (size_t)nslots_max * kLutSize;
   const int tid = threadIdx.x;
+  (void)nslots_max;
 
   if (!FIRST) {
     // cheap uniform exit: nothing upstream of this CTA moved
@@ -403,7 +481,7 @@ k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ ct
   }
 
   ImageDev im; uint32_t chunk_bit0;
-  const bool live = entropy_prologue(S, luts, chunk, imgs, cta_base, nimg, tsets, out, d_us, seg_start, true, im, chunk_bit0);
+  const bool live = entropy_prologue(S, luts, imgs, cta_base, nimg, tsets, out, im, chunk_bit0);
   const int cta = (int)blockIdx.x, local_cta = cta - im.cta_base;
   const int gsub = im.sub_base + local_cta * kCT + tid;
   if (!live) {
@@ -417,47 +495,38 @@ k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ ct
     return;
   }
   const uint32_t *seg = seg_start + im.seg_base;
-  const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits, hi = lo + kSubBits;
-  BitReader<true> rd; rd.base = chunk;
+  const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
+  BitReader rd; rd.base = reinterpret_cast<const uint4 *>(d_us + im.raw_off);
 
-  SubState used; SubResult R;
   if (FIRST) {
-    used.p = lo; used.blk = 0;                                  // guess; exact for the image's first sub
-    R = decode_sub_sync(S, luts, rd, chunk_bit0, seg, used, hi);
-  } else {
-    used = sub_used[gsub];
-    R.e = sub_e[gsub];
-    const Seg5 s = seg5_from(sub_info[gsub]);
-    R.nb = s.nb; R.d0 = s.d0; R.d1 = s.d1; R.d2 = s.d2; R.flag = s.flag;
-    if (tid == 0) { S.cta_in = bnd_in[cta - 1]; }
-  }
-  S.e[tid] = R.e;
-  __syncthreads();
-  for (int round = 0; round < kCT; ++round) {
-    SubState prev;
-    bool have = true;
-    if (tid == 0) { if (FIRST) have = false; else prev = S.cta_in; }
-    else prev = S.e[tid - 1];
-    const bool need = have && (prev.p != used.p || prev.blk != used.blk);
-    __syncthreads();                                            // every S.e read happens before any write
-    if (need) {
-      used = prev;
-      R = decode_sub_sync(S, luts, rd, chunk_bit0, seg, used, hi);
-      S.e[tid] = R.e;
+    SubResult R;
+    SubState from; from.p = S.us_bits; from.blk = 0;
+    if (lo < S.us_bits) {
+      // start at the last segment start at or before lo if it is within reach (exact), else guess
+      const int k = seg_find(seg, 0, im.nseg - 1, lo);
+      const uint32_t sb = seg[k];
+      from.p = (lo >= (uint32_t)kOverlapBits && lo - (uint32_t)kOverlapBits > sb) ? lo - (uint32_t)kOverlapBits : sb;
     }
-    if (!__syncthreads_or(need ? 1 : 0)) break;
+    decode_span<false>(S, luts, rd, seg, im.nseg, from, lo, lo + kSubBits, R, nullptr);
+    S.e[tid] = R.e; S.used[tid] = R.start; S.info[tid] = info_of(R);
+  } else {
+    S.e[tid] = sub_e[gsub]; S.used[tid] = sub_used[gsub]; S.info[tid] = sub_info[gsub];
+    if (tid == 0) S.cta_in = bnd_in[cta - 1];
   }
-  sub_e[gsub] = R.e; sub_used[gsub] = used;
-  Seg5 mine; mine.nb = R.nb; mine.d0 = R.d0; mine.d1 = R.d1; mine.d2 = R.d2; mine.flag = R.flag;
-  sub_info[gsub] = seg5_to(mine);
+  __syncthreads();
+  entropy_repair(S, luts, rd, seg, im.nseg, chunk_bit0, !FIRST);
+  const SubState e = S.e[tid];
+  sub_e[gsub] = e; sub_used[gsub] = S.used[tid];
+  const SubInfo mine = S.info[tid];
+  sub_info[gsub] = mine;
   Seg5 total;
-  seg5_cta_excl(mine, &total);
+  seg5_cta_excl(seg5_from(mine), &total);
   if (tid == kCT - 1) {
     if (!FIRST) {
       const SubState old = bnd_in[cta];
-      if (old.p != R.e.p || old.blk != R.e.blk) atomicOr(changed_flag, 1u);
+      if (old.p != e.p || old.blk != e.blk) atomicOr(changed_flag, 1u);
     }
-    bnd_out[cta] = R.e;
+    bnd_out[cta] = e;
   }
   if (tid == 0) cta_tot[cta] = seg5_to(total);
 }
@@ -468,14 +537,14 @@ B2_GLOBAL void k_entropy_scan(const ImageDev *__restrict__ imgs, int nimg, const
   const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (i >= nimg) return;
   const int c0 = imgs[i].cta_base, nc = imgs[i].ncta;
-  Seg5 carry; carry.nb = carry.d0 = carry.d1 = carry.d2 = carry.flag = 0;
+  Seg5 carry = seg5_zero();
   for (int b = 0; b < nc; b += 32) {
     const int c = b + lane;
-    Seg5 v; v.nb = v.d0 = v.d1 = v.d2 = v.flag = 0;
+    Seg5 v = seg5_zero();
     if (c < nc) v = seg5_from(cta_tot[c0 + c]);
     const Seg5 inc = seg5_warp_incl(v);
     Seg5 prev = seg5_shfl_up(inc, 1);
-    if (lane == 0) { prev.nb = prev.d0 = prev.d1 = prev.d2 = prev.flag = 0; }
+    if (lane == 0) prev = seg5_zero();
     if (c < nc) cta_pre[c0 + c] = seg5_to(seg5_combine(carry, prev));
     carry = seg5_combine(carry, seg5_shfl(inc, 31));
   }
@@ -488,25 +557,20 @@ k_entropy_write(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ c
                 const uint32_t *__restrict__ seg_start, const SubState *__restrict__ sub_e,
                 const SubInfo *__restrict__ sub_info, const SubInfo *__restrict__ cta_pre,
                 int16_t *__restrict__ coef, int nslots_max) {
-  B2_DYN_SMEM(uint32_t, smem);
+  B2_DYN_SMEM(uint32_t, luts);
   B2_SHARED EntropyShared S;
-  uint32_t *luts = smem;
-  uint32_t *chunk = smem + (size_t)nslots_max * kLutSize;
-  uint4 *stage4 = reinterpret_cast<uint4 *>(chunk + ((kChunkSmemWords + 3) & ~3));
+  uint4 *stage4 = reinterpret_cast<uint4 *>(luts + (size_t)nslots_max * kLutSize);
   const int tid = threadIdx.x;
   ImageDev im; uint32_t chunk_bit0;
-  if (!entropy_prologue(S, luts, chunk, imgs, cta_base, nimg, tsets, out, d_us, seg_start, true, im, chunk_bit0)) return;
+  if (!entropy_prologue(S, luts, imgs, cta_base, nimg, tsets, out, im, chunk_bit0)) return;
   const int cta = (int)blockIdx.x, local_cta = cta - im.cta_base;
   const int gsub = im.sub_base + local_cta * kCT + tid;
   const uint32_t *seg = seg_start + im.seg_base;
   const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
-  uint32_t hi = lo + kSubBits;
-  if (hi > S.us_bits) hi = S.us_bits;
 
   // first output block and DC predictors of this sub
-  const Seg5 mine = seg5_from(sub_info[gsub]);
   Seg5 total;
-  Seg5 pre = seg5_cta_excl(mine, &total);
+  Seg5 pre = seg5_cta_excl(seg5_from(sub_info[gsub]), &total);
   pre = seg5_combine(seg5_from(cta_pre[cta]), pre);
 
   SubState start;
@@ -516,53 +580,23 @@ k_entropy_write(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ c
   // staging: chunk k (8 coefficients) of thread t at stage4[k*kCT + t]
 #pragma unroll
   for (int k = 0; k < 8; ++k) stage4[k * kCT + tid] = make_uint4(0, 0, 0, 0);
-  uint16_t *stage = reinterpret_cast<uint16_t *>(stage4 + tid);
 
-  uint32_t p = start.p, blk = start.blk, err = 0;
-  if (p < hi) {
-    int k = seg_find(seg, S.seg_lo, S.seg_hi, p);
-    uint32_t B = seg[k + 1];
-    const int seg_blocks = im.restart_interval * im.bpm;            // 0 when there is one segment
-    int bidx = k * seg_blocks + pre.nb;                              // first output block
-    int limit = (k + 1 < im.nseg) ? (k + 1) * seg_blocks : im.nblocks;
-    int pred[3] = {pre.d0, pre.d1, pre.d2};
-    BitReader<true> rd; rd.base = chunk;
-    rd.seek(p - chunk_bit0);
-    int16_t *obase = coef + im.coef_base * 64;
-    while (p < hi) {
-      const int ds = S.dc_slot[blk], as = S.ac_slot[blk];
-      int diff;
-      decode_block<true>(rd, luts + ds * kLutSize, luts + as * kLutSize, S.slow[ds], S.slow[as], diff, stage, kCT, &err);
-      const int c = S.comp_of[blk];
-      const int dc = (pred[c] += diff);
-      if (dc < -32768 || dc > 32767) err |= ST_DC_RANGE;
-      stage[0] = (uint16_t)dc;
-      if (bidx < limit) {                                            // blocks past the segment's quota are trailing garbage
-        uint4 *o = reinterpret_cast<uint4 *>(obase + (int64_t)bidx * 64);
-#pragma unroll
-        for (int q = 0; q < 8; ++q) { o[q] = stage4[q * kCT + tid]; }
-      }
-#pragma unroll
-      for (int q = 0; q < 8; ++q) stage4[q * kCT + tid] = make_uint4(0, 0, 0, 0);
-      ++bidx;
-      const uint32_t pe = chunk_bit0 + rd.pos();
-      if (segment_done(rd, pe, B)) {
-        if (pe > B) err |= ST_OVERRUN;
-        if (bidx < limit) err |= ST_BLOCK_COUNT;
-        if (bidx > limit && k + 1 < im.nseg) err |= ST_BLOCK_COUNT;
-        p = B; blk = 0;
-        if (B >= S.us_bits) break;
-        ++k; B = seg[k + 1];
-        bidx = k * seg_blocks; limit = (k + 1 < im.nseg) ? (k + 1) * seg_blocks : im.nblocks;
-        pred[0] = pred[1] = pred[2] = 0;
-        rd.seek(p - chunk_bit0);
-      } else {
-        p = pe;
-        blk = blk + 1 == (uint32_t)S.bpm ? 0 : blk + 1;
-      }
-    }
+  WriteCtx W;
+  W.stage4 = stage4 + tid;
+  W.obase = coef + im.coef_base * 64;
+  W.seg_blocks = im.restart_interval * im.bpm;                       // 0 when there is one segment
+  W.nseg = im.nseg; W.nblocks = im.nblocks;
+  W.err = 0;
+  if (lo < S.us_bits && start.p < lo + kSubBits && start.p < S.us_bits) {
+    const int k = seg_find(seg, 0, im.nseg - 1, start.p);
+    W.bidx = k * W.seg_blocks + pre.nb;
+    W.limit = (k + 1 < im.nseg) ? (k + 1) * W.seg_blocks : im.nblocks;
+    W.pred[0] = pre.d0; W.pred[1] = pre.d1; W.pred[2] = pre.d2;
+    BitReader rd; rd.base = reinterpret_cast<const uint4 *>(d_us + im.raw_off);
+    SubResult R;
+    decode_span<true>(S, luts, rd, seg, im.nseg, start, lo, lo + kSubBits, R, &W);
   }
-  if (err) atomicOr(&out[S.img].status, err);
+  if (W.err) atomicOr(&out[S.img].status, W.err);
 }
 
 }  // namespace b2

@@ -235,19 +235,20 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
 // layout (types.hpp:32-50): int16 [bhR*bwR][3][64], natural order, chroma at anchor positions.
 B2_GLOBAL void k_export_coef(ImageDev im, int bwr, const int16_t *__restrict__ coef, int16_t *__restrict__ dst) {
   constexpr int zz[64] = {B2_ZZ_LIST};
-  const int64_t blk = (int64_t)blockIdx.x * (blockDim.x / 64) + threadIdx.x / 64;
   const int k = threadIdx.x & 63;
-  if (blk >= im.nblocks) return;
-  const int mcu = (int)(blk / im.bpm), b = (int)(blk - (int64_t)mcu * im.bpm);
-  const int my = mcu / im.mcux, mx = mcu - my * im.mcux;
-  const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
-  int comp, by, bx;
-  if (b < nluma) { comp = 0; by = my * im.vs + b / im.hs; bx = mx * im.hs + b % im.hs; }
-  else { comp = b - nluma + 1; by = my * im.vs; bx = mx * im.hs; }
-  if (im.ncomp == 1) { by = my; bx = mx; }
   int nat = 0;
   for (int j = 0; j < 64; ++j) if (j == k) nat = zz[j];
-  dst[(((int64_t)by * bwr + bx) * 3 + comp) * 64 + nat] = coef[(im.coef_base + blk) * 64 + k];
+  const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+  for (int64_t blk = (int64_t)blockIdx.x * (blockDim.x / 64) + threadIdx.x / 64; blk < im.nblocks;
+       blk += (int64_t)gridDim.x * (blockDim.x / 64)) {
+    const int mcu = (int)(blk / im.bpm), b = (int)(blk - (int64_t)mcu * im.bpm);
+    const int my = mcu / im.mcux, mx = mcu - my * im.mcux;
+    int comp, by, bx;
+    if (b < nluma) { comp = 0; by = my * im.vs + b / im.hs; bx = mx * im.hs + b % im.hs; }
+    else { comp = b - nluma + 1; by = my * im.vs; bx = mx * im.hs; }
+    if (im.ncomp == 1) { by = my; bx = mx; }
+    dst[(((int64_t)by * bwr + bx) * 3 + comp) * 64 + nat] = coef[(im.coef_base + blk) * 64 + k];
+  }
 }
 
 }  // namespace b2

@@ -241,7 +241,12 @@ struct Pipeline {
       const size_t bytes = (size_t)P.bwr[i] * P.bhr[i] * 3 * 64 * sizeof(int16_t);
       if (!d_export.reserve(be, bytes)) return B200JPEG_E_NOMEM;
       be.fill(d_export.p, 0, bytes);   // MCU[] is value-initialised, jpeg.cpp:407
-      B2_LAUNCH(k_export_coef, (im.nblocks + 3) / 4, 256, 0, be.stream, im, P.bwr[i], d_coef.as<int16_t>(),
+      #ifdef B200JPEG_EMU
+      const int egrid = 4;
+#else
+      const int egrid = im.nblocks / 4 + 1 < 2368 ? im.nblocks / 4 + 1 : 2368;
+#endif
+      B2_LAUNCH(k_export_coef, egrid, 256, 0, be.stream, im, P.bwr[i], d_coef.as<int16_t>(),
                 d_export.as<int16_t>());
       be.d2h(coef_out[i], d_export.p, bytes);
       be.sync();

@@ -17,6 +17,7 @@
 #include <memory>
 #include <thread>
 #include <vector>
+#include <cstdio>
 
 struct uint2 { uint32_t x, y; };
 struct uint4 { uint32_t x, y, z, w; };

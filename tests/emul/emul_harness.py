@@ -10,7 +10,9 @@ from jpeg_decoder_b200 import abi
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(os.path.dirname(_HERE))
 SO = os.path.join(_HERE, "_build", "libb200jpeg_emul.so")
+SO_STRESS = os.path.join(_HERE, "_build", "libb200jpeg_emul_stress.so")
 _lib = None
+_libs = {}
 
 
 def build(force=False):
@@ -22,19 +24,20 @@ def build(force=False):
     return SO
 
 
-def _load():
-    global _lib
-    if _lib is None:
+def _load(stress=False):
+    if stress not in _libs:
         build()
-        _lib = C.CDLL(SO)
-        abi.bind_parse(_lib)
-        _lib.emu_decode_batch.restype = C.c_int
-    return _lib
+        lib = C.CDLL(SO_STRESS if stress else SO)
+        abi.bind_parse(lib)
+        lib.emu_decode_batch.restype = C.c_int
+        _libs[stress] = lib
+    return _libs[stress]
 
 
-def decode(datas, flags=0, want_coef=True):
-    """Same contract as jpeg_decoder_b200.Decoder.decode, run on the emulation."""
-    L = _load()
+def decode(datas, flags=0, want_coef=True, stress=False):
+    """Same contract as jpeg_decoder_b200.Decoder.decode, run on the emulation.
+    stress=True: the build with 512-bit subs and no run-in (exercises the repair/fix paths)."""
+    L = _load(stress)
     n = len(datas)
     descs = (abi.ImageDesc * n)()
     bufs = [np.frombuffer(d, dtype=np.uint8).copy() for d in datas]

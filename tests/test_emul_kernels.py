@@ -7,8 +7,8 @@ import pytest
 from tests.conftest import fixture_bytes
 
 
-def check(emul, oracle_mod, datas, flags=0):
-    st, rgbs, coefs, info = emul.decode(datas, flags=flags)
+def check(emul, oracle_mod, datas, flags=0, stress=False):
+    st, rgbs, coefs, info = emul.decode(datas, flags=flags, stress=stress)
     for i, d in enumerate(datas):
         rc, _, oc, orgb = oracle_mod.port_decode(d, flags=flags)
         assert rc == 0 and st[i] == 0, (i, rc, st[i])
@@ -55,3 +55,12 @@ def test_corrupt_streams_are_flagged_not_fatal(emul, harness):
     assert st[1] & abi.ST_NO_EOI
     assert st[2] & abi.ST_BAD_MARKER
     assert st[3] & abi.ST_BAD_RST_COUNT
+
+
+def test_repair_and_fix_paths_under_stress(emul, oracle_mod, harness):
+    # 512-bit subs, no run-in: most subs start out of sync, so the in-CTA Jacobi repair, the
+    # cross-CTA fix launches and the host-side "keep repairing" loop all have to work
+    datas = [harness.synth_jpeg(51, 320, 240, 90, 2, 2, False, 0), harness.synth_jpeg(52, 200, 160, 85, 2, 1, False, 5),
+             fixture_bytes("img2.jpg")]
+    info = check(emul, oracle_mod, datas, stress=True)
+    assert info["sync_rounds"] >= 2
