@@ -19,6 +19,18 @@ bool allow_smem(K kernel, size_t bytes, std::string &err) {
   return true;
 }
 
+// k_pixel is persistent: allow its shared memory and size its grid to the CTAs the device keeps resident
+template <int HS, int VS, int NC>
+bool setup_pixel(b200jpeg_ctx *c, int f, int sms) {
+  const size_t smem = b2::PixCfg<HS, VS, NC>::kSmemBytes;
+  if (!allow_smem(b2::k_pixel<HS, VS, NC>, smem, c->last_error)) return false;
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2::k_pixel<HS, VS, NC>, b2::kPixThreads, smem);
+  if (e != cudaSuccess || per_sm < 1) { c->last_error = "k_pixel does not fit on an SM"; return false; }
+  c->pipe.pix_grid_cap[f] = per_sm * sms;
+  return true;
+}
+
 int fail(b200jpeg_ctx *c, int rc) {
   if (rc == B200JPEG_E_CUDA && !c->pipe.be.err.empty()) c->last_error = c->pipe.be.err;
   return rc;
@@ -53,6 +65,9 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
   const size_t es = b2::entropy_smem_bytes(b2::kMaxSlots, true);
   bool ok = allow_smem(b2::k_entropy_sync<true>, es, c->last_error) && allow_smem(b2::k_entropy_sync<false>, es, c->last_error) &&
             allow_smem(b2::k_entropy_write, es, c->last_error);
+  ok = ok && setup_pixel<1, 1, 3>(c, b2::PF_444, prop.multiProcessorCount) && setup_pixel<2, 1, 3>(c, b2::PF_422, prop.multiProcessorCount) &&
+       setup_pixel<1, 2, 3>(c, b2::PF_440, prop.multiProcessorCount) && setup_pixel<2, 2, 3>(c, b2::PF_420, prop.multiProcessorCount) &&
+       setup_pixel<1, 1, 1>(c, b2::PF_GRAY, prop.multiProcessorCount);
   if (!ok) { b200jpeg_destroy(c); return B200JPEG_E_CUDA; }
   *out = c;
   return B200JPEG_OK;

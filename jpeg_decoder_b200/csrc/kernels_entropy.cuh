@@ -22,7 +22,9 @@
 //
 // Output layout: int16 coef[block][64], blocks in scan order (MCU by MCU, inside an MCU the
 // hs*vs luma blocks row-major, then Cb, then Cr -- jpeg.cpp:426-435), the 64 entries in ZIG-ZAG
-// order (the order they arrive in; stage P de-zig-zags for free when it names its registers).
+// order (the order they arrive in; stage P de-zig-zags for free when it names its registers);
+// the eight 16-byte chunks of a block are stored at chunk ^ (block & 7) so that stage P can read a
+// dense TMA copy of consecutive blocks from shared memory without bank conflicts.
 // Algorithmic bytes: scan bytes in (each pass) + 128 B per coded block out.
 #pragma once
 #include "platform.h"
@@ -258,7 +260,7 @@ B2_DEVICE void decode_span(const EntropyShared &S, const uint32_t *__restrict__ 
       if (W->bidx < W->limit) {                  // blocks past the segment's quota are trailing garbage
         uint4 *o = reinterpret_cast<uint4 *>(W->obase + (int64_t)W->bidx * 64);
 #pragma unroll
-        for (int q = 0; q < 8; ++q) o[q] = W->stage4[q * kCT];
+        for (int q = 0; q < 8; ++q) o[q ^ (W->bidx & 7)] = W->stage4[q * kCT];   // chunk swizzle, see kernels_pixel.cuh
       }
 #pragma unroll
       for (int q = 0; q < 8; ++q) W->stage4[q * kCT] = make_uint4(0, 0, 0, 0);

@@ -10,12 +10,23 @@
 // double->float initialisers produce (types.hpp:5-19).  int16 coefficient x 8-bit quantiser
 // is < 2^24, so float(c)*float(q) is exact and equals the reference's int product converted.
 //
-// Mapping: a CTA of 96 threads owns a tile of 96 consecutive coded blocks of one MCU row
-// (16 / 24 / 32 / 96 MCUs for 4:2:0 / 4:2:2,4:4:0 / 4:4:4 / grey).  Phase 1: one thread per
-// block, all 64 values in registers, de-zig-zag by register naming, column pass, row pass,
-// results to shared-memory planes.  Phase 2: one thread per 16 pixels of a row: nearest-neighbour
-// chroma (jpeg.cpp:518-520), colour, pack, three 128-bit stores (48 contiguous bytes).
-// Algorithmic bytes per tile: 96*128 in + 3 B per pixel out.
+// Mapping (v2, warp-autonomous and persistent): every WARP owns a private slice of shared memory
+// and walks the tile list with stride (warps in the grid).  A tile is kTM consecutive MCUs of one
+// MCU row = at most 32 consecutive coded blocks (30 for 4:2:0 / 4:4:4), i.e. one contiguous run of
+// the coefficient buffer.  Per tile:
+//   load   lane 0 starts a TMA 1-D bulk copy (cp.async.bulk -> mbarrier) of the tile's coefficients
+//          into one of two stage buffers -- issued one tile AHEAD, so HBM latency hides behind the
+//          previous tile's arithmetic and no register is spent on prefetching;
+//   idct   one lane per coded block, all 64 values in registers: de-zig-zag by register naming,
+//          dequantise, column pass, row pass; results to fp32 planes in shared memory.
+//          The entropy stage stores each block's eight 16-byte chunks XOR-swizzled by (block & 7)
+//          so that the lanes' 128-bit reads of a dense copy are bank-conflict free; the planes use
+//          the same XOR on their own chunks;
+//   colour one lane per 8 pixels of a row: nearest-neighbour chroma (jpeg.cpp:518-520), colour sums,
+//          truncate + clamp, 24 bytes into the (now free) stage buffer as RGB staging;
+//   store  the staged rows leave as fully coalesced 128-bit streaming stores.
+// Only __syncwarp() separates the phases; there is no CTA-wide barrier in the kernel.
+// Algorithmic bytes per tile: 128 B per coded block in + 3 B per pixel out.
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -23,7 +34,9 @@
 
 namespace b2 {
 
-constexpr int kPixThreads = 96;
+constexpr int kPixWarps = 4;                 // warps per CTA (each fully independent)
+constexpr int kPixThreads = kPixWarps * 32;
+constexpr int kQStride = 68;                 // floats between the per-component quantiser rows (272 B: rows land in different bank groups)
 
 B2_DEVICE float f32_bits(uint32_t u) {
 #ifdef B200JPEG_EMU
@@ -52,6 +65,10 @@ B2_DEVICE float f32_bits(uint32_t u) {
 #define B2_CR_G f32_bits(0x3f36c8b4u)   /* 0.714f */
 #define B2_CB_B f32_bits(0x3fe2d0e5u)   /* 1.772f */
 
+#ifndef B2_PIX_TRUNC
+#define B2_PIX_TRUNC(x) truncf(x)
+#endif
+
 // One AAN 1-D pass in place, jpeg.cpp:598-662 / 666-730.
 B2_DEVICE void idct8(float &x0, float &x1, float &x2, float &x3, float &x4, float &x5, float &x6, float &x7) {
   const float g0 = __fmul_rn(x0, B2_S0), g1 = __fmul_rn(x4, B2_S4), g2 = __fmul_rn(x2, B2_S2), g3 = __fmul_rn(x6, B2_S6);
@@ -65,31 +82,62 @@ B2_DEVICE void idct8(float &x0, float &x1, float &x2, float &x3, float &x4, floa
   const float c5 = __fadd_rn(d5, e7), c6 = __fsub_rn(d6, d8), c8 = __fsub_rn(c5, c6);
   const float b0 = __fadd_rn(c0, e3), b1 = __fadd_rn(c1, c2), b2 = __fsub_rn(c1, c2), b3 = __fsub_rn(c0, e3);
   const float b4 = __fsub_rn(c4, c8), b6 = __fsub_rn(c6, e7);
-  x0 = truncf(__fadd_rn(b0, e7)); x1 = truncf(__fadd_rn(b1, b6)); x2 = truncf(__fadd_rn(b2, c8));
-  x3 = truncf(__fadd_rn(b3, b4)); x4 = truncf(__fsub_rn(b3, b4)); x5 = truncf(__fsub_rn(b2, c8));
-  x6 = truncf(__fsub_rn(b1, b6)); x7 = truncf(__fsub_rn(b0, e7));
+  x0 = B2_PIX_TRUNC(__fadd_rn(b0, e7)); x1 = B2_PIX_TRUNC(__fadd_rn(b1, b6)); x2 = B2_PIX_TRUNC(__fadd_rn(b2, c8));
+  x3 = B2_PIX_TRUNC(__fadd_rn(b3, b4)); x4 = B2_PIX_TRUNC(__fsub_rn(b3, b4)); x5 = B2_PIX_TRUNC(__fsub_rn(b2, c8));
+  x6 = B2_PIX_TRUNC(__fsub_rn(b1, b6)); x7 = B2_PIX_TRUNC(__fsub_rn(b0, e7));
 }
 
 #define B2_ZZ_LIST                                                                                      \
   0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, \
       7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, \
       31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63
+B2_CONSTANT uint8_t c_zigzag[64] = {B2_ZZ_LIST};   // zig-zag position -> natural index (types.hpp:23-31)
 
 template <int HS, int VS, int NC>
 struct PixCfg {
   static constexpr int kLuma = NC == 1 ? 1 : HS * VS;
   static constexpr int kBpm = NC == 1 ? 1 : HS * VS + 2;
-  static constexpr int kTM = kPixThreads / kBpm;        // MCUs per tile
-  static constexpr int kYW = kTM * 8 * HS;              // luma tile width (pixels)
-  static constexpr int kYH = 8 * VS;
-  static constexpr int kCW = NC == 1 ? 0 : kTM * 8;     // chroma tile width (samples)
-  static constexpr int kGroups = kYW / 16;              // 16-pixel groups per tile row
-  static constexpr int kItems = kYH * kGroups;
-  static constexpr size_t kSmemFloats = (size_t)kYH * kYW + 2 * 8 * (size_t)kCW + 3 * 64;
+  static constexpr int kTM = 32 / kBpm;                  // MCUs per warp tile: 10 / 8 / 8 / 5 / 32
+  static constexpr int kLanes = kTM * kBpm;              // lanes that own a block: 30 / 32 / 32 / 30 / 32
+  static constexpr int kW = kTM * 8 * HS;                // tile width in pixels
+  static constexpr int kH = 8 * VS;
+  static constexpr int kRowBytes = 3 * kW;               // multiple of 16 for every format
+  static constexpr int kIPM = 8 * VS * HS;               // 8-pixel items per MCU
+  static constexpr int kItems = kTM * kIPM;
+  static constexpr int kInBytes = kLanes * 128;
+  static constexpr int kOutBytes = kH * kRowBytes;
+  static constexpr int kStageBytes = ((kInBytes > kOutBytes ? kInBytes : kOutBytes) + 127) / 128 * 128;
+  static constexpr int kPlaneBytes = kLanes * 256;
+  static constexpr int kQBytes = 3 * kQStride * 4 + 16;  // 832
+  static constexpr int kWarpBytes = (2 * kStageBytes + kPlaneBytes + kQBytes + 16 + 127) / 128 * 128;
+  static constexpr size_t kSmemBytes = (size_t)kPixWarps * kWarpBytes;
 };
 
 B2_DEVICE uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
+}
+
+struct PixTile {
+  int img, my, mx0, nm;
+  int64_t blk0;     // global index (in the coefficient buffer) of the tile's first block
+};
+
+// Tile t of a sampling-format group -> image, MCU row, first MCU, MCU count.  `g` walks forward
+// only (a warp's tile numbers increase), so the lookup is O(1) amortised.
+template <int TM, int BPM>
+B2_DEVICE PixTile pix_locate(int t, int &g, const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img,
+                             const int32_t *__restrict__ grp_pre) {
+  while (t >= grp_pre[g + 1]) ++g;
+  PixTile T;
+  T.img = grp_img[g];
+  const int mcux = imgs[T.img].mcux;
+  const int tpr = (mcux + TM - 1) / TM;
+  const int lt = t - grp_pre[g];
+  T.my = lt / tpr;
+  T.mx0 = (lt - T.my * tpr) * TM;
+  T.nm = min(TM, mcux - T.mx0);
+  T.blk0 = imgs[T.img].coef_base + ((int64_t)T.my * mcux + T.mx0) * BPM;
+  return T;
 }
 
 // Tile lookup arrays are per sampling format: grp_img[g] = image index, grp_pre = exclusive
@@ -100,58 +148,77 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
         int ngrp, const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
         const int16_t *__restrict__ coef, uint8_t *__restrict__ rgb) {
   typedef PixCfg<HS, VS, NC> C;
-  B2_DYN_SMEM(float, sm);
-  float *yp = sm;                               // [kYH][kYW]
-  float *cbp = sm + C::kYH * C::kYW;            // [8][kCW]
-  float *crp = cbp + 8 * C::kCW;
-  float *qf = crp + 8 * C::kCW;                 // [3][64] quantisers as float, zig-zag order
-  B2_SHARED int s_g;
-  const int tid = threadIdx.x;
-  if (tid == 0) s_g = find_owner(grp_pre, ngrp, (int)blockIdx.x);
-  __syncthreads();
-  const int img = grp_img[s_g];
-  const ImageDev im = imgs[img];
-  if (out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) return;   // nothing was decoded
-  const int t = (int)blockIdx.x - grp_pre[s_g];
-  const int tiles_per_row = (im.mcux + C::kTM - 1) / C::kTM;
-  const int my = t / tiles_per_row, mx0 = (t - my * tiles_per_row) * C::kTM;
-  const int nm = min(C::kTM, im.mcux - mx0);
+  B2_DYN_SMEM(unsigned char, smraw);
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  unsigned char *wsm = smraw + (size_t)wib * C::kWarpBytes;
+  unsigned char *planes = wsm + 2 * C::kStageBytes;
+  float *qf = reinterpret_cast<float *>(planes + C::kPlaneBytes);
+  uint64_t *mbar = reinterpret_cast<uint64_t *>(planes + C::kPlaneBytes + C::kQBytes);
+
+  const int ntiles = grp_pre[ngrp];
+  const int GW = (int)gridDim.x * kPixWarps;
+  int t = (int)blockIdx.x * kPixWarps + wib;
+  if (t >= ntiles) return;
+
+  if (lane == 0) { b2_mbar_init(&mbar[0], 1); b2_mbar_init(&mbar[1], 1); b2_mbar_init_fence(); }
+  __syncwarp();
 
   constexpr int zz[64] = {B2_ZZ_LIST};
-  {
-    const TableSet &ts = tsets[im.tset];
-    for (int k = tid; k < NC * 64; k += kPixThreads) {
-      const int c = k >> 6, i = k & 63;
-      int nat = 0;
-#pragma unroll
-      for (int j = 0; j < 64; ++j) if (j == i) nat = zz[j];
-      qf[k] = (float)ts.q[im.tq[c] & 3][nat];
-    }
-  }
-  __syncthreads();
+  int g = 0, q_img = -1;
+  PixTile cur = pix_locate<C::kTM, C::kBpm>(t, g, imgs, grp_img, grp_pre);
+  if (lane == 0) b2_bulk_load(wsm, coef + cur.blk0 * 64, (uint32_t)(cur.nm * C::kBpm * 128), &mbar[0]);
 
-  // ---- phase 1: one thread per coded block ----
-  {
-    const int m = tid / C::kBpm, b = tid - m * C::kBpm;
-    if (m < nm) {
-      const int64_t blk = im.coef_base + ((int64_t)my * im.mcux + mx0 + m) * C::kBpm + b;
-      const uint4 *src = reinterpret_cast<const uint4 *>(coef + blk * 64);
-      uint4 raw[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) raw[k] = b2_ld_nc_v4(src + k);
+  for (int n = 0;; ++n) {
+    const int s = n & 1;
+    unsigned char *st_cur = wsm + s * C::kStageBytes, *st_nxt = wsm + (s ^ 1) * C::kStageBytes;
+    // ---- start the NEXT tile's copy into the other stage (free since the end of the last iteration)
+    const int tn = t + GW;
+    PixTile nxt = cur;
+    if (tn < ntiles) {
+      nxt = pix_locate<C::kTM, C::kBpm>(tn, g, imgs, grp_img, grp_pre);
+      if (lane == 0) {
+        b2_fence_proxy_async();
+        b2_bulk_load(st_nxt, coef + nxt.blk0 * 64, (uint32_t)(nxt.nm * C::kBpm * 128), &mbar[s ^ 1]);
+      }
+    }
+    const int img = cur.img;
+    const bool dead = (out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) != 0;   // nothing was decoded
+    const int width = imgs[img].width, height = imgs[img].height;
+
+    // ---- quantiser rows of this image (float, zig-zag order), rebuilt when the image changes
+    if (img != q_img) {
+      const TableSet &ts = tsets[imgs[img].tset];
+      for (int k = lane; k < NC * 64; k += 32) {
+        const int c = k >> 6, i = k & 63;
+        qf[c * kQStride + i] = (float)ts.q[imgs[img].tq[c] & 3][c_zigzag[i]];
+      }
+      q_img = img;
+      __syncwarp();
+    }
+
+    b2_mbar_wait(&mbar[s], (uint32_t)(n >> 1) & 1u);
+
+    // ---- idct: one lane per coded block ----
+    if (lane < cur.nm * C::kBpm && !dead) {
+      const int b = lane % C::kBpm;
       const int comp = b < C::kLuma ? 0 : b - C::kLuma + 1;
-      const float *q = qf + comp * 64;
+      const uint32_t key = (uint32_t)(cur.blk0 + lane) & 7u;
+      const uint4 *src = reinterpret_cast<const uint4 *>(st_cur + lane * 128);
+      const float4 *q4 = reinterpret_cast<const float4 *>(qf + comp * kQStride);
       float v[64];
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const uint32_t w[4] = {raw[k].x, raw[k].y, raw[k].z, raw[k].w};
+        const uint4 raw = src[(uint32_t)k ^ key];
+        const float4 qa = q4[2 * k], qb = q4[2 * k + 1];
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        const float q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const int i0 = k * 8 + j * 2;       // position in zig-zag order
           const float c0 = (float)(int)(int16_t)(w[j] & 0xffffu);
           const float c1 = (float)(int)(int16_t)(w[j] >> 16);
-          v[zz[i0]] = __fmul_rn(c0, q[i0]);        // jpeg.cpp:567 (exact, see header)
-          v[zz[i0 + 1]] = __fmul_rn(c1, q[i0 + 1]);
+          v[zz[i0]] = __fmul_rn(c0, q[2 * j]);          // jpeg.cpp:567 (exact, see header)
+          v[zz[i0 + 1]] = __fmul_rn(c1, q[2 * j + 1]);
         }
       }
 #pragma unroll
@@ -160,84 +227,123 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
 #pragma unroll
       for (int i = 0; i < 8; ++i)                  // rows, jpeg.cpp:664-731
         idct8(v[i * 8 + 0], v[i * 8 + 1], v[i * 8 + 2], v[i * 8 + 3], v[i * 8 + 4], v[i * 8 + 5], v[i * 8 + 6], v[i * 8 + 7]);
-      float *dst; int pitch;
-      if (b < C::kLuma) {
-        const int bv = b / HS, bu = b - bv * HS;
-        dst = yp + (bv * 8) * C::kYW + (m * HS + bu) * 8; pitch = C::kYW;
-      } else {
-        dst = (b == C::kLuma ? cbp : crp) + m * 8; pitch = C::kCW;
-      }
+      float4 *dst = reinterpret_cast<float4 *>(planes + lane * 256);
+      const uint32_t pk = (uint32_t)lane & 7u;
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
-        float4 *d4 = reinterpret_cast<float4 *>(dst + r * pitch);
-        d4[0] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
-        d4[1] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
+        dst[(uint32_t)(2 * r) ^ pk] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
+        dst[(uint32_t)(2 * r + 1) ^ pk] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
       }
     }
-  }
-  __syncthreads();
+    __syncwarp();
 
-  // ---- phase 2: one thread per 16 pixels of one row ----
-  const int width_px = nm * 8 * HS;
-  for (int it = tid; it < C::kItems; it += kPixThreads) {
-    const int row = it / C::kGroups, x = (it - row * C::kGroups) * 16;
-    const int gy = my * C::kYH + row, gx = mx0 * 8 * HS + x;
-    if (x >= width_px || gy >= im.height || gx >= im.width) continue;
-    float yv[16], cbv[16], crv[16];
-    {
-      const float4 *s = reinterpret_cast<const float4 *>(yp + row * C::kYW + x);
+    // ---- colour: one lane per 8 pixels of a row; RGB goes to the stage buffer the copy came through ----
+    if (!dead) {
+      unsigned char *stg = st_cur;
+#pragma unroll 1
+      for (int it = lane; it < C::kItems; it += 32) {
+        const int m = it / C::kIPM, wi = it % C::kIPM, r = wi / HS, hx = wi % HS;
+        if (m >= cur.nm) break;
+        float yv[8], cbv[8], crv[8];
+        {
+          const int yl = m * C::kBpm + (NC == 1 ? 0 : (r >> 3) * HS + hx);
+          const float4 *yp = reinterpret_cast<const float4 *>(planes + yl * 256);
+          const uint32_t c0 = (uint32_t)(r & 7) * 2u, yk = (uint32_t)yl & 7u;
+          const float4 a = yp[c0 ^ yk], c = yp[(c0 + 1) ^ yk];
+          yv[0] = a.x; yv[1] = a.y; yv[2] = a.z; yv[3] = a.w; yv[4] = c.x; yv[5] = c.y; yv[6] = c.z; yv[7] = c.w;
+        }
+        if (NC == 3) {
+          // chroma sample (row/VS, x/HS): the reference's (y/Vs + 4v)*8 + (x/Hs + 4h), jpeg.cpp:518-520
+          const int cl = m * C::kBpm + C::kLuma;
+          const float4 *bp = reinterpret_cast<const float4 *>(planes + cl * 256);
+          const float4 *rp = reinterpret_cast<const float4 *>(planes + (cl + 1) * 256);
+          const uint32_t bk = (uint32_t)cl & 7u, rk = (uint32_t)(cl + 1) & 7u;
+          const uint32_t crow = (uint32_t)(r / VS);
+          if (HS == 2) {
+            const uint32_t ch = crow * 2u + (uint32_t)hx;
+            const float4 a = bp[ch ^ bk], c = rp[ch ^ rk];
+            cbv[0] = a.x; cbv[1] = a.y; cbv[2] = a.z; cbv[3] = a.w;
+            crv[0] = c.x; crv[1] = c.y; crv[2] = c.z; crv[3] = c.w;
+          } else {
+            const float4 a0 = bp[(crow * 2u) ^ bk], a1 = bp[(crow * 2u + 1u) ^ bk];
+            const float4 c0 = rp[(crow * 2u) ^ rk], c1 = rp[(crow * 2u + 1u) ^ rk];
+            cbv[0] = a0.x; cbv[1] = a0.y; cbv[2] = a0.z; cbv[3] = a0.w; cbv[4] = a1.x; cbv[5] = a1.y; cbv[6] = a1.z; cbv[7] = a1.w;
+            crv[0] = c0.x; crv[1] = c0.y; crv[2] = c0.z; crv[3] = c0.w; crv[4] = c1.x; crv[5] = c1.y; crv[6] = c1.z; crv[7] = c1.w;
+          }
+        }
+        uint32_t px[24];
+        if (NC == 3) {
+          float p_r[8 / HS], p_g1[8 / HS], p_g2[8 / HS], p_b[8 / HS];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) { const float4 a = s[k]; yv[4 * k] = a.x; yv[4 * k + 1] = a.y; yv[4 * k + 2] = a.z; yv[4 * k + 3] = a.w; }
-    }
-    if (NC == 3) {
-      // chroma sample (row/VS, x/HS): the reference's (y/Vs + 4v)*8 + (x/Hs + 4h), jpeg.cpp:518-520
-      const int crow = row / VS, cx = x / HS;
-      const float4 *sb = reinterpret_cast<const float4 *>(cbp + crow * C::kCW + cx);
-      const float4 *sr = reinterpret_cast<const float4 *>(crp + crow * C::kCW + cx);
+          for (int j = 0; j < 8 / HS; ++j) {        // the four products of jpeg.cpp:521-523, once per chroma sample
+            p_r[j] = __fmul_rn(B2_CR_R, crv[j]); p_g1[j] = __fmul_rn(B2_CB_G, cbv[j]);
+            p_g2[j] = __fmul_rn(B2_CR_G, crv[j]); p_b[j] = __fmul_rn(B2_CB_B, cbv[j]);
+          }
 #pragma unroll
-      for (int k = 0; k < 16 / HS / 4; ++k) {
-        const float4 a = sb[k], c = sr[k];
-        cbv[4 * k] = a.x; cbv[4 * k + 1] = a.y; cbv[4 * k + 2] = a.z; cbv[4 * k + 3] = a.w;
-        crv[4 * k] = c.x; crv[4 * k + 1] = c.y; crv[4 * k + 2] = c.z; crv[4 * k + 3] = c.w;
+          for (int k = 0; k < 8; ++k) {
+            const int j = k / HS;
+            const float rr = __fadd_rn(__fadd_rn(yv[k], p_r[j]), 128.0f);                          // jpeg.cpp:521
+            const float gg = __fadd_rn(__fsub_rn(__fsub_rn(yv[k], p_g1[j]), p_g2[j]), 128.0f);     // :522
+            const float bb = __fadd_rn(__fadd_rn(yv[k], p_b[j]), 128.0f);                          // :523
+            px[3 * k] = b2_f2u8_rz_sat(rr); px[3 * k + 1] = b2_f2u8_rz_sat(gg); px[3 * k + 2] = b2_f2u8_rz_sat(bb);  // :524-538
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {             // Cb = Cr = 0: every product is +-0 and drops out
+            const uint32_t y8 = b2_f2u8_rz_sat(__fadd_rn(yv[k], 128.0f));
+            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = y8;
+          }
+        }
+        uint2 *o = reinterpret_cast<uint2 *>(stg + r * C::kRowBytes + (m * 8 * HS + hx * 8) * 3);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+          o[q] = make_uint2(pack4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
+                            pack4(px[8 * q + 4], px[8 * q + 5], px[8 * q + 6], px[8 * q + 7]));
       }
     }
-    uint32_t px[48];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      float r, g, b;
-      if (NC == 3) {
-        const float cb = cbv[k / HS], cr = crv[k / HS];
-        r = __fadd_rn(__fadd_rn(yv[k], __fmul_rn(B2_CR_R, cr)), 128.0f);                                   // jpeg.cpp:521
-        g = __fadd_rn(__fsub_rn(__fsub_rn(yv[k], __fmul_rn(B2_CB_G, cb)), __fmul_rn(B2_CR_G, cr)), 128.0f); // :522
-        b = __fadd_rn(__fadd_rn(yv[k], __fmul_rn(B2_CB_B, cb)), 128.0f);                                   // :523
-      } else {
-        r = g = b = __fadd_rn(yv[k], 128.0f);   // Cb = Cr = 0: every product is +-0 and drops out
+    __syncwarp();
+
+    // ---- store: staged rows -> global, 16 bytes per lane, lanes contiguous ----
+    if (!dead) {
+      const int gy0 = cur.my * C::kH, gx0 = cur.mx0 * 8 * HS;
+      const uint32_t pitch = imgs[img].rgb_pitch;
+      const int rows = min(C::kH, height - gy0);
+      const int room = (int)pitch - gx0 * 3;                                  // multiple of 16
+      int rowb = (cur.nm * 8 * HS * 3 + 15) & ~15;
+      if (rowb > room) rowb = room;
+      uint8_t *gbase = rgb + imgs[img].rgb_off + (uint64_t)gy0 * pitch + (uint64_t)gx0 * 3;
+      if (gx0 < width && rows > 0) {
+        if (rowb == C::kRowBytes) {
+          constexpr int cpr = C::kRowBytes / 16;
+          const int total = rows * cpr;
+          for (int idx = lane; idx < total; idx += 32) {
+            const int row = idx / cpr, ch = idx - row * cpr;
+            const uint4 w = *reinterpret_cast<const uint4 *>(st_cur + idx * 16);
+            b2_st_cs_v4(reinterpret_cast<uint4 *>(gbase + (uint64_t)row * pitch) + ch, w);
+          }
+        } else {
+          const int cpr = rowb >> 4;
+          for (int row = 0; row < rows; ++row)
+            for (int ch = lane; ch < cpr; ch += 32) {
+              const uint4 w = *reinterpret_cast<const uint4 *>(st_cur + row * C::kRowBytes + ch * 16);
+              b2_st_cs_v4(reinterpret_cast<uint4 *>(gbase + (uint64_t)row * pitch) + ch, w);
+            }
+        }
       }
-      px[3 * k] = b2_f2u8_rz_sat(r); px[3 * k + 1] = b2_f2u8_rz_sat(g); px[3 * k + 2] = b2_f2u8_rz_sat(b); // :524-538
     }
-    uint8_t *o = rgb + im.rgb_off + (uint64_t)gy * im.rgb_pitch + (uint64_t)gx * 3;
-    uint4 *o4 = reinterpret_cast<uint4 *>(o);
-    const uint32_t room = im.rgb_pitch - (uint32_t)gx * 3;
-#pragma unroll
-    for (int q = 0; q < 3; ++q) {
-      if ((uint32_t)q * 16 < room) {
-        const uint4 w = make_uint4(pack4(px[16 * q + 0], px[16 * q + 1], px[16 * q + 2], px[16 * q + 3]),
-                                   pack4(px[16 * q + 4], px[16 * q + 5], px[16 * q + 6], px[16 * q + 7]),
-                                   pack4(px[16 * q + 8], px[16 * q + 9], px[16 * q + 10], px[16 * q + 11]),
-                                   pack4(px[16 * q + 12], px[16 * q + 13], px[16 * q + 14], px[16 * q + 15]));
-        b2_st_cs_v4(o4 + q, w);
-      }
-    }
+    __syncwarp();      // the stage buffer is the target of the copy started at the top of the next iteration
+
+    if (tn >= ntiles) break;
+    t = tn;
+    cur = nxt;
   }
 }
 
-// Optional export for parity checks: scan-order/zig-zag int16 -> the reference's MCU-array
-// layout (types.hpp:32-50): int16 [bhR*bwR][3][64], natural order, chroma at anchor positions.
+// Optional export for parity checks: scan-order/zig-zag/chunk-swizzled int16 -> the reference's
+// MCU-array layout (types.hpp:32-50): int16 [bhR*bwR][3][64], natural order, chroma at anchor positions.
 B2_GLOBAL void k_export_coef(ImageDev im, int bwr, const int16_t *__restrict__ coef, int16_t *__restrict__ dst) {
-  constexpr int zz[64] = {B2_ZZ_LIST};
   const int k = threadIdx.x & 63;
-  int nat = 0;
-  for (int j = 0; j < 64; ++j) if (j == k) nat = zz[j];
+  const int nat = c_zigzag[k];
   const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
   for (int64_t blk = (int64_t)blockIdx.x * (blockDim.x / 64) + threadIdx.x / 64; blk < im.nblocks;
        blk += (int64_t)gridDim.x * (blockDim.x / 64)) {
@@ -247,7 +353,9 @@ B2_GLOBAL void k_export_coef(ImageDev im, int bwr, const int16_t *__restrict__ c
     if (b < nluma) { comp = 0; by = my * im.vs + b / im.hs; bx = mx * im.hs + b % im.hs; }
     else { comp = b - nluma + 1; by = my * im.vs; bx = mx * im.hs; }
     if (im.ncomp == 1) { by = my; bx = mx; }
-    dst[(((int64_t)by * bwr + bx) * 3 + comp) * 64 + nat] = coef[(im.coef_base + blk) * 64 + k];
+    const int64_t gb = im.coef_base + blk;
+    const int phys = (((k >> 3) ^ (int)(gb & 7)) << 3) | (k & 7);          // undo the chunk swizzle
+    dst[(((int64_t)by * bwr + bx) * 3 + comp) * 64 + nat] = coef[gb * 64 + phys];
   }
 }
 

@@ -105,8 +105,8 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // Sampling formats the pixel kernel is instantiated for.
 enum PixFormat { PF_444 = 0, PF_422 = 1, PF_440 = 2, PF_420 = 3, PF_GRAY = 4, PF_COUNT = 5 };
-inline int pix_tm(int f) {   // MCUs per pixel tile, PixCfg::kTM
-  switch (f) { case PF_444: return 32; case PF_422: case PF_440: return 24; case PF_420: return 16; default: return 96; }
+inline int pix_tm(int f) {   // MCUs per pixel tile, PixCfg::kTM = 32 / blocks per MCU
+  switch (f) { case PF_444: return 10; case PF_422: case PF_440: return 8; case PF_420: return 5; default: return 32; }
 }
 
 struct BatchPlan {
@@ -195,7 +195,7 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     im.sub_base = sub_base; sub_base += im.ncta * kCT;
     im.cta_base = P.cta_base[i]; P.cta_base[i + 1] = im.cta_base + im.ncta;
     im.nblocks = (int32_t)(mcus * im.bpm);
-    im.coef_base = coef_base; coef_base += im.nblocks;
+    im.coef_base = coef_base; coef_base += (im.nblocks + 7) & ~7;   // multiple of 8: the chunk swizzle key is (block & 7)
     im.rgb_pitch = (uint32_t)align_up((size_t)3 * im.width, 16);
     im.rgb_off = rgb_off; rgb_off += align_up((size_t)im.rgb_pitch * im.height, 256);
     P.bwr[i] = d.mcuWidthReal; P.bhr[i] = d.mcuHeightReal;

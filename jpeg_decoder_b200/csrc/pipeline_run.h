@@ -19,6 +19,7 @@ struct Pipeline {
   std::vector<ImageOut> h_out;
   std::vector<uint32_t> h_flags;
   int launches = 0, sync_rounds = 0;
+  int pix_grid_cap[PF_COUNT] = {2, 2, 2, 2, 2};   // resident CTAs of k_pixel per format (emulation: 2, so the tile loop is exercised)
   int64_t h2d_bytes = 0, d2h_bytes = 0;
   bool timing = false;
   float last_ms[B200JPEG_T_COUNT] = {0, 0, 0, 0, 0};
@@ -111,8 +112,13 @@ struct Pipeline {
     if (P.grp_img[f].empty()) return;
     const int ngrp = (int)P.grp_img[f].size();
     const int tiles = P.grp_pre[f].back();
-    const size_t smem = sizeof(float) * PixCfg<HS, VS, NC>::kSmemFloats;
-    B2_LAUNCH((k_pixel<HS, VS, NC>), tiles, kPixThreads, smem, be.stream, d_imgs.as<ImageDev>(),
+    const size_t smem = PixCfg<HS, VS, NC>::kSmemBytes;
+    // persistent: one CTA slot per resident CTA of the device (pix_grid_cap[f], set at create), never more
+    // CTAs than there are groups of kPixWarps tiles
+    int grid = (tiles + kPixWarps - 1) / kPixWarps;
+    if (pix_grid_cap[f] > 0 && grid > pix_grid_cap[f]) grid = pix_grid_cap[f];
+    if (grid <= 0) return;
+    B2_LAUNCH((k_pixel<HS, VS, NC>), grid, kPixThreads, smem, be.stream, d_imgs.as<ImageDev>(),
               d_grp_img[f].as<int32_t>(), d_grp_pre[f].as<int32_t>(), ngrp, d_tsets.as<TableSet>(),
               d_out.as<ImageOut>(), d_coef.as<int16_t>(), d_rgb.as<uint8_t>());
     ++launches;

@@ -19,8 +19,9 @@
 #define B2_SHARED __shared__
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
-#define B2_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw_[]; \
+#define B2_DYN_SMEM(type, name) extern __shared__ __align__(128) unsigned char name##_raw_[]; \
   type *name = reinterpret_cast<type *>(name##_raw_)
+#define B2_CONSTANT __constant__
 
 B2_DEVICE uint32_t b2_ld_nc_u32(const uint32_t *p) { return __ldg(p); }
 B2_DEVICE uint4 b2_ld_nc_v4(const uint4 *p) { return __ldg(p); }
@@ -31,6 +32,39 @@ B2_DEVICE uint32_t b2_f2u8_rz_sat(float x) {
   return r;
 }
 B2_DEVICE void b2_st_cs_v4(uint4 *p, uint4 v) { __stcs(p, v); }
+
+// ---- TMA 1-D bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier, the sm_90+/sm_100 async-copy path ----
+B2_DEVICE uint32_t b2_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+B2_DEVICE void b2_mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(b2_smem_addr(bar)), "r"(count) : "memory");
+}
+B2_DEVICE void b2_mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+// orders this thread's earlier generic-proxy accesses of shared memory before later async-proxy (TMA) ones
+B2_DEVICE void b2_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// one thread: arm the barrier with `bytes` and start the global -> shared bulk copy that completes it
+B2_DEVICE void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b2_smem_addr(bar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(b2_smem_addr(dst)), "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(b2_smem_addr(bar))
+               : "memory");
+}
+B2_DEVICE void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "B2_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra B2_DONE;\n"
+      "bra B2_WAIT;\n"
+      "B2_DONE:\n"
+      "}" ::"r"(b2_smem_addr(bar)), "r"(parity) : "memory");
+}
+// float -> integer-valued float, toward zero, for |x| < 2^23, without the XU pipe (FRND):
+// |x| + 2^23 rounded toward zero is floor(|x|) + 2^23 exactly; subtract and restore the sign.
+B2_DEVICE float b2_trunc_small(float x) {
+  const float a = __fadd_rz(fabsf(x), 8388608.0f);
+  return copysignf(__fsub_rn(a, 8388608.0f), x);
+}
 #else
 // ------------------------------------------------------------------ emulation
 #include "../../tests/emul/cuda_emul.h"

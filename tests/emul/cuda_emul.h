@@ -55,7 +55,7 @@ void launch(dim3 grid, dim3 block, size_t smem, F body) {
   const unsigned nt = block.x * block.y * block.z;
   if (grid.x == 0 || nt == 0) return;
   Cta c; cta() = &c;
-  c.dyn_smem.assign(smem + 16, 0);
+  c.dyn_smem.assign(smem + 128, 0);
   c.vote[0] = c.vote[1] = 0; c.count[0] = c.count[1] = 0;
   std::barrier<> outer(nt);
   auto setup = [&]() {
@@ -109,7 +109,8 @@ inline unsigned linear_tid() {
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
   emu::launch(dim3(grid), dim3(block), (smem), [&]() { kernel(__VA_ARGS__); })
 #define B2_DYN_SMEM(type, name) \
-  type *name = reinterpret_cast<type *>((reinterpret_cast<uintptr_t>(emu::cta()->dyn_smem.data()) + 15) & ~uintptr_t(15))
+  type *name = reinterpret_cast<type *>((reinterpret_cast<uintptr_t>(emu::cta()->dyn_smem.data()) + 127) & ~uintptr_t(127))
+#define B2_CONSTANT static const
 #define __restrict__
 #define __launch_bounds__(...)
 
@@ -233,3 +234,15 @@ static inline uint32_t b2_f2u8_rz_sat(float x) {
   return (uint32_t)(int)x;
 }
 static inline void b2_st_cs_v4(uint4 *p, uint4 v) { *p = v; }
+// mbarrier / bulk copy: the barrier word counts completed phases; the copy is done by the issuing thread
+static inline void b2_mbar_init(uint64_t *bar, uint32_t) { __atomic_store_n(bar, (uint64_t)0, __ATOMIC_SEQ_CST); }
+static inline void b2_mbar_init_fence() {}
+static inline void b2_fence_proxy_async() {}
+static inline void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+  memcpy(dst, src, bytes);
+  __atomic_fetch_add(bar, (uint64_t)1, __ATOMIC_SEQ_CST);
+}
+static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
+  while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
+}
+static inline float b2_trunc_small(float x) { return truncf(x); }
