@@ -16,7 +16,8 @@ from . import abi
 from .abi import ImageDesc  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_SO = os.path.join(_HERE, "libb200jpeg.so")
+# B200JPEG_LIB: another build of the SAME sources (kernel tuning experiments, scripts/gpu_variants.sh)
+LIB_SO = os.environ.get("B200JPEG_LIB") or os.path.join(_HERE, "libb200jpeg.so")
 _lib = None
 
 

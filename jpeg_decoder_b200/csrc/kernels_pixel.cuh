@@ -18,12 +18,13 @@
 //          into one of two stage buffers -- issued one tile AHEAD, so HBM latency hides behind the
 //          previous tile's arithmetic and no register is spent on prefetching;
 //   idct   one lane per coded block, all 64 values in registers: de-zig-zag by register naming,
-//          dequantise, column pass, row pass; results to fp32 planes in shared memory.
-//          The entropy stage stores each block's eight 16-byte chunks XOR-swizzled by (block & 7)
-//          so that the lanes' 128-bit reads of a dense copy are bank-conflict free; the planes use
-//          the same XOR on their own chunks;
-//   colour one lane per 8 pixels of a row: nearest-neighbour chroma (jpeg.cpp:518-520), colour sums,
-//          truncate + clamp, 24 bytes into the (now free) stage buffer as RGB staging;
+//          dequantise, column pass, row pass.  The entropy stage stores each block's eight 16-byte
+//          chunks XOR-swizzled by (block & 7) so that the lanes' 128-bit reads of a dense copy are
+//          bank-conflict free.  Chroma lanes publish their block as an fp32 plane in shared memory
+//          (same XOR on its chunks); luma blocks never leave their registers;
+//   colour every luma lane converts its own 8x8 block: nearest-neighbour chroma from the planes
+//          (jpeg.cpp:518-520), the four chroma products once per chroma sample, colour sums,
+//          truncate + clamp, 24 bytes per row into the (now free) stage buffer as RGB staging;
 //   store  the staged rows leave as fully coalesced 128-bit streaming stores.
 // Only __syncwarp() separates the phases; there is no CTA-wide barrier in the kernel.
 // Algorithmic bytes per tile: 128 B per coded block in + 3 B per pixel out.
@@ -65,6 +66,9 @@ B2_DEVICE float f32_bits(uint32_t u) {
 #define B2_CR_G f32_bits(0x3f36c8b4u)   /* 0.714f */
 #define B2_CB_B f32_bits(0x3fe2d0e5u)   /* 1.772f */
 
+#ifndef B2_PIX_MAXCTAS
+#define B2_PIX_MAXCTAS 4
+#endif
 #ifndef B2_PIX_TRUNC
 #define B2_PIX_TRUNC(x) truncf(x)
 #endif
@@ -102,15 +106,15 @@ struct PixCfg {
   static constexpr int kW = kTM * 8 * HS;                // tile width in pixels
   static constexpr int kH = 8 * VS;
   static constexpr int kRowBytes = 3 * kW;               // multiple of 16 for every format
-  static constexpr int kIPM = 8 * VS * HS;               // 8-pixel items per MCU
-  static constexpr int kItems = kTM * kIPM;
   static constexpr int kInBytes = kLanes * 128;
   static constexpr int kOutBytes = kH * kRowBytes;
   static constexpr int kStageBytes = ((kInBytes > kOutBytes ? kInBytes : kOutBytes) + 127) / 128 * 128;
-  static constexpr int kPlaneBytes = kLanes * 256;
+  static constexpr int kPlaneBytes = NC == 3 ? kTM * 2 * 256 : 0;   // fp32 planes of the chroma blocks only
   static constexpr int kQBytes = 3 * kQStride * 4 + 16;  // 832
   static constexpr int kWarpBytes = (2 * kStageBytes + kPlaneBytes + kQBytes + 16 + 127) / 128 * 128;
   static constexpr size_t kSmemBytes = (size_t)kPixWarps * kWarpBytes;
+  // resident CTAs per SM the register budget must allow (shared memory allows this many)
+  static constexpr int kMinCtas = (int)(232448 / (kSmemBytes + 1024)) > B2_PIX_MAXCTAS ? B2_PIX_MAXCTAS : (int)(232448 / (kSmemBytes + 1024));
 };
 
 B2_DEVICE uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -143,7 +147,7 @@ B2_DEVICE PixTile pix_locate(int t, int &g, const ImageDev *__restrict__ imgs, c
 // Tile lookup arrays are per sampling format: grp_img[g] = image index, grp_pre = exclusive
 // prefix of tiles over the group's images (ngrp+1 entries).
 template <int HS, int VS, int NC>
-B2_GLOBAL void __launch_bounds__(kPixThreads)
+B2_GLOBAL void __launch_bounds__(kPixThreads, (PixCfg<HS, VS, NC>::kMinCtas))
 k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, const int32_t *__restrict__ grp_pre,
         int ngrp, const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
         const int16_t *__restrict__ coef, uint8_t *__restrict__ rgb) {
@@ -164,7 +168,7 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
   __syncwarp();
 
   constexpr int zz[64] = {B2_ZZ_LIST};
-  int g = 0, q_img = -1;
+  int g = 0, q_key = -1;
   PixTile cur = pix_locate<C::kTM, C::kBpm>(t, g, imgs, grp_img, grp_pre);
   if (lane == 0) b2_bulk_load(wsm, coef + cur.blk0 * 64, (uint32_t)(cur.nm * C::kBpm * 128), &mbar[0]);
 
@@ -185,27 +189,32 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
     const bool dead = (out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) != 0;   // nothing was decoded
     const int width = imgs[img].width, height = imgs[img].height;
 
-    // ---- quantiser rows of this image (float, zig-zag order), rebuilt when the image changes
-    if (img != q_img) {
-      const TableSet &ts = tsets[imgs[img].tset];
-      for (int k = lane; k < NC * 64; k += 32) {
-        const int c = k >> 6, i = k & 63;
-        qf[c * kQStride + i] = (float)ts.q[imgs[img].tq[c] & 3][c_zigzag[i]];
+    // ---- quantiser rows (float, zig-zag order), rebuilt only when the TABLES change: consecutive tiles of
+    //      a warp usually lie in different images, but images of a batch mostly share one table set
+    {
+      const int qkey = (imgs[img].tset << 6) | (imgs[img].tq[0] & 3) | ((imgs[img].tq[1] & 3) << 2) | ((imgs[img].tq[2] & 3) << 4);
+      if (qkey != q_key) {
+        const TableSet &ts = tsets[imgs[img].tset];
+        for (int k = lane; k < NC * 64; k += 32) {
+          const int c = k >> 6, i = k & 63;
+          qf[c * kQStride + i] = (float)ts.q[imgs[img].tq[c] & 3][c_zigzag[i]];
+        }
+        q_key = qkey;
+        __syncwarp();
       }
-      q_img = img;
-      __syncwarp();
     }
 
     b2_mbar_wait(&mbar[s], (uint32_t)(n >> 1) & 1u);
 
-    // ---- idct: one lane per coded block ----
-    if (lane < cur.nm * C::kBpm && !dead) {
-      const int b = lane % C::kBpm;
+    // ---- idct: one lane per coded block; the block stays in registers ----
+    const bool has_blk = lane < cur.nm * C::kBpm && !dead;
+    const int b = lane % C::kBpm, m = lane / C::kBpm;
+    float v[64];
+    if (has_blk) {
       const int comp = b < C::kLuma ? 0 : b - C::kLuma + 1;
       const uint32_t key = (uint32_t)(cur.blk0 + lane) & 7u;
       const uint4 *src = reinterpret_cast<const uint4 *>(st_cur + lane * 128);
       const float4 *q4 = reinterpret_cast<const float4 *>(qf + comp * kQStride);
-      float v[64];
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const uint4 raw = src[(uint32_t)k ^ key];
@@ -227,74 +236,71 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
 #pragma unroll
       for (int i = 0; i < 8; ++i)                  // rows, jpeg.cpp:664-731
         idct8(v[i * 8 + 0], v[i * 8 + 1], v[i * 8 + 2], v[i * 8 + 3], v[i * 8 + 4], v[i * 8 + 5], v[i * 8 + 6], v[i * 8 + 7]);
-      float4 *dst = reinterpret_cast<float4 *>(planes + lane * 256);
-      const uint32_t pk = (uint32_t)lane & 7u;
+      if (NC == 3 && b >= C::kLuma) {              // chroma lanes publish their block: plane 2m (Cb), 2m+1 (Cr)
+        const int ord = m * 2 + (b - C::kLuma);
+        float4 *dst = reinterpret_cast<float4 *>(planes + ord * 256);
+        const uint32_t pk = (uint32_t)ord & 7u;
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        dst[(uint32_t)(2 * r) ^ pk] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
-        dst[(uint32_t)(2 * r + 1) ^ pk] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
+        for (int r = 0; r < 8; ++r) {
+          dst[(uint32_t)(2 * r) ^ pk] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
+          dst[(uint32_t)(2 * r + 1) ^ pk] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
+        }
       }
     }
     __syncwarp();
 
-    // ---- colour: one lane per 8 pixels of a row; RGB goes to the stage buffer the copy came through ----
-    if (!dead) {
-      unsigned char *stg = st_cur;
-#pragma unroll 1
-      for (int it = lane; it < C::kItems; it += 32) {
-        const int m = it / C::kIPM, wi = it % C::kIPM, r = wi / HS, hx = wi % HS;
-        if (m >= cur.nm) break;
-        float yv[8], cbv[8], crv[8];
-        {
-          const int yl = m * C::kBpm + (NC == 1 ? 0 : (r >> 3) * HS + hx);
-          const float4 *yp = reinterpret_cast<const float4 *>(planes + yl * 256);
-          const uint32_t c0 = (uint32_t)(r & 7) * 2u, yk = (uint32_t)yl & 7u;
-          const float4 a = yp[c0 ^ yk], c = yp[(c0 + 1) ^ yk];
-          yv[0] = a.x; yv[1] = a.y; yv[2] = a.z; yv[3] = a.w; yv[4] = c.x; yv[5] = c.y; yv[6] = c.z; yv[7] = c.w;
-        }
-        if (NC == 3) {
+    // ---- colour: every luma lane converts its own 8x8 block (Y in registers, chroma from the planes);
+    //      RGB goes to the stage buffer the copy came through ----
+    if (has_blk && b < C::kLuma) {
+      const int by = NC == 1 ? 0 : b / HS, bx = NC == 1 ? 0 : b % HS;
+      unsigned char *orow = st_cur + (by * 8) * C::kRowBytes + (m * 8 * HS + bx * 8) * 3;
+      const float4 *bp = reinterpret_cast<const float4 *>(planes + (m * 2) * 256);
+      const float4 *rp = reinterpret_cast<const float4 *>(planes + (m * 2 + 1) * 256);
+      const uint32_t bk = (uint32_t)(m * 2) & 7u, rk = bk | 1u;
+      const uint32_t crow0 = (uint32_t)(by * (8 / VS));        // chroma row of this block's row 0
+      float p_r[8 / HS], p_g1[8 / HS], p_g2[8 / HS], p_b[8 / HS];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        if (NC == 3 && (r % VS) == 0) {
           // chroma sample (row/VS, x/HS): the reference's (y/Vs + 4v)*8 + (x/Hs + 4h), jpeg.cpp:518-520
-          const int cl = m * C::kBpm + C::kLuma;
-          const float4 *bp = reinterpret_cast<const float4 *>(planes + cl * 256);
-          const float4 *rp = reinterpret_cast<const float4 *>(planes + (cl + 1) * 256);
-          const uint32_t bk = (uint32_t)cl & 7u, rk = (uint32_t)(cl + 1) & 7u;
-          const uint32_t crow = (uint32_t)(r / VS);
+          const uint32_t crow = crow0 + (uint32_t)(r / VS);
+          float cbv[8 / HS], crv[8 / HS];
           if (HS == 2) {
-            const uint32_t ch = crow * 2u + (uint32_t)hx;
+            const uint32_t ch = crow * 2u + (uint32_t)bx;
             const float4 a = bp[ch ^ bk], c = rp[ch ^ rk];
             cbv[0] = a.x; cbv[1] = a.y; cbv[2] = a.z; cbv[3] = a.w;
             crv[0] = c.x; crv[1] = c.y; crv[2] = c.z; crv[3] = c.w;
           } else {
             const float4 a0 = bp[(crow * 2u) ^ bk], a1 = bp[(crow * 2u + 1u) ^ bk];
             const float4 c0 = rp[(crow * 2u) ^ rk], c1 = rp[(crow * 2u + 1u) ^ rk];
-            cbv[0] = a0.x; cbv[1] = a0.y; cbv[2] = a0.z; cbv[3] = a0.w; cbv[4] = a1.x; cbv[5] = a1.y; cbv[6] = a1.z; cbv[7] = a1.w;
-            crv[0] = c0.x; crv[1] = c0.y; crv[2] = c0.z; crv[3] = c0.w; crv[4] = c1.x; crv[5] = c1.y; crv[6] = c1.z; crv[7] = c1.w;
+            cbv[0] = a0.x; cbv[1] = a0.y; cbv[2] = a0.z; cbv[3] = a0.w;
+            crv[0] = c0.x; crv[1] = c0.y; crv[2] = c0.z; crv[3] = c0.w;
+            if (HS == 1) {
+              cbv[(8 / HS) - 4] = a1.x; cbv[(8 / HS) - 3] = a1.y; cbv[(8 / HS) - 2] = a1.z; cbv[(8 / HS) - 1] = a1.w;
+              crv[(8 / HS) - 4] = c1.x; crv[(8 / HS) - 3] = c1.y; crv[(8 / HS) - 2] = c1.z; crv[(8 / HS) - 1] = c1.w;
+            }
           }
-        }
-        uint32_t px[24];
-        if (NC == 3) {
-          float p_r[8 / HS], p_g1[8 / HS], p_g2[8 / HS], p_b[8 / HS];
 #pragma unroll
           for (int j = 0; j < 8 / HS; ++j) {        // the four products of jpeg.cpp:521-523, once per chroma sample
             p_r[j] = __fmul_rn(B2_CR_R, crv[j]); p_g1[j] = __fmul_rn(B2_CB_G, cbv[j]);
             p_g2[j] = __fmul_rn(B2_CR_G, crv[j]); p_b[j] = __fmul_rn(B2_CB_B, cbv[j]);
           }
+        }
+        uint32_t px[24];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < 8; ++k) {
+          const float y = v[r * 8 + k];
+          if (NC == 3) {
             const int j = k / HS;
-            const float rr = __fadd_rn(__fadd_rn(yv[k], p_r[j]), 128.0f);                          // jpeg.cpp:521
-            const float gg = __fadd_rn(__fsub_rn(__fsub_rn(yv[k], p_g1[j]), p_g2[j]), 128.0f);     // :522
-            const float bb = __fadd_rn(__fadd_rn(yv[k], p_b[j]), 128.0f);                          // :523
+            const float rr = __fadd_rn(__fadd_rn(y, p_r[j]), 128.0f);                          // jpeg.cpp:521
+            const float gg = __fadd_rn(__fsub_rn(__fsub_rn(y, p_g1[j]), p_g2[j]), 128.0f);     // :522
+            const float bb = __fadd_rn(__fadd_rn(y, p_b[j]), 128.0f);                          // :523
             px[3 * k] = b2_f2u8_rz_sat(rr); px[3 * k + 1] = b2_f2u8_rz_sat(gg); px[3 * k + 2] = b2_f2u8_rz_sat(bb);  // :524-538
-          }
-        } else {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {             // Cb = Cr = 0: every product is +-0 and drops out
-            const uint32_t y8 = b2_f2u8_rz_sat(__fadd_rn(yv[k], 128.0f));
-            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = y8;
+          } else {                                  // Cb = Cr = 0: every product is +-0 and drops out
+            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = b2_f2u8_rz_sat(__fadd_rn(y, 128.0f));
           }
         }
-        uint2 *o = reinterpret_cast<uint2 *>(stg + r * C::kRowBytes + (m * 8 * HS + hx * 8) * 3);
+        uint2 *o = reinterpret_cast<uint2 *>(orow + r * C::kRowBytes);
 #pragma unroll
         for (int q = 0; q < 3; ++q)
           o[q] = make_uint2(pack4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
