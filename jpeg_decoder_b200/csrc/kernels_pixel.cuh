@@ -286,25 +286,24 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
             p_g2[j] = __fmul_rn(B2_CR_G, crv[j]); p_b[j] = __fmul_rn(B2_CB_B, cbv[j]);
           }
         }
-        uint32_t px[24];
+        float px[24];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float y = v[r * 8 + k];
           if (NC == 3) {
             const int j = k / HS;
-            const float rr = __fadd_rn(__fadd_rn(y, p_r[j]), 128.0f);                          // jpeg.cpp:521
-            const float gg = __fadd_rn(__fsub_rn(__fsub_rn(y, p_g1[j]), p_g2[j]), 128.0f);     // :522
-            const float bb = __fadd_rn(__fadd_rn(y, p_b[j]), 128.0f);                          // :523
-            px[3 * k] = b2_f2u8_rz_sat(rr); px[3 * k + 1] = b2_f2u8_rz_sat(gg); px[3 * k + 2] = b2_f2u8_rz_sat(bb);  // :524-538
+            px[3 * k] = __fadd_rn(__fadd_rn(y, p_r[j]), 128.0f);                              // jpeg.cpp:521
+            px[3 * k + 1] = __fadd_rn(__fsub_rn(__fsub_rn(y, p_g1[j]), p_g2[j]), 128.0f);     // :522
+            px[3 * k + 2] = __fadd_rn(__fadd_rn(y, p_b[j]), 128.0f);                          // :523
           } else {                                  // Cb = Cr = 0: every product is +-0 and drops out
-            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = b2_f2u8_rz_sat(__fadd_rn(y, 128.0f));
+            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = __fadd_rn(y, 128.0f);
           }
         }
         uint2 *o = reinterpret_cast<uint2 *>(orow + r * C::kRowBytes);
 #pragma unroll
-        for (int q = 0; q < 3; ++q)
-          o[q] = make_uint2(pack4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
-                            pack4(px[8 * q + 4], px[8 * q + 5], px[8 * q + 6], px[8 * q + 7]));
+        for (int q = 0; q < 3; ++q)                 // truncate, clamp (jpeg.cpp:524-535), pack
+          o[q] = make_uint2(b2_f4_to_u8x4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
+                            b2_f4_to_u8x4(px[8 * q + 4], px[8 * q + 5], px[8 * q + 6], px[8 * q + 7]));
       }
     }
     __syncwarp();

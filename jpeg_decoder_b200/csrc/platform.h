@@ -32,6 +32,15 @@ B2_DEVICE uint32_t b2_f2u8_rz_sat(float x) {
   return r;
 }
 B2_DEVICE void b2_st_cs_v4(uint4 *p, uint4 v) { __stcs(p, v); }
+// four floats -> truncate toward zero, clamp to [0,255], pack a | b<<8 | c<<16 | d<<24.
+// cvt.rzi.s32.f32 + cvt.pack.sat.u8.s32 fuse into two F2IP.U8.F32.TRUNC (two floats each, merged): no PRMT.
+B2_DEVICE uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
+  const int ia = __float2int_rz(a), ib = __float2int_rz(b), ic = __float2int_rz(c), id = __float2int_rz(d);
+  uint32_t hi, r;
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, 0;" : "=r"(hi) : "r"(id), "r"(ic));
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(ib), "r"(ia), "r"(hi));
+  return r;
+}
 
 // ---- TMA 1-D bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier, the sm_90+/sm_100 async-copy path ----
 B2_DEVICE uint32_t b2_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -234,6 +234,9 @@ static inline uint32_t b2_f2u8_rz_sat(float x) {
   return (uint32_t)(int)x;
 }
 static inline void b2_st_cs_v4(uint4 *p, uint4 v) { *p = v; }
+static inline uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
+  return b2_f2u8_rz_sat(a) | (b2_f2u8_rz_sat(b) << 8) | (b2_f2u8_rz_sat(c) << 16) | (b2_f2u8_rz_sat(d) << 24);
+}
 // mbarrier / bulk copy: the barrier word counts completed phases; the copy is done by the issuing thread
 static inline void b2_mbar_init(uint64_t *bar, uint32_t) { __atomic_store_n(bar, (uint64_t)0, __ATOMIC_SEQ_CST); }
 static inline void b2_mbar_init_fence() {}
