@@ -69,6 +69,9 @@ B2_DEVICE float f32_bits(uint32_t u) {
 #ifndef B2_PIX_MAXCTAS
 #define B2_PIX_MAXCTAS 4
 #endif
+#ifndef B2_PIX_TMA_STORE
+#define B2_PIX_TMA_STORE 1
+#endif
 #ifndef B2_PIX_TRUNC
 #define B2_PIX_TRUNC(x) truncf(x)
 #endif
@@ -109,7 +112,11 @@ struct PixCfg {
   static constexpr int kInBytes = kLanes * 128;
   static constexpr int kOutBytes = kH * kRowBytes;
   static constexpr int kStageBytes = ((kInBytes > kOutBytes ? kInBytes : kOutBytes) + 127) / 128 * 128;
-  static constexpr int kPlaneBytes = NC == 3 ? kTM * 2 * 256 : 0;   // fp32 planes of the chroma blocks only
+  static constexpr int kKeep = NC == 1 ? 8 : (HS * VS == 4 ? 6 : (HS * VS == 2 ? 4 : 3));   // luma rows a luma lane converts itself
+  static constexpr int kTake = NC == 1 ? 0 : (HS * VS == 1 ? 3 : 4);                          // row iterations of a chroma lane
+  static constexpr int kChromaBytes = NC == 3 ? kTM * 2 * 256 : 0;   // fp32 planes of the chroma blocks only
+  static constexpr int kSpillBytes = NC == 3 ? kTM * kLuma * (8 - kKeep) * 32 : 0;   // luma rows handed to the chroma lanes
+  static constexpr int kPlaneBytes = kChromaBytes + kSpillBytes;
   static constexpr int kQBytes = 3 * kQStride * 4 + 16;  // 832
   static constexpr int kWarpBytes = (2 * kStageBytes + kPlaneBytes + kQBytes + 16 + 127) / 128 * 128;
   static constexpr size_t kSmemBytes = (size_t)kPixWarps * kWarpBytes;
@@ -123,24 +130,67 @@ B2_DEVICE uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
 
 struct PixTile {
   int img, my, mx0, nm;
+  int width, height, qkey;
+  uint32_t pitch, dead;
   int64_t blk0;     // global index (in the coefficient buffer) of the tile's first block
+  uint64_t rgb_off;
 };
 
-// Tile t of a sampling-format group -> image, MCU row, first MCU, MCU count.  `g` walks forward
-// only (a warp's tile numbers increase), so the lookup is O(1) amortised.
+// A sampling-format group whose images all have the same geometry and tables and lie at a constant
+// stride in the coefficient / RGB buffers (the normal batch): the tile -> image mapping is then pure
+// arithmetic on kernel parameters, with no dependent global loads at the head of a tile.
+struct PixUni {
+  int32_t enabled;
+  int32_t img0;                 // images are img0, img0+1, ...
+  int32_t mcux, tpr, tpi;       // MCUs per row, tiles per MCU row, tiles per image
+  int32_t width, height, qkey;
+  uint32_t pitch;
+  uint32_t pad;
+  uint64_t magic_tpi, magic_tpr;   // ceil(2^40 / d): n / d == (n * magic) >> 40 for n < 2^24, d < 2^16
+  int64_t coef_base0, coef_stride; // blocks
+  uint64_t rgb_off0, rgb_stride;   // bytes
+};
+
+B2_DEVICE uint32_t pix_dead(const ImageOut *__restrict__ out, int img) {
+  return (out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) != 0;   // nothing was decoded
+}
+B2_DEVICE int pix_qkey(const ImageDev &im) {
+  return (im.tset << 6) | (im.tq[0] & 3) | ((im.tq[1] & 3) << 2) | ((im.tq[2] & 3) << 4);
+}
+
+// Tile t of a sampling-format group -> image, MCU row, first MCU, MCU count.  General path: `g` walks
+// forward only (a warp's tile numbers increase), so the lookup is O(1) amortised.
 template <int TM, int BPM>
-B2_DEVICE PixTile pix_locate(int t, int &g, const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img,
-                             const int32_t *__restrict__ grp_pre) {
-  while (t >= grp_pre[g + 1]) ++g;
+B2_DEVICE PixTile pix_locate(int t, int &g, const PixUni &u, const ImageDev *__restrict__ imgs,
+                             const int32_t *__restrict__ grp_img, const int32_t *__restrict__ grp_pre,
+                             const ImageOut *__restrict__ out) {
   PixTile T;
+  if (u.enabled) {
+    const int gi = (int)(((uint64_t)(uint32_t)t * u.magic_tpi) >> 40);
+    const int lt = t - gi * u.tpi;
+    T.img = u.img0 + gi;
+    T.my = (int)(((uint64_t)(uint32_t)lt * u.magic_tpr) >> 40);
+    T.mx0 = (lt - T.my * u.tpr) * TM;
+    T.nm = min(TM, u.mcux - T.mx0);
+    T.blk0 = u.coef_base0 + (int64_t)gi * u.coef_stride + ((int64_t)T.my * u.mcux + T.mx0) * BPM;
+    T.rgb_off = u.rgb_off0 + (uint64_t)gi * u.rgb_stride;
+    T.width = u.width; T.height = u.height; T.pitch = u.pitch; T.qkey = u.qkey;
+    T.dead = pix_dead(out, T.img);
+    return T;
+  }
+  while (t >= grp_pre[g + 1]) ++g;
   T.img = grp_img[g];
-  const int mcux = imgs[T.img].mcux;
+  const ImageDev &im = imgs[T.img];
+  const int mcux = im.mcux;
   const int tpr = (mcux + TM - 1) / TM;
   const int lt = t - grp_pre[g];
   T.my = lt / tpr;
   T.mx0 = (lt - T.my * tpr) * TM;
   T.nm = min(TM, mcux - T.mx0);
-  T.blk0 = imgs[T.img].coef_base + ((int64_t)T.my * mcux + T.mx0) * BPM;
+  T.blk0 = im.coef_base + ((int64_t)T.my * mcux + T.mx0) * BPM;
+  T.rgb_off = im.rgb_off;
+  T.width = im.width; T.height = im.height; T.pitch = im.rgb_pitch; T.qkey = pix_qkey(im);
+  T.dead = pix_dead(out, T.img);
   return T;
 }
 
@@ -149,13 +199,14 @@ B2_DEVICE PixTile pix_locate(int t, int &g, const ImageDev *__restrict__ imgs, c
 template <int HS, int VS, int NC>
 B2_GLOBAL void __launch_bounds__(kPixThreads, (PixCfg<HS, VS, NC>::kMinCtas))
 k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, const int32_t *__restrict__ grp_pre,
-        int ngrp, const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
+        int ngrp, const PixUni uni, const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
         const int16_t *__restrict__ coef, uint8_t *__restrict__ rgb) {
   typedef PixCfg<HS, VS, NC> C;
   B2_DYN_SMEM(unsigned char, smraw);
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   unsigned char *wsm = smraw + (size_t)wib * C::kWarpBytes;
   unsigned char *planes = wsm + 2 * C::kStageBytes;
+  unsigned char *spill = planes + C::kChromaBytes;
   float *qf = reinterpret_cast<float *>(planes + C::kPlaneBytes);
   uint64_t *mbar = reinterpret_cast<uint64_t *>(planes + C::kPlaneBytes + C::kQBytes);
 
@@ -169,7 +220,7 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
 
   constexpr int zz[64] = {B2_ZZ_LIST};
   int g = 0, q_key = -1;
-  PixTile cur = pix_locate<C::kTM, C::kBpm>(t, g, imgs, grp_img, grp_pre);
+  PixTile cur = pix_locate<C::kTM, C::kBpm>(t, g, uni, imgs, grp_img, grp_pre, out);
   if (lane == 0) b2_bulk_load(wsm, coef + cur.blk0 * 64, (uint32_t)(cur.nm * C::kBpm * 128), &mbar[0]);
 
   for (int n = 0;; ++n) {
@@ -179,20 +230,20 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
     const int tn = t + GW;
     PixTile nxt = cur;
     if (tn < ntiles) {
-      nxt = pix_locate<C::kTM, C::kBpm>(tn, g, imgs, grp_img, grp_pre);
+      nxt = pix_locate<C::kTM, C::kBpm>(tn, g, uni, imgs, grp_img, grp_pre, out);
       if (lane == 0) {
         b2_fence_proxy_async();
         b2_bulk_load(st_nxt, coef + nxt.blk0 * 64, (uint32_t)(nxt.nm * C::kBpm * 128), &mbar[s ^ 1]);
       }
     }
     const int img = cur.img;
-    const bool dead = (out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) != 0;   // nothing was decoded
-    const int width = imgs[img].width, height = imgs[img].height;
+    const bool dead = cur.dead != 0;
+    const int width = cur.width, height = cur.height;
 
     // ---- quantiser rows (float, zig-zag order), rebuilt only when the TABLES change: consecutive tiles of
     //      a warp usually lie in different images, but images of a batch mostly share one table set
     {
-      const int qkey = (imgs[img].tset << 6) | (imgs[img].tq[0] & 3) | ((imgs[img].tq[1] & 3) << 2) | ((imgs[img].tq[2] & 3) << 4);
+      const int qkey = cur.qkey;
       if (qkey != q_key) {
         const TableSet &ts = tsets[imgs[img].tset];
         for (int k = lane; k < NC * 64; k += 32) {
@@ -236,6 +287,14 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
 #pragma unroll
       for (int i = 0; i < 8; ++i)                  // rows, jpeg.cpp:664-731
         idct8(v[i * 8 + 0], v[i * 8 + 1], v[i * 8 + 2], v[i * 8 + 3], v[i * 8 + 4], v[i * 8 + 5], v[i * 8 + 6], v[i * 8 + 7]);
+      if (NC == 3 && b < C::kLuma) {               // luma lanes hand rows [kKeep,8) to the chroma lanes
+        float4 *sp = reinterpret_cast<float4 *>(spill + (m * C::kLuma + b) * (8 - C::kKeep) * 32);
+#pragma unroll
+        for (int r = C::kKeep; r < 8; ++r) {
+          sp[(r - C::kKeep) * 2] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
+          sp[(r - C::kKeep) * 2 + 1] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
+        }
+      }
       if (NC == 3 && b >= C::kLuma) {              // chroma lanes publish their block: plane 2m (Cb), 2m+1 (Cr)
         const int ord = m * 2 + (b - C::kLuma);
         float4 *dst = reinterpret_cast<float4 *>(planes + ord * 256);
@@ -249,21 +308,51 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
     }
     __syncwarp();
 
-    // ---- colour: every luma lane converts its own 8x8 block (Y in registers, chroma from the planes);
-    //      RGB goes to the stage buffer the copy came through ----
-    if (has_blk && b < C::kLuma) {
-      const int by = NC == 1 ? 0 : b / HS, bx = NC == 1 ? 0 : b % HS;
-      unsigned char *orow = st_cur + (by * 8) * C::kRowBytes + (m * 8 * HS + bx * 8) * 3;
+    // ---- colour: the 8*kLuma luma rows of an MCU are shared out over ALL its lanes.  A luma lane keeps
+    //      rows [0,kKeep) of its block in registers and spills the rest to shared memory; the two chroma
+    //      lanes (whose own block now lives in the planes) pick those rows up into their registers.
+    //      Every lane then runs the same kKeep row iterations; RGB goes to the stage buffer the copy
+    //      came through ----
+    const bool is_luma = b < C::kLuma;
+    const int cidx = b - C::kLuma;                  // 0 = Cb lane, 1 = Cr lane
+    if (NC == 3) {
+      if (has_blk && !is_luma) {
+#pragma unroll
+        for (int i = 0; i < C::kKeep; ++i) {
+          int lb, r;
+          if (HS * VS == 4) { lb = 2 * cidx + (i >> 1); r = 6 + (i & 1); }
+          else if (HS * VS == 2) { lb = cidx; r = 4 + i; }
+          else { lb = 0; r = 3 + 3 * cidx + i; }
+          if (i < C::kTake && r < 8) {
+            const float4 *sp = reinterpret_cast<const float4 *>(spill + (((m * C::kLuma + lb) * (8 - C::kKeep)) + (r - C::kKeep)) * 32);
+            const float4 a = sp[0], c = sp[1];
+            v[i * 8 + 0] = a.x; v[i * 8 + 1] = a.y; v[i * 8 + 2] = a.z; v[i * 8 + 3] = a.w;
+            v[i * 8 + 4] = c.x; v[i * 8 + 5] = c.y; v[i * 8 + 6] = c.z; v[i * 8 + 7] = c.w;
+          }
+        }
+      }
+    }
+    if (has_blk) {
       const float4 *bp = reinterpret_cast<const float4 *>(planes + (m * 2) * 256);
       const float4 *rp = reinterpret_cast<const float4 *>(planes + (m * 2 + 1) * 256);
       const uint32_t bk = (uint32_t)(m * 2) & 7u, rk = bk | 1u;
-      const uint32_t crow0 = (uint32_t)(by * (8 / VS));        // chroma row of this block's row 0
       float p_r[8 / HS], p_g1[8 / HS], p_g2[8 / HS], p_b[8 / HS];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        if (NC == 3 && (r % VS) == 0) {
+      for (int i = 0; i < C::kKeep; ++i) {
+        // which luma block / row this lane converts in iteration i
+        int lb = b, r = i;
+        bool valid = true;
+        if (NC == 3 && !is_luma) {
+          if (HS * VS == 4) { lb = 2 * cidx + (i >> 1); r = 6 + (i & 1); }
+          else if (HS * VS == 2) { lb = cidx; r = 4 + i; }
+          else { lb = 0; r = 3 + 3 * cidx + i; }
+          valid = i < C::kTake && r < 8;
+          if (!valid) { lb = 0; r = 0; }
+        }
+        const int by = NC == 1 ? 0 : lb / HS, bx = NC == 1 ? 0 : lb % HS;
+        if (NC == 3 && (i % VS) == 0) {
           // chroma sample (row/VS, x/HS): the reference's (y/Vs + 4v)*8 + (x/Hs + 4h), jpeg.cpp:518-520
-          const uint32_t crow = crow0 + (uint32_t)(r / VS);
+          const uint32_t crow = (uint32_t)((by * 8 + (r & 7)) / VS);
           float cbv[8 / HS], crv[8 / HS];
           if (HS == 2) {
             const uint32_t ch = crow * 2u + (uint32_t)bx;
@@ -289,7 +378,7 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
         float px[24];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          const float y = v[r * 8 + k];
+          const float y = v[i * 8 + k];
           if (NC == 3) {
             const int j = k / HS;
             px[3 * k] = __fadd_rn(__fadd_rn(y, p_r[j]), 128.0f);                              // jpeg.cpp:521
@@ -299,11 +388,13 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
             px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = __fadd_rn(y, 128.0f);
           }
         }
-        uint2 *o = reinterpret_cast<uint2 *>(orow + r * C::kRowBytes);
+        if (valid) {
+          uint2 *o = reinterpret_cast<uint2 *>(st_cur + (by * 8 + r) * C::kRowBytes + (m * 8 * HS + bx * 8) * 3);
 #pragma unroll
-        for (int q = 0; q < 3; ++q)                 // truncate, clamp (jpeg.cpp:524-535), pack
-          o[q] = make_uint2(b2_f4_to_u8x4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
-                            b2_f4_to_u8x4(px[8 * q + 4], px[8 * q + 5], px[8 * q + 6], px[8 * q + 7]));
+          for (int q = 0; q < 3; ++q)               // truncate, clamp (jpeg.cpp:524-535), pack
+            o[q] = make_uint2(b2_f4_to_u8x4(px[8 * q + 0], px[8 * q + 1], px[8 * q + 2], px[8 * q + 3]),
+                              b2_f4_to_u8x4(px[8 * q + 4], px[8 * q + 5], px[8 * q + 6], px[8 * q + 7]));
+        }
       }
     }
     __syncwarp();
@@ -311,12 +402,23 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
     // ---- store: staged rows -> global, 16 bytes per lane, lanes contiguous ----
     if (!dead) {
       const int gy0 = cur.my * C::kH, gx0 = cur.mx0 * 8 * HS;
-      const uint32_t pitch = imgs[img].rgb_pitch;
+      const uint32_t pitch = cur.pitch;
       const int rows = min(C::kH, height - gy0);
       const int room = (int)pitch - gx0 * 3;                                  // multiple of 16
       int rowb = (cur.nm * 8 * HS * 3 + 15) & ~15;
       if (rowb > room) rowb = room;
-      uint8_t *gbase = rgb + imgs[img].rgb_off + (uint64_t)gy0 * pitch + (uint64_t)gx0 * 3;
+      uint8_t *gbase = rgb + cur.rgb_off + (uint64_t)gy0 * pitch + (uint64_t)gx0 * 3;
+#if B2_PIX_TMA_STORE
+      // one TMA bulk store per row, issued by the lane of that row number; the group is drained
+      // (source read) before the stage buffer is handed back to the load pipeline
+      b2_fence_proxy_async();
+      __syncwarp();
+      if (gx0 < width && lane < rows && rowb > 0) {
+        b2_bulk_store(gbase + (uint64_t)lane * pitch, st_cur + lane * C::kRowBytes, (uint32_t)rowb);
+        b2_bulk_commit();
+        b2_bulk_wait_read();
+      }
+#else
       if (gx0 < width && rows > 0) {
         if (rowb == C::kRowBytes) {
           constexpr int cpr = C::kRowBytes / 16;
@@ -335,6 +437,7 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
             }
         }
       }
+#endif
     }
     __syncwarp();      // the stage buffer is the target of the copy started at the top of the next iteration
 

@@ -115,6 +115,7 @@ struct BatchPlan {
   std::vector<TableSet> tsets;
   std::vector<int32_t> tile_base, cta_base;           // n+1 exclusive prefixes
   std::vector<int32_t> grp_img[PF_COUNT], grp_pre[PF_COUNT];
+  PixUni uni[PF_COUNT];                               // arithmetic tile lookup for uniform groups
   std::vector<int> bwr, bhr;                          // reference block grid (coef export)
   size_t raw_bytes = 0, rgb_bytes = 0;
   int64_t nblocks = 0, pixels = 0, scan_bytes = 0;
@@ -206,6 +207,30 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     const int tiles = im.mcuy * ((im.mcux + pix_tm(f) - 1) / pix_tm(f));
     P.grp_img[f].push_back(i);
     P.grp_pre[f].push_back(P.grp_pre[f].back() + tiles);
+  }
+  for (int f = 0; f < PF_COUNT; ++f) {                // uniform groups: see PixUni
+    PixUni &u = P.uni[f];
+    memset(&u, 0, sizeof u);
+    const std::vector<int32_t> &gi = P.grp_img[f];
+    if (gi.empty()) continue;
+    const ImageDev &a = P.imgs[gi[0]];
+    const int tpr = (a.mcux + pix_tm(f) - 1) / pix_tm(f), tpi = tpr * a.mcuy;
+    bool ok = tpr < 65536 && tpi < 65536 && (int64_t)tpi * (int64_t)gi.size() < (1 << 24);
+    const int64_t cstride = gi.size() > 1 ? P.imgs[gi[1]].coef_base - a.coef_base : 0;
+    const uint64_t rstride = gi.size() > 1 ? P.imgs[gi[1]].rgb_off - a.rgb_off : 0;
+    for (size_t k = 0; ok && k < gi.size(); ++k) {
+      const ImageDev &b = P.imgs[gi[k]];
+      ok = gi[k] == gi[0] + (int)k && b.mcux == a.mcux && b.mcuy == a.mcuy && b.width == a.width && b.height == a.height &&
+           b.rgb_pitch == a.rgb_pitch && b.tset == a.tset && !memcmp(b.tq, a.tq, sizeof a.tq) &&
+           b.coef_base == a.coef_base + (int64_t)k * cstride && b.rgb_off == a.rgb_off + (uint64_t)k * rstride;
+    }
+    if (!ok) continue;
+    u.enabled = 1; u.img0 = gi[0]; u.mcux = a.mcux; u.tpr = tpr; u.tpi = tpi;
+    u.width = a.width; u.height = a.height; u.pitch = a.rgb_pitch;
+    u.qkey = (a.tset << 6) | (a.tq[0] & 3) | ((a.tq[1] & 3) << 2) | ((a.tq[2] & 3) << 4);
+    u.magic_tpi = (((uint64_t)1 << 40) + (uint64_t)tpi - 1) / (uint64_t)tpi;
+    u.magic_tpr = (((uint64_t)1 << 40) + (uint64_t)tpr - 1) / (uint64_t)tpr;
+    u.coef_base0 = a.coef_base; u.coef_stride = cstride; u.rgb_off0 = a.rgb_off; u.rgb_stride = rstride;
   }
   P.raw_bytes = raw_off; P.rgb_bytes = rgb_off; P.nblocks = coef_base;
   P.ntiles = P.tile_base[n]; P.nctas = P.cta_base[n]; P.nsubs = sub_base; P.nsegs = seg_base;

@@ -119,7 +119,7 @@ struct Pipeline {
     if (pix_grid_cap[f] > 0 && grid > pix_grid_cap[f]) grid = pix_grid_cap[f];
     if (grid <= 0) return;
     B2_LAUNCH((k_pixel<HS, VS, NC>), grid, kPixThreads, smem, be.stream, d_imgs.as<ImageDev>(),
-              d_grp_img[f].as<int32_t>(), d_grp_pre[f].as<int32_t>(), ngrp, d_tsets.as<TableSet>(),
+              d_grp_img[f].as<int32_t>(), d_grp_pre[f].as<int32_t>(), ngrp, P.uni[f], d_tsets.as<TableSet>(),
               d_out.as<ImageOut>(), d_coef.as<int16_t>(), d_rgb.as<uint8_t>());
     ++launches;
   }

@@ -57,6 +57,13 @@ B2_DEVICE void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t
                ::"r"(b2_smem_addr(dst)), "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(b2_smem_addr(bar))
                : "memory");
 }
+// shared -> global bulk copy (TMA store, bulk-group completion); every issuing thread commits and waits itself
+B2_DEVICE void b2_bulk_store(void *dst, const void *src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(__cvta_generic_to_global(dst)), "r"(b2_smem_addr(src)), "r"(bytes) : "memory");
+}
+B2_DEVICE void b2_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+B2_DEVICE void b2_bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 B2_DEVICE void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   asm volatile(
       "{\n"

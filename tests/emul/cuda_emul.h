@@ -245,6 +245,9 @@ static inline void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint
   memcpy(dst, src, bytes);
   __atomic_fetch_add(bar, (uint64_t)1, __ATOMIC_SEQ_CST);
 }
+static inline void b2_bulk_store(void *dst, const void *src, uint32_t bytes) { memcpy(dst, src, bytes); }
+static inline void b2_bulk_commit() {}
+static inline void b2_bulk_wait_read() {}
 static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
 }
