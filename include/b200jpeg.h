@@ -183,6 +183,13 @@ typedef struct {
 } b200jpeg_batch_stats;
 int b200jpeg_batch_get_stats(const b200jpeg_ctx *ctx, b200jpeg_batch_stats *stats);
 
+/* Entropy decoder of the following batches.  AUTO picks per batch: SEGMENT (one thread per restart
+ * segment, decoded in one pass straight from the stuffed bytes) when the batch holds enough segments to
+ * fill the GPU, else SYNC (self-synchronising sub-sequences inside each scan).  Both give identical
+ * results; the override exists for tests and measurements. */
+enum { B200JPEG_ENTROPY_AUTO = 0, B200JPEG_ENTROPY_SEGMENT = 1, B200JPEG_ENTROPY_SYNC = 2 };
+int b200jpeg_set_entropy_path(b200jpeg_ctx *ctx, int mode);
+
 /* Per-stage CUDA-event times of the last b200jpeg_batch_run (milliseconds): unstuff, entropy
  * sync, entropy write, pixel, total.  Only recorded when enabled (adds event records). */
 enum { B200JPEG_T_UNSTUFF = 0, B200JPEG_T_SYNC = 1, B200JPEG_T_WRITE = 2, B200JPEG_T_PIXEL = 3,

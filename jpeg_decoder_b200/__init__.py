@@ -106,6 +106,10 @@ class Decoder:
         self.lib.b200jpeg_batch_get_stats(self.h, C.byref(s))
         return {k: getattr(s, k) for k, _ in s._fields_}
 
+    def set_entropy_path(self, mode=abi.ENTROPY_AUTO):
+        """abi.ENTROPY_AUTO / ENTROPY_SEGMENT / ENTROPY_SYNC (b200jpeg_set_entropy_path)."""
+        self._check(self.lib.b200jpeg_set_entropy_path(self.h, int(mode)), "set_entropy_path")
+
     def set_timing(self, on=True):
         self.lib.b200jpeg_set_timing(self.h, int(on))
 

@@ -27,6 +27,7 @@ E_NOT_JPEG, E_PROGRESSIVE, E_COMPONENTS, E_SAMPLING, E_TABLE_ID, E_DHT = -10, -1
 E_SOS, E_DRI, E_NO_SOS, E_TABLE_MISSING, E_TRUNCATED, E_COMPONENT_ID, E_UNSUPPORTED = -16, -17, -18, -19, -20, -21, -22
 
 PARSE_REFERENCE, PARSE_SPEC = 0, 1
+ENTROPY_AUTO, ENTROPY_SEGMENT, ENTROPY_SYNC = 0, 1, 2
 
 T_UNSTUFF, T_SYNC, T_WRITE, T_PIXEL, T_TOTAL, T_COUNT = 0, 1, 2, 3, 4, 5
 
@@ -106,6 +107,8 @@ def bind(lib):
     lib.b200jpeg_stream.argtypes = [C.c_void_p]
     lib.b200jpeg_batch_get_stats.restype = C.c_int
     lib.b200jpeg_batch_get_stats.argtypes = [C.c_void_p, P(BatchStats)]
+    lib.b200jpeg_set_entropy_path.restype = C.c_int
+    lib.b200jpeg_set_entropy_path.argtypes = [C.c_void_p, C.c_int]
     lib.b200jpeg_set_timing.restype = C.c_int
     lib.b200jpeg_set_timing.argtypes = [C.c_void_p, C.c_int]
     lib.b200jpeg_last_timing.restype = C.c_int

@@ -64,7 +64,8 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
   for (int i = 0; i <= B200JPEG_T_COUNT; ++i) cudaEventCreate(&c->pipe.ev[i]);
   const size_t es = b2::entropy_smem_bytes(b2::kMaxSlots, true);
   bool ok = allow_smem(b2::k_entropy_sync<true>, es, c->last_error) && allow_smem(b2::k_entropy_sync<false>, es, c->last_error) &&
-            allow_smem(b2::k_entropy_write, es, c->last_error);
+            allow_smem(b2::k_entropy_write, es, c->last_error) &&
+            allow_smem(b2::k_entropy_seg, b2::segdec_smem_bytes(), c->last_error);
   ok = ok && setup_pixel<1, 1, 3>(c, b2::PF_444, prop.multiProcessorCount) && setup_pixel<2, 1, 3>(c, b2::PF_422, prop.multiProcessorCount) &&
        setup_pixel<1, 2, 3>(c, b2::PF_440, prop.multiProcessorCount) && setup_pixel<2, 2, 3>(c, b2::PF_420, prop.multiProcessorCount) &&
        setup_pixel<1, 1, 1>(c, b2::PF_GRAY, prop.multiProcessorCount);
@@ -138,6 +139,12 @@ int b200jpeg_batch_get_stats(const b200jpeg_ctx *c, b200jpeg_batch_stats *s) {
   for (int i = 0; i < P.n; ++i) s->rgb_bytes += (int64_t)3 * P.imgs[i].width * P.imgs[i].height;
   s->h2d_bytes = c->pipe.h2d_bytes; s->d2h_bytes = c->pipe.d2h_bytes;
   s->kernel_launches = c->pipe.launches; s->sync_rounds = c->pipe.sync_rounds;
+  return B200JPEG_OK;
+}
+
+int b200jpeg_set_entropy_path(b200jpeg_ctx *c, int mode) {
+  if (!c || mode < 0 || mode > 2) return B200JPEG_E_ARG;
+  c->pipe.force_path = mode;
   return B200JPEG_OK;
 }
 

@@ -12,6 +12,7 @@ namespace b2 {
 
 constexpr int kMaxBpm = 6;          // blocks per MCU: hs*vs + 2 with hs,vs in {1,2}; 1 for grey
 constexpr uint32_t kNone = 0xffffffffu;
+enum : int32_t { kPathSync = 0, kPathSegment = 1 };   // kernels_entropy.cuh / kernels_segdec.cuh
 
 // per-image status bits (0 = decoded)
 enum : uint32_t {
@@ -58,7 +59,7 @@ struct ImageDev {
   int32_t sub_base, nsub_max;   // subsequences
   int32_t cta_base, ncta;       // entropy CTAs (kCT subs each)
   int32_t nblocks;              // coded blocks = mcux*mcuy*bpm
-  int32_t pad1;
+  int32_t path;                 // kPathSync / kPathSegment: which entropy decoder takes this image
   int64_t coef_base;            // first block of this image in the coefficient buffer
   uint64_t rgb_off;             // byte offset of this image in the RGB buffer
   uint32_t rgb_pitch;           // bytes per row on the device (3*width rounded up to 16)

@@ -13,12 +13,14 @@
 #include <string.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 
 #include "../../include/b200jpeg.h"
 #include "platform.h"
 #include "dev_types.h"
 #include "kernels_unstuff.cuh"
 #include "kernels_entropy.cuh"
+#include "kernels_segdec.cuh"
 #include "kernels_pixel.cuh"
 
 namespace b2 {
@@ -120,12 +122,40 @@ struct BatchPlan {
   size_t raw_bytes = 0, rgb_bytes = 0;
   int64_t nblocks = 0, pixels = 0, scan_bytes = 0;
   int ntiles = 0, nsubs = 0, nctas = 0, nsegs = 0, nslots_max = 2;
+  // entropy path of the batch (kPathSegment: one thread per restart segment, kernels_segdec.cuh)
+  int path = kPathSync;
+  std::vector<uint2> units;                           // (image, segment), grouped by table set, padded per group
+  int nunit_ctas = 0;
 };
 
+// Which entropy decoder takes the batch.  The segment path runs one long dependent chain per
+// segment: its time is ~47 ns per byte of the LONGEST segment whatever the batch holds, while the
+// self-synchronising path costs ~0.04 ns per byte of the WHOLE batch (measured, profiles/).  So the
+// segment path wins once the batch holds >= ~1200 segments' worth of its longest segment.
+constexpr int64_t kSegPathRatio = 1200;
+enum { kForceAuto = 0, kForceSegment = 1, kForceSync = 2 };
+inline int choose_path(const b200jpeg_image_desc *descs, int n, int force) {
+  if (force == kForceSegment) return kPathSegment;
+  if (force == kForceSync) return kPathSync;
+  int64_t total = 0, longest = 1;
+  for (int i = 0; i < n; ++i) {
+    const b200jpeg_image_desc &d = descs[i];
+    const int hs = d.numComponents == 1 ? 1 : d.horizontalSamplingFactor, vs = d.numComponents == 1 ? 1 : d.verticalSamplingFactor;
+    if (hs < 1 || vs < 1) return kPathSync;
+    const int64_t mcus = (int64_t)((d.mcuWidth + hs - 1) / hs) * ((d.mcuHeight + vs - 1) / vs);
+    const int64_t nseg = d.restartInterval > 0 ? (mcus + d.restartInterval - 1) / d.restartInterval : 1;
+    total += d.scan_length;
+    const int64_t unit = d.scan_length / (nseg > 0 ? nseg : 1) + 1;
+    if (unit > longest) longest = unit;
+  }
+  return total >= kSegPathRatio * longest ? kPathSegment : kPathSync;
+}
+
 // Build the plan.  Returns 0 or a B200JPEG_E_* code.
-inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file_sizes, BatchPlan &P) {
+inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file_sizes, BatchPlan &P, int force_path = kForceAuto) {
   P = BatchPlan();
   P.n = n;
+  P.path = choose_path(descs, n, force_path);
   P.imgs.resize(n);
   P.tile_base.assign(n + 1, 0);
   P.cta_base.assign(n + 1, 0);
@@ -191,7 +221,8 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     im.seg_base = seg_base; seg_base += im.nseg + 1;
     im.ntiles = (int)((d.scan_length + kUTile - 1) / kUTile);
     im.tile_base = P.tile_base[i]; P.tile_base[i + 1] = im.tile_base + im.ntiles;
-    im.nsub_max = (int)(((int64_t)d.scan_length * 8 + kSubBits - 1) / kSubBits);
+    im.path = P.path;
+    im.nsub_max = P.path == kPathSync ? (int)(((int64_t)d.scan_length * 8 + kSubBits - 1) / kSubBits) : 0;
     im.ncta = (im.nsub_max + kCT - 1) / kCT;
     im.sub_base = sub_base; sub_base += im.ncta * kCT;
     im.cta_base = P.cta_base[i]; P.cta_base[i + 1] = im.cta_base + im.ncta;
@@ -231,6 +262,22 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     u.magic_tpi = (((uint64_t)1 << 40) + (uint64_t)tpi - 1) / (uint64_t)tpi;
     u.magic_tpr = (((uint64_t)1 << 40) + (uint64_t)tpr - 1) / (uint64_t)tpr;
     u.coef_base0 = a.coef_base; u.coef_stride = cstride; u.rgb_off0 = a.rgb_off; u.rgb_stride = rstride;
+  }
+  if (P.path == kPathSegment) {                       // units grouped by table set; every CTA sees one set
+    std::vector<int> order(n);
+    for (int i = 0; i < n; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return P.imgs[a].tset < P.imgs[b].tset; });
+    int cur_set = -1;
+    for (int oi = 0; oi < n; ++oi) {
+      const ImageDev &im = P.imgs[order[oi]];
+      if (im.tset != cur_set) {
+        while (P.units.size() % kSegThreads) P.units.push_back(make_uint2(kSegNoUnit, 0));
+        cur_set = im.tset;
+      }
+      for (int k = 0; k < im.nseg; ++k) P.units.push_back(make_uint2((uint32_t)order[oi], (uint32_t)k));
+    }
+    while (P.units.size() % kSegThreads) P.units.push_back(make_uint2(kSegNoUnit, 0));
+    P.nunit_ctas = (int)(P.units.size() / kSegThreads);
   }
   P.raw_bytes = raw_off; P.rgb_bytes = rgb_off; P.nblocks = coef_base;
   P.ntiles = P.tile_base[n]; P.nctas = P.cta_base[n]; P.nsubs = sub_base; P.nsegs = seg_base;

@@ -16,6 +16,8 @@ struct Pipeline {
   DevBuf d_raw, d_us, d_imgs, d_tsets, d_out, d_tile_base, d_cta_base, d_tile_cnt, d_tile_pre, d_seg;
   DevBuf d_sub_e, d_sub_used, d_sub_info, d_cta_tot, d_cta_pre, d_bnd[2], d_flags, d_coef, d_rgb, d_export;
   DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
+  DevBuf d_units, d_luts;
+  int force_path = kForceAuto;
   std::vector<ImageOut> h_out;
   std::vector<uint32_t> h_flags;
   int launches = 0, sync_rounds = 0;
@@ -30,7 +32,7 @@ struct Pipeline {
   void destroy() {
     DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_cta_base, &d_tile_cnt, &d_tile_pre,
                      &d_seg, &d_sub_e, &d_sub_used, &d_sub_info, &d_cta_tot, &d_cta_pre, &d_bnd[0], &d_bnd[1],
-                     &d_flags, &d_coef, &d_rgb, &d_export};
+                     &d_flags, &d_coef, &d_rgb, &d_export, &d_units, &d_luts};
     for (DevBuf *b : all) b->destroy(be);
     for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
   }
@@ -39,12 +41,14 @@ struct Pipeline {
   int prepare(const b200jpeg_image_desc *descs, int n, const uint8_t *const *files, const size_t *sizes) {
     prepared = ran = false;
     if (n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
-    const int rc = make_plan(descs, n, sizes, plan);
+    const int rc = make_plan(descs, n, sizes, plan, force_path);
     if (rc) return rc;
     const BatchPlan &P = plan;
     bool ok = true;
     ok &= d_raw.reserve(be, P.raw_bytes + 1024);
-    ok &= d_us.reserve(be, P.raw_bytes + (size_t)kChunkWords * 4 + 1024);
+    if (P.path == kPathSync) ok &= d_us.reserve(be, P.raw_bytes + (size_t)kChunkWords * 4 + 1024);
+    ok &= d_luts.reserve(be, sizeof(uint32_t) * (size_t)kHTabsPerSet * kHTab * P.tsets.size());
+    if (!P.units.empty()) ok &= d_units.reserve(be, sizeof(uint2) * P.units.size());
     ok &= d_imgs.reserve(be, sizeof(ImageDev) * n);
     ok &= d_tsets.reserve(be, sizeof(TableSet) * P.tsets.size());
     ok &= d_out.reserve(be, sizeof(ImageOut) * n);
@@ -87,6 +91,7 @@ struct Pipeline {
     be.h2d(d_tsets.p, P.tsets.data(), sizeof(TableSet) * P.tsets.size());
     be.h2d(d_tile_base.p, P.tile_base.data(), 4 * (size_t)(n + 1));
     be.h2d(d_cta_base.p, P.cta_base.data(), 4 * (size_t)(n + 1));
+    if (!P.units.empty()) { be.h2d(d_units.p, P.units.data(), sizeof(uint2) * P.units.size()); h2d_bytes += (int64_t)(sizeof(uint2) * P.units.size()); }
     h2d_bytes += (int64_t)(sizeof(ImageDev) * n + sizeof(TableSet) * P.tsets.size() + 8 * (size_t)(n + 1));
     for (int f = 0; f < PF_COUNT; ++f) if (!P.grp_img[f].empty()) {
       be.h2d(d_grp_img[f].p, P.grp_img[f].data(), 4 * P.grp_img[f].size());
@@ -148,6 +153,10 @@ struct Pipeline {
               P.nslots_max);
     ++launches;
     mark(3);
+    launch_pixels();
+  }
+
+  void launch_pixels() {
     launch_pixel<1, 1, 3>(PF_444);
     launch_pixel<2, 1, 3>(PF_422);
     launch_pixel<1, 2, 3>(PF_440);
@@ -167,6 +176,37 @@ struct Pipeline {
     be.fill(d_flags.p, 0, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
     B2_LAUNCH(k_reset_out, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n);
     ++launches;
+    B2_LAUNCH(k_build_luts, (int)P.tsets.size() * kHTabsPerSet, 256, 0, be.stream, d_tsets.as<TableSet>(), d_luts.as<uint32_t>());
+    ++launches;
+    if (P.path == kPathSegment) {
+      // marker pass over the raw bytes: segment starts, EOI, illegal markers (no unstuffed copy is made)
+      if (P.ntiles > 0) {
+        B2_LAUNCH(k_mark_count, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
+                  P.n, d_raw.as<uint8_t>(), d_tile_cnt.as<uint32_t>(), d_out.as<ImageOut>());
+        B2_LAUNCH(k_unstuff_scan, (P.n + 7) / 8, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n,
+                  d_tile_cnt.as<uint32_t>(), d_tile_pre.as<uint2>());
+        B2_LAUNCH(k_mark_scatter, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
+                  P.n, d_raw.as<uint8_t>(), d_tile_pre.as<uint2>(), d_seg.as<uint32_t>(), d_out.as<ImageOut>());
+        launches += 3;
+      }
+      B2_LAUNCH(k_mark_finish, (P.n + 255) / 256, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n, d_seg.as<uint32_t>(),
+                d_out.as<ImageOut>());
+      ++launches;
+      mark(1);
+      mark(2);
+      if (P.nunit_ctas > 0) {
+        B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream, d_units.as<uint2>(),
+                  d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(), d_seg.as<uint32_t>(),
+                  d_raw.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>());
+        ++launches;
+      }
+      mark(3);
+      launch_pixels();
+      mark(5);
+      be.check("kernel launch");
+      ran = true;
+      return be.ok() ? 0 : B200JPEG_E_CUDA;
+    }
     if (P.ntiles > 0) {
       B2_LAUNCH(k_unstuff_count, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
                 P.n, d_raw.as<uint8_t>(), d_tile_cnt.as<uint32_t>(), d_out.as<ImageOut>());
@@ -208,7 +248,7 @@ struct Pipeline {
       be.d2h(h_flags.data(), d_flags.p, 4 * h_flags.size());
       be.sync();
       if (!be.ok()) return B200JPEG_E_CUDA;
-      if (P.nctas == 0 || h_flags[k] == 0) break;
+      if (P.path != kPathSync || P.nctas == 0 || h_flags[k] == 0) break;
       if (k + 1 >= kFixLaunches + kMaxExtraFix) {
         B2_LAUNCH(k_raise_status, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n, (uint32_t)ST_NOT_CONVERGED);
         break;

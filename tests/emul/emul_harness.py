@@ -34,7 +34,7 @@ def _load(stress=False):
     return _libs[stress]
 
 
-def decode(datas, flags=0, want_coef=True, stress=False):
+def decode(datas, flags=0, want_coef=True, stress=False, path=0):
     """Same contract as jpeg_decoder_b200.Decoder.decode, run on the emulation.
     stress=True: the build with 512-bit subs and no run-in (exercises the repair/fix paths)."""
     L = _load(stress)
@@ -52,7 +52,8 @@ def decode(datas, flags=0, want_coef=True, stress=False):
     prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
     pco = (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None
     st = (C.c_int32 * n)()
-    info = (C.c_int32 * 2)()
+    info = (C.c_int32 * 3)()
+    info[2] = path
     rc = L.emu_decode_batch(descs, n, files, sizes, prgb, pco, st, info)
     if rc:
         raise RuntimeError("emu_decode_batch rc=%d" % rc)

@@ -8,8 +8,9 @@
 
 extern "C" int emu_decode_batch(const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
                                 const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out,
-                                int32_t *status, int32_t *info /* [0]=launches [1]=sync_rounds */) {
+                                int32_t *status, int32_t *info /* out [0]=launches [1]=sync_rounds, in [2]=entropy path */) {
   b2::Pipeline P;
+  if (info) P.force_path = info[2];      // in: 0 auto, 1 segment path, 2 self-synchronising path
   int rc = P.prepare(descs, n, files, sizes);
   if (rc) return rc;
   rc = P.run();

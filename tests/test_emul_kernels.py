@@ -7,8 +7,9 @@ import pytest
 from tests.conftest import fixture_bytes
 
 
-def check(emul, oracle_mod, datas, flags=0, stress=False):
-    st, rgbs, coefs, info = emul.decode(datas, flags=flags, stress=stress)
+def check(emul, oracle_mod, datas, flags=0, stress=False, path=2):
+    """path: 2 = self-synchronising entropy decoder, 1 = segment-parallel decoder (b200jpeg.h)."""
+    st, rgbs, coefs, info = emul.decode(datas, flags=flags, stress=stress, path=path)
     for i, d in enumerate(datas):
         rc, _, oc, orgb = oracle_mod.port_decode(d, flags=flags)
         assert rc == 0 and st[i] == 0, (i, rc, st[i])
@@ -31,6 +32,32 @@ def test_mixed_batch_all_formats(emul, oracle_mod, harness):
              (17, 9, 90, 2, 2, 0, 1), (300, 200, 50, 1, 1, 1, 0), (300, 200, 90, 1, 1, 1, 5)]
     datas = [harness.synth_jpeg(100 + i, *c) for i, c in enumerate(cases)]
     check(emul, oracle_mod, datas, flags=1)
+
+
+def test_segment_path_all_formats_and_fixtures(emul, oracle_mod, harness):
+    # one thread per restart segment, straight from the stuffed bytes (kernels_segdec.cuh): RSTn every MCU row,
+    # every 3/5/7 MCUs, none at all; optimised tables with long codes (fixtures); grey; odd sizes
+    cases = [(64, 64, 90, 2, 2, 0, 0), (200, 120, 90, 2, 2, 0, -1), (200, 120, 90, 2, 1, 0, 7),
+             (200, 120, 75, 1, 2, 0, 3), (123, 77, 95, 1, 1, 0, 0), (8, 8, 50, 2, 2, 0, 0), (1, 1, 90, 1, 1, 0, 0),
+             (17, 9, 90, 2, 2, 0, 1), (300, 200, 50, 1, 1, 1, 0), (300, 200, 90, 1, 1, 1, 5)]
+    datas = [harness.synth_jpeg(100 + i, *c) for i, c in enumerate(cases)]
+    datas += [fixture_bytes("img2.jpg"), fixture_bytes("img4.jpg")]
+    info = check(emul, oracle_mod, datas, flags=1, path=1)
+    assert info["sync_rounds"] == 0
+
+
+def test_segment_path_flags_corrupt_streams(emul, harness):
+    from jpeg_decoder_b200 import abi
+    good = bytearray(harness.synth_jpeg(41, 160, 96, 85, 2, 2, False, -1))
+    body = good.find(b"\xff\xda") + 14
+    a = bytearray(good); a[-2:] = b"\x00\x00"
+    b = bytearray(good); b[body + 40:body + 42] = b"\xff\xc4"
+    c = bytearray(good); k = c.find(b"\xff\xd1", body); c[k:k + 2] = b"\x12\x34"
+    e = bytearray(good); e[body + 100:body + 140] = bytes(40)
+    st, rgbs, _, _ = emul.decode([bytes(good), bytes(a), bytes(b), bytes(c), bytes(e), bytes(good)], path=1)
+    assert st[0] == 0 and st[5] == 0
+    assert st[1] & abi.ST_NO_EOI and st[2] & abi.ST_BAD_MARKER and st[3] & abi.ST_BAD_RST_COUNT
+    assert np.array_equal(rgbs[0], rgbs[5])
 
 
 def test_multi_cta_scan_without_restart(emul, oracle_mod, harness):

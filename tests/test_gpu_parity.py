@@ -15,10 +15,14 @@ FIXTURES = ["img.jpg", "img2.jpg", "img3.jpg", "img4.jpg", "img5.jpg", "img6.jpg
 RGB_TOL = 1   # LSB per channel, north_star
 
 
-@pytest.fixture(scope="module")
-def dec(lib_so):
+@pytest.fixture(scope="module", params=["sync", "segment"])
+def dec(lib_so, request):
+    """Every parity test runs through BOTH entropy decoders: the self-synchronising path
+    (kernels_entropy.cuh) and the one-thread-per-restart-segment path (kernels_segdec.cuh)."""
     import jpeg_decoder_b200 as jd
+    from jpeg_decoder_b200 import abi
     d = jd.Decoder(0)
+    d.set_entropy_path(abi.ENTROPY_SYNC if request.param == "sync" else abi.ENTROPY_SEGMENT)
     yield d
     d.close()
 
