@@ -93,7 +93,6 @@ B2_GLOBAL void k_unstuff_count(const ImageDev *__restrict__ imgs, const int32_t 
   __syncthreads();
   const int i = s_img;
   const ImageDev im = imgs[i];
-  if (im.path != kPathSync) return;      // the segment path has its own marker pass (kernels_segdec.cuh)
   const uint32_t pos = ((uint32_t)blockIdx.x - (uint32_t)im.tile_base) * kUTile + threadIdx.x * kUBytesPerThread;
   UClass c;
   u_classify(d_raw + im.raw_off, pos, im.raw_len, c);
@@ -136,7 +135,6 @@ B2_GLOBAL void k_unstuff_scatter(const ImageDev *__restrict__ imgs, const int32_
   __syncthreads();
   const int i = s_img;
   const ImageDev im = imgs[i];
-  if (im.path != kPathSync) return;
   const uint32_t pos = ((uint32_t)blockIdx.x - (uint32_t)im.tile_base) * kUTile + threadIdx.x * kUBytesPerThread;
   UClass c;
   u_classify(d_raw + im.raw_off, pos, im.raw_len, c);
@@ -164,7 +162,7 @@ B2_GLOBAL void k_unstuff_scatter(const ImageDev *__restrict__ imgs, const int32_
 B2_GLOBAL void k_unstuff_finish(const ImageDev *__restrict__ imgs, int nimg, uint32_t *__restrict__ seg_start,
                                 ImageOut *__restrict__ out) {
   const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
-  if (i >= nimg || imgs[i].path != kPathSync) return;
+  if (i >= nimg) return;
   ImageOut o = out[i];
   uint32_t st = o.status;
   if (o.end_pos == kNone) st |= ST_NO_EOI;

@@ -271,13 +271,13 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     for (int oi = 0; oi < n; ++oi) {
       const ImageDev &im = P.imgs[order[oi]];
       if (im.tset != cur_set) {
-        while (P.units.size() % kSegThreads) P.units.push_back(make_uint2(kSegNoUnit, 0));
+        while (P.units.size() % kSegUnits) P.units.push_back(make_uint2(kSegNoUnit, 0));
         cur_set = im.tset;
       }
       for (int k = 0; k < im.nseg; ++k) P.units.push_back(make_uint2((uint32_t)order[oi], (uint32_t)k));
     }
-    while (P.units.size() % kSegThreads) P.units.push_back(make_uint2(kSegNoUnit, 0));
-    P.nunit_ctas = (int)(P.units.size() / kSegThreads);
+    while (P.units.size() % kSegUnits) P.units.push_back(make_uint2(kSegNoUnit, 0));
+    P.nunit_ctas = (int)(P.units.size() / kSegUnits);
   }
   P.raw_bytes = raw_off; P.rgb_bytes = rgb_off; P.nblocks = coef_base;
   P.ntiles = P.tile_base[n]; P.nctas = P.cta_base[n]; P.nsubs = sub_base; P.nsegs = seg_base;

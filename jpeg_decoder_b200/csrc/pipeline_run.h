@@ -46,7 +46,7 @@ struct Pipeline {
     const BatchPlan &P = plan;
     bool ok = true;
     ok &= d_raw.reserve(be, P.raw_bytes + 1024);
-    if (P.path == kPathSync) ok &= d_us.reserve(be, P.raw_bytes + (size_t)kChunkWords * 4 + 1024);
+    ok &= d_us.reserve(be, P.raw_bytes + (size_t)kChunkWords * 4 + 1024);
     ok &= d_luts.reserve(be, sizeof(uint32_t) * (size_t)kHTabsPerSet * kHTab * P.tsets.size());
     if (!P.units.empty()) ok &= d_units.reserve(be, sizeof(uint2) * P.units.size());
     ok &= d_imgs.reserve(be, sizeof(ImageDev) * n);
@@ -178,35 +178,6 @@ struct Pipeline {
     ++launches;
     B2_LAUNCH(k_build_luts, (int)P.tsets.size() * kHTabsPerSet, 256, 0, be.stream, d_tsets.as<TableSet>(), d_luts.as<uint32_t>());
     ++launches;
-    if (P.path == kPathSegment) {
-      // marker pass over the raw bytes: segment starts, EOI, illegal markers (no unstuffed copy is made)
-      if (P.ntiles > 0) {
-        B2_LAUNCH(k_mark_count, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
-                  P.n, d_raw.as<uint8_t>(), d_tile_cnt.as<uint32_t>(), d_out.as<ImageOut>());
-        B2_LAUNCH(k_unstuff_scan, (P.n + 7) / 8, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n,
-                  d_tile_cnt.as<uint32_t>(), d_tile_pre.as<uint2>());
-        B2_LAUNCH(k_mark_scatter, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
-                  P.n, d_raw.as<uint8_t>(), d_tile_pre.as<uint2>(), d_seg.as<uint32_t>(), d_out.as<ImageOut>());
-        launches += 3;
-      }
-      B2_LAUNCH(k_mark_finish, (P.n + 255) / 256, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n, d_seg.as<uint32_t>(),
-                d_out.as<ImageOut>());
-      ++launches;
-      mark(1);
-      mark(2);
-      if (P.nunit_ctas > 0) {
-        B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream, d_units.as<uint2>(),
-                  d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(), d_seg.as<uint32_t>(),
-                  d_raw.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>());
-        ++launches;
-      }
-      mark(3);
-      launch_pixels();
-      mark(5);
-      be.check("kernel launch");
-      ran = true;
-      return be.ok() ? 0 : B200JPEG_E_CUDA;
-    }
     if (P.ntiles > 0) {
       B2_LAUNCH(k_unstuff_count, P.ntiles, kUThreads, 0, be.stream, d_imgs.as<ImageDev>(), d_tile_base.as<int32_t>(),
                 P.n, d_raw.as<uint8_t>(), d_tile_cnt.as<uint32_t>(), d_out.as<ImageOut>());
@@ -221,6 +192,21 @@ struct Pipeline {
               d_out.as<ImageOut>());
     ++launches;
     mark(1);
+    if (P.path == kPathSegment) {
+      mark(2);
+      if (P.nunit_ctas > 0) {
+        B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream, d_units.as<uint2>(),
+                  d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(), d_seg.as<uint32_t>(),
+                  d_us.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>());
+        ++launches;
+      }
+      mark(3);
+      launch_pixels();
+      mark(5);
+      be.check("kernel launch");
+      ran = true;
+      return be.ok() ? 0 : B200JPEG_E_CUDA;
+    }
     if (P.nctas > 0) {
       const size_t smem = entropy_smem_bytes(P.nslots_max, false);
       B2_LAUNCH((k_entropy_sync<true>), P.nctas, kCT, smem, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(),

@@ -42,6 +42,16 @@ B2_DEVICE uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
   return r;
 }
 
+// ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass the register file ----
+B2_DEVICE void b2_cp_async16(void *dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
+}
+B2_DEVICE void b2_cp_async4(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
+}
+B2_DEVICE void b2_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> B2_DEVICE void b2_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // ---- TMA 1-D bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier, the sm_90+/sm_100 async-copy path ----
 B2_DEVICE uint32_t b2_smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 B2_DEVICE void b2_mbar_init(uint64_t *bar, uint32_t count) {

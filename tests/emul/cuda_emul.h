@@ -245,6 +245,10 @@ static inline void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint
   memcpy(dst, src, bytes);
   __atomic_fetch_add(bar, (uint64_t)1, __ATOMIC_SEQ_CST);
 }
+static inline void b2_cp_async16(void *dst, const void *src) { memcpy(dst, src, 16); }
+static inline void b2_cp_async4(void *dst, const void *src) { memcpy(dst, src, 4); }
+static inline void b2_cp_async_commit() {}
+template <int N> static inline void b2_cp_async_wait() {}
 static inline void b2_bulk_store(void *dst, const void *src, uint32_t bytes) { memcpy(dst, src, bytes); }
 static inline void b2_bulk_commit() {}
 static inline void b2_bulk_wait_read() {}
