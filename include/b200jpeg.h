@@ -174,12 +174,14 @@ int b200jpeg_sync(b200jpeg_ctx *ctx);
 int b200jpeg_device_rgb(b200jpeg_ctx *ctx, int i, void **dev_ptr, size_t *pitch_bytes);
 void *b200jpeg_stream(b200jpeg_ctx *ctx);   /* cudaStream_t */
 
-/* Counters of the current batch. */
+/* Counters of the current batch (after b200jpeg_decode_batch: summed over its chunks). */
 typedef struct {
   int64_t images, pixels, scan_bytes, coded_blocks, rgb_bytes;
   int64_t h2d_bytes, d2h_bytes;
   int32_t kernel_launches;      /* kernels launched by the last b200jpeg_batch_run */
   int32_t sync_rounds;          /* fix launches the last run needed */
+  int32_t entropy_path;         /* decoder that took the batch: 0 self-synchronising, 1 segment-parallel */
+  int32_t reserved;
 } b200jpeg_batch_stats;
 int b200jpeg_batch_get_stats(const b200jpeg_ctx *ctx, b200jpeg_batch_stats *stats);
 

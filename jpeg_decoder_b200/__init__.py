@@ -121,6 +121,17 @@ class Decoder:
     def stream(self):
         return self.lib.b200jpeg_stream(self.h)
 
+    def decode_batch(self, descs, bufs, rgbs):
+        """b200jpeg_decode_batch: whole files in host memory in, RGB in host memory out, one call
+        (chunked and double-buffered inside the library).  Returns the per-image status list."""
+        n = len(bufs)
+        files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+        prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
+        st = (C.c_int32 * n)()
+        self._check(self.lib.b200jpeg_decode_batch(self.h, descs, n, files, sizes, prgb, None, st), "decode_batch")
+        return list(st)
+
     # ---- one-call API -----------------------------------------------------------------------
     def decode(self, datas, flags=abi.PARSE_REFERENCE, want_coef=False):
         """datas: list of bytes.  Returns (status list, rgb arrays [H,W,3], coef arrays or None);

@@ -62,7 +62,8 @@ class ImageDesc(C.Structure):
 class BatchStats(C.Structure):
     _fields_ = [("images", C.c_int64), ("pixels", C.c_int64), ("scan_bytes", C.c_int64),
                 ("coded_blocks", C.c_int64), ("rgb_bytes", C.c_int64), ("h2d_bytes", C.c_int64),
-                ("d2h_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("sync_rounds", C.c_int32)]
+                ("d2h_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("sync_rounds", C.c_int32),
+                ("entropy_path", C.c_int32), ("reserved", C.c_int32)]
 
 
 # every symbol include/b200jpeg.h declares
@@ -71,7 +72,7 @@ EXPORTS = [
     "b200jpeg_decode_batch", "b200jpeg_batch_prepare", "b200jpeg_batch_run", "b200jpeg_batch_fetch",
     "b200jpeg_sync", "b200jpeg_device_rgb", "b200jpeg_stream", "b200jpeg_batch_get_stats",
     "b200jpeg_set_timing", "b200jpeg_last_timing", "b200jpeg_host_alloc", "b200jpeg_host_free",
-    "b200jpeg_abi_version",
+    "b200jpeg_abi_version", "b200jpeg_set_entropy_path",
 ]
 
 

@@ -6,7 +6,10 @@
 
 struct b200jpeg_ctx {
   int device = 0;
-  b2::Pipeline pipe;
+  b2::Pipeline pipe;         // the batch of prepare / run / fetch; even chunks of decode_batch
+  b2::Pipeline pipe2;        // odd chunks of decode_batch (own stream and arenas)
+  bool agg_valid = false;    // counters of the last pipelined decode_batch
+  b200jpeg_batch_stats agg;
   std::string last_error;
 };
 
@@ -27,8 +30,13 @@ bool setup_pixel(b200jpeg_ctx *c, int f, int sms) {
   int per_sm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2::k_pixel<HS, VS, NC>, b2::kPixThreads, smem);
   if (e != cudaSuccess || per_sm < 1) { c->last_error = "k_pixel does not fit on an SM"; return false; }
-  c->pipe.pix_grid_cap[f] = per_sm * sms;
+  c->pipe.pix_grid_cap[f] = c->pipe2.pix_grid_cap[f] = per_sm * sms;
   return true;
+}
+
+int fail2(b200jpeg_ctx *c, b2::Pipeline &p, int rc) {
+  if (rc == B200JPEG_E_CUDA && !p.be.err.empty()) c->last_error = p.be.err;
+  return rc;
 }
 
 int fail(b200jpeg_ctx *c, int rc) {
@@ -61,7 +69,8 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
     return B200JPEG_E_CUDA;
   }
   if (cudaStreamCreateWithFlags(&c->pipe.be.stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return B200JPEG_E_CUDA; }
-  for (int i = 0; i <= B200JPEG_T_COUNT; ++i) cudaEventCreate(&c->pipe.ev[i]);
+  if (cudaStreamCreateWithFlags(&c->pipe2.be.stream, cudaStreamNonBlocking) != cudaSuccess) { b200jpeg_destroy(c); return B200JPEG_E_CUDA; }
+  for (int i = 0; i <= B200JPEG_T_COUNT; ++i) { cudaEventCreate(&c->pipe.ev[i]); cudaEventCreate(&c->pipe2.ev[i]); }
   const size_t es = b2::entropy_smem_bytes(b2::kMaxSlots, true);
   bool ok = allow_smem(b2::k_entropy_sync<true>, es, c->last_error) && allow_smem(b2::k_entropy_sync<false>, es, c->last_error) &&
             allow_smem(b2::k_entropy_write, es, c->last_error) &&
@@ -77,10 +86,12 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
 void b200jpeg_destroy(b200jpeg_ctx *c) {
   if (!c) return;
   DeviceGuard g(c->device);
-  if (c->pipe.be.stream) cudaStreamSynchronize(c->pipe.be.stream);
-  c->pipe.destroy();
-  for (int i = 0; i <= B200JPEG_T_COUNT; ++i) if (c->pipe.ev[i]) cudaEventDestroy(c->pipe.ev[i]);
-  if (c->pipe.be.stream) cudaStreamDestroy(c->pipe.be.stream);
+  for (b2::Pipeline *p : {&c->pipe, &c->pipe2}) {
+    if (p->be.stream) cudaStreamSynchronize(p->be.stream);
+    p->destroy();
+    for (int i = 0; i <= B200JPEG_T_COUNT; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
+    if (p->be.stream) cudaStreamDestroy(p->be.stream);
+  }
   delete c;
 }
 
@@ -91,6 +102,7 @@ int b200jpeg_batch_prepare(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, in
   if (!c) return B200JPEG_E_ARG;
   DeviceGuard g(c->device);
   c->pipe.be.err.clear();
+  c->agg_valid = false;
   return fail(c, c->pipe.prepare(descs, n, files, sizes));
 }
 
@@ -113,13 +125,64 @@ int b200jpeg_sync(b200jpeg_ctx *c) {
   return fail(c, c->pipe.be.ok() ? 0 : B200JPEG_E_CUDA);
 }
 
+// Host buffers in, host buffers out.  Large batches are cut into chunks that alternate between two
+// pipelines (own stream, own arenas): while chunk k's RGB travels device -> host, chunk k+1's files
+// travel host -> device and its kernels run, so the call is bounded by the slower PCIe direction
+// instead of the sum of copy + decode + copy.
 int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
                           const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
-  int rc = b200jpeg_batch_prepare(c, descs, n, files, sizes);
-  if (rc) return rc;
-  rc = b200jpeg_batch_run(c);
-  if (rc) return rc;
-  return b200jpeg_batch_fetch(c, rgb_out, coef_out, status);
+  if (!c || n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
+  int chunk = (n + 7) / 8;
+  if (chunk < 8) chunk = 8;
+  if (chunk > 64) chunk = 64;
+  if (coef_out || n <= chunk) {
+    int rc = b200jpeg_batch_prepare(c, descs, n, files, sizes);
+    if (rc) return rc;
+    rc = b200jpeg_batch_run(c);
+    if (rc) return rc;
+    return b200jpeg_batch_fetch(c, rgb_out, coef_out, status);
+  }
+  DeviceGuard g(c->device);
+  b2::Pipeline *slot[2] = {&c->pipe, &c->pipe2};
+  int first[2] = {0, 0};
+  bool busy[2] = {false, false};
+  b200jpeg_batch_stats a;
+  memset(&a, 0, sizeof a);
+  c->pipe2.force_path = c->pipe.force_path;
+  const bool timing0 = c->pipe.timing;     // per-stage event times are a single-batch facility
+  int rc = 0;
+  auto drain = [&](int k) {
+    if (!busy[k]) return 0;
+    busy[k] = false;
+    b2::Pipeline &p = *slot[k];
+    const int r = p.complete(rgb_out ? rgb_out + first[k] : nullptr, status ? status + first[k] : nullptr);
+    a.d2h_bytes += p.d2h_bytes; a.kernel_launches += p.launches; a.sync_rounds += p.sync_rounds;
+    return r ? fail2(c, p, r) : 0;
+  };
+  int k = 0;
+  for (int at = 0; at < n && !rc; at += chunk, k ^= 1) {
+    const int cnt = n - at < chunk ? n - at : chunk;
+    rc = drain(k);
+    if (rc) break;
+    b2::Pipeline &p = *slot[k];
+    p.be.err.clear();
+    p.timing = false;
+    rc = p.prepare(descs + at, cnt, files + at, sizes + at);
+    if (!rc) rc = p.run();
+    if (rc) { rc = fail2(c, p, rc); break; }
+    p.d2h_bytes = 0;
+    p.enqueue_rgb(rgb_out ? rgb_out + at : nullptr);
+    first[k] = at; busy[k] = true;
+    a.entropy_path = p.plan.path;
+    a.images += cnt; a.pixels += p.plan.pixels; a.scan_bytes += p.plan.scan_bytes; a.coded_blocks += p.plan.nblocks;
+    a.h2d_bytes += p.h2d_bytes;
+    for (int i = 0; i < cnt; ++i) a.rgb_bytes += (int64_t)3 * p.plan.imgs[i].width * p.plan.imgs[i].height;
+  }
+  const int r0 = drain(k), r1 = drain(k ^ 1);      // oldest first
+  if (!rc) rc = r0 ? r0 : r1;
+  c->agg = a; c->agg_valid = true;
+  c->pipe.timing = timing0;
+  return rc;
 }
 
 int b200jpeg_device_rgb(b200jpeg_ctx *c, int i, void **dev_ptr, size_t *pitch) {
@@ -133,18 +196,20 @@ void *b200jpeg_stream(b200jpeg_ctx *c) { return c ? (void *)c->pipe.be.stream : 
 
 int b200jpeg_batch_get_stats(const b200jpeg_ctx *c, b200jpeg_batch_stats *s) {
   if (!c || !s) return B200JPEG_E_ARG;
+  if (c->agg_valid) { *s = c->agg; return B200JPEG_OK; }
   const b2::BatchPlan &P = c->pipe.plan;
   s->images = P.n; s->pixels = P.pixels; s->scan_bytes = P.scan_bytes; s->coded_blocks = P.nblocks;
   s->rgb_bytes = 0;
   for (int i = 0; i < P.n; ++i) s->rgb_bytes += (int64_t)3 * P.imgs[i].width * P.imgs[i].height;
   s->h2d_bytes = c->pipe.h2d_bytes; s->d2h_bytes = c->pipe.d2h_bytes;
   s->kernel_launches = c->pipe.launches; s->sync_rounds = c->pipe.sync_rounds;
+  s->entropy_path = P.path; s->reserved = 0;
   return B200JPEG_OK;
 }
 
 int b200jpeg_set_entropy_path(b200jpeg_ctx *c, int mode) {
   if (!c || mode < 0 || mode > 2) return B200JPEG_E_ARG;
-  c->pipe.force_path = mode;
+  c->pipe.force_path = c->pipe2.force_path = mode;
   return B200JPEG_OK;
 }
 

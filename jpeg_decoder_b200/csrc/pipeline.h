@@ -32,6 +32,8 @@ struct Backend {
   bool ok() const { return err.empty(); }
   void *alloc(size_t n) { return calloc(n ? n : 1, 1); }
   void release(void *p) { free(p); }
+  void *host_alloc(size_t n) { return calloc(n ? n : 1, 1); }
+  void host_release(void *p) { free(p); }
   void h2d(void *d, const void *s, size_t n) { memcpy(d, s, n); }
   void d2h(void *d, const void *s, size_t n) { memcpy(d, s, n); }
   void d2h_2d(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h) {
@@ -57,6 +59,13 @@ struct Backend {
     return p;
   }
   void release(void *p) { if (p) cudaFree(p); }
+  void *host_alloc(size_t n) {   // pinned: copies into it are truly asynchronous
+    void *p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, n ? n : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) { fail("cudaHostAlloc", e); return nullptr; }
+    return p;
+  }
+  void host_release(void *p) { if (p) cudaFreeHost(p); }
   void h2d(void *d, const void *s, size_t n) {
     if (!n) return;
     cudaError_t e = cudaMemcpyAsync(d, s, n, cudaMemcpyHostToDevice, stream);
@@ -129,10 +138,11 @@ struct BatchPlan {
 };
 
 // Which entropy decoder takes the batch.  The segment path runs one long dependent chain per
-// segment: its time is ~47 ns per byte of the LONGEST segment whatever the batch holds, while the
-// self-synchronising path costs ~0.04 ns per byte of the WHOLE batch (measured, profiles/).  So the
-// segment path wins once the batch holds >= ~1200 segments' worth of its longest segment.
-constexpr int64_t kSegPathRatio = 1200;
+// segment: its time is ~0.55 us per byte of the LONGEST segment (measured: 4.8 ms for 8.8 KB segments)
+// whatever the batch holds, until the SMs fill up; the self-synchronising path costs ~0.034 us per KiB
+// of the WHOLE batch (5.2 ms for 153 MB).  So the segment path wins once the batch holds >= ~16000
+// segments' worth of its longest segment (profiles/README.md).
+constexpr int64_t kSegPathRatio = 16000;
 enum { kForceAuto = 0, kForceSegment = 1, kForceSync = 2 };
 inline int choose_path(const b200jpeg_image_desc *descs, int n, int force) {
   if (force == kForceSegment) return kPathSegment;

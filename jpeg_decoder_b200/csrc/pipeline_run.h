@@ -18,8 +18,13 @@ struct Pipeline {
   DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
   DevBuf d_units, d_luts;
   int force_path = kForceAuto;
-  std::vector<ImageOut> h_out;
-  std::vector<uint32_t> h_flags;
+  // small results (per-image ImageOut, convergence flags) land in PINNED host memory, copied right behind
+  // the kernels and BEFORE the bulk RGB copies: a pageable read-back would queue behind the other
+  // pipeline's RGB traffic in the D2H engine and stall the host for milliseconds
+  ImageOut *h_out = nullptr;
+  uint32_t *h_flags = nullptr;
+  size_t h_out_cap = 0;
+  bool results_enqueued = false;
   int launches = 0, sync_rounds = 0;
   int pix_grid_cap[PF_COUNT] = {2, 2, 2, 2, 2};   // resident CTAs of k_pixel per format (emulation: 2, so the tile loop is exercised)
   int64_t h2d_bytes = 0, d2h_bytes = 0;
@@ -35,6 +40,24 @@ struct Pipeline {
                      &d_flags, &d_coef, &d_rgb, &d_export, &d_units, &d_luts};
     for (DevBuf *b : all) b->destroy(be);
     for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
+    be.host_release(h_out); be.host_release(h_flags);
+    h_out = nullptr; h_flags = nullptr; h_out_cap = 0;
+  }
+
+  static constexpr size_t kFlagWords = kFixLaunches + kMaxExtraFix + 2;
+  bool reserve_host(int n) {
+    if (!h_flags) h_flags = static_cast<uint32_t *>(be.host_alloc(4 * kFlagWords));
+    if ((size_t)n > h_out_cap) {
+      be.host_release(h_out);
+      h_out_cap = (size_t)n + (size_t)n / 4 + 16;
+      h_out = static_cast<ImageOut *>(be.host_alloc(sizeof(ImageOut) * h_out_cap));
+    }
+    return h_flags && h_out;
+  }
+  void enqueue_small_results() {      // flags + per-image ImageOut, asynchronous
+    be.d2h(h_flags, d_flags.p, 4 * kFlagWords);
+    be.d2h(h_out, d_out.p, sizeof(ImageOut) * plan.n);
+    results_enqueued = true;
   }
 
   // plan + H2D of the scans and descriptors
@@ -71,6 +94,7 @@ struct Pipeline {
       ok &= d_grp_img[f].reserve(be, 4 * P.grp_img[f].size());
       ok &= d_grp_pre[f].reserve(be, 4 * P.grp_pre[f].size());
     }
+    ok &= reserve_host(n);
     if (!ok) return be.ok() ? B200JPEG_E_NOMEM : B200JPEG_E_CUDA;
     h2d_bytes = 0;
     // scans: one copy per image, adjacent source ranges merged into one
@@ -170,6 +194,7 @@ struct Pipeline {
     if (!prepared) return B200JPEG_E_STATE;
     const BatchPlan &P = plan;
     launches = 0; sync_rounds = 0;
+    results_enqueued = false;
     mark(0);
     // ImageOut: end_pos/err_pos = kNone, the rest 0
     be.fill(d_out.p, 0xff, sizeof(ImageOut) * P.n);
@@ -227,24 +252,24 @@ struct Pipeline {
   int finish() {
     if (!ran) return B200JPEG_E_STATE;
     const BatchPlan &P = plan;
-    h_flags.assign(kFixLaunches + kMaxExtraFix + 2, 0);
-    h_out.resize(P.n);
     int k = kFixLaunches - 1;
     for (;;) {
-      be.d2h(h_flags.data(), d_flags.p, 4 * h_flags.size());
+      if (!results_enqueued) enqueue_small_results();
       be.sync();
+      results_enqueued = false;
       if (!be.ok()) return B200JPEG_E_CUDA;
       if (P.path != kPathSync || P.nctas == 0 || h_flags[k] == 0) break;
       if (k + 1 >= kFixLaunches + kMaxExtraFix) {
         B2_LAUNCH(k_raise_status, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n, (uint32_t)ST_NOT_CONVERGED);
+        enqueue_small_results();
+        be.sync();
+        results_enqueued = false;
         break;
       }
       ++k;
       launch_fix(k);
       launch_tail(k);
     }
-    be.d2h(h_out.data(), d_out.p, sizeof(ImageOut) * P.n);
-    be.sync();
 #ifndef B200JPEG_EMU
     if (timing) {
       for (int s = 0; s < 4; ++s) cudaEventElapsedTime(&last_ms[s], ev[s], ev[s + 1]);
@@ -254,12 +279,10 @@ struct Pipeline {
     return be.ok() ? 0 : B200JPEG_E_CUDA;
   }
 
-  int fetch(uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
-    const int rc = finish();
-    if (rc) return rc;
+  // asynchronous D2H of every RGB image on the pipeline's stream (no wait)
+  void enqueue_rgb(uint8_t *const *rgb_out) {
     const BatchPlan &P = plan;
-    d2h_bytes = 0;
-    if (status) for (int i = 0; i < P.n; ++i) status[i] = (int32_t)h_out[i].status;
+    if (!results_enqueued) enqueue_small_results();
     if (rgb_out) for (int i = 0; i < P.n; ++i) if (rgb_out[i]) {
       const ImageDev &im = P.imgs[i];
       const uint8_t *src = d_rgb.as<uint8_t>() + im.rgb_off;
@@ -268,6 +291,27 @@ struct Pipeline {
       else be.d2h_2d(rgb_out[i], row, src, im.rgb_pitch, row, im.height);
       d2h_bytes += (int64_t)(row * im.height);
     }
+  }
+
+  // second half of a pipelined decode: the RGB copies were enqueued right behind the kernels
+  // (enqueue_rgb); wait, and only if the self-synchronising decoder needed more repair rounds than
+  // were launched (rare) copy again after the repair
+  int complete(uint8_t *const *rgb_out, int32_t *status) {
+    const int before = launches;
+    const int rc = finish();
+    if (rc) return rc;
+    if (launches != before) { enqueue_rgb(rgb_out); be.sync(); }
+    if (status) for (int i = 0; i < plan.n; ++i) status[i] = (int32_t)h_out[i].status;
+    return be.ok() ? 0 : B200JPEG_E_CUDA;
+  }
+
+  int fetch(uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+    const int rc = finish();
+    if (rc) return rc;
+    const BatchPlan &P = plan;
+    d2h_bytes = 0;
+    if (status) for (int i = 0; i < P.n; ++i) status[i] = (int32_t)h_out[i].status;
+    enqueue_rgb(rgb_out);
     if (coef_out) for (int i = 0; i < P.n; ++i) if (coef_out[i]) {
       const ImageDev &im = P.imgs[i];
       const size_t bytes = (size_t)P.bwr[i] * P.bhr[i] * 3 * 64 * sizeof(int16_t);

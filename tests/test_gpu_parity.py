@@ -118,3 +118,25 @@ def test_truncated_and_random_garbage_do_not_crash(dec, harness):
         datas.append(bytes(m))
     st, rgbs, _ = dec.decode(datas)
     assert st[0] == 0 and len(rgbs) == 7
+
+
+def test_decode_batch_is_chunked_and_matches_single_batch(dec, harness):
+    # b200jpeg_decode_batch cuts batches of more than 8 images into chunks that alternate between two
+    # pipelines (H2D / kernels / D2H overlap): results must equal the staged single-batch API
+    import ctypes as C
+    from jpeg_decoder_b200 import abi
+    datas = [harness.synth_jpeg(700 + i, 96 + 8 * (i % 5), 64 + 16 * (i % 3), 85, 2, 2, False, -1 if i % 2 else 0) for i in range(21)]
+    st, want, _ = dec.decode(datas)
+    assert st == [0] * len(datas)
+    n = len(datas)
+    bufs = [np.frombuffer(d, dtype=np.uint8) for d in datas]
+    descs = (abi.ImageDesc * n)()
+    for i, b in enumerate(bufs):
+        assert dec.lib.b200jpeg_parse_header(b.ctypes.data, b.size, 0, C.byref(descs[i])) == 0
+    rgbs = [np.zeros_like(w) for w in want]
+    st2 = dec.decode_batch(descs, bufs, rgbs)
+    assert st2 == [0] * n
+    for a, b in zip(want, rgbs):
+        assert np.array_equal(a, b)
+    s = dec.stats()
+    assert s["images"] == n and s["rgb_bytes"] == sum(w.size for w in want) and s["d2h_bytes"] == s["rgb_bytes"]
