@@ -1,0 +1,274 @@
+// b200jpeg.hpp -- C++ host surface over the C ABI (b200jpeg.h), keeping the reference's names.
+//
+// aswanthabam/JPEG_Decoder is one translation unit: class Image (jpeg.cpp:19-914) reads the markers
+// into HuffmanTable (include/huffman.hpp:8-49), QuantizationTable / ColorComponent / MCU
+// (include/types.hpp:32-110) and then runs its private process_image_data() (jpeg.cpp:755-789) on the
+// CPU.  A maintainer who wants the B200 path keeps exactly that surface:
+//
+//   b200jpeg::Image img("picture.jpg");   // Image::Image, jpeg.cpp:797-807 (SOI check)
+//   img.readJPEG();                       // jpeg.cpp:826-907: markers -> tables -> process_image_data()
+//   img.image_width, img.image_height, img.mcuWidthReal, img.mcuHeightReal      // jpeg.cpp:792-795
+//   img.rgb();                            // headless replacement of display() (display.hpp:15-120)
+//   img.mcus();                           // the MCU array after YCbCrToRGB, gathered as display.hpp:19-34 reads it
+//   img.saveToBMP("out.bmp");             // jpeg.cpp:809-816, with the channel order put right
+//
+// Differences, all deliberate: the file is read once into memory (the reference allocates per byte,
+// file.hpp:26-52); errors throw b200jpeg::Error carrying the B200JPEG_E_* code where the reference
+// prints and calls exit(1); process_image_data() runs on the GPU through b200jpeg_decode_batch() and
+// FAILS (throws) when no B200-class device is present -- there is no CPU fallback.
+// Batches: b200jpeg::Image::decode_batch() decodes many files in one call (images are independent, the
+// library chunks and double-buffers them).
+#ifndef B200JPEG_HPP
+#define B200JPEG_HPP
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "b200jpeg.h"
+
+namespace b200jpeg {
+
+struct Error : std::runtime_error {
+  int code;
+  Error(int c, const std::string &what) : std::runtime_error(what + " (b200jpeg error " + std::to_string(c) + ")"), code(c) {}
+};
+
+// include/types.hpp:23-31
+static const int zigZagMap[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                  41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                  30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+// include/huffman.hpp:8-49.  Same members; symbols hold up to 176 entries because read_huffman_table
+// admits that many (jpeg.cpp:177).
+class HuffmanTable {
+ public:
+  unsigned char offset[17] = {0};
+  unsigned char symbols[176] = {0};
+  unsigned int codes[176] = {0};
+  bool set = false;
+  void generateCodes() {                       // huffman.hpp:17-29
+    unsigned int code = 0;
+    for (int i = 0; i < 16; i++) {
+      for (int j = offset[i]; j < offset[i + 1]; j++) codes[j] = code++;
+      code <<= 1;
+    }
+  }
+};
+
+// include/types.hpp:79-110: de-zig-zagged on construction, operator[] in natural order.
+class QuantizationTable {
+  int table[64];
+  int header;
+
+ public:
+  bool set = false;
+  QuantizationTable() : header(0) { std::memset(table, 0, sizeof table); }
+  QuantizationTable(int header_, const unsigned char *raw) : header(header_) {
+    for (int i = 0; i < 64; i++) table[zigZagMap[i]] = (int)raw[i];
+    set = true;
+  }
+  int operator[](int index) const { return table[index]; }
+  int id() const { return header & 15; }
+};
+
+// include/types.hpp:69-77
+struct ColorComponent {
+  int horizontal_sampling_factor = 0;
+  int vertical_sampling_factor = 0;
+  int quantizationTableID = 0;
+  int huffmanDCTTableID = 0;
+  int huffmanACTableID = 0;
+  bool set = false;
+};
+
+// include/types.hpp:32-67: one 8x8 block position; y/cb/cr before YCbCrToRGB, r/g/b after.
+struct MCU {
+  union { int y[64] = {0}; int r[64]; };
+  union { int cb[64] = {0}; int g[64]; };
+  union { int cr[64] = {0}; int b[64]; };
+  int *operator[](int index) { return index == 0 ? y : index == 1 ? cb : index == 2 ? cr : nullptr; }
+};
+
+// One GPU context per device, shared by the Images of a process (b200jpeg_create / _destroy).
+class Context {
+  b200jpeg_ctx *ctx_ = nullptr;
+
+ public:
+  explicit Context(int device = 0) {
+    const int rc = b200jpeg_create(device, &ctx_);
+    if (rc) throw Error(rc, "b200jpeg_create: no usable sm_100 GPU (the decode path has no CPU fallback)");
+  }
+  ~Context() { b200jpeg_destroy(ctx_); }
+  Context(const Context &) = delete;
+  Context &operator=(const Context &) = delete;
+  b200jpeg_ctx *get() const { return ctx_; }
+  static Context &shared() { static Context c(0); return c; }
+};
+
+class Image {
+  std::string filename_;
+  std::vector<uint8_t> file_;          // the whole file, read once
+  b200jpeg_image_desc desc_;           // Image's private state at the seam (jpeg.cpp:21-34)
+  std::vector<uint8_t> rgb_;           // interleaved R,G,B, row-major, top-down
+  std::vector<int16_t> coef_;          // quantised coefficients, MCU-array layout, kept on request
+  int status_ = 0;
+  bool parsed_ = false, decoded_ = false;
+
+  void load_tables() {                 // struct mirror -> the reference's objects
+    for (int t = 0; t < 4; ++t) {
+      const b200jpeg_huffman_table *src[2] = {&desc_.huffmanDCTTable[t], &desc_.huffmanACTable[t]};
+      HuffmanTable *dst[2] = {&huffmanDCTTable[t], &huffmanACTable[t]};
+      for (int k = 0; k < 2; ++k) {
+        std::memcpy(dst[k]->offset, src[k]->offset, 17);
+        std::memcpy(dst[k]->symbols, src[k]->symbols, 176);
+        dst[k]->set = src[k]->set != 0;
+        if (dst[k]->set) dst[k]->generateCodes();
+      }
+      if (desc_.quantization_tables[t].set) {
+        unsigned char raw[64];
+        for (int i = 0; i < 64; ++i) raw[i] = (unsigned char)desc_.quantization_tables[t].table[zigZagMap[i]];
+        quantization_tables[t] = QuantizationTable(t, raw);
+      }
+    }
+    for (int c = 0; c < 3; ++c) {
+      const b200jpeg_component &s = desc_.color_components[c];
+      color_components[c].horizontal_sampling_factor = s.horizontal_sampling_factor;
+      color_components[c].vertical_sampling_factor = s.vertical_sampling_factor;
+      color_components[c].quantizationTableID = s.quantizationTableID;
+      color_components[c].huffmanDCTTableID = s.huffmanDCTTableID;
+      color_components[c].huffmanACTableID = s.huffmanACTableID;
+      color_components[c].set = c < desc_.numComponents;
+    }
+  }
+
+ public:
+  // jpeg.cpp:792-795
+  int image_width = 0, image_height = 0, mcuWidthReal = 0, mcuHeightReal = 0;
+  // jpeg.cpp:22-27 (public here: they are the drop-in seam)
+  QuantizationTable quantization_tables[4];
+  ColorComponent color_components[3];
+  HuffmanTable huffmanDCTTable[4], huffmanACTable[4];
+  int restartInterval = 0;
+  int parse_flags = B200JPEG_PARSE_REFERENCE;   // B200JPEG_PARSE_SPEC: grey scans, COM segments, ...
+  bool keep_coefficients = false;               // also fetch the MCU array after decodeHuffman()
+
+  // Image::Image, jpeg.cpp:797-807
+  explicit Image(const std::string &filename) : filename_(filename) {
+    std::memset(&desc_, 0, sizeof desc_);
+    std::ifstream f(filename, std::ios::binary);
+    if (!f) throw Error(B200JPEG_E_NOT_JPEG, "cannot open " + filename);
+    file_.assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+    if (file_.size() < 2 || file_[0] != 0xff || file_[1] != 0xd8) throw Error(B200JPEG_E_NOT_JPEG, "Invalid JPEG file");
+  }
+  Image(const uint8_t *bytes, size_t n) : filename_("<memory>"), file_(bytes, bytes + n) {
+    std::memset(&desc_, 0, sizeof desc_);
+    if (n < 2 || bytes[0] != 0xff || bytes[1] != 0xd8) throw Error(B200JPEG_E_NOT_JPEG, "Invalid JPEG file");
+  }
+
+  // The marker loop up to SOS (jpeg.cpp:826-867) -- host only, no GPU needed.
+  void readHeaders() {
+    const int rc = b200jpeg_parse_header(file_.data(), file_.size(), parse_flags, &desc_);
+    if (rc) throw Error(rc, "readJPEG: " + filename_);
+    image_width = desc_.image_width; image_height = desc_.image_height;
+    mcuWidthReal = desc_.mcuWidthReal; mcuHeightReal = desc_.mcuHeightReal;
+    restartInterval = desc_.restartInterval;
+    load_tables();
+    parsed_ = true;
+  }
+
+  // jpeg.cpp:755-789, on the GPU: decodeHuffman + dequantize + inverseDCT + YCbCrToRGB.
+  void process_image_data(Context &ctx = Context::shared()) {
+    if (!parsed_) readHeaders();
+    rgb_.assign((size_t)3 * image_width * image_height, 0);
+    const uint8_t *files[1] = {file_.data()};
+    const size_t sizes[1] = {file_.size()};
+    uint8_t *out[1] = {rgb_.data()};
+    int16_t *co[1] = {nullptr};
+    if (keep_coefficients) { coef_.assign((size_t)mcuWidthReal * mcuHeightReal * 3 * 64, 0); co[0] = coef_.data(); }
+    int32_t st = 0;
+    const int rc = b200jpeg_decode_batch(ctx.get(), &desc_, 1, files, sizes, out, keep_coefficients ? co : nullptr, &st);
+    if (rc) throw Error(rc, std::string("process_image_data: ") + b200jpeg_last_error(ctx.get()));
+    status_ = st;
+    if (st) throw Error(B200JPEG_E_STATE, "process_image_data: corrupt scan, status bits " + std::to_string(st));
+    decoded_ = true;
+  }
+
+  // jpeg.cpp:826-907: headers, then the scan (the reference calls process_image_data at SOS, :858-863).
+  void readJPEG(Context &ctx = Context::shared()) { readHeaders(); process_image_data(ctx); }
+
+  // Many images, one call: headers on the host, every scan through ONE b200jpeg_decode_batch()
+  // (images are independent; the library chunks and double-buffers the batch).  Returns the per-image
+  // status words (0 = decoded); images[i]->rgb() holds the pixels.  Nothing throws for a corrupt scan.
+  static std::vector<int> decode_batch(const std::vector<Image *> &images, Context &ctx = Context::shared()) {
+    const int n = (int)images.size();
+    std::vector<b200jpeg_image_desc> descs((size_t)n);
+    std::vector<const uint8_t *> files((size_t)n);
+    std::vector<size_t> sizes((size_t)n);
+    std::vector<uint8_t *> out((size_t)n);
+    std::vector<int32_t> st((size_t)n, 0);
+    for (int i = 0; i < n; ++i) {
+      Image &im = *images[(size_t)i];
+      if (!im.parsed_) im.readHeaders();
+      im.rgb_.assign((size_t)3 * im.image_width * im.image_height, 0);
+      descs[(size_t)i] = im.desc_; files[(size_t)i] = im.file_.data(); sizes[(size_t)i] = im.file_.size(); out[(size_t)i] = im.rgb_.data();
+    }
+    if (n == 0) return std::vector<int>();
+    const int rc = b200jpeg_decode_batch(ctx.get(), descs.data(), n, files.data(), sizes.data(), out.data(), nullptr, st.data());
+    if (rc) throw Error(rc, std::string("decode_batch: ") + b200jpeg_last_error(ctx.get()));
+    for (int i = 0; i < n; ++i) { images[(size_t)i]->status_ = st[(size_t)i]; images[(size_t)i]->decoded_ = st[(size_t)i] == 0; }
+    return std::vector<int>(st.begin(), st.end());
+  }
+
+  const b200jpeg_image_desc &desc() const { return desc_; }
+  const std::vector<uint8_t> &file() const { return file_; }
+  int status() const { return status_; }
+  // Headless display(): interleaved RGB8, pitch 3*image_width (the display.hpp:27-34 gather flattened).
+  const std::vector<uint8_t> &rgb() const { return rgb_; }
+  const std::vector<int16_t> &coefficients() const { return coef_; }
+
+  // The reference's MCU array after YCbCrToRGB (r/g/b planes per block position), rebuilt from rgb().
+  std::vector<MCU> mcus() const {
+    std::vector<MCU> m((size_t)mcuWidthReal * mcuHeightReal);
+    for (int yy = 0; yy < image_height; ++yy)
+      for (int xx = 0; xx < image_width; ++xx) {
+        MCU &b = m[(size_t)(yy / 8) * mcuWidthReal + xx / 8];
+        const uint8_t *p = &rgb_[((size_t)yy * image_width + xx) * 3];
+        const int k = (yy % 8) * 8 + xx % 8;
+        b.r[k] = p[0]; b.g[k] = p[1]; b.b[k] = p[2];
+      }
+    return m;
+  }
+
+  // jpeg.cpp:448-509 / :809-816 with what it gets wrong put right: BITMAPCOREHEADER, bottom-up rows,
+  // B,G,R byte order, rows padded to 4 bytes.
+  void saveToBMP(const std::string &filename) const {
+    if (!decoded_) throw Error(B200JPEG_E_STATE, "saveToBMP before readJPEG");
+    const int pad = (4 - (image_width * 3) % 4) % 4;
+    const uint32_t size = 14 + 12 + (uint32_t)(image_width * 3 + pad) * image_height;
+    std::ofstream o(filename, std::ios::binary);
+    auto put16 = [&](int v) { o.put((char)(v & 255)); o.put((char)((v >> 8) & 255)); };
+    auto put32 = [&](uint32_t v) { put16((int)(v & 0xffff)); put16((int)(v >> 16)); };
+    o.put('B'); o.put('M'); put32(size); put32(0); put32(26);
+    put32(12); put16(image_width); put16(image_height); put16(1); put16(24);
+    for (int yy = image_height - 1; yy >= 0; --yy) {
+      for (int xx = 0; xx < image_width; ++xx) {
+        const uint8_t *p = &rgb_[((size_t)yy * image_width + xx) * 3];
+        o.put((char)p[2]); o.put((char)p[1]); o.put((char)p[0]);
+      }
+      for (int k = 0; k < pad; ++k) o.put(0);
+    }
+  }
+  void savePPM(const std::string &filename) const {
+    if (!decoded_) throw Error(B200JPEG_E_STATE, "savePPM before readJPEG");
+    std::ofstream o(filename, std::ios::binary);
+    o << "P6\n" << image_width << " " << image_height << "\n255\n";
+    o.write(reinterpret_cast<const char *>(rgb_.data()), (std::streamsize)rgb_.size());
+  }
+};
+
+}  // namespace b200jpeg
+#endif

@@ -32,10 +32,26 @@ def build_lib(force=False, verbose=False):
     return LIB_SO
 
 
+CLI_SRC = os.path.join(_HERE, "..", "tools", "b200jpeg_cli.cpp")
+CLI_BIN = os.path.join(_HERE, "b200jpeg")
+
+
+def build_cli(force=False):
+    """tools/b200jpeg_cli.cpp: the reference's main() (jpeg.cpp:916-929) over include/b200jpeg.hpp."""
+    build_lib()
+    inc = os.path.join(_HERE, "..", "include")
+    deps = [CLI_SRC, os.path.join(inc, "b200jpeg.hpp"), os.path.join(inc, "b200jpeg.h"), LIB_SO]
+    if force or _stale(CLI_BIN, deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-o", CLI_BIN, CLI_SRC, "-L" + _HERE, "-lb200jpeg",
+                               "-Wl,-rpath,$ORIGIN"])
+    return CLI_BIN
+
+
 def build_all(force=False, verbose=False):
     from .harness.synth import build_harness
     build_lib(force, verbose)
     build_harness(force)
+    build_cli(force)
 
 
 if __name__ == "__main__":
