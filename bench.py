@@ -116,6 +116,18 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel, images):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json);
+    None when the capture was taken on another batch size or does not hold the kernel."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        k = t["kernels"][kernel]
+        return k["read"] + k["write"] if t["images"] == images else None
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 # ------------------------------------------------------------------ CPU side (oracle as baseline)
 def cpu_reference_run(files, per_worker, workers):
     """Time the reference's own CPU path on `workers` processes, `per_worker` images each.
@@ -182,7 +194,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     import jpeg_decoder_b200 as jd
-    from jpeg_decoder_b200 import abi
+    from jpeg_decoder_b200 import abi, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
@@ -192,7 +204,8 @@ def run_gpu_arm(args, rank, world, local_rank):
     lib = jd.load()
     dec = jd.Decoder(local_rank)
     n = args.images
-    arena, files = make_batch(n, 1000 + rank * n, pinned_alloc=lib.b200jpeg_host_alloc)   # pinned host files
+    seed0, _ = sharding.weak_shard(n, rank)
+    arena, files = make_batch(n, seed0, pinned_alloc=lib.b200jpeg_host_alloc)   # pinned host files
     descs = (abi.ImageDesc * n)()
     for i, b in enumerate(files):
         rc = lib.b200jpeg_parse_header(b.ctypes.data, b.size, 0, C.byref(descs[i]))
@@ -210,11 +223,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         dec.sync()
 
     def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return sharding.max_over_ranks(x, device="cuda")
 
     # ---- device-resident: value ----
     dec.set_timing(True)
@@ -275,7 +284,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         dom = max(("pixel", "entropy_decode"), key=lambda k: kernels[k]["ms"])
         roofline = {"kernel": kernels[dom]["name"], "bound": "hbm",
                     "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kernels[dom]["frac"],
-                    "traffic": None, "peak_source": peak_src,
+                    "traffic": ncu_traffic(kernels[dom]["name"], n), "peak_source": peak_src,
                     "note": "entropy decoding is latency/issue bound (one dependent chain per stream), see DESIGN.md; "
                             "the HBM-bound kernel of the path is the pixel kernel",
                     "pixel_kernel": {"achieved": kernels["pixel"]["gbs"], "frac": kernels["pixel"]["frac"]},

@@ -13,8 +13,8 @@ python bench.py --steps 2 --warmup 1 > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
     python bench.py --steps 2 --warmup 1 > $OUT/ncu_launches.log 2>&1
 echo "ncu launches exit $?"
-python bench.py --steps 1 --warmup 1 --images 64 > $OUT/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'k_pixel|k_entropy|k_unstuff_(count|scatter)|k_seg|k_decode' -c 14 \
-    -o $OUT/prof python bench.py --steps 1 --warmup 1 --images 64 > $OUT/ncu_full.log 2>&1
+python bench.py --steps 1 --warmup 1 > $OUT/plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'k_pixel|k_entropy|k_unstuff_(count|scatter)|k_build_luts' -c 10 \
+    -o $OUT/prof python bench.py --steps 1 --warmup 1 > $OUT/ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT

@@ -11,10 +11,11 @@ import os, sys, torch, torch.distributed as dist
 sys.path.insert(0, os.environ["B2_ROOT"])
 dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
+from jpeg_decoder_b200 import sharding
 n = 256
-seeds = list(range(1000 + rank * n, 1000 + (rank + 1) * n))      # bench.py: seed0 = 1000 + rank*n
-t = torch.tensor([float(rank + 1)], dtype=torch.float64)
-dist.all_reduce(t, op=dist.ReduceOp.MAX)                          # time = max over ranks
+lo, hi = sharding.weak_shard(n, rank)                             # what bench.py decodes on this rank
+seeds = list(range(lo, hi))
+t = torch.tensor([sharding.max_over_ranks(float(rank + 1))], dtype=torch.float64)   # time = max over ranks
 mine = torch.tensor([seeds[0], seeds[-1]], dtype=torch.int64)
 allr = [torch.zeros(2, dtype=torch.int64) for _ in range(world)]
 dist.all_gather(allr, mine)
@@ -36,3 +37,14 @@ def test_weak_scaling_shards_are_disjoint(tmp_path):
                          capture_output=True, text=True, env=env, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "SHARD_OK" in out.stdout
+
+
+def test_shard_range_partitions_any_batch():
+    from jpeg_decoder_b200.sharding import shard_range
+    for total in (0, 1, 7, 256, 16384, 16385):
+        for world in (1, 2, 3, 4, 8):
+            parts = [shard_range(total, r, world) for r in range(world)]
+            assert parts[0][0] == 0 and parts[-1][1] == total
+            assert all(parts[i][1] == parts[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in parts]
+            assert max(sizes) - min(sizes) <= 1
