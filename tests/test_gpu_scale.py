@@ -56,6 +56,15 @@ def test_c3_full_size_properties(dec, harness):
     assert st == [0]
     st2, rgbs2, _ = dec.decode([d, d])
     assert st2 == [0, 0] and np.array_equal(rgbs2[0], rgbs[0]) and np.array_equal(rgbs2[1], rgbs[0])
+    # the same picture encoded WITH restart markers (one per MCU row) carries the same coefficients in a
+    # different bit stream (DC prediction restarts, byte alignment, RSTn): the segment-parallel decoder on it
+    # and the self-synchronising decoder on the marker-free stream must produce identical pixels
+    from jpeg_decoder_b200 import abi
+    dr = harness.synth_jpeg(3001, 8192, 8192, 95, 1, 1, False, -1)
+    dec.set_entropy_path(abi.ENTROPY_SEGMENT)
+    st3, rgbs3, _ = dec.decode([dr])
+    dec.set_entropy_path(abi.ENTROPY_AUTO)
+    assert st3 == [0] and np.array_equal(rgbs3[0], rgbs[0])
     # the decoded picture must resemble the source it was encoded from (q95: high PSNR)
     src = harness.synth_rgb(3001, 8192, 8192)
     mse = np.mean((rgbs[0][::8, ::8].astype(np.float32) - src[::8, ::8].astype(np.float32)) ** 2)
