@@ -186,8 +186,9 @@ typedef struct {
 int b200jpeg_batch_get_stats(const b200jpeg_ctx *ctx, b200jpeg_batch_stats *stats);
 
 /* Entropy decoder of the following batches.  AUTO picks per batch: SEGMENT (one thread per restart
- * segment, decoded in one pass) when the batch holds enough segments to fill the GPU, else SYNC (self-synchronising sub-sequences inside each scan).  Both give identical
- * results; the override exists for tests and measurements. */
+ * segment, one pass) when the batch holds enough segments to fill the GPU, else SYNC (self-synchronising
+ * sub-sequences inside each scan).  Both give identical results; the override exists for tests and
+ * measurements. */
 enum { B200JPEG_ENTROPY_AUTO = 0, B200JPEG_ENTROPY_SEGMENT = 1, B200JPEG_ENTROPY_SYNC = 2 };
 int b200jpeg_set_entropy_path(b200jpeg_ctx *ctx, int mode);
 
