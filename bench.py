@@ -203,6 +203,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = jd.load()
     dec = jd.Decoder(local_rank)
+    dec.set_entropy_path({"auto": abi.ENTROPY_AUTO, "segment": abi.ENTROPY_SEGMENT, "sync": abi.ENTROPY_SYNC}[args.entropy])
     n = args.images
     seed0, _ = sharding.weak_shard(n, rank)
     arena, files = make_batch(n, seed0, pinned_alloc=lib.b200jpeg_host_alloc)   # pinned host files
@@ -322,6 +323,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--images", type=int, default=256, help="images per GPU per step")
+    ap.add_argument("--entropy", default="auto", choices=["auto", "segment", "sync"],
+                    help="entropy decoder (auto = the library's own choice; the others are for measurements)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -1,4 +1,4 @@
-// kernels_segdec.cuh -- stage E, segment-parallel path: one THREAD per restart segment (or per
+// kernels_segdec.cuh -- stage E, segment-parallel path: one lane per restart segment (or per
 // whole scan when the file has no RSTn), decoding the unstuffed scan into the final coefficient
 // blocks in ONE pass.  Replaces, for batches that offer thousands of independently decodable
 // segments, BitStream (file.hpp:122-165) and Image::decodeHuffman / decodeMCUComponent /
@@ -8,20 +8,28 @@
 // Why this shape: a segment starts byte-aligned with the DC predictors reset (jpeg.cpp:419-425)
 // and its first block index is known a priori (k * RI * blocks-per-MCU), so nothing has to be
 // synchronised or prefix-summed -- the self-synchronising path (kernels_entropy.cuh) pays three
-// passes over the stream for that.  The price is one long dependent chain per thread, so the
-// planner only takes this path when the batch has enough segments (pipeline.h, choose_path).
+// passes over the stream for that.  The price is one long dependent chain per lane and, with a few
+// thousand segments per batch, only about one warp per SM sub-partition: the kernel is bound by the
+// LATENCY of that chain (position -> window -> table entry -> position), not by issue slots or memory.
+// Two things follow.
 //
-// What a SIMT Huffman decoder has to avoid is divergence: events that are rare for one lane
-// (bit-buffer refill, end of block) happen in almost every step for SOME lane of a warp, and a
-// branch then costs all 32 lanes.  So every step is made the same for every lane:
+// (1) Every step is the same for every lane.  Events that are rare for one lane (bit-buffer refill,
+//     end of block) happen in almost every step for SOME lane of a warp, and a branch then costs all 32:
 //   * no bit buffer: the 32-bit window is re-read each step from the bit position, out of a
 //     per-lane ring of the next 32 stream words in shared memory laid out [word][lane] (bank =
 //     lane: conflict-free whatever the lanes' positions);
 //   * the ring is topped up by cp.async (LDGSTS, no register in between) under a per-lane
 //     PREDICATE once every four steps -- four steps consume at most 108 bits, one top-up brings 128;
-//   * DC and AC tables are looked up together and selected afterwards;
-//   * finished blocks wait in a per-thread ring of four staged blocks and leave through a
-//     warp-cooperative flush (8 lanes move one 128-byte block), a few times per hundred steps.
+//   * DC and AC tables are looked up together and selected afterwards.
+//
+// (2) Only what the chain needs stays on the chain.  Each DECODER warp is paired with a WRITER warp of
+//     the same CTA.  The decoder walks the codes -- window, table entry, advance, block/table
+//     bookkeeping -- and pushes (window, entry) per lane and step into a shared-memory FIFO; the writer
+//     pops them and does everything that merely CONSUMES a symbol: magnitude extension (jpeg.cpp:335-343,
+//     388-397), DC prediction (jpeg.cpp:344-345), zig-zag placement, the stores, zero-filling the next
+//     block, the range checks.  The two warps run on the idle issue slots of their sub-partitions in
+//     parallel, so the dependent chain per symbol is roughly halved.  Hand-over is a pair of counters
+//     (st.release / ld.acquire in shared memory), one update per round of four steps.
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -30,20 +38,23 @@
 
 namespace b2 {
 
-#ifndef B2_SEG_LANES
-#define B2_SEG_LANES 32
+#ifndef B2_SEG_PAIRS
+#define B2_SEG_PAIRS 2
 #endif
-#ifndef B2_SEG_THREADS
-#define B2_SEG_THREADS 64
+#ifndef B2_SEG_FIFO
+#define B2_SEG_FIFO 8
 #endif
-constexpr int kSegThreads = B2_SEG_THREADS;   // threads per CTA of k_entropy_seg
-constexpr int kSegLanes = B2_SEG_LANES;       // lanes of a warp that take a segment (the rest idle: less divergence per warp, more warps)
-constexpr int kSegUnits = kSegThreads / 32 * kSegLanes;   // segments per CTA
+constexpr int kSegPairs = B2_SEG_PAIRS;       // decoder/writer warp pairs per CTA
+constexpr int kSegThreads = kSegPairs * 64;   // threads per CTA of k_entropy_seg: warps [0,kSegPairs) decode, the rest write
+constexpr int kSegUnits = kSegPairs * 32;     // segments per CTA
 constexpr uint32_t kSegNoUnit = 0xffffffffu;
+constexpr int kSegWords = 32;                 // stream words per lane in the window ring
+constexpr int kSegFifo = B2_SEG_FIFO;         // rounds (of four steps) the FIFO between a decoder and its writer holds
+constexpr int kSegRoundWords = 4 * 2 * 32;    // one round: 4 steps x (window, entry) x 32 lanes
+constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter with the last round
 
-constexpr int kSegWords = 32;            // stream words per lane in the window ring
 B2_HD size_t segdec_smem_bytes() {
-  return sizeof(uint32_t) * (size_t)kHTabsPerSet * kHTab + (size_t)kSegThreads * kSegWords * 4;
+  return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegPairs * (kSegWords * 32 + kSegFifo * kSegRoundWords + 32));
 }
 
 B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:335-343, 388-397; size >= 1
@@ -54,12 +65,35 @@ B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.c
 // Coefficients go straight to global memory: at the start of a block its 128-byte line is zeroed with
 // eight 128-bit stores (MCU[] is value-initialised, jpeg.cpp:407), then every non-zero coefficient is one
 // 2-byte store into that line (same thread, same addresses: program order holds; L2 merges the line).
-// No staging, no flush, no lane waits for another.  Chunk c of block b lives at chunk c ^ (b & 7)
-// (kernels_pixel.cuh).
+// Chunk c of block b lives at chunk c ^ (b & 7) (kernels_pixel.cuh).
 B2_DEVICE void seg_zero_block(int16_t *__restrict__ coef, int64_t gb) {
   uint4 *o = reinterpret_cast<uint4 *>(coef) + gb * 8;
 #pragma unroll
   for (int q = 0; q < 8; ++q) o[q] = make_uint4(0, 0, 0, 0);
+}
+
+// What both warps of a pair know about a lane's segment before the first symbol.
+struct SegLane {
+  bool live;                 // there is something to decode
+  int img, bidx, bend;       // image, first block of the segment, first block past it
+  int bpm, nluma;
+  int64_t gb;                // global index of the first block in the coefficient buffer
+};
+B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, const ImageOut *__restrict__ out) {
+  SegLane L;
+  L.live = false; L.img = 0; L.bidx = L.bend = 0; L.bpm = 1; L.nluma = 1; L.gb = 0;
+  if (unit.x == kSegNoUnit) return L;
+  L.img = (int)unit.x;
+  const ImageDev &im = imgs[L.img];
+  if (out[L.img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) return L;   // nothing to decode
+  const int k = (int)unit.y;
+  L.bpm = im.bpm; L.nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+  const int seg_blocks = im.restart_interval * L.bpm;                                  // 0 when there is one segment
+  L.bidx = k * seg_blocks;
+  L.bend = (k + 1 < im.nseg) ? L.bidx + seg_blocks : im.nblocks;
+  L.gb = im.coef_base + L.bidx;
+  L.live = L.bidx < L.bend;
+  return L;
 }
 
 // units[u] = (image, segment); the units of one CTA share a table set (the planner pads each
@@ -69,9 +103,14 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
               const uint32_t *__restrict__ luts, const uint32_t *__restrict__ seg_start,
               const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef) {
   B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab]
-  uint32_t *ring = lut + kHTabsPerSet * kHTab;                  // [warp][word][lane]
-  const int tid = threadIdx.x, lane = tid & 31;
-  const uint2 unit = lane < kSegLanes ? units[(size_t)blockIdx.x * kSegUnits + (tid >> 5) * kSegLanes + lane] : make_uint2(kSegNoUnit, 0);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool decoder = warp < kSegPairs;
+  const int pair = decoder ? warp : warp - kSegPairs;
+  uint32_t *pbase = lut + kHTabsPerSet * kHTab + pair * (kSegWords * 32 + kSegFifo * kSegRoundWords + 32);
+  uint32_t *ringl = pbase + lane;                               // window ring: word j of this lane at ringl[(j & 31) * 32]
+  uint32_t *fifo = pbase + kSegWords * 32;                      // [round][step][window|entry][lane]
+  uint32_t *prod = fifo + kSegFifo * kSegRoundWords;            // rounds produced (| kSegFin), then rounds consumed
+  uint32_t *cons = prod + 1;
   {
     // the CTA's table set: that of its first unit (never padding)
     const int set = imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset;
@@ -82,117 +121,146 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       if (!used) continue;
       for (int k = tid; k < kHTab / 4; k += kSegThreads) dst[t * (kHTab / 4) + k] = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
     }
+    if (decoder && lane == 0) { *prod = 0; *cons = 0; }
   }
   __syncthreads();
 
-  // ---- per-lane setup ----
-  bool done = true;
-  int img = 0, bend = 0, bidx = 0, bpm = 1, nluma = 1;
-  uint32_t dcb0 = 0, dcb1 = 0, dcb2 = 0, acb0 = 0, acb1 = 0, acb2 = 0;
-  int64_t gb = 0;                           // global index of the block being decoded
-  uint32_t p = 0, pend = 0, rw = 0;          // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
-  const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
-  uint32_t *ringl = ring + (tid >> 5) * (kSegWords * 32) + lane;        // word j of this lane at ringl[(j & 31) * 32]
-  if (unit.x != kSegNoUnit) {
-    img = (int)unit.x;
-    const ImageDev &im = imgs[img];
-    const int k = (int)unit.y;
-    if (!(out[img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT))) {     // else: nothing to decode
-      bpm = im.bpm; nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
-      const int seg_blocks = im.restart_interval * bpm;                            // 0 when there is one segment
-      bidx = k * seg_blocks;
-      bend = (k + 1 < im.nseg) ? bidx + seg_blocks : im.nblocks;
-      if (bidx < bend) {
-        done = false;
-        // table bases (u32 entries) per component: DC table td -> slot td, AC table ta -> slot 4+ta
-        dcb0 = (uint32_t)(im.td[0] & 3) * kHTab; dcb1 = (uint32_t)(im.td[1] & 3) * kHTab; dcb2 = (uint32_t)(im.td[2] & 3) * kHTab;
-        acb0 = (uint32_t)(4 + (im.ta[0] & 3)) * kHTab; acb1 = (uint32_t)(4 + (im.ta[1] & 3)) * kHTab; acb2 = (uint32_t)(4 + (im.ta[2] & 3)) * kHTab;
-        gb = im.coef_base + bidx;
-        seg_zero_block(coef, gb);
-        us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
-        p = seg_start[im.seg_base + k];
-        pend = seg_start[im.seg_base + k + 1];
-        rw = (p >> 5) & ~3u;
-        for (int i = 0; i < kSegWords; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
-        rw += kSegWords;
-      }
-    }
-  }
-  b2_cp_async_commit();
-  b2_cp_async_wait<0>();
-  int pcur = 0, pred0 = 0, pred1 = 0, pred2 = 0;     // pcur: predictor of the current block's component
-  uint32_t err = 0;
+  const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + pair * 32 + lane];
+  const SegLane L = seg_lane(unit, imgs, out);
+  int bidx = L.bidx;
   int blk = 0, comp = 0;                 // block inside the MCU, its component
-  uint32_t dcb = dcb0, acb = acb0;
-  uint32_t z = 0;
-  for (;;) {
-    // ---- top-up: once per four steps, the same instructions for every lane, predicated per lane ----
-    if (!done && rw - (p >> 5) <= (uint32_t)(kSegWords - 4)) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
-      rw += 4;
-      b2_cp_async_commit();        // groups are per thread: only real top-ups count
+  uint32_t z = 0, err = 0;
+  bool done = !L.live;
+
+  if (decoder) {
+    // =========================== the chain: codes only ===========================
+    uint32_t dcb0 = 0, dcb1 = 0, dcb2 = 0, acb0 = 0, acb1 = 0, acb2 = 0;
+    uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
+    const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
+    if (L.live) {
+      const ImageDev &im = imgs[L.img];
+      // table bases (u32 entries) per component: DC table td -> slot td, AC table ta -> slot 4+ta
+      dcb0 = (uint32_t)(im.td[0] & 3) * kHTab; dcb1 = (uint32_t)(im.td[1] & 3) * kHTab; dcb2 = (uint32_t)(im.td[2] & 3) * kHTab;
+      acb0 = (uint32_t)(4 + (im.ta[0] & 3)) * kHTab; acb1 = (uint32_t)(4 + (im.ta[1] & 3)) * kHTab; acb2 = (uint32_t)(4 + (im.ta[2] & 3)) * kHTab;
+      us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
+      p = seg_start[im.seg_base + (int)unit.y];
+      pend = seg_start[im.seg_base + (int)unit.y + 1];
+      rw = (p >> 5) & ~3u;
+      for (int i = 0; i < kSegWords; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
+      rw += kSegWords;
     }
-    // the window (words wi, wi+1) is more than 24 words behind rw, i.e. older than the 5 newest groups:
-    // a copy has ~20 words (~140 steps) to land before it is needed
-    b2_cp_async_wait<5>();
-    bool all_done = false;
+    b2_cp_async_commit();
+    b2_cp_async_wait<0>();
+    uint32_t dcb = dcb0, acb = acb0;
+    uint32_t rounds = 0;
+    for (;;) {
+      // room in the FIFO: the writer has finished round (rounds - kSegFifo)
+      while ((int)(rounds - b2_ld_acquire_smem(cons)) >= kSegFifo) {}
+      // ---- top-up: once per four steps, the same instructions for every lane, predicated per lane ----
+      if (!done && rw - (p >> 5) <= (uint32_t)(kSegWords - 4)) {
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (!done) {
-        const uint32_t wi = p >> 5;
-        const uint32_t w0 = ringl[(wi & (kSegWords - 1)) * 32], w1 = ringl[((wi + 1) & (kSegWords - 1)) * 32];
-        const uint32_t w = __funnelshift_l(w1, w0, p & 31u);
-        const uint32_t idx = w >> (32 - kHLutBits);
-        const uint32_t e_ac = lut[acb + idx], e_dc = lut[dcb + idx];              // both at once: the select is off the critical path
-        const bool is_dc = z == 0;
-        uint32_t e = is_dc ? e_dc : e_ac;
-        if (e & kHSpecial) {                                                      // rare: long code, or an error entry
-          const uint32_t base = is_dc ? dcb : acb;
-          if (e & kHLong) e = lut[base + (e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)];
-          if (e & kHOverflow) {
-            const ImageDev &im = imgs[img];
-            e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
+        for (int i = 0; i < 4; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
+        rw += 4;
+        b2_cp_async_commit();        // groups are per thread: only real top-ups count
+      }
+      // the window (words wi, wi+1) is more than 24 words behind rw, i.e. older than the 5 newest groups:
+      // a copy has ~20 words (~140 steps) to land before it is needed
+      b2_cp_async_wait<5>();
+      uint32_t *slot = fifo + (rounds & (uint32_t)(kSegFifo - 1)) * kSegRoundWords + lane;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        uint32_t w = 0, e = 0;                                                      // entry 0: nothing for the writer
+        if (!done) {
+          const uint32_t wi = p >> 5;
+          const uint32_t w0 = ringl[(wi & (kSegWords - 1)) * 32], w1 = ringl[((wi + 1) & (kSegWords - 1)) * 32];
+          w = __funnelshift_l(w1, w0, p & 31u);
+          const uint32_t idx = w >> (32 - kHLutBits);
+          const uint32_t e_ac = lut[acb + idx], e_dc = lut[dcb + idx];              // both at once: the select is off the critical path
+          const bool is_dc = z == 0;
+          e = is_dc ? e_dc : e_ac;
+          if (e & kHSpecial) {                                                      // rare: long code, or an error entry
+            const uint32_t base = is_dc ? dcb : acb;
+            if (e & kHLong) e = lut[base + (e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)];
+            if (e & kHOverflow) {
+              const ImageDev &im = imgs[L.img];
+              e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
+            }
+            if (e & kHBadCode) err |= ST_BAD_CODE;
+            if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
           }
-          if (e & kHBadCode) err |= ST_BAD_CODE;
-          if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
+          p += e & 31u;
+          z += (e >> 10) & 127u;
+          if (z >= 64u) {
+            // ---- block end: the next block's tables; the last block ends the lane ----
+            if (++bidx == L.bend) {
+              done = true;
+              if (p > pend) err |= ST_OVERRUN;                                      // the last block ran past the segment's end (file.hpp:36-40)
+              else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                        // more than padding is left: the segment holds more blocks
+            } else {
+              blk = blk + 1 == L.bpm ? 0 : blk + 1;
+              comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+              dcb = comp == 0 ? dcb0 : (comp == 1 ? dcb1 : dcb2);
+              acb = comp == 0 ? acb0 : (comp == 1 ? acb1 : acb2);
+              z = 0;
+            }
+          }
         }
-        const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zinc = (e >> 10) & 127u;
-        const uint32_t size = adv - len;
-        int val = size ? seg_extend(w, len, size) : 0;
-        p += adv;
-        const uint32_t zn = z + zinc;
-        if (is_dc) { pcur += val; val = pcur; }                                   // jpeg.cpp:335-345
-        const uint32_t pos = is_dc ? 0u : zn - 1u;                                // z + run
-        if ((is_dc || size != 0u) && pos < 64u)
-          coef[gb * 64 + (int64_t)((((pos >> 3) ^ ((uint32_t)gb & 7u)) << 3) | (pos & 7u))] = (int16_t)val;
-        z = zn;
-        if (z >= 64u) {
-          // ---- block end: EOB, or the index ran to 64.  jpeg.cpp:372-376: a run that reaches 64 is an error ----
-          if (!(e & kHEob) && !(size != 0u && z == 64u)) err |= ST_BAD_RUN;
-          if (pcur < -32768 || pcur > 32767) err |= ST_DC_RANGE;
-          ++gb;
-          if (++bidx == bend) {
-            done = true;
-            if (p > pend) err |= ST_OVERRUN;                                      // the last block ran past the segment's end (file.hpp:36-40)
-            else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                        // more than padding is left: the segment holds more blocks
-          } else {
-            if (comp == 0) pred0 = pcur; else if (comp == 1) pred1 = pcur; else pred2 = pcur;
-            blk = blk + 1 == bpm ? 0 : blk + 1;
-            comp = blk < nluma ? 0 : blk - nluma + 1;
-            pcur = comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2);
-            dcb = comp == 0 ? dcb0 : (comp == 1 ? dcb1 : dcb2);
-            acb = comp == 0 ? acb0 : (comp == 1 ? acb1 : acb2);
-            z = 0;
-            seg_zero_block(coef, gb);
+        slot[(2 * u) * 32] = w;
+        slot[(2 * u + 1) * 32] = e;
+      }
+      const bool fin = __all_sync(0xffffffffu, done);   // also orders the lanes' FIFO stores before lane 0's release
+      ++rounds;
+      if (lane == 0) b2_st_release_smem(prod, rounds | (fin ? kSegFin : 0u));
+      if (fin) break;
+    }
+  } else {
+    // =========================== off the chain: values and stores ===========================
+    int64_t gb = L.gb;
+    int pcur = 0, pred0 = 0, pred1 = 0, pred2 = 0;     // pcur: predictor of the current block's component
+    if (L.live) seg_zero_block(coef, gb);
+    uint32_t r = 0;
+    for (;;) {
+      uint32_t pr;
+      do pr = b2_ld_acquire_smem(prod); while ((pr & ~kSegFin) <= r && !(pr & kSegFin));
+      if ((pr & ~kSegFin) <= r) break;                                              // the last round has been consumed
+      const uint32_t *slot = fifo + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundWords + lane;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t w = slot[(2 * u) * 32], e = slot[(2 * u + 1) * 32];
+        if (e != 0u && !done) {
+          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zinc = (e >> 10) & 127u;
+          const uint32_t size = adv - len;
+          const bool is_dc = z == 0;
+          int val = size ? seg_extend(w, len, size) : 0;
+          const uint32_t zn = z + zinc;
+          if (is_dc) { pcur += val; val = pcur; }                                   // jpeg.cpp:335-345
+          const uint32_t pos = is_dc ? 0u : zn - 1u;                                // z + run
+          if ((is_dc || size != 0u) && pos < 64u)
+            coef[gb * 64 + (int64_t)((((pos >> 3) ^ ((uint32_t)gb & 7u)) << 3) | (pos & 7u))] = (int16_t)val;
+          z = zn;
+          if (z >= 64u) {
+            // ---- block end: EOB, or the index ran to 64.  jpeg.cpp:372-376: a run that reaches 64 is an error ----
+            if (!(e & kHEob) && !(size != 0u && z == 64u)) err |= ST_BAD_RUN;
+            if (pcur < -32768 || pcur > 32767) err |= ST_DC_RANGE;
+            ++gb;
+            if (++bidx == L.bend) done = true;
+            else {
+              if (comp == 0) pred0 = pcur; else if (comp == 1) pred1 = pcur; else pred2 = pcur;
+              blk = blk + 1 == L.bpm ? 0 : blk + 1;
+              comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+              pcur = comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2);
+              z = 0;
+              seg_zero_block(coef, gb);
+            }
           }
         }
       }
+      __syncwarp();                                     // every lane has read the round before it is handed back
+      ++r;
+      if (lane == 0) b2_st_release_smem(cons, r);
     }
-    all_done = __all_sync(0xffffffffu, done);
-    if (all_done) break;
   }
-  if (err) atomicOr(&out[img].status, err);
+  if (err) atomicOr(&out[L.img].status, err);
 }
 
 }  // namespace b2

@@ -57,30 +57,49 @@ struct UClass {
   uint32_t rst_mask;    // bit k: byte k completes an RSTn marker
   uint32_t end_mask;    // bit k: byte k completes FF D9
   uint32_t err_mask;    // bit k: byte k completes an illegal marker
-  uint8_t bytes[16];
-  uint8_t prev;
+  uint32_t ow[4];       // the 16 bytes as they are emitted (a stuffed 00 after FF already turned into FF)
 };
 
+// 0xff in every byte lane where a and b agree
+B2_DEVICE uint32_t u_eq4(uint32_t a, uint32_t b) {
+#ifdef B200JPEG_EMU
+  uint32_t r = 0;
+  for (int k = 0; k < 4; ++k) if (((a >> (8 * k)) & 0xffu) == ((b >> (8 * k)) & 0xffu)) r |= 0xffu << (8 * k);
+  return r;
+#else
+  return __vcmpeq4(a, b);
+#endif
+}
+B2_DEVICE uint32_t u_nibble(uint32_t m) { return (((m & 0x01010101u) * 0x01020408u) >> 24) & 0xfu; }   // byte lanes -> 4 bits
+
+// Four bytes at a time with byte-lane compares; called by every thread of the CTA (warp shuffle inside).
 B2_DEVICE void u_classify(const uint8_t *__restrict__ raw, uint32_t pos, uint32_t raw_len, UClass &c) {
   c.emit_mask = c.rst_mask = c.end_mask = c.err_mask = 0;
-  if (pos >= raw_len) { c.prev = 0; return; }
-  const uint4 v = b2_ld_nc_v4(reinterpret_cast<const uint4 *>(raw + pos));
-  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-  uint8_t prev = pos ? raw[pos - 1] : 0;
-  c.prev = prev;
+  const bool live = pos < raw_len;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (live) v = b2_ld_nc_v4(reinterpret_cast<const uint4 *>(raw + pos));
+  // the byte before this thread's sixteen: the last byte of the previous lane, or one load for lane 0
+  uint32_t prev = __shfl_up_sync(0xffffffffu, v.w >> 24, 1);
+  if ((threadIdx.x & 31) == 0) prev = (live && pos) ? raw[pos - 1] : 0;
+  c.ow[0] = v.x; c.ow[1] = v.y; c.ow[2] = v.z; c.ow[3] = v.w;
+  if (!live) return;
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint8_t cur = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
-    c.bytes[k] = cur;
-    if (pos + k < raw_len) {
-      if (prev == 0xff) {
-        if (cur == 0x00) c.emit_mask |= 1u << k;
-        else if ((cur & 0xf8) == 0xd0) c.rst_mask |= 1u << k;
-        else if (cur == 0xd9) c.end_mask |= 1u << k;
-        else if (cur != 0xff) c.err_mask |= 1u << k;
-      } else if (cur != 0xff) c.emit_mask |= 1u << k;
-    }
-    prev = cur;
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t w = c.ow[j];
+    const uint32_t pw = (w << 8) | prev;
+    prev = w >> 24;
+    const uint32_t fc = u_eq4(w, 0xffffffffu), fp = u_eq4(pw, 0xffffffffu), zc = u_eq4(w, 0u);
+    const uint32_t rs = u_eq4(w & 0xf8f8f8f8u, 0xd0d0d0d0u), d9 = u_eq4(w, 0xd9d9d9d9u);
+    c.emit_mask |= u_nibble((~fp & ~fc) | (fp & zc)) << (4 * j);
+    c.rst_mask |= u_nibble(fp & rs) << (4 * j);
+    c.end_mask |= u_nibble(fp & d9) << (4 * j);
+    c.err_mask |= u_nibble(fp & ~(zc | rs | d9 | fc)) << (4 * j);
+    c.ow[j] = w | fp;                       // FF 00 -> the 00 is what gets emitted, as FF
+  }
+  const uint32_t left = raw_len - pos;
+  if (left < 16u) {
+    const uint32_t m = (1u << left) - 1u;
+    c.emit_mask &= m; c.rst_mask &= m; c.end_mask &= m; c.err_mask &= m;
   }
 }
 
@@ -143,18 +162,66 @@ B2_GLOBAL void k_unstuff_scatter(const ImageDev *__restrict__ imgs, const int32_
   const uint2 tp = tile_pre[blockIdx.x];
   uint32_t e = tp.x + (pre & 0xffffu), r = tp.y + (pre >> 16);
   const uint32_t end_pos = out[i].end_pos;
-  uint8_t *us = d_us + im.raw_off;
-  uint8_t prev = c.prev;
+  // The tile's output is the contiguous byte range [tp.x, tp.x + emits) of the unstuffed scan.  It is put
+  // together in shared memory (byte stores, already word-swapped) and leaves as 128-bit stores; only the
+  // ragged first and last 16 bytes, which neighbouring tiles share, go out byte by byte.
+  B2_SHARED uint4 sbuf4[kUTile / 16 + 1];
+  uint8_t *sbuf = reinterpret_cast<uint8_t *>(sbuf4);
+  const uint32_t a = tp.x & ~15u;                 // 16-byte aligned start of the range in the scan
+  uint32_t *sbuf32 = reinterpret_cast<uint32_t *>(sbuf4);
+  const uint32_t q = e - a;                       // where this thread's bytes start in the staging buffer
+  if (c.emit_mask == 0xffffu) {
+    // all sixteen bytes pass (no FF near: 94 % of the threads): whole big-endian words, ragged ends as bytes
+    const uint32_t sh = q & 3u, wb = q >> 2;
+    uint32_t B[4];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const uint32_t bit = 1u << k;
-    if (c.emit_mask & bit) { us[e ^ 3u] = prev == 0xff ? (uint8_t)0xff : c.bytes[k]; ++e; }
-    if (c.rst_mask & bit) {
-      if (pos + k < end_pos && (int)r + 1 < im.nseg) seg_start[im.seg_base + 1 + (int)r] = e * 8u;
-      ++r;
+    for (int j = 0; j < 4; ++j) B[j] = __byte_perm(c.ow[j], 0, 0x0123);
+    if (sh == 0) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sbuf32[wb + j] = B[j];
+    } else {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) sbuf32[wb + j] = __funnelshift_r(B[j], B[j - 1], 8u * sh);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if ((uint32_t)k < 4u - sh) sbuf[(q + k) ^ 3u] = (uint8_t)(c.ow[0] >> (8 * k));
+        if ((uint32_t)k < sh) sbuf[(q + 16u - sh + k) ^ 3u] = (uint8_t)(c.ow[3] >> (8u * (4u - sh + k)));
+      }
     }
-    if ((c.end_mask & bit) && pos + k == end_pos) { out[i].us_len = e; out[i].nrst = r; }
-    prev = c.bytes[k];
+  } else {
+    uint32_t ee = q;
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (c.emit_mask & (1u << k)) { sbuf[ee ^ 3u] = (uint8_t)(c.ow[k >> 2] >> (8 * (k & 3))); ++ee; }
+  }
+  for (uint32_t m = c.rst_mask; m; m &= m - 1) {  // rare: a restart marker ends at byte k
+    const int k = __ffs((int)m) - 1;
+    const uint32_t before = (uint32_t)__popc(c.rst_mask & ((1u << k) - 1u));
+    const uint32_t ek = e + (uint32_t)__popc(c.emit_mask & ((1u << k) - 1u));
+    if (pos + k < end_pos && (int)(r + before) + 1 < im.nseg) seg_start[im.seg_base + 1 + (int)(r + before)] = ek * 8u;
+  }
+  if (c.end_mask) {                                // rare: FF D9; the first one of the image closes the scan
+    for (uint32_t m = c.end_mask; m; m &= m - 1) {
+      const int k = __ffs((int)m) - 1;
+      if (pos + k == end_pos) {
+        out[i].us_len = e + (uint32_t)__popc(c.emit_mask & ((1u << k) - 1u));
+        out[i].nrst = r + (uint32_t)__popc(c.rst_mask & ((1u << k) - 1u));
+      }
+    }
+  }
+  __syncthreads();
+  uint8_t *us = d_us + im.raw_off;
+  const uint32_t lo = tp.x, hi = tp.x + (tot & 0xffffu);          // byte range this tile owns
+  const uint32_t c0 = (lo + 15u) & ~15u, c1 = hi & ~15u;           // whole 16-byte chunks inside it
+  for (uint32_t g = c0 + threadIdx.x * 16u; g < c1; g += kUThreads * 16u)
+    *reinterpret_cast<uint4 *>(us + g) = *reinterpret_cast<const uint4 *>(sbuf + (g - a));
+  if (threadIdx.x < 32) {                                          // ragged edges: at most 15 bytes each
+    const uint32_t head_end = c0 < hi ? c0 : hi;
+    const uint32_t g0 = lo + threadIdx.x;
+    if (g0 < head_end) us[g0 ^ 3u] = sbuf[(g0 - a) ^ 3u];
+    const uint32_t tail0 = c1 > head_end ? c1 : head_end;
+    const uint32_t g1 = tail0 + threadIdx.x;
+    if (g1 < hi) us[g1 ^ 3u] = sbuf[(g1 - a) ^ 3u];
   }
 }
 

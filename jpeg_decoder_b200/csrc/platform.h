@@ -85,6 +85,15 @@ B2_DEVICE void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
       "B2_DONE:\n"
       "}" ::"r"(b2_smem_addr(bar)), "r"(parity) : "memory");
 }
+// ---- producer/consumer words in shared memory between two warps of one CTA ----
+B2_DEVICE uint32_t b2_ld_acquire_smem(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(b2_smem_addr(p)) : "memory");
+  return v;
+}
+B2_DEVICE void b2_st_release_smem(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(b2_smem_addr(p)), "r"(v) : "memory");
+}
 // float -> integer-valued float, toward zero, for |x| < 2^23, without the XU pipe (FRND):
 // |x| + 2^23 rounded toward zero is floor(|x|) + 2^23 exactly; subtract and restore the sign.
 B2_DEVICE float b2_trunc_small(float x) {

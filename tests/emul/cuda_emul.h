@@ -256,3 +256,8 @@ static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
 }
 static inline float b2_trunc_small(float x) { return truncf(x); }
+static inline uint32_t b2_ld_acquire_smem(const uint32_t *p) {
+  std::this_thread::yield();                    // callers spin on it: one OS thread per CUDA thread here
+  return __atomic_load_n(p, __ATOMIC_ACQUIRE);
+}
+static inline void b2_st_release_smem(uint32_t *p, uint32_t v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
