@@ -127,21 +127,25 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
 
   const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + pair * 32 + lane];
   const SegLane L = seg_lane(unit, imgs, out);
-  int bidx = L.bidx;
-  int blk = 0, comp = 0;                 // block inside the MCU, its component
+  int left = L.live ? L.bend - L.bidx : 0;       // blocks of the segment still to finish
+  int blk = 0, comp = 0;                         // block inside the MCU, its component
   uint32_t z = 0, err = 0;
-  bool done = !L.live;
+  // the inner loops address shared memory through 32-bit window addresses (register + immediate)
+  const uint32_t fifo_a = b2_dsm_addr(fifo) + 4u * (uint32_t)lane;
 
   if (decoder) {
     // =========================== the chain: codes only ===========================
-    uint32_t dcb0 = 0, dcb1 = 0, dcb2 = 0, acb0 = 0, acb1 = 0, acb2 = 0;
+    const uint32_t lut_a = b2_dsm_addr(lut), ring_a = b2_dsm_addr(ringl);
+    uint32_t dca0 = lut_a, dca1 = lut_a, dca2 = lut_a, aca0 = lut_a, aca1 = lut_a, aca2 = lut_a;   // table addresses per component
     uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
     const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
+    bool done = !L.live;
     if (L.live) {
       const ImageDev &im = imgs[L.img];
-      // table bases (u32 entries) per component: DC table td -> slot td, AC table ta -> slot 4+ta
-      dcb0 = (uint32_t)(im.td[0] & 3) * kHTab; dcb1 = (uint32_t)(im.td[1] & 3) * kHTab; dcb2 = (uint32_t)(im.td[2] & 3) * kHTab;
-      acb0 = (uint32_t)(4 + (im.ta[0] & 3)) * kHTab; acb1 = (uint32_t)(4 + (im.ta[1] & 3)) * kHTab; acb2 = (uint32_t)(4 + (im.ta[2] & 3)) * kHTab;
+      // DC table td -> slot td, AC table ta -> slot 4+ta
+      dca0 += (uint32_t)(im.td[0] & 3) * (kHTab * 4); dca1 += (uint32_t)(im.td[1] & 3) * (kHTab * 4); dca2 += (uint32_t)(im.td[2] & 3) * (kHTab * 4);
+      aca0 += (uint32_t)(4 + (im.ta[0] & 3)) * (kHTab * 4); aca1 += (uint32_t)(4 + (im.ta[1] & 3)) * (kHTab * 4);
+      aca2 += (uint32_t)(4 + (im.ta[2] & 3)) * (kHTab * 4);
       us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
       p = seg_start[im.seg_base + (int)unit.y];
       pend = seg_start[im.seg_base + (int)unit.y + 1];
@@ -151,7 +155,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
     }
     b2_cp_async_commit();
     b2_cp_async_wait<0>();
-    uint32_t dcb = dcb0, acb = acb0;
+    uint32_t dca = dca0, aca = aca0;
     uint32_t rounds = 0;
     for (;;) {
       // room in the FIFO: the writer has finished round (rounds - kSegFifo)
@@ -166,47 +170,45 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       // the window (words wi, wi+1) is more than 24 words behind rw, i.e. older than the 5 newest groups:
       // a copy has ~20 words (~140 steps) to land before it is needed
       b2_cp_async_wait<5>();
-      uint32_t *slot = fifo + (rounds & (uint32_t)(kSegFifo - 1)) * kSegRoundWords + lane;
+      const uint32_t slot_a = fifo_a + (rounds & (uint32_t)(kSegFifo - 1)) * (kSegRoundWords * 4);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        uint32_t w = 0, e = 0;                                                      // entry 0: nothing for the writer
-        if (!done) {
-          const uint32_t wi = p >> 5;
-          const uint32_t w0 = ringl[(wi & (kSegWords - 1)) * 32], w1 = ringl[((wi + 1) & (kSegWords - 1)) * 32];
-          w = __funnelshift_l(w1, w0, p & 31u);
-          const uint32_t idx = w >> (32 - kHLutBits);
-          const uint32_t e_ac = lut[acb + idx], e_dc = lut[dcb + idx];              // both at once: the select is off the critical path
+        // a finished lane keeps stepping in place: its entry is forced to 0 (no advance, nothing for the writer)
+        const uint32_t wi = p >> 5;
+        const uint32_t w0 = b2_lds(ring_a + ((wi & 31u) << 7)), w1 = b2_lds(ring_a + (((wi + 1u) & 31u) << 7));
+        const uint32_t w = __funnelshift_l(w1, w0, p);
+        const uint32_t i4 = (w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4);
+        const uint32_t e_ac = b2_lds(aca + i4), e_dc = b2_lds(dca + i4);            // both at once: the select is off the critical path
+        uint32_t e = z == 0 ? e_dc : e_ac;
+        e = done ? 0u : e;
+        if (e >= kHOverflow) {                                                       // rare: long code, or an error entry
           const bool is_dc = z == 0;
-          e = is_dc ? e_dc : e_ac;
-          if (e & kHSpecial) {                                                      // rare: long code, or an error entry
-            const uint32_t base = is_dc ? dcb : acb;
-            if (e & kHLong) e = lut[base + (e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)];
-            if (e & kHOverflow) {
-              const ImageDev &im = imgs[L.img];
-              e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
-            }
-            if (e & kHBadCode) err |= ST_BAD_CODE;
-            if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
+          if (e & kHLong) e = b2_lds((is_dc ? dca : aca) + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+          if (e & kHOverflow) {
+            const ImageDev &im = imgs[L.img];
+            e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
           }
-          p += e & 31u;
-          z += (e >> 10) & 127u;
-          if (z >= 64u) {
-            // ---- block end: the next block's tables; the last block ends the lane ----
-            if (++bidx == L.bend) {
-              done = true;
-              if (p > pend) err |= ST_OVERRUN;                                      // the last block ran past the segment's end (file.hpp:36-40)
-              else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                        // more than padding is left: the segment holds more blocks
-            } else {
-              blk = blk + 1 == L.bpm ? 0 : blk + 1;
-              comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-              dcb = comp == 0 ? dcb0 : (comp == 1 ? dcb1 : dcb2);
-              acb = comp == 0 ? acb0 : (comp == 1 ? acb1 : acb2);
-              z = 0;
-            }
+          if (e & kHBadCode) err |= ST_BAD_CODE;
+          if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
+        }
+        b2_sts(slot_a + (uint32_t)u * 256u, w);
+        b2_sts(slot_a + (uint32_t)u * 256u + 128u, e);
+        p += e & 31u;
+        z += (e >> 10) & 127u;
+        if (z >= 64u) {
+          // ---- block end: the next block's tables; the last block ends the lane ----
+          z = 0;
+          if (--left == 0) {
+            done = true;
+            if (p > pend) err |= ST_OVERRUN;                                        // the last block ran past the segment's end (file.hpp:36-40)
+            else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                          // more than padding is left: the segment holds more blocks
+          } else {
+            blk = blk + 1 == L.bpm ? 0 : blk + 1;
+            comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+            dca = comp == 0 ? dca0 : (comp == 1 ? dca1 : dca2);
+            aca = comp == 0 ? aca0 : (comp == 1 ? aca1 : aca2);
           }
         }
-        slot[(2 * u) * 32] = w;
-        slot[(2 * u + 1) * 32] = e;
       }
       const bool fin = __all_sync(0xffffffffu, done);   // also orders the lanes' FIFO stores before lane 0's release
       ++rounds;
@@ -215,42 +217,45 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
     }
   } else {
     // =========================== off the chain: values and stores ===========================
-    int64_t gb = L.gb;
+    int16_t *bp = coef + L.gb * 64;                    // the block being filled
+    uint32_t key = ((uint32_t)L.gb & 7u) << 3;         // its chunk swizzle: coefficient pos lives at pos ^ key
     int pcur = 0, pred0 = 0, pred1 = 0, pred2 = 0;     // pcur: predictor of the current block's component
-    if (L.live) seg_zero_block(coef, gb);
+    uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
+    if (L.live) seg_zero_block(bp, 0);
     uint32_t r = 0;
     for (;;) {
       uint32_t pr;
       do pr = b2_ld_acquire_smem(prod); while ((pr & ~kSegFin) <= r && !(pr & kSegFin));
       if ((pr & ~kSegFin) <= r) break;                                              // the last round has been consumed
-      const uint32_t *slot = fifo + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundWords + lane;
+      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * (kSegRoundWords * 4);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const uint32_t w = slot[(2 * u) * 32], e = slot[(2 * u + 1) * 32];
-        if (e != 0u && !done) {
+        const uint32_t w = b2_lds(slot_a + (uint32_t)u * 256u), e = b2_lds(slot_a + (uint32_t)u * 256u + 128u);
+        if (e != 0u) {
           const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zinc = (e >> 10) & 127u;
           const uint32_t size = adv - len;
+          // EXTEND (jpeg.cpp:335-343, 388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
+          const uint32_t v = b2_shr(w << len, 32u - size), t = b2_shl(1u, size) - 1u;
+          const int val = (int)v - (v + v > t ? 0 : (int)t);
           const bool is_dc = z == 0;
-          int val = size ? seg_extend(w, len, size) : 0;
           const uint32_t zn = z + zinc;
-          if (is_dc) { pcur += val; val = pcur; }                                   // jpeg.cpp:335-345
+          pcur += is_dc ? val : 0;                                                  // jpeg.cpp:344-345
+          const int o = is_dc ? pcur : val;
           const uint32_t pos = is_dc ? 0u : zn - 1u;                                // z + run
-          if ((is_dc || size != 0u) && pos < 64u)
-            coef[gb * 64 + (int64_t)((((pos >> 3) ^ ((uint32_t)gb & 7u)) << 3) | (pos & 7u))] = (int16_t)val;
+          if ((is_dc || size != 0u) && pos < 64u) bp[pos ^ key] = (int16_t)o;
           z = zn;
           if (z >= 64u) {
             // ---- block end: EOB, or the index ran to 64.  jpeg.cpp:372-376: a run that reaches 64 is an error ----
             if (!(e & kHEob) && !(size != 0u && z == 64u)) err |= ST_BAD_RUN;
-            if (pcur < -32768 || pcur > 32767) err |= ST_DC_RANGE;
-            ++gb;
-            if (++bidx == L.bend) done = true;
-            else {
-              if (comp == 0) pred0 = pcur; else if (comp == 1) pred1 = pcur; else pred2 = pcur;
+            dcbad |= (uint32_t)(pcur + 32768) >> 16;
+            z = 0;
+            if (--left != 0) {
+              pred0 = comp == 0 ? pcur : pred0; pred1 = comp == 1 ? pcur : pred1; pred2 = comp == 2 ? pcur : pred2;
               blk = blk + 1 == L.bpm ? 0 : blk + 1;
               comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
               pcur = comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2);
-              z = 0;
-              seg_zero_block(coef, gb);
+              bp += 64; key = (key + 8u) & 0x38u;
+              seg_zero_block(bp, 0);
             }
           }
         }
@@ -259,6 +264,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       ++r;
       if (lane == 0) b2_st_release_smem(cons, r);
     }
+    if (dcbad) err |= ST_DC_RANGE;
   }
   if (err) atomicOr(&out[L.img].status, err);
 }

@@ -94,6 +94,18 @@ B2_DEVICE uint32_t b2_ld_acquire_smem(const uint32_t *p) {
 B2_DEVICE void b2_st_release_smem(uint32_t *p, uint32_t v) {
   asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(b2_smem_addr(p)), "r"(v) : "memory");
 }
+// ---- dynamic shared memory through 32-bit window addresses (register + immediate addressing, no
+//      generic-pointer arithmetic in inner loops) ----
+B2_DEVICE uint32_t b2_dsm_addr(const void *p) { return b2_smem_addr(p); }
+B2_DEVICE uint32_t b2_lds(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+B2_DEVICE void b2_sts(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+// shifts that give 0 for counts >= 32 (PTX semantics; undefined in C++)
+B2_DEVICE uint32_t b2_shr(uint32_t v, uint32_t n) { uint32_t r; asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
+B2_DEVICE uint32_t b2_shl(uint32_t v, uint32_t n) { uint32_t r; asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
 // float -> integer-valued float, toward zero, for |x| < 2^23, without the XU pipe (FRND):
 // |x| + 2^23 rounded toward zero is floor(|x|) + 2^23 exactly; subtract and restore the sign.
 B2_DEVICE float b2_trunc_small(float x) {
