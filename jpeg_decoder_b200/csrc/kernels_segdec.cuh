@@ -22,14 +22,21 @@
 //     PREDICATE once every four steps -- four steps consume at most 108 bits, one top-up brings 128;
 //   * DC and AC tables are looked up together and selected afterwards.
 //
-// (2) Only what the chain needs stays on the chain.  Each DECODER warp is paired with a WRITER warp of
-//     the same CTA.  The decoder walks the codes -- window, table entry, advance, block/table
-//     bookkeeping -- and pushes (window, entry) per lane and step into a shared-memory FIFO; the writer
-//     pops them and does everything that merely CONSUMES a symbol: magnitude extension (jpeg.cpp:335-343,
-//     388-397), DC prediction (jpeg.cpp:344-345), zig-zag placement, the stores, zero-filling the next
-//     block, the range checks.  The two warps run on the idle issue slots of their sub-partitions in
-//     parallel, so the dependent chain per symbol is roughly halved.  Hand-over is a pair of counters
-//     (st.release / ld.acquire in shared memory), one update per round of four steps.
+// (2) Only what the chain needs stays on the chain.  A segment is worked on by FOUR warps of the same CTA
+//     (32 segments each):
+//       decoder   walks the codes -- window, table entry, advance, block/table bookkeeping -- and pushes
+//                 (window, entry | zig-zag index, block number) per lane and step into a shared-memory FIFO;
+//       writer A/B take the even / the odd rounds of the FIFO and place the AC coefficients: magnitude
+//                 extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store.  They keep no state
+//                 between symbols -- everything they need is in the FIFO entry -- so two of them (or more)
+//                 work in parallel;
+//       DC warp   sees every round but only the DC symbols: extension, prediction per component
+//                 (jpeg.cpp:335-345), store, range check.
+//     The warps run on the idle issue slots of their sub-partitions in parallel; the dependent chain per
+//     symbol is what the decoder alone executes.  Hand-over is a producer counter and one consumer counter
+//     per warp (st.release / ld.acquire in shared memory), one update per round of four steps.
+//     The coefficient buffer is zero-filled beforehand (a memset on a side stream, pipeline_run.h): MCU[] is
+//     value-initialised in the reference (jpeg.cpp:407) and the warps only store what is not zero.
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -42,37 +49,32 @@ namespace b2 {
 #define B2_SEG_PAIRS 2
 #endif
 #ifndef B2_SEG_FIFO
-#define B2_SEG_FIFO 8
+#define B2_SEG_FIFO 4
 #endif
-constexpr int kSegPairs = B2_SEG_PAIRS;       // decoder/writer warp pairs per CTA
-constexpr int kSegThreads = kSegPairs * 64;   // threads per CTA of k_entropy_seg: warps [0,kSegPairs) decode, the rest write
+constexpr int kSegPairs = B2_SEG_PAIRS;       // groups of four warps (decoder, writer A, writer B, DC) per CTA
+constexpr int kSegRoles = 4;
+constexpr int kSegThreads = kSegPairs * kSegRoles * 32;   // threads per CTA of k_entropy_seg
 constexpr int kSegUnits = kSegPairs * 32;     // segments per CTA
 constexpr uint32_t kSegNoUnit = 0xffffffffu;
 constexpr int kSegWords = 32;                 // stream words per lane in the window ring
-constexpr int kSegFifo = B2_SEG_FIFO;         // rounds (of four steps) the FIFO between a decoder and its writer holds
-constexpr int kSegRoundWords = 4 * 2 * 32;    // one round: 4 steps x (window, entry) x 32 lanes
+constexpr int kSegFifo = B2_SEG_FIFO;         // rounds the FIFO holds
+constexpr int kSegSteps = 8;                  // symbols per lane and round: the per-round work (top-up, hand-over) is paid once per 8 steps
+constexpr int kSegStepBytes = 3 * 128;        // one step: (window, entry, block number) x 32 lanes
+constexpr int kSegRoundBytes = kSegSteps * kSegStepBytes;
 constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter with the last round
+#ifndef B2_SEG_POLL_NS
+#define B2_SEG_POLL_NS 200
+#endif
+constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
+constexpr int kSegZShift = 18;                // the zig-zag index before the symbol rides in bits 18..23 of the entry
+// per group: window ring | FIFO | per-lane table addresses by block-in-MCU | counters
+constexpr int kSegGroupWords = kSegWords * 32 + kSegFifo * kSegRoundBytes / 4 + kMaxBpm * 32 + 32;
 
 B2_HD size_t segdec_smem_bytes() {
-  return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegPairs * (kSegWords * 32 + kSegFifo * kSegRoundWords + 32));
+  return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegPairs * kSegGroupWords);
 }
 
-B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:335-343, 388-397; size >= 1
-  const uint32_t v = (w << len) >> (32u - size);
-  return (v >> (size - 1u)) ? (int)v : (int)v - (int)((1u << size) - 1u);
-}
-
-// Coefficients go straight to global memory: at the start of a block its 128-byte line is zeroed with
-// eight 128-bit stores (MCU[] is value-initialised, jpeg.cpp:407), then every non-zero coefficient is one
-// 2-byte store into that line (same thread, same addresses: program order holds; L2 merges the line).
-// Chunk c of block b lives at chunk c ^ (b & 7) (kernels_pixel.cuh).
-B2_DEVICE void seg_zero_block(int16_t *__restrict__ coef, int64_t gb) {
-  uint4 *o = reinterpret_cast<uint4 *>(coef) + gb * 8;
-#pragma unroll
-  for (int q = 0; q < 8; ++q) o[q] = make_uint4(0, 0, 0, 0);
-}
-
-// What both warps of a pair know about a lane's segment before the first symbol.
+// What every warp of a group knows about a lane's segment before the first symbol.
 struct SegLane {
   bool live;                 // there is something to decode
   int img, bidx, bend;       // image, first block of the segment, first block past it
@@ -104,13 +106,12 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
               const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef) {
   B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const bool decoder = warp < kSegPairs;
-  const int pair = decoder ? warp : warp - kSegPairs;
-  uint32_t *pbase = lut + kHTabsPerSet * kHTab + pair * (kSegWords * 32 + kSegFifo * kSegRoundWords + 32);
+  const int pair = warp % kSegPairs, role = warp / kSegPairs;    // role 0 decoder, 1/2 AC writers, 3 DC warp
+  uint32_t *pbase = lut + kHTabsPerSet * kHTab + pair * kSegGroupWords;
   uint32_t *ringl = pbase + lane;                               // window ring: word j of this lane at ringl[(j & 31) * 32]
-  uint32_t *fifo = pbase + kSegWords * 32;                      // [round][step][window|entry][lane]
-  uint32_t *prod = fifo + kSegFifo * kSegRoundWords;            // rounds produced (| kSegFin), then rounds consumed
-  uint32_t *cons = prod + 1;
+  uint32_t *fifo = pbase + kSegWords * 32;                      // [round][step][window|entry|block][lane]
+  uint32_t *tb = fifo + kSegFifo * kSegRoundBytes / 4;          // [block-in-MCU][lane]: DC table offset | AC table offset << 16
+  uint32_t *ctr = tb + kMaxBpm * 32;                            // [0] rounds produced (| kSegFin), [1..3] next round of writer A, B, DC warp
   {
     // the CTA's table set: that of its first unit (never padding)
     const int set = imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset;
@@ -121,148 +122,177 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       if (!used) continue;
       for (int k = tid; k < kHTab / 4; k += kSegThreads) dst[t * (kHTab / 4) + k] = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
     }
-    if (decoder && lane == 0) { *prod = 0; *cons = 0; }
+    if (role == 0 && lane == 0) { ctr[0] = 0; ctr[1] = 0; ctr[2] = 1; ctr[3] = 0; }
   }
   __syncthreads();
 
   const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + pair * 32 + lane];
   const SegLane L = seg_lane(unit, imgs, out);
-  int left = L.live ? L.bend - L.bidx : 0;       // blocks of the segment still to finish
-  int blk = 0, comp = 0;                         // block inside the MCU, its component
-  uint32_t z = 0, err = 0;
+  uint32_t err = 0;
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
   const uint32_t fifo_a = b2_dsm_addr(fifo) + 4u * (uint32_t)lane;
+  int16_t *const base = coef + L.gb * 64;          // block 0 of the segment; block n, coefficient pos: base[n*64 + (pos ^ key(n))]
+  const uint32_t g0 = (uint32_t)L.gb & 7u;         // key(n) = ((g0 + n) & 7) << 3
 
-  if (decoder) {
+  if (role == 0) {
     // =========================== the chain: codes only ===========================
-    const uint32_t lut_a = b2_dsm_addr(lut), ring_a = b2_dsm_addr(ringl);
-    uint32_t dca0 = lut_a, dca1 = lut_a, dca2 = lut_a, aca0 = lut_a, aca1 = lut_a, aca2 = lut_a;   // table addresses per component
+    const uint32_t lut_a = b2_dsm_addr(lut), ring_a = b2_dsm_addr(ringl), tb_a = b2_dsm_addr(tb) + 4u * (uint32_t)lane;
     uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
     const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
+    const uint32_t total = L.live ? (uint32_t)(L.bend - L.bidx) : 0u;
     bool done = !L.live;
     if (L.live) {
       const ImageDev &im = imgs[L.img];
-      // DC table td -> slot td, AC table ta -> slot 4+ta
-      dca0 += (uint32_t)(im.td[0] & 3) * (kHTab * 4); dca1 += (uint32_t)(im.td[1] & 3) * (kHTab * 4); dca2 += (uint32_t)(im.td[2] & 3) * (kHTab * 4);
-      aca0 += (uint32_t)(4 + (im.ta[0] & 3)) * (kHTab * 4); aca1 += (uint32_t)(4 + (im.ta[1] & 3)) * (kHTab * 4);
-      aca2 += (uint32_t)(4 + (im.ta[2] & 3)) * (kHTab * 4);
+      for (int b = 0; b < L.bpm; ++b) {             // DC table td -> slot td, AC table ta -> slot 4+ta
+        const int c = b < L.nluma ? 0 : b - L.nluma + 1;
+        tb[b * 32 + lane] = (uint32_t)(im.td[c] & 3) * (kHTab * 4) | ((uint32_t)(4 + (im.ta[c] & 3)) * (kHTab * 4)) << 16;
+      }
       us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
       p = seg_start[im.seg_base + (int)unit.y];
       pend = seg_start[im.seg_base + (int)unit.y + 1];
       rw = (p >> 5) & ~3u;
       for (int i = 0; i < kSegWords; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
       rw += kSegWords;
-    }
+    } else tb[lane] = 0;
     b2_cp_async_commit();
     b2_cp_async_wait<0>();
-    uint32_t dca = dca0, aca = aca0;
+    const uint32_t tb_end = tb_a + (uint32_t)L.bpm * 128u;
+    uint32_t tba = tb_a;                             // this lane's table entry of the current block-in-MCU
+    uint32_t z = 0, nb = 0;                          // zig-zag index, blocks finished
     uint32_t rounds = 0;
     for (;;) {
-      // room in the FIFO: the writer has finished round (rounds - kSegFifo)
-      while ((int)(rounds - b2_ld_acquire_smem(cons)) >= kSegFifo) {}
-      // ---- top-up: once per four steps, the same instructions for every lane, predicated per lane ----
-      if (!done && rw - (p >> 5) <= (uint32_t)(kSegWords - 4)) {
+      // the consumers' counters are read now and looked at after the round: room for the NEXT round
+      const uint32_t ca = b2_ld_acquire_smem(ctr + 1), cb = b2_ld_acquire_smem(ctr + 2), cc = b2_ld_acquire_smem(ctr + 3);
+      // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
+      //      A round consumes at most 8 x 27 bits < 7 words; a top-up brings 8 ----
+      const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
-        rw += 4;
-        b2_cp_async_commit();        // groups are per thread: only real top-ups count
-      }
-      // the window (words wi, wi+1) is more than 24 words behind rw, i.e. older than the 5 newest groups:
-      // a copy has ~20 words (~140 steps) to land before it is needed
-      b2_cp_async_wait<5>();
-      const uint32_t slot_a = fifo_a + (rounds & (uint32_t)(kSegFifo - 1)) * (kSegRoundWords * 4);
+      for (int i = 0; i < 8; ++i) b2_cp_async4_if(need, ring_a + (((rw + i) & (kSegWords - 1)) << 7), us + rw + i);
+      rw += need ? 8u : 0u;
+      b2_cp_async_commit();
+      // rw is at least 25 words ahead of the window and the round needs at most 8 more: everything but the two
+      // newest groups must have landed -- copies issued two rounds (16 steps) ago
+      b2_cp_async_wait<2>();
+      const uint32_t slot_a = fifo_a + (rounds & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        // a finished lane keeps stepping in place: its entry is forced to 0 (no advance, nothing for the writer)
+      for (int u = 0; u < kSegSteps; ++u) {
+        // a finished lane keeps stepping in place: its entry is forced to 0 (no advance, nothing for the writers)
+        const uint32_t t = b2_lds(tba);                                              // table offsets of this block: DC | AC << 16
+        const uint32_t cur = lut_a + (z == 0 ? (t & 0xffffu) : (t >> 16));           // chosen while the window is still on its way
         const uint32_t wi = p >> 5;
         const uint32_t w0 = b2_lds(ring_a + ((wi & 31u) << 7)), w1 = b2_lds(ring_a + (((wi + 1u) & 31u) << 7));
         const uint32_t w = __funnelshift_l(w1, w0, p);
         const uint32_t i4 = (w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4);
-        const uint32_t e_ac = b2_lds(aca + i4), e_dc = b2_lds(dca + i4);            // both at once: the select is off the critical path
-        uint32_t e = z == 0 ? e_dc : e_ac;
+        uint32_t e = b2_lds(cur + i4);
         e = done ? 0u : e;
         if (e >= kHOverflow) {                                                       // rare: long code, or an error entry
           const bool is_dc = z == 0;
-          if (e & kHLong) e = b2_lds((is_dc ? dca : aca) + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+          if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
           if (e & kHOverflow) {
             const ImageDev &im = imgs[L.img];
+            const int blk = (int)((tba - tb_a) >> 7), comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
             e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
           }
           if (e & kHBadCode) err |= ST_BAD_CODE;
           if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
         }
-        b2_sts(slot_a + (uint32_t)u * 256u, w);
-        b2_sts(slot_a + (uint32_t)u * 256u + 128u, e);
+        b2_sts(slot_a + (uint32_t)u * kSegStepBytes, w);
+        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 128u, e | (z << kSegZShift));
+        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 256u, nb);
         p += e & 31u;
         z += (e >> 10) & 127u;
-        if (z >= 64u) {
-          // ---- block end: the next block's tables; the last block ends the lane ----
-          z = 0;
-          if (--left == 0) {
-            done = true;
-            if (p > pend) err |= ST_OVERRUN;                                        // the last block ran past the segment's end (file.hpp:36-40)
-            else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                          // more than padding is left: the segment holds more blocks
-          } else {
-            blk = blk + 1 == L.bpm ? 0 : blk + 1;
-            comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-            dca = comp == 0 ? dca0 : (comp == 1 ? dca1 : dca2);
-            aca = comp == 0 ? aca0 : (comp == 1 ? aca1 : aca2);
-          }
+        // ---- block end without a branch: some lane ends a block in four steps out of five ----
+        const bool end = z >= 64u;
+        const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
+        z = end ? 0u : z;
+        tba = end ? tbn : tba;
+        nb += end ? 1u : 0u;
+        if (end && nb == total) {                                                    // once per lane: the segment is finished
+          done = true;
+          if (p > pend) err |= ST_OVERRUN;                                          // the last block ran past the segment's end (file.hpp:36-40)
+          else if (pend - p > 7u) err |= ST_BLOCK_COUNT;                            // more than padding is left: the segment holds more blocks
         }
       }
       const bool fin = __all_sync(0xffffffffu, done);   // also orders the lanes' FIFO stores before lane 0's release
       ++rounds;
-      if (lane == 0) b2_st_release_smem(prod, rounds | (fin ? kSegFin : 0u));
+      if (lane == 0) b2_st_release_smem(ctr, rounds | (fin ? kSegFin : 0u));
       if (fin) break;
+      // room in the FIFO for the next round: every consumer is past round (rounds - kSegFifo)
+      uint32_t m = ca < cb ? (ca < cc ? ca : cc) : (cb < cc ? cb : cc);
+      while ((int)(rounds - m) >= kSegFifo) {
+        b2_backoff(kSegPollNs);
+        const uint32_t a = b2_ld_acquire_smem(ctr + 1), b = b2_ld_acquire_smem(ctr + 2), c = b2_ld_acquire_smem(ctr + 3);
+        m = a < b ? (a < c ? a : c) : (b < c ? b : c);
+      }
+    }
+  } else if (role < 3) {
+    // =========================== AC coefficients: stateless, every other round ===========================
+    uint32_t r = (uint32_t)(role - 1);
+    for (;;) {
+      uint32_t pr;
+      while (pr = b2_ld_acquire_smem(ctr), (pr & ~kSegFin) <= r && !(pr & kSegFin)) b2_backoff(kSegPollNs);
+      if ((pr & ~kSegFin) <= r) break;                                              // no such round: the decoder has finished
+      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
+      uint32_t fw[kSegSteps], fe[kSegSteps], fn[kSegSteps];
+#pragma unroll
+      for (int u = 0; u < kSegSteps; ++u) {
+        fw[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes); fe[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 128u);
+        fn[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 256u);
+      }
+      __syncwarp();                                     // every lane has read the round before it is handed back
+      if (lane == 0) b2_st_release_smem(ctr + role, r + 2u);
+#pragma unroll
+      for (int u = 0; u < kSegSteps; ++u) {
+        const uint32_t e = fe[u], z = (e >> kSegZShift) & 63u;
+        if (z != 0u) {                                  // an AC symbol (entry 0 and DC symbols carry z = 0)
+          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zn = z + ((e >> 10) & 127u);
+          const uint32_t size = adv - len;
+          // EXTEND (jpeg.cpp:388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
+          const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
+          const int val = (int)v - (v + v > t ? 0 : (int)t);
+          const uint32_t pos = zn - 1u;                                             // z + run
+          if (size != 0u && pos < 64u) base[fn[u] * 64u + (pos ^ (((g0 + fn[u]) & 7u) << 3))] = (int16_t)val;
+          // EOB, or the index ran to 64; a run that reaches past 63 is an error (jpeg.cpp:372-376)
+          if (zn >= 64u && !(e & kHEob) && !(size != 0u && zn == 64u)) err |= ST_BAD_RUN;
+        }
+      }
+      r += 2u;
     }
   } else {
-    // =========================== off the chain: values and stores ===========================
-    int16_t *bp = coef + L.gb * 64;                    // the block being filled
-    uint32_t key = ((uint32_t)L.gb & 7u) << 3;         // its chunk swizzle: coefficient pos lives at pos ^ key
-    int pcur = 0, pred0 = 0, pred1 = 0, pred2 = 0;     // pcur: predictor of the current block's component
+    // =========================== DC coefficients: prediction per component ===========================
+    int pred0 = 0, pred1 = 0, pred2 = 0;
+    int blk = 0;
     uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
-    if (L.live) seg_zero_block(bp, 0);
     uint32_t r = 0;
     for (;;) {
       uint32_t pr;
-      do pr = b2_ld_acquire_smem(prod); while ((pr & ~kSegFin) <= r && !(pr & kSegFin));
-      if ((pr & ~kSegFin) <= r) break;                                              // the last round has been consumed
-      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * (kSegRoundWords * 4);
+      while (pr = b2_ld_acquire_smem(ctr), (pr & ~kSegFin) <= r && !(pr & kSegFin)) b2_backoff(kSegPollNs);
+      if ((pr & ~kSegFin) <= r) break;
+      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
+      uint32_t fw[kSegSteps], fe[kSegSteps], fn[kSegSteps];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t w = b2_lds(slot_a + (uint32_t)u * 256u), e = b2_lds(slot_a + (uint32_t)u * 256u + 128u);
-        if (e != 0u) {
-          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zinc = (e >> 10) & 127u;
-          const uint32_t size = adv - len;
-          // EXTEND (jpeg.cpp:335-343, 388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
-          const uint32_t v = b2_shr(w << len, 32u - size), t = b2_shl(1u, size) - 1u;
-          const int val = (int)v - (v + v > t ? 0 : (int)t);
-          const bool is_dc = z == 0;
-          const uint32_t zn = z + zinc;
-          pcur += is_dc ? val : 0;                                                  // jpeg.cpp:344-345
-          const int o = is_dc ? pcur : val;
-          const uint32_t pos = is_dc ? 0u : zn - 1u;                                // z + run
-          if ((is_dc || size != 0u) && pos < 64u) bp[pos ^ key] = (int16_t)o;
-          z = zn;
-          if (z >= 64u) {
-            // ---- block end: EOB, or the index ran to 64.  jpeg.cpp:372-376: a run that reaches 64 is an error ----
-            if (!(e & kHEob) && !(size != 0u && z == 64u)) err |= ST_BAD_RUN;
-            dcbad |= (uint32_t)(pcur + 32768) >> 16;
-            z = 0;
-            if (--left != 0) {
-              pred0 = comp == 0 ? pcur : pred0; pred1 = comp == 1 ? pcur : pred1; pred2 = comp == 2 ? pcur : pred2;
-              blk = blk + 1 == L.bpm ? 0 : blk + 1;
-              comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-              pcur = comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2);
-              bp += 64; key = (key + 8u) & 0x38u;
-              seg_zero_block(bp, 0);
-            }
-          }
+      for (int u = 0; u < kSegSteps; ++u) {
+        fw[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes); fe[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 128u);
+        fn[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 256u);
+      }
+      __syncwarp();
+      ++r;
+      if (lane == 0) b2_st_release_smem(ctr + 3, r);
+#pragma unroll
+      for (int u = 0; u < kSegSteps; ++u) {
+        const uint32_t e = fe[u];
+        if (e != 0u && ((e >> kSegZShift) & 63u) == 0u) {                           // a DC symbol opens a block
+          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, size = adv - len;
+          const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
+          const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
+          const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+          const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
+          pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
+          dcbad |= (uint32_t)(dc + 32768) >> 16;
+          base[fn[u] * 64u + (((g0 + fn[u]) & 7u) << 3)] = (int16_t)dc;             // position 0 of chunk 0 ^ key
+          blk = blk + 1 == L.bpm ? 0 : blk + 1;
         }
       }
-      __syncwarp();                                     // every lane has read the round before it is handed back
-      ++r;
-      if (lane == 0) b2_st_release_smem(cons, r);
     }
     if (dcbad) err |= ST_DC_RANGE;
   }

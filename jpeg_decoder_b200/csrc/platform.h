@@ -49,6 +49,11 @@ B2_DEVICE void b2_cp_async16(void *dst, const void *src) {
 B2_DEVICE void b2_cp_async4(void *dst, const void *src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
 }
+// predicated 4-byte copy to a shared WINDOW address: no branch around it
+B2_DEVICE void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) {
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %0, 0;\n@p cp.async.ca.shared.global [%1], [%2], 4;\n}" ::"r"((int)on), "r"(dst_smem),
+               "l"(__cvta_generic_to_global(src)) : "memory");
+}
 B2_DEVICE void b2_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> B2_DEVICE void b2_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -94,6 +99,8 @@ B2_DEVICE uint32_t b2_ld_acquire_smem(const uint32_t *p) {
 B2_DEVICE void b2_st_release_smem(uint32_t *p, uint32_t v) {
   asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"(b2_smem_addr(p)), "r"(v) : "memory");
 }
+// a waiting warp must not hammer the LSU of the sub-partition it shares with the warp it waits for
+B2_DEVICE void b2_backoff(unsigned ns) { __nanosleep(ns); }
 // ---- dynamic shared memory through 32-bit window addresses (register + immediate addressing, no
 //      generic-pointer arithmetic in inner loops) ----
 B2_DEVICE uint32_t b2_dsm_addr(const void *p) { return b2_smem_addr(p); }

@@ -256,6 +256,7 @@ static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
 }
 static inline float b2_trunc_small(float x) { return truncf(x); }
+static inline void b2_backoff(unsigned) { std::this_thread::yield(); }
 // 32-bit window addresses of the CTA's dynamic shared memory
 static inline unsigned char *b2_dsm_base() {
   return reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(emu::cta()->dyn_smem.data()) + 127) & ~uintptr_t(127));
@@ -265,6 +266,7 @@ static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_base()
 static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_base() + a, &v, 4); }
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
 static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
+static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) memcpy(b2_dsm_base() + dst_smem, src, 4); }
 static inline uint32_t b2_ld_acquire_smem(const uint32_t *p) {
   std::this_thread::yield();                    // callers spin on it: one OS thread per CUDA thread here
   return __atomic_load_n(p, __ATOMIC_ACQUIRE);
