@@ -179,6 +179,7 @@ static inline unsigned __ballot_sync(unsigned, int p) {
   w.bar->arrive_and_wait();
   return m;
 }
+static inline void __threadfence() { __atomic_thread_fence(__ATOMIC_SEQ_CST); }
 static inline int __any_sync(unsigned m, int p) { return __ballot_sync(m, p) != 0; }
 static inline int __all_sync(unsigned m, int p) {
   const unsigned b = __ballot_sync(m, p);
