@@ -145,7 +145,7 @@ struct PixUni {
   int32_t mcux, tpr, tpi;       // MCUs per row, tiles per MCU row, tiles per image
   int32_t width, height, qkey;
   uint32_t pitch;
-  uint32_t pad;
+  uint32_t tmap_ok;             // the launch carries a tensor map of the group's RGB output (whole-tile TMA stores)
   uint64_t magic_tpi, magic_tpr;   // ceil(2^40 / d): n / d == (n * magic) >> 40 for n < 2^24, d < 2^16
   int64_t coef_base0, coef_stride; // blocks
   uint64_t rgb_off0, rgb_stride;   // bytes
@@ -200,7 +200,7 @@ template <int HS, int VS, int NC>
 B2_GLOBAL void __launch_bounds__(kPixThreads, (PixCfg<HS, VS, NC>::kMinCtas))
 k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, const int32_t *__restrict__ grp_pre,
         int ngrp, const PixUni uni, const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
-        const int16_t *__restrict__ coef, uint8_t *__restrict__ rgb) {
+        const int16_t *__restrict__ coef, uint8_t *__restrict__ rgb, const B2_GRID_CONSTANT B2TensorMap tmap) {
   typedef PixCfg<HS, VS, NC> C;
   B2_DYN_SMEM(unsigned char, smraw);
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -413,7 +413,15 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
       // (source read) before the stage buffer is handed back to the load pipeline
       b2_fence_proxy_async();
       __syncwarp();
-      if (gx0 < width && lane < rows && rowb > 0) {
+      if (uni.tmap_ok) {
+        // the whole tile in one instruction: box kRowBytes x kH at (byte column / 4, row, image); rows past the
+        // image's height and columns past its pitch are clipped by the TMA unit
+        if (lane == 0 && gx0 < width && rows > 0) {
+          b2_tensor_store_3d(&tmap, st_cur, gx0 * 3 / 4, gy0, cur.img - uni.img0);
+          b2_bulk_commit();
+          b2_bulk_wait_read();
+        }
+      } else if (gx0 < width && lane < rows && rowb > 0) {
         b2_bulk_store(gbase + (uint64_t)lane * pitch, st_cur + lane * C::kRowBytes, (uint32_t)rowb);
         b2_bulk_commit();
         b2_bulk_wait_read();

@@ -168,10 +168,45 @@ struct Pipeline {
 #endif
   }
 
+  // Tensor map of a uniform group's RGB output: u32 elements, dims (pitch/4, height, images), strides (pitch,
+  // image stride); box = one pixel tile.  The pixel kernel then stores a tile with one TMA instruction.
+  B2TensorMap tmap[PF_COUNT];
+  template <int HS, int VS, int NC>
+  void make_tmap(int f) {
+    plan.uni[f].tmap_ok = 0;
+#ifndef B200JPEG_EMU
+    typedef PixCfg<HS, VS, NC> C;
+    const PixUni &u = plan.uni[f];
+    if (!u.enabled || plan.grp_img[f].empty()) return;
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+      void *fn = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) { cudaGetLastError(); return; }
+      encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const uint64_t nimg = plan.grp_img[f].size();
+    const uint64_t istride = nimg > 1 ? u.rgb_stride : align_up((size_t)u.pitch * u.height, 256);
+    if ((u.pitch & 15u) || (istride & 15u) || C::kRowBytes / 4 > 256) return;
+    const cuuint64_t dims[3] = {u.pitch / 4, (cuuint64_t)u.height, nimg};
+    const cuuint64_t strides[2] = {u.pitch, istride};
+    const cuuint32_t box[3] = {(cuuint32_t)(C::kRowBytes / 4), (cuuint32_t)C::kH, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = encode(&tmap[f].map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, d_rgb.as<uint8_t>() + u.rgb_off0, dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r == CUDA_SUCCESS) plan.uni[f].tmap_ok = 1;
+#endif
+  }
+
   template <int HS, int VS, int NC>
   void launch_pixel(int f) {
+    if (plan.grp_img[f].empty()) return;
+    make_tmap<HS, VS, NC>(f);
     const BatchPlan &P = plan;
-    if (P.grp_img[f].empty()) return;
     const int ngrp = (int)P.grp_img[f].size();
     const int tiles = P.grp_pre[f].back();
     const size_t smem = PixCfg<HS, VS, NC>::kSmemBytes;
@@ -182,7 +217,7 @@ struct Pipeline {
     if (grid <= 0) return;
     B2_LAUNCH((k_pixel<HS, VS, NC>), grid, kPixThreads, smem, be.stream, d_imgs.as<ImageDev>(),
               d_grp_img[f].as<int32_t>(), d_grp_pre[f].as<int32_t>(), ngrp, P.uni[f], d_tsets.as<TableSet>(),
-              d_out.as<ImageOut>(), d_coef.as<int16_t>(), d_rgb.as<uint8_t>());
+              d_out.as<ImageOut>(), d_coef.as<int16_t>(), d_rgb.as<uint8_t>(), tmap[f]);
     ++launches;
   }
 

@@ -11,7 +11,10 @@
 
 #ifndef B200JPEG_EMU
 // ------------------------------------------------------------------ CUDA
+#include <cuda.h>
 #include <cuda_runtime.h>
+struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__grid_constant__)
+#define B2_GRID_CONSTANT __grid_constant__
 #define B2_DEVICE __device__ __forceinline__
 #define B2_HD __host__ __device__ __forceinline__
 #define B2_MEMBER __device__ __forceinline__
@@ -76,6 +79,12 @@ B2_DEVICE void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t
 B2_DEVICE void b2_bulk_store(void *dst, const void *src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                ::"l"(__cvta_generic_to_global(dst)), "r"(b2_smem_addr(src)), "r"(bytes) : "memory");
+}
+// shared -> global TILE store through a 3-D tensor map (cp.async.bulk.tensor, SASS UTMASTG): one instruction
+// moves a whole box (rows x bytes) and clips it at the tensor's bounds; issued by ONE lane
+B2_DEVICE void b2_tensor_store_3d(const void *tmap, const void *src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];"
+               ::"l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(b2_smem_addr(src)) : "memory");
 }
 B2_DEVICE void b2_bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 B2_DEVICE void b2_bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

@@ -251,6 +251,9 @@ static inline void b2_cp_async4(void *dst, const void *src) { memcpy(dst, src, 4
 static inline void b2_cp_async_commit() {}
 template <int N> static inline void b2_cp_async_wait() {}
 static inline void b2_bulk_store(void *dst, const void *src, uint32_t bytes) { memcpy(dst, src, bytes); }
+struct B2TensorMap { int unused; };                     // the emulation always takes the row-by-row store
+#define B2_GRID_CONSTANT
+static inline void b2_tensor_store_3d(const void *, const void *, int, int, int) {}
 static inline void b2_bulk_commit() {}
 static inline void b2_bulk_wait_read() {}
 static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
