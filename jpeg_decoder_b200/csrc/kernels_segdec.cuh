@@ -66,7 +66,9 @@ constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter wit
 #define B2_SEG_POLL_NS 200
 #endif
 constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
-constexpr int kSegZShift = 18;                // the zig-zag index before the symbol rides in bits 18..23 of the entry
+// third FIFO word of a step: zig-zag index before the symbol | two symbols taken << 6 | block number << 7
+constexpr uint32_t kSegPairBit = 1u << 6;
+constexpr int kSegNbShift = 7;
 // per group: window ring | FIFO | per-lane table addresses by block-in-MCU | counters
 constexpr int kSegGroupWords = kSegWords * 32 + kSegFifo * kSegRoundBytes / 4 + kMaxBpm * 32 + 32;
 
@@ -130,13 +132,13 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   const SegLane L = seg_lane(unit, imgs, out);
   uint32_t err = 0;
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
-  const uint32_t fifo_a = b2_dsm_addr(fifo) + 4u * (uint32_t)lane;
+  const uint32_t fifo_a = b2_dsm_addr(fifo) + 4u * (uint32_t)lane, lut_a = b2_dsm_addr(lut);
   int16_t *const base = coef + L.gb * 64;          // block 0 of the segment; block n, coefficient pos: base[n*64 + (pos ^ key(n))]
   const uint32_t g0 = (uint32_t)L.gb & 7u;         // key(n) = ((g0 + n) & 7) << 3
 
   if (role == 0) {
     // =========================== the chain: codes only ===========================
-    const uint32_t lut_a = b2_dsm_addr(lut), ring_a = b2_dsm_addr(ringl), tb_a = b2_dsm_addr(tb) + 4u * (uint32_t)lane;
+    const uint32_t ring_a = b2_dsm_addr(ringl), tb_a = b2_dsm_addr(tb) + 4u * (uint32_t)lane;
     uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
     const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
     const uint32_t total = L.live ? (uint32_t)(L.bend - L.bidx) : 0u;
@@ -197,10 +199,13 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
           if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
         }
         b2_sts(slot_a + (uint32_t)u * kSegStepBytes, w);
-        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 128u, e | (z << kSegZShift));
-        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 256u, nb);
-        p += e & 31u;
-        z += (e >> 10) & 127u;
+        // an AC entry may describe TWO symbols (kernels_huff.cuh); both are taken unless the first ends the block
+        const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
+        const bool pair = a2 != 0u && z + z1 < 64u;
+        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 128u, e);
+        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 256u, z | (pair ? kSegPairBit : 0u) | (nb << kSegNbShift));
+        p += huff_adv(e) + (pair ? a2 : 0u);
+        z += z1 + (pair ? huff_zinc2(e) : 0u);
         // ---- block end without a branch: some lane ends a block in four steps out of five ----
         const bool end = z >= 64u;
         const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
@@ -243,17 +248,30 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       if (lane == 0) b2_st_release_smem(ctr + role, r + 2u);
 #pragma unroll
       for (int u = 0; u < kSegSteps; ++u) {
-        const uint32_t e = fe[u], z = (e >> kSegZShift) & 63u;
-        if (z != 0u) {                                  // an AC symbol (entry 0 and DC symbols carry z = 0)
-          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, zn = z + ((e >> 10) & 127u);
+        const uint32_t e = fe[u], z = fn[u] & 63u, nblk = fn[u] >> kSegNbShift;
+        if (z != 0u) {                                  // AC (entry 0 and DC symbols carry z = 0)
+          int16_t *const bp = base + nblk * 64u;
+          const uint32_t key = ((g0 + nblk) & 7u) << 3;
+          const uint32_t adv = huff_adv(e), len = huff_len(e), zn = z + huff_zinc(e);
           const uint32_t size = adv - len;
           // EXTEND (jpeg.cpp:388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
           const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
           const int val = (int)v - (v + v > t ? 0 : (int)t);
           const uint32_t pos = zn - 1u;                                             // z + run
-          if (size != 0u && pos < 64u) base[fn[u] * 64u + (pos ^ (((g0 + fn[u]) & 7u) << 3))] = (int16_t)val;
+          if (size != 0u && pos < 64u) bp[pos ^ key] = (int16_t)val;
           // EOB, or the index ran to 64; a run that reaches past 63 is an error (jpeg.cpp:372-376)
           if (zn >= 64u && !(e & kHEob) && !(size != 0u && zn == 64u)) err |= ST_BAD_RUN;
+          if (fn[u] & kSegPairBit) {
+            // the second symbol of the entry: its bits follow the first one's; its details come from the same table
+            const uint32_t w2 = fw[u] << adv;
+            const uint32_t e2 = b2_lds(lut_a + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+            const uint32_t adv2 = huff_adv(e2), len2 = huff_len(e2), zn2 = zn + huff_zinc(e2), size2 = adv2 - len2;
+            const uint32_t v2 = b2_shr(w2 << len2, 32u - size2), t2 = b2_shl(1u, size2) - 1u;
+            const int val2 = (int)v2 - (v2 + v2 > t2 ? 0 : (int)t2);
+            const uint32_t pos2 = zn2 - 1u;
+            if (size2 != 0u && pos2 < 64u) bp[pos2 ^ key] = (int16_t)val2;
+            if (zn2 >= 64u && !(e2 & kHEob) && !(size2 != 0u && zn2 == 64u)) err |= ST_BAD_RUN;
+          }
         }
       }
       r += 2u;
@@ -281,15 +299,15 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
 #pragma unroll
       for (int u = 0; u < kSegSteps; ++u) {
         const uint32_t e = fe[u];
-        if (e != 0u && ((e >> kSegZShift) & 63u) == 0u) {                           // a DC symbol opens a block
-          const uint32_t adv = e & 31u, len = (e >> 5) & 31u, size = adv - len;
+        if (e != 0u && (fn[u] & 63u) == 0u) {                                       // a DC symbol opens a block
+          const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len, nblk = fn[u] >> kSegNbShift;
           const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
           const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
           const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
           const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
           pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
           dcbad |= (uint32_t)(dc + 32768) >> 16;
-          base[fn[u] * 64u + (((g0 + fn[u]) & 7u) << 3)] = (int16_t)dc;             // position 0 of chunk 0 ^ key
+          base[nblk * 64u + (((g0 + nblk) & 7u) << 3)] = (int16_t)dc;               // position 0 of chunk 0 ^ key
           blk = blk + 1 == L.bpm ? 0 : blk + 1;
         }
       }
