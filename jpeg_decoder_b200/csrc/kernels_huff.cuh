@@ -86,7 +86,7 @@ B2_HD uint32_t huff_search(const HuffSpec &spec, const HuffCanon &c, uint32_t w1
   return huff_entry(16, 16, 64, kHBadCode | kHEob);                         // jpeg.cpp:319 "return -1"
 }
 // resolves a code the tables could not (kHOverflow): straight from the DHT data in global memory
-B2_DEVICE uint32_t huff_slow(const HuffSpec &spec, uint32_t w16, bool is_dc) {
+B2_COLD uint32_t huff_slow(const HuffSpec &spec, uint32_t w16, bool is_dc) {
   HuffCanon c;
   huff_canon(spec, c);
   return huff_search(spec, c, w16, kHLutBits + 1, 16, is_dc);

@@ -62,9 +62,13 @@ constexpr int kSegSteps = 8;                  // symbols per lane and round: the
 constexpr int kSegStepBytes = 3 * 128;        // one step: (window, entry, block number) x 32 lanes
 constexpr int kSegRoundBytes = kSegSteps * kSegStepBytes;
 constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter with the last round
+#ifndef B2_SEG_UNROLL
+#define B2_SEG_UNROLL 2
+#endif
 #ifndef B2_SEG_POLL_NS
 #define B2_SEG_POLL_NS 200
 #endif
+constexpr int kSegUnroll = B2_SEG_UNROLL;      // how far the decoder's step loop is unrolled (instruction-cache footprint)
 constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
 // third FIFO word of a step: zig-zag index before the symbol | two symbols taken << 6 | block number << 7
 constexpr uint32_t kSegPairBit = 1u << 6;
@@ -176,7 +180,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       // newest groups must have landed -- copies issued two rounds (16 steps) ago
       b2_cp_async_wait<2>();
       const uint32_t slot_a = fifo_a + (rounds & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
-#pragma unroll
+#pragma unroll kSegUnroll
       for (int u = 0; u < kSegSteps; ++u) {
         // a finished lane keeps stepping in place: its entry is forced to 0 (no advance, nothing for the writers)
         const uint32_t t = b2_lds(tba);                                              // table offsets of this block: DC | AC << 16

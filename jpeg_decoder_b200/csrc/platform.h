@@ -18,6 +18,7 @@ struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__
 #define B2_DEVICE __device__ __forceinline__
 #define B2_HD __host__ __device__ __forceinline__
 #define B2_MEMBER __device__ __forceinline__
+#define B2_COLD __device__ __noinline__            /* rare paths stay out of the hot loops' instruction footprint */
 #define B2_GLOBAL __global__
 #define B2_SHARED __shared__
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \

@@ -104,6 +104,7 @@ inline unsigned linear_tid() {
 #define B2_DEVICE static inline
 #define B2_HD static inline
 #define B2_MEMBER inline
+#define B2_COLD static
 #define B2_GLOBAL static
 #define B2_SHARED static
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
