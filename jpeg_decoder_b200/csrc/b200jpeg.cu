@@ -135,6 +135,7 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
   int chunk = (n + 7) / 8;
   if (chunk < 8) chunk = 8;
   if (chunk > 64) chunk = 64;
+  if (const char *ev = getenv("B200JPEG_CHUNK")) { const int v = atoi(ev); if (v > 0) chunk = v; }   // tuning knob (images per chunk)
   if (coef_out || n <= chunk) {
     int rc = b200jpeg_batch_prepare(c, descs, n, files, sizes);
     if (rc) return rc;

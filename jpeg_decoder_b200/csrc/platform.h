@@ -120,6 +120,62 @@ B2_DEVICE uint32_t b2_lds(uint32_t a) {
   return v;
 }
 B2_DEVICE void b2_sts(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+// load of data that does not change while the caller's loop runs (lookup tables), or whose producer is ordered by
+// other means (cp.async groups): NOT volatile and no memory clobber, so the compiler may schedule it freely --
+// hoist the next step's loads over this step's stores.  The address must come out of b2_launder() placed after
+// whatever made the data visible, or the load could be moved in front of that.
+B2_DEVICE uint32_t b2_lds_ro(uint32_t a) {
+  uint32_t v;
+  asm("ld.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+B2_DEVICE uint4 b2_lds_v4(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared::cta.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+  return v;
+}
+B2_DEVICE void b2_sts_v4(uint32_t a, uint4 v) {
+  asm volatile("st.shared::cta.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// ---- thread-block clusters: distributed shared memory between the CTAs of a cluster ----
+B2_DEVICE uint32_t b2_cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+B2_DEVICE uint32_t b2_cluster_id_x() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
+// the shared::cluster address of what sits at window address `a` in CTA `rank` of the cluster
+B2_DEVICE uint32_t b2_mapa(uint32_t a, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+  return r;
+}
+B2_DEVICE void b2_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// 16 bytes into ANOTHER CTA's shared memory; the store completes 16 bytes of the transaction count of an mbarrier
+// over there: no fence and no release on the producer's side, the consumer's wait on the barrier sees the data
+B2_DEVICE void b2_st_async_v4(uint32_t raddr, uint4 v, uint32_t rbar) {
+  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(raddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(rbar) : "memory");
+}
+B2_DEVICE void b2_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+B2_DEVICE void b2_mbar_arrive_remote(uint32_t rbar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar) : "memory");
+}
+B2_DEVICE void b2_mbar_init_a(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+B2_DEVICE void b2_mbar_wait_a(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "B2_WAITA:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra B2_DONEA;\n"
+      "bra B2_WAITA;\n"
+      "B2_DONEA:\n"
+      "}" ::"r"(bar), "r"(parity) : "memory");
+}
+B2_DEVICE uint32_t b2_launder(uint32_t v) { asm volatile("" : "+r"(v) :: "memory"); return v; }
 // shifts that give 0 for counts >= 32 (PTX semantics; undefined in C++)
 B2_DEVICE uint32_t b2_shr(uint32_t v, uint32_t n) { uint32_t r; asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
 B2_DEVICE uint32_t b2_shl(uint32_t v, uint32_t n) { uint32_t r; asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }

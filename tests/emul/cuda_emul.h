@@ -269,6 +269,10 @@ static inline unsigned char *b2_dsm_base() {
 static inline uint32_t b2_dsm_addr(const void *p) { return (uint32_t)(reinterpret_cast<const unsigned char *>(p) - b2_dsm_base()); }
 static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_base() + a, 4); return v; }
 static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_base() + a, &v, 4); }
+static inline uint32_t b2_lds_ro(uint32_t a) { return b2_lds(a); }
+static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_base() + a, 16); return v; }
+static inline void b2_sts_v4(uint32_t a, uint4 v) { memcpy(b2_dsm_base() + a, &v, 16); }
+static inline uint32_t b2_launder(uint32_t v) { return v; }
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
 static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
 static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) memcpy(b2_dsm_base() + dst_smem, src, 4); }
