@@ -22,21 +22,31 @@
 //     PREDICATE once every four steps -- four steps consume at most 108 bits, one top-up brings 128;
 //   * DC and AC tables are looked up together and selected afterwards.
 //
-// (2) Only what the chain needs stays on the chain.  A segment is worked on by FOUR warps of the same CTA
-//     (32 segments each):
+// (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by several warps of the
+//     same CTA:
 //       decoder   walks the codes -- window, table entry, advance, block/table bookkeeping -- and pushes
-//                 (window, entry | zig-zag index, block number) per lane and step into a shared-memory FIFO;
-//       writer A/B take the even / the odd rounds of the FIFO and place the AC coefficients: magnitude
-//                 extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store.  They keep no state
-//                 between symbols -- everything they need is in the FIFO entry -- so two of them (or more)
-//                 work in parallel;
+//                 (window, entry, zig-zag index | block number) per lane and step into a shared-memory FIFO;
+//       AC writers take every kSegAcW-th round of the FIFO: magnitude extension (jpeg.cpp:388-397), zig-zag
+//                 position.  They keep no state between symbols -- everything they need is in the FIFO entry;
 //       DC warp   sees every round but only the DC symbols: extension, prediction per component
-//                 (jpeg.cpp:335-345), store, range check.
-//     The warps run on the idle issue slots of their sub-partitions in parallel; the dependent chain per
-//     symbol is what the decoder alone executes.  Hand-over is a producer counter and one consumer counter
-//     per warp (st.release / ld.acquire in shared memory), one update per round of four steps.
-//     The coefficient buffer is zero-filled beforehand (a memset on a side stream, pipeline_run.h): MCU[] is
-//     value-initialised in the reference (jpeg.cpp:407) and the warps only store what is not zero.
+//                 (jpeg.cpp:335-345), range check -- and it FLUSHES finished blocks.
+//     Hand-over is a producer counter and one consumer counter per warp (st.release / ld.acquire in shared
+//     memory), one update per round.
+//
+// (3) Coefficients leave the SM as whole 128-byte blocks.  A 2-byte store per coefficient from 32 lanes that work on
+//     32 different segments is 32 sectors per instruction: one L1 tag cycle each (233 M sectors per bench step = 0.8 ms
+//     of every SM's load/store path, in front of which the decoder's shared-memory loads queue), a read-modify-write
+//     in L2 for every sector, and a 1.6 GB memset beforehand because only non-zero values were stored.  Instead the
+//     writers put the values into a per-lane ring of kSegAsm block images in SHARED memory (st.shared.u16), and the
+//     DC warp, once a round's AC writer is through, copies the blocks that round finished to global memory with
+//     128-bit stores -- eight lanes per block, full lines, zeros included, no memset, no read-modify-write -- and
+//     clears the images.  A writer checks, per lane, that the blocks of its round are less than kSegAsm ahead of the
+//     flushed ones (they almost always are: a lane finishes 0.65 blocks per round) and waits otherwise.
+//
+//     Tried and dropped: decoders and consumers on different SMs (thread-block clusters, FIFO through DSMEM with
+//     st.async + mbarrier transaction counts).  It works, but a consumer SM then carries the scattered stores of
+//     eight groups (1.74 ms of tag cycles alone, measured 4.1 ms), and with block assembly its shared memory does not
+//     hold eight groups' images (profiles/r01e_segdec_experiments.md).
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -45,28 +55,19 @@
 
 namespace b2 {
 
-#ifndef B2_SEG_PAIRS
-#define B2_SEG_PAIRS 2
+#ifndef B2_SEG_GROUPS
+#ifdef B200JPEG_EMU
+#define B2_SEG_GROUPS 2
+#else
+#define B2_SEG_GROUPS 4
+#endif
 #endif
 #ifndef B2_SEG_FIFO
-#define B2_SEG_FIFO 4
+#define B2_SEG_FIFO 2
 #endif
-constexpr int kSegPairs = B2_SEG_PAIRS;       // groups of four warps (decoder, writer A, writer B, DC) per CTA
 #ifndef B2_SEG_ACW
 #define B2_SEG_ACW 2
 #endif
-constexpr int kSegAcW = B2_SEG_ACW;           // AC writer warps per group: writer w takes the rounds r with r % kSegAcW == w
-constexpr int kSegRoles = kSegAcW + 2;        // decoder, AC writers, DC warp
-constexpr int kSegThreads = kSegPairs * kSegRoles * 32;   // threads per CTA of k_entropy_seg
-constexpr int kSegUnits = kSegPairs * 32;     // segments per CTA
-constexpr uint32_t kSegNoUnit = 0xffffffffu;
-constexpr int kSegWords = 32;                 // stream words per lane in the window ring
-constexpr int kSegFifo = B2_SEG_FIFO;         // rounds the FIFO holds
-constexpr int kSegSteps = 8;                  // symbols per lane and round: the per-round work (top-up, hand-over) is paid once per 8 steps
-constexpr int kSegStepBytes = 3 * 128;        // one step: (window, entry, block number) x 32 lanes
-constexpr int kSegSlots = kSegSteps + 1;      // FIFO slots per round: the steps + one for symbols the first-level table does not resolve
-constexpr int kSegRoundBytes = kSegSlots * kSegStepBytes;
-constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter with the last round
 #ifndef B2_SEG_UNROLL
 #define B2_SEG_UNROLL 2
 #endif
@@ -74,26 +75,43 @@ constexpr uint32_t kSegFin = 0x80000000u;     // set in the producer counter wit
 #define B2_SEG_POLL_NS 200
 #endif
 #ifndef B2_SEG_DIAG
-#define B2_SEG_DIAG 0     // measurements only: 1 = consumers acknowledge rounds without working on them, 2 = decoder alone (no FIFO)
+#define B2_SEG_DIAG 0     // measurements only: 4 = DC warp does not compute, 5 = AC writers do not compute
 #endif
-#ifndef B2_SEG_ROLEMAP
-#define B2_SEG_ROLEMAP 0  // 0: warp = role * pairs + pair; 1: roles rotated per pair so that the decoders sit on different sub-partitions
-#endif
-#if B2_SEG_DIAG == 3       // 3 = everything but the AC stores (the condition keeps the arithmetic alive)
-#define B2_SEG_NOSTORE(w) && (w) == 0x12345678u
-#else
-#define B2_SEG_NOSTORE(w)
-#endif
-constexpr int kSegUnroll = B2_SEG_UNROLL;      // how far the decoder's step loop is unrolled (instruction-cache footprint)
+constexpr int kSegGroups = B2_SEG_GROUPS;     // groups (32 segments: one decoder warp + its consumers) per CTA
+constexpr int kSegAcW = B2_SEG_ACW;           // AC writer warps per group: writer w takes the rounds r with r % kSegAcW == w
+constexpr int kSegRoles = kSegAcW + 3;        // decoder, AC writers, DC warp, flusher
+constexpr int kSegThreads = kSegGroups * kSegRoles * 32;   // threads per CTA of k_entropy_seg
+constexpr int kSegUnits = kSegGroups * 32;    // segments per CTA
+constexpr uint32_t kSegNoUnit = 0xffffffffu;
+constexpr int kSegWords = 32;                 // stream words per lane in the window ring (+ one slot that repeats slot 0)
+constexpr int kSegFifo = B2_SEG_FIFO;         // rounds the FIFO holds
+constexpr int kSegSteps = 8;                  // symbols per lane and round: the per-round work (top-up, hand-over) is paid once per 8 steps
+constexpr int kSegSlots = kSegSteps + 1;      // FIFO slots per round: the steps + one for symbols the first-level table does not resolve
+constexpr int kSegSlotBytes = 3 * 128;        // one slot: (window, entry, zig-zag index | block number) x 32 lanes
+constexpr int kSegRoundBytes = kSegSlots * kSegSlotBytes + 128;   // + per lane: blocks finished after the round << 1 | decoder has finished
+constexpr int kSegAsm = 8;                    // block images per lane in the assembly ring; a round touches at most 6 blocks of a lane
+constexpr int kSegUnroll = B2_SEG_UNROLL;     // how far the decoder's step loop is unrolled (instruction-cache footprint)
 constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
 // third FIFO word of a step: zig-zag index before the symbol | two symbols taken << 6 | block number << 7
 constexpr uint32_t kSegPairBit = 1u << 6;
 constexpr int kSegNbShift = 7;
-// per group: window ring | FIFO | per-lane table addresses by block-in-MCU | counters
-constexpr int kSegGroupWords = (kSegWords + 1) * 32 + kSegFifo * kSegRoundBytes / 4 + kMaxBpm * 32 + 32;
+constexpr uint32_t kSegFinFlag = 1u;
+static_assert((kSegFifo & (kSegFifo - 1)) == 0 && (kSegAsm & (kSegAsm - 1)) == 0, "ring sizes are powers of two");
+static_assert(kSegAsm >= (kSegSlots + 1) / 2 + 1, "the blocks one round touches must fit the assembly ring");
+
+// shared memory of a group (32-bit words), after the CTA's copy of the lookup tables:
+//   window ring | per-lane table offsets by block-in-MCU | FIFO | block images [image][lane][32 words] |
+//   flushed-block count per lane | counters
+constexpr int kSegOffTb = (kSegWords + 1) * 32;
+constexpr int kSegOffFifo = kSegOffTb + kMaxBpm * 32;
+constexpr int kSegOffAsm = kSegOffFifo + kSegFifo * kSegRoundBytes / 4;
+constexpr int kSegOffFl = kSegOffAsm + kSegAsm * 32 * 32;
+constexpr int kSegOffCtr = kSegOffFl + 32;
+constexpr int kSegGroupWords = kSegOffCtr + 32;
+static_assert(kSegOffFifo % 4 == 0 && kSegOffAsm % 4 == 0 && kSegGroupWords % 4 == 0, "16-byte alignment of the FIFO and the block images");
 
 B2_HD size_t segdec_smem_bytes() {
-  return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegPairs * kSegGroupWords);
+  return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegGroups * kSegGroupWords);
 }
 
 // What every warp of a group knows about a lane's segment before the first symbol.
@@ -109,37 +127,339 @@ B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, 
   if (unit.x == kSegNoUnit) return L;
   L.img = (int)unit.x;
   const ImageDev &im = imgs[L.img];
-  if (out[L.img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT)) return L;   // nothing to decode
   const int k = (int)unit.y;
   L.bpm = im.bpm; L.nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
   const int seg_blocks = im.restart_interval * L.bpm;                                  // 0 when there is one segment
   L.bidx = k * seg_blocks;
   L.bend = (k + 1 < im.nseg) ? L.bidx + seg_blocks : im.nblocks;
   L.gb = im.coef_base + L.bidx;
-  L.live = L.bidx < L.bend;
+  // a scan stage U gave up on is not decoded: its blocks read zero
+  L.live = L.bidx < L.bend && !(out[L.img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT));
   return L;
 }
 
-// units[u] = (image, segment); the units of one CTA share a table set (the planner pads each
-// table-set group to a multiple of kSegUnits with kSegNoUnit).  d_us / seg_start: stage U's output.
+// ------------------------------------------------------------------ the FIFO between a decoder and its consumers
+// Round r lives at (r % kSegFifo) * kSegRoundBytes: kSegSlots slots of three words x 32 lanes, then one word per lane
+// (blocks finished after the round << 1 | kSegFinFlag).  ctr[0] rounds produced; ctr[1 + w] next round AC writer w
+// will READ, ctr[1 + kSegAcW] the same for the DC warp, ctr[2 + kSegAcW] for the flusher; ctr[kSegWorked + w] next round
+// AC writer w will WORK on (all its earlier rounds are in the block images), ctr[kSegWorked + kSegAcW] the same for the
+// DC warp.  st.release / ld.acquire in shared memory.
+constexpr int kSegReaders = kSegAcW + 2;      // AC writers, DC warp, flusher
+constexpr int kSegWorked = 1 + kSegReaders;   // first "worked" counter
+struct SegFifo {
+  uint32_t fifo_a;           // window address of slot 0 of round 0, this lane
+  uint32_t *ctr;
+  B2_MEMBER uint32_t round_a(uint32_t r) const { return fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes; }
+  // ---- producer ----
+  B2_MEMBER uint32_t readers() const {                           // the round every reader is past
+    uint32_t m = b2_ld_acquire_smem(ctr + 1);
+#pragma unroll
+    for (int c = 2; c <= kSegReaders; ++c) { const uint32_t v = b2_ld_acquire_smem(ctr + c); m = v < m ? v : m; }
+    return m;
+  }
+  B2_MEMBER void wait_room(uint32_t r, uint32_t m) const {       // round r may be written once every reader is past round r - kSegFifo
+    while ((int)(r - m) >= kSegFifo) { b2_backoff(kSegPollNs); m = readers(); }
+  }
+  B2_MEMBER void publish(uint32_t produced, int lane) const {    // every lane's stores of the round are ordered before lane 0's release
+    __syncwarp();
+    if (lane == 0) b2_st_release_smem(ctr, produced);
+  }
+  // ---- consumers ----
+  B2_MEMBER void wait(uint32_t r) const { while (b2_ld_acquire_smem(ctr) <= r) b2_backoff(kSegPollNs); }
+  B2_MEMBER void release(int who, uint32_t next, int lane) const {   // the warp has the round in registers
+    __syncwarp();
+    if (lane == 0) b2_st_release_smem(ctr + who, next);
+  }
+};
+
+// =========================== the chain: codes only ===========================
+// The eight steps of a round are ONE basic block: no branch, table and window loads that the compiler may
+// schedule freely (b2_lds_ro), so the off-chain work of step i overlaps the chain of step i+1.  What needs a
+// branch is taken out of the steps: a lane that meets an entry the first-level table cannot resolve (code longer
+// than kHLutBits -- one symbol in 200 --, an error entry) STAYS where it is for the rest of the round (its
+// entries read 0: no advance, nothing for the consumers) and the symbol is resolved after the last step, in the
+// round's extra slot.
+B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 unit, const ImageDev *__restrict__ imgs,
+                          const TableSet *__restrict__ tsets, const uint32_t *__restrict__ seg_start,
+                          const uint8_t *__restrict__ d_us, uint32_t *ringl, uint32_t *tb, uint32_t lut_a, uint32_t &err) {
+  uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
+  const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
+  const uint32_t total = L.live ? (uint32_t)(L.bend - L.bidx) : 0u;
+  bool done = !L.live;
+  if (L.live) {
+    const ImageDev &im = imgs[L.img];
+    for (int b = 0; b < L.bpm; ++b) {             // DC table td -> slot td, AC table ta -> slot 4+ta
+      const int c = b < L.nluma ? 0 : b - L.nluma + 1;
+      tb[b * 32 + lane] = (uint32_t)(im.td[c] & 3) * (kHTab * 4) | ((uint32_t)(4 + (im.ta[c] & 3)) * (kHTab * 4)) << 16;
+    }
+    us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
+    p = seg_start[im.seg_base + (int)unit.y];
+    pend = seg_start[im.seg_base + (int)unit.y + 1];
+    rw = (p >> 5) & ~3u;
+    for (int i = 0; i < kSegWords; ++i) {
+      b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
+      if (((rw + i) & (kSegWords - 1)) == 0u) b2_cp_async4(ringl + kSegWords * 32, us + rw + i);   // slot 32 repeats slot 0
+    }
+    rw += kSegWords;
+  } else tb[lane] = 0;
+  b2_cp_async_commit();
+  b2_cp_async_wait<0>();
+  __syncwarp();
+  // window addresses, taken AFTER the tables and the ring were filled (b2_lds_ro), and kept in registers
+  const uint32_t ring_a = b2_launder(b2_dsm_addr(ringl)), tb_a = b2_launder(b2_dsm_addr(tb) + 4u * (uint32_t)lane);
+  const uint32_t lut_r = b2_launder(lut_a);
+  const uint32_t tb_end = tb_a + (uint32_t)L.bpm * 128u;
+  uint32_t tba = tb_a;                             // this lane's table entry of the current block-in-MCU
+  uint32_t z = 0, nb = 0;                          // zig-zag index, blocks finished
+  // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
+  auto advance = [&](uint32_t e, uint32_t &fn) {
+    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
+    const bool pair = a2 != 0u && z + z1 < 64u;    // an AC entry may describe TWO symbols; both are taken unless the first ends the block
+    fn = z | (pair ? kSegPairBit : 0u) | (nb << kSegNbShift);
+    p += huff_adv(e) + (pair ? a2 : 0u);
+    z += z1 + (pair ? huff_zinc2(e) : 0u);
+    // ---- block end without a branch: some lane ends a block in four steps out of five ----
+    const bool end = z >= 64u;
+    const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
+    z = end ? 0u : z;
+    tba = end ? tbn : tba;
+    nb += end ? 1u : 0u;
+    // ---- once per lane: the segment is finished.  The last block ran past the segment's end (file.hpp:36-40),
+    //      or more than padding is left: the segment holds more blocks ----
+    const bool fin_now = end && nb == total;
+    const uint32_t fe = p > pend ? (uint32_t)ST_OVERRUN : (pend - p > 7u ? (uint32_t)ST_BLOCK_COUNT : 0u);
+    err |= fin_now ? fe : 0u;
+    done = done || fin_now;
+  };
+  uint32_t r = 0;
+  for (;; ++r) {
+    const uint32_t readers = ff.readers();         // read now, looked at after the top-up
+    // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
+    //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8 ----
+    const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) b2_cp_async4_if(need, ring_a + (((rw + i) & (kSegWords - 1)) << 7), us + rw + i);
+    // slot 32 repeats slot 0 (the window's second word is always at +128); rw is a multiple of 4
+    b2_cp_async4_if(need && (rw & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw);
+    b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
+    rw += need ? 8u : 0u;
+    b2_cp_async_commit();
+    ff.wait_room(r, readers);
+    const uint32_t slot_a = ff.round_a(r);
+    // rw is at least 25 words ahead of the window and the round needs at most 8 more: everything but the two
+    // newest groups must have landed -- copies issued two rounds (16 steps) ago
+    b2_cp_async_wait<2>();
+    uint32_t w = 0, cur = 0, eraw = 0;
+#pragma unroll kSegUnroll
+    for (int u = 0; u < kSegSteps; ++u) {
+      const uint32_t t = b2_lds_ro(tba);                                           // table offsets of this block: DC | AC << 16
+      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));                          // chosen while the window is still on its way
+      const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
+      const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
+      w = __funnelshift_l(w1, w0, p);
+      eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+      // a finished lane, and one that waits for the extra slot, step in place: entry 0
+      const uint32_t e = (done || eraw >= kHOverflow) ? 0u : eraw;
+      uint32_t fn;
+      advance(e, fn);
+      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes, w);
+      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, e);
+      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, fn);
+    }
+    // ---- the extra slot: whoever is waiting in front of a symbol the first-level table did not resolve ----
+    const bool stuck = !done && eraw >= kHOverflow;                                // then w, cur and eraw are still those of p
+    uint32_t e = 0, fn = 0;
+    if (__any_sync(0xffffffffu, stuck)) {
+      if (stuck) {
+        const bool is_dc = z == 0;
+        e = eraw;
+        if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+        if (e & kHOverflow) {
+          const ImageDev &im = imgs[L.img];
+          const int blk = (int)((tba - tb_a) >> 7), comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+          e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
+        }
+        if (e & kHBadCode) err |= ST_BAD_CODE;
+        if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
+        advance(e, fn);
+      }
+    }
+    const bool fin = __all_sync(0xffffffffu, done);
+    b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes, w);
+    b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 128u, e);
+    b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 256u, fn);
+    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | (fin ? kSegFinFlag : 0u));
+    ff.publish(r + 1u, lane);
+    if (fin) break;
+  }
+  // the AC writers whose turn did not come with the last round each get an empty one that tells them to stop
+  for (int k = 1; k < kSegAcW; ++k) {
+    ++r;
+    ff.wait_room(r, ff.readers());
+    const uint32_t slot_a = ff.round_a(r);
+    for (int u = 0; u < kSegSlots; ++u) { b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, 0u); b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, 0u); }
+    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | kSegFinFlag);
+    ff.publish(r + 1u, lane);
+  }
+}
+
+// a coefficient goes into the lane's image of block nblk: [image nblk % kSegAsm][lane][64 x int16], position ^ key as in
+// the global block (the pixel stage's swizzle), so an image is the block as it will sit in global memory
+B2_DEVICE uint32_t seg_asm_addr(uint32_t asm_a, uint32_t nblk, uint32_t pos_key) {
+  return asm_a + ((nblk & (uint32_t)(kSegAsm - 1)) << 12) + 2u * pos_key;
+}
+
+// =========================== AC coefficients: stateless, every kSegAcW-th round ===========================
+// magnitude extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store into the block image; everything a symbol
+// needs is in its FIFO entry, so the writers keep no state between symbols and several of them work in parallel.
+B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a, uint32_t asm_a, const uint32_t *fl,
+                             uint32_t g0, uint32_t &err) {
+  for (uint32_t r = (uint32_t)w;; r += (uint32_t)kSegAcW) {
+    ff.wait(r);
+    const uint32_t ra = ff.round_a(r);
+    uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
+#pragma unroll
+    for (int u = 0; u < kSegSlots; ++u) {
+      fw[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes); fe[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 128u);
+      fn[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
+    }
+    const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
+    ff.release(1 + w, r + (uint32_t)kSegAcW, lane);              // every lane has read the round before it is handed back
+    // the blocks of this round (the highest is the one in progress after it) must fit the ring of images in front of
+    // the flushed ones
+    while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);
+#pragma unroll
+    for (int u = 0; u < (B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
+      const uint32_t e = fe[u], z = fn[u] & 63u, nblk = fn[u] >> kSegNbShift;
+      if (z != 0u && e != 0u) {                       // AC (DC symbols carry z = 0, a lane that steps in place entry 0)
+        const uint32_t key = ((g0 + nblk) & 7u) << 3;
+        const uint32_t adv = huff_adv(e), len = huff_len(e), zn = z + huff_zinc(e);
+        const uint32_t size = adv - len;
+        // EXTEND (jpeg.cpp:388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
+        const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
+        const int val = (int)v - (v + v > t ? 0 : (int)t);
+        const uint32_t pos = zn - 1u;                                             // z + run
+        if (size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, nblk, pos ^ key), (uint32_t)val);
+        // EOB, or the index ran to 64; a run that reaches past 63 is an error (jpeg.cpp:372-376)
+        if (zn >= 64u && !(e & kHEob) && !(size != 0u && zn == 64u)) err |= ST_BAD_RUN;
+        if (fn[u] & kSegPairBit) {
+          // the second symbol of the entry: its bits follow the first one's; its details come from the same table
+          const uint32_t w2 = fw[u] << adv;
+          const uint32_t e2 = b2_lds(lut_a + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+          const uint32_t adv2 = huff_adv(e2), len2 = huff_len(e2), zn2 = zn + huff_zinc(e2), size2 = adv2 - len2;
+          const uint32_t v2 = b2_shr(w2 << len2, 32u - size2), t2 = b2_shl(1u, size2) - 1u;
+          const int val2 = (int)v2 - (v2 + v2 > t2 ? 0 : (int)t2);
+          const uint32_t pos2 = zn2 - 1u;
+          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, nblk, pos2 ^ key), (uint32_t)val2);
+          if (zn2 >= 64u && !(e2 & kHEob) && !(size2 != 0u && zn2 == 64u)) err |= ST_BAD_RUN;
+        }
+      }
+    }
+    ff.release(kSegWorked + w, r + (uint32_t)kSegAcW, lane);     // the round's values are in the block images
+    if (tail & kSegFinFlag) break;
+  }
+}
+
+// =========================== DC coefficients: prediction per component ===========================
+// sees every round but only the DC symbols: extension, prediction (jpeg.cpp:335-345), range check
+B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_a, const uint32_t *fl, uint32_t g0, uint32_t &err) {
+  int pred0 = 0, pred1 = 0, pred2 = 0;
+  int blk = 0;
+  uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
+  for (uint32_t r = 0;; ++r) {
+    ff.wait(r);
+    const uint32_t ra = ff.round_a(r);
+    uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
+#pragma unroll
+    for (int u = 0; u < kSegSlots; ++u) {
+      fw[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes); fe[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 128u);
+      fn[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
+    }
+    const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
+    ff.release(1 + kSegAcW, r + 1u, lane);
+    while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);   // room, as for the AC writers
+#pragma unroll
+    for (int u = 0; u < (B2_SEG_DIAG == 4 ? 0 : kSegSlots); ++u) {
+      const uint32_t e = fe[u];
+      if (e != 0u && (fn[u] & 63u) == 0u) {                                       // a DC symbol opens a block
+        const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len, nblk = fn[u] >> kSegNbShift;
+        const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
+        const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
+        const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+        const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
+        pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
+        dcbad |= (uint32_t)(dc + 32768) >> 16;
+        b2_sts_u16(seg_asm_addr(asm_a, nblk, ((g0 + nblk) & 7u) << 3), (uint32_t)dc);   // position 0 of chunk 0 ^ key
+        blk = blk + 1 == L.bpm ? 0 : blk + 1;
+      }
+    }
+    ff.release(kSegWorked + kSegAcW, r + 1u, lane);
+    if (tail & kSegFinFlag) break;
+  }
+  if (dcbad) err |= ST_DC_RANGE;
+}
+
+// =========================== the way out ===========================
+// Once a round's AC writer and the DC warp are through with it, the blocks the round finished leave: thread t moves
+// 16 bytes (t & 7) of the block of lane (t >> 3) + 4 i, i = 0..7 -- eight lanes per block, whole 128-byte lines -- and
+// clears the image.
+B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t *fl,
+                           uint4 *__restrict__ coef4) {
+  const uint32_t gblk = (uint32_t)L.gb;              // the coefficient buffer holds fewer than 2^32 blocks (512 GB)
+  if (__any_sync(0xffffffffu, !L.live && L.bidx < L.bend)) {
+    // a scan that is not decoded (stage U found it broken) still gets its blocks: zeros
+    if (!L.live)
+      for (uint32_t b = 0; b < (uint32_t)(L.bend - L.bidx); ++b)
+        for (int c = 0; c < 8; ++c) coef4[(size_t)(gblk + b) * 8 + c] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  uint32_t gsrc[8];                                  // first global block of the lanes this thread flushes for
+#pragma unroll
+  for (int i = 0; i < 8; ++i) gsrc[i] = __shfl_sync(0xffffffffu, gblk, (lane >> 3) + 4 * i);
+  uint32_t flushed = 0;                              // blocks of this lane that have left
+  for (uint32_t r = 0;; ++r) {
+    ff.wait(r);
+    const uint32_t tail = b2_lds(ff.round_a(r) + (uint32_t)kSegSlots * kSegSlotBytes);
+    ff.release(2 + kSegAcW, r + 1u, lane);
+    const uint32_t *const wa = ff.ctr + kSegWorked + (int)(r % (uint32_t)kSegAcW), *const wd = ff.ctr + kSegWorked + kSegAcW;
+    while (b2_ld_acquire_smem(wa) <= r || b2_ld_acquire_smem(wd) <= r) b2_backoff(kSegPollNs);
+    const uint32_t upto = tail >> 1, cnt = upto - flushed;
+    const uint32_t mine = flushed | (cnt << 28);
+    uint32_t src[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) src[i] = __shfl_sync(0xffffffffu, mine, (lane >> 3) + 4 * i);
+    for (uint32_t k = 0; __any_sync(0xffffffffu, k < cnt); ++k) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (k < (src[i] >> 28)) {
+          const uint32_t b = (src[i] & 0x0fffffffu) + k;
+          const uint32_t sa = asm_g + ((b & (uint32_t)(kSegAsm - 1)) << 12) + ((uint32_t)((lane >> 3) + 4 * i) << 7) + ((uint32_t)(lane & 7) << 4);
+          coef4[(size_t)(gsrc[i] + b) * 8 + (lane & 7)] = b2_lds_v4(sa);
+          b2_sts_v4(sa, make_uint4(0u, 0u, 0u, 0u));
+        }
+      }
+    }
+    flushed = upto;
+    __syncwarp();                                    // the images are cleared before anybody learns that they are free
+    b2_st_release_smem(fl, flushed);
+    if (tail & kSegFinFlag) break;
+  }
+}
+
+// units[u] = (image, segment); the units of one CTA share a table set (the planner pads each table-set group to a
+// multiple of kSegUnits with kSegNoUnit).  d_us / seg_start: stage U's output.  Every block of every unit is written
+// (whole, zeros included): the coefficient buffer needs no clearing.
 B2_GLOBAL void __launch_bounds__(kSegThreads)
 k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs, const TableSet *__restrict__ tsets,
               const uint32_t *__restrict__ luts, const uint32_t *__restrict__ seg_start,
               const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef) {
-  B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab]
+  B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab], then the groups
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-#if B2_SEG_ROLEMAP == 1
-  const int pair = warp / kSegRoles, role = (warp + pair) % kSegRoles;   // sub-partition = warp % 4: pair 0's decoder on 0, pair 1's on 3
-#elif B2_SEG_ROLEMAP == 2
-  const int pair = warp / kSegRoles, role = (warp + pair + (blockIdx.x >= 148u ? 2 : 0)) % kSegRoles;   // second CTA of an SM: decoders on 2 and 1
-#else
-  const int pair = warp % kSegPairs, role = warp / kSegPairs;    // role 0 decoder, 1/2 AC writers, 3 DC warp
-#endif
-  uint32_t *pbase = lut + kHTabsPerSet * kHTab + pair * kSegGroupWords;
-  uint32_t *ringl = pbase + lane;                               // window ring: word j of this lane at ringl[(j & 31) * 32]
-  uint32_t *fifo = pbase + (kSegWords + 1) * 32;                      // [round][step][window|entry|block][lane]
-  uint32_t *tb = fifo + kSegFifo * kSegRoundBytes / 4;          // [block-in-MCU][lane]: DC table offset | AC table offset << 16
-  uint32_t *ctr = tb + kMaxBpm * 32;                            // [0] rounds produced (| kSegFin), [1..3] next round of writer A, B, DC warp
+  const int g = warp % kSegGroups, role = warp / kSegGroups;    // role 0 decoder, 1 .. kSegAcW AC writers, kSegAcW + 1 DC warp, kSegAcW + 2 flusher
+  uint32_t *const grp = lut + kHTabsPerSet * kHTab + g * kSegGroupWords;
+  uint32_t *const ringl = grp + lane;                           // window ring: word j of this lane at ringl[(j & 31) * 32]
+  uint32_t *const tb = grp + kSegOffTb;                         // [block-in-MCU][lane]: DC table offset | AC table offset << 16
+  uint32_t *const fl = grp + kSegOffFl + lane;                  // blocks of this lane that have left the assembly ring
+  uint32_t *const ctr = grp + kSegOffCtr;
   {
     // the CTA's table set: that of its first unit (never padding)
     const int set = imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset;
@@ -150,242 +470,31 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       if (!used) continue;
       for (int k = tid; k < kHTab / 4; k += kSegThreads) dst[t * (kHTab / 4) + k] = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
     }
-    if (role == 0 && lane <= kSegAcW + 1) ctr[lane] = lane >= 1 && lane <= kSegAcW ? (uint32_t)(lane - 1) : 0u;
+    // block images and flushed counts start at zero
+    for (int gg = 0; gg < kSegGroups; ++gg) {
+      uint4 *z = reinterpret_cast<uint4 *>(lut + kHTabsPerSet * kHTab + gg * kSegGroupWords + kSegOffAsm);
+      for (int k = tid; k < (kSegAsm * 32 * 32 + 32) / 4; k += kSegThreads) z[k] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    // an AC writer's counters start at its first round, everybody else's at 0
+    if (role == 0 && lane <= kSegWorked + kSegAcW)
+      ctr[lane] = lane >= 1 && lane <= kSegAcW ? (uint32_t)(lane - 1)
+                  : (lane >= kSegWorked && lane < kSegWorked + kSegAcW ? (uint32_t)(lane - kSegWorked) : 0u);
   }
   __syncthreads();
 
-  const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + pair * 32 + lane];
+  const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + g * 32 + lane];
   const SegLane L = seg_lane(unit, imgs, out);
   uint32_t err = 0;
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
-  const uint32_t fifo_a = b2_dsm_addr(fifo) + 4u * (uint32_t)lane, lut_a = b2_dsm_addr(lut);
-  int16_t *const base = coef + L.gb * 64;          // block 0 of the segment; block n, coefficient pos: base[n*64 + (pos ^ key(n))]
-  const uint32_t g0 = (uint32_t)L.gb & 7u;         // key(n) = ((g0 + n) & 7) << 3
-
-  if (role == 0) {
-    // =========================== the chain: codes only ===========================
-    // The eight steps of a round are ONE basic block: no branch, table and window loads that the compiler may
-    // schedule freely (b2_lds_ro), so the off-chain work of step i overlaps the chain of step i+1.  What needs a
-    // branch is taken out of the steps: a lane that meets an entry the first-level table cannot resolve (code longer
-    // than kHLutBits -- one symbol in 200 --, an error entry) STAYS where it is for the rest of the round (its
-    // entries read 0: no advance, nothing for the consumers) and the symbol is resolved after the last step, in the
-    // round's extra slot.
-    uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
-    const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
-    const uint32_t total = L.live ? (uint32_t)(L.bend - L.bidx) : 0u;
-    bool done = !L.live;
-    if (L.live) {
-      const ImageDev &im = imgs[L.img];
-      for (int b = 0; b < L.bpm; ++b) {             // DC table td -> slot td, AC table ta -> slot 4+ta
-        const int c = b < L.nluma ? 0 : b - L.nluma + 1;
-        tb[b * 32 + lane] = (uint32_t)(im.td[c] & 3) * (kHTab * 4) | ((uint32_t)(4 + (im.ta[c] & 3)) * (kHTab * 4)) << 16;
-      }
-      us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
-      p = seg_start[im.seg_base + (int)unit.y];
-      pend = seg_start[im.seg_base + (int)unit.y + 1];
-      rw = (p >> 5) & ~3u;
-      for (int i = 0; i < kSegWords; ++i) {
-        b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
-        if (((rw + i) & (kSegWords - 1)) == 0u) b2_cp_async4(ringl + kSegWords * 32, us + rw + i);   // slot 32 repeats slot 0
-      }
-      rw += kSegWords;
-    } else tb[lane] = 0;
-    b2_cp_async_commit();
-    b2_cp_async_wait<0>();
-    __syncwarp();
-    // window addresses, taken AFTER the tables and the ring were filled (b2_lds_ro), and kept in registers
-    const uint32_t ring_a = b2_launder(b2_dsm_addr(ringl)), tb_a = b2_launder(b2_dsm_addr(tb) + 4u * (uint32_t)lane);
-    const uint32_t lut_r = b2_launder(lut_a);
-    const uint32_t tb_end = tb_a + (uint32_t)L.bpm * 128u;
-    uint32_t tba = tb_a;                             // this lane's table entry of the current block-in-MCU
-    uint32_t z = 0, nb = 0;                          // zig-zag index, blocks finished
-    uint32_t rounds = 0;
-    // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
-    auto advance = [&](uint32_t e, uint32_t &fn) {
-      const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
-      const bool pair = a2 != 0u && z + z1 < 64u;    // an AC entry may describe TWO symbols; both are taken unless the first ends the block
-      fn = z | (pair ? kSegPairBit : 0u) | (nb << kSegNbShift);
-      p += huff_adv(e) + (pair ? a2 : 0u);
-      z += z1 + (pair ? huff_zinc2(e) : 0u);
-      // ---- block end without a branch: some lane ends a block in four steps out of five ----
-      const bool end = z >= 64u;
-      const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
-      z = end ? 0u : z;
-      tba = end ? tbn : tba;
-      nb += end ? 1u : 0u;
-      // ---- once per lane: the segment is finished.  The last block ran past the segment's end (file.hpp:36-40),
-      //      or more than padding is left: the segment holds more blocks ----
-      const bool fin_now = end && nb == total;
-      const uint32_t fe = p > pend ? (uint32_t)ST_OVERRUN : (pend - p > 7u ? (uint32_t)ST_BLOCK_COUNT : 0u);
-      err |= fin_now ? fe : 0u;
-      done = done || fin_now;
-    };
-    for (;;) {
-      // the consumers' counters are read now and looked at after the round: room for the NEXT round
-      uint32_t m = b2_ld_acquire_smem(ctr + 1);
-#pragma unroll
-      for (int c = 2; c <= kSegAcW + 1; ++c) { const uint32_t v = b2_ld_acquire_smem(ctr + c); m = v < m ? v : m; }
-      // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
-      //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8 ----
-      const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) b2_cp_async4_if(need, ring_a + (((rw + i) & (kSegWords - 1)) << 7), us + rw + i);
-      // slot 32 repeats slot 0 (the window's second word is always at +128); rw is a multiple of 4
-      b2_cp_async4_if(need && (rw & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw);
-      b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
-      rw += need ? 8u : 0u;
-      b2_cp_async_commit();
-      // rw is at least 25 words ahead of the window and the round needs at most 8 more: everything but the two
-      // newest groups must have landed -- copies issued two rounds (16 steps) ago
-      b2_cp_async_wait<2>();
-      const uint32_t slot_a = fifo_a + (rounds & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
-      uint32_t w = 0, cur = 0, eraw = 0;
-#pragma unroll kSegUnroll
-      for (int u = 0; u < kSegSteps; ++u) {
-        const uint32_t t = b2_lds_ro(tba);                                           // table offsets of this block: DC | AC << 16
-        cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));                          // chosen while the window is still on its way
-        const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
-        const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
-        w = __funnelshift_l(w1, w0, p);
-        eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-        // a finished lane, and one that waits for the extra slot, step in place: entry 0
-        const uint32_t e = (done || eraw >= kHOverflow) ? 0u : eraw;
-        uint32_t fn;
-        advance(e, fn);
-#if B2_SEG_DIAG != 2
-        b2_sts(slot_a + (uint32_t)u * kSegStepBytes, w);
-        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 128u, e);
-        b2_sts(slot_a + (uint32_t)u * kSegStepBytes + 256u, fn);
-#endif
-      }
-      {
-        // ---- the extra slot: whoever is waiting in front of a symbol the first-level table did not resolve ----
-        const bool stuck = !done && eraw >= kHOverflow;                              // then w, cur and eraw are still those of p
-        uint32_t e = 0, fn = 0;
-        if (__any_sync(0xffffffffu, stuck)) {
-          if (stuck) {
-            const bool is_dc = z == 0;
-            e = eraw;
-            if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
-            if (e & kHOverflow) {
-              const ImageDev &im = imgs[L.img];
-              const int blk = (int)((tba - tb_a) >> 7), comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-              e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
-            }
-            if (e & kHBadCode) err |= ST_BAD_CODE;
-            if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
-            advance(e, fn);
-          }
-        }
-#if B2_SEG_DIAG != 2
-        b2_sts(slot_a + (uint32_t)kSegSteps * kSegStepBytes, w);
-        b2_sts(slot_a + (uint32_t)kSegSteps * kSegStepBytes + 128u, e);
-        b2_sts(slot_a + (uint32_t)kSegSteps * kSegStepBytes + 256u, fn);
-#endif
-      }
-      const bool fin = __all_sync(0xffffffffu, done);   // also orders the lanes' FIFO stores before lane 0's release
-      ++rounds;
-      if (lane == 0) b2_st_release_smem(ctr, rounds | (fin ? kSegFin : 0u));
-      if (fin) break;
-      // room in the FIFO for the next round: every consumer is past round (rounds - kSegFifo)
-#if B2_SEG_DIAG == 2
-      m = rounds;
-#endif
-      while ((int)(rounds - m) >= kSegFifo) {
-        b2_backoff(kSegPollNs);
-        m = b2_ld_acquire_smem(ctr + 1);
-#pragma unroll
-        for (int c = 2; c <= kSegAcW + 1; ++c) { const uint32_t v = b2_ld_acquire_smem(ctr + c); m = v < m ? v : m; }
-      }
-    }
-  }
-#if B2_SEG_DIAG == 2
-  else if (role > 0) return;
-#endif
-  else if (role <= kSegAcW) {
-    // =========================== AC coefficients: stateless, every other round ===========================
-    uint32_t r = (uint32_t)(role - 1);
-    for (;;) {
-      uint32_t pr;
-      while (pr = b2_ld_acquire_smem(ctr), (pr & ~kSegFin) <= r && !(pr & kSegFin)) b2_backoff(kSegPollNs);
-      if ((pr & ~kSegFin) <= r) break;                                              // no such round: the decoder has finished
-      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
-      uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
-#pragma unroll
-      for (int u = 0; u < kSegSlots; ++u) {
-        fw[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes); fe[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 128u);
-        fn[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 256u);
-      }
-      __syncwarp();                                     // every lane has read the round before it is handed back
-      if (lane == 0) b2_st_release_smem(ctr + role, r + (uint32_t)kSegAcW);
-#pragma unroll
-      for (int u = 0; u < (B2_SEG_DIAG == 1 || B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
-        const uint32_t e = fe[u], z = fn[u] & 63u, nblk = fn[u] >> kSegNbShift;
-        if (z != 0u && e != 0u) {                       // AC (DC symbols carry z = 0, a lane that steps in place entry 0)
-          int16_t *const bp = base + nblk * 64u;
-          const uint32_t key = ((g0 + nblk) & 7u) << 3;
-          const uint32_t adv = huff_adv(e), len = huff_len(e), zn = z + huff_zinc(e);
-          const uint32_t size = adv - len;
-          // EXTEND (jpeg.cpp:388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
-          const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
-          const int val = (int)v - (v + v > t ? 0 : (int)t);
-          const uint32_t pos = zn - 1u;                                             // z + run
-          if (size != 0u && pos < 64u B2_SEG_NOSTORE(fw[u])) bp[pos ^ key] = (int16_t)val;
-          // EOB, or the index ran to 64; a run that reaches past 63 is an error (jpeg.cpp:372-376)
-          if (zn >= 64u && !(e & kHEob) && !(size != 0u && zn == 64u)) err |= ST_BAD_RUN;
-          if (fn[u] & kSegPairBit) {
-            // the second symbol of the entry: its bits follow the first one's; its details come from the same table
-            const uint32_t w2 = fw[u] << adv;
-            const uint32_t e2 = b2_lds(lut_a + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-            const uint32_t adv2 = huff_adv(e2), len2 = huff_len(e2), zn2 = zn + huff_zinc(e2), size2 = adv2 - len2;
-            const uint32_t v2 = b2_shr(w2 << len2, 32u - size2), t2 = b2_shl(1u, size2) - 1u;
-            const int val2 = (int)v2 - (v2 + v2 > t2 ? 0 : (int)t2);
-            const uint32_t pos2 = zn2 - 1u;
-            if (size2 != 0u && pos2 < 64u B2_SEG_NOSTORE(w2)) bp[pos2 ^ key] = (int16_t)val2;
-            if (zn2 >= 64u && !(e2 & kHEob) && !(size2 != 0u && zn2 == 64u)) err |= ST_BAD_RUN;
-          }
-        }
-      }
-      r += (uint32_t)kSegAcW;
-    }
-  } else {
-    // =========================== DC coefficients: prediction per component ===========================
-    int pred0 = 0, pred1 = 0, pred2 = 0;
-    int blk = 0;
-    uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
-    uint32_t r = 0;
-    for (;;) {
-      uint32_t pr;
-      while (pr = b2_ld_acquire_smem(ctr), (pr & ~kSegFin) <= r && !(pr & kSegFin)) b2_backoff(kSegPollNs);
-      if ((pr & ~kSegFin) <= r) break;
-      const uint32_t slot_a = fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes;
-      uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
-#pragma unroll
-      for (int u = 0; u < kSegSlots; ++u) {
-        fw[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes); fe[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 128u);
-        fn[u] = b2_lds(slot_a + (uint32_t)u * kSegStepBytes + 256u);
-      }
-      __syncwarp();
-      ++r;
-      if (lane == 0) b2_st_release_smem(ctr + kSegAcW + 1, r);
-#pragma unroll
-      for (int u = 0; u < (B2_SEG_DIAG == 1 || B2_SEG_DIAG == 4 ? 0 : kSegSlots); ++u) {
-        const uint32_t e = fe[u];
-        if (e != 0u && (fn[u] & 63u) == 0u) {                                       // a DC symbol opens a block
-          const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len, nblk = fn[u] >> kSegNbShift;
-          const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
-          const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
-          const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-          const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
-          pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
-          dcbad |= (uint32_t)(dc + 32768) >> 16;
-          base[nblk * 64u + (((g0 + nblk) & 7u) << 3)] = (int16_t)dc;               // position 0 of chunk 0 ^ key
-          blk = blk + 1 == L.bpm ? 0 : blk + 1;
-        }
-      }
-    }
-    if (dcbad) err |= ST_DC_RANGE;
-  }
+  SegFifo ff;
+  ff.fifo_a = b2_dsm_addr(grp + kSegOffFifo) + 4u * (uint32_t)lane;
+  ff.ctr = ctr;
+  const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
+  const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
+  if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);
+  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, lut_a, asm_g + ((uint32_t)lane << 7), fl, g0, err);
+  else if (role == kSegAcW + 1) seg_dc_warp(ff, lane, L, asm_g + ((uint32_t)lane << 7), fl, g0, err);
+  else seg_flusher(ff, lane, L, asm_g, fl, reinterpret_cast<uint4 *>(coef));
   if (err) atomicOr(&out[L.img].status, err);
 }
 

@@ -32,37 +32,7 @@ struct Pipeline {
   float last_ms[B200JPEG_T_COUNT] = {0, 0, 0, 0, 0};
 #ifndef B200JPEG_EMU
   cudaEvent_t ev[B200JPEG_T_COUNT + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  // side stream: zero-fills the coefficient buffer for the segment decoder while stage U runs
-  cudaStream_t side = nullptr;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 #endif
-
-  // The segment decoder stores only non-zero coefficients (kernels_segdec.cuh): the buffer is cleared first,
-  // on a side stream forked here (after everything queued so far, i.e. after the previous batch's pixel
-  // stage has read it) and joined right before the decoder, so the memset overlaps stage U.
-  void zero_coef_fork() {
-    const size_t bytes = 128 * (size_t)plan.nblocks;
-#ifdef B200JPEG_EMU
-    be.fill(d_coef.p, 0, bytes);
-#else
-    if (!side) {
-      cudaError_t e = cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking);
-      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming);
-      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming);
-      if (e != cudaSuccess) { be.fail("side stream", e); return; }
-    }
-    cudaEventRecord(ev_fork, be.stream);
-    cudaStreamWaitEvent(side, ev_fork, 0);
-    cudaError_t e = cudaMemsetAsync(d_coef.p, 0, bytes, side);
-    if (e != cudaSuccess) be.fail("cudaMemsetAsync (coefficients)", e);
-    cudaEventRecord(ev_join, side);
-#endif
-  }
-  void zero_coef_join() {
-#ifndef B200JPEG_EMU
-    cudaStreamWaitEvent(be.stream, ev_join, 0);
-#endif
-  }
 
   void destroy() {
     DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_cta_base, &d_tile_cnt, &d_tile_pre,
@@ -72,9 +42,6 @@ struct Pipeline {
     for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
     be.host_release(h_out); be.host_release(h_flags);
     h_out = nullptr; h_flags = nullptr; h_out_cap = 0;
-#ifndef B200JPEG_EMU
-    if (side) { cudaStreamDestroy(side); cudaEventDestroy(ev_fork); cudaEventDestroy(ev_join); side = nullptr; }
-#endif
   }
 
   static constexpr size_t kFlagWords = kFixLaunches + kMaxExtraFix + 2;
@@ -264,7 +231,6 @@ struct Pipeline {
     launches = 0; sync_rounds = 0;
     results_enqueued = false;
     mark(0);
-    if (P.path == kPathSegment && P.nunit_ctas > 0) zero_coef_fork();
     // ImageOut: end_pos/err_pos = kNone, the rest 0
     be.fill(d_out.p, 0xff, sizeof(ImageOut) * P.n);
     be.fill(d_flags.p, 0, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
@@ -289,7 +255,6 @@ struct Pipeline {
     if (P.path == kPathSegment) {
       mark(2);
       if (P.nunit_ctas > 0) {
-        zero_coef_join();
         B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream, d_units.as<uint2>(),
                   d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(), d_seg.as<uint32_t>(),
                   d_us.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>());

@@ -23,6 +23,18 @@ struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__
 #define B2_SHARED __shared__
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+// launch as thread-block clusters of `cluster` CTAs along x (grid = clusters x cluster)
+template <class... KArgs, class... Args>
+inline cudaError_t b2_launch_cluster(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream, int cluster,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 #define B2_DYN_SMEM(type, name) extern __shared__ __align__(128) unsigned char name##_raw_[]; \
   type *name = reinterpret_cast<type *>(name##_raw_)
 #define B2_CONSTANT __constant__
@@ -129,6 +141,7 @@ B2_DEVICE uint32_t b2_lds_ro(uint32_t a) {
   asm("ld.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(a));
   return v;
 }
+B2_DEVICE void b2_sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
 B2_DEVICE uint4 b2_lds_v4(uint32_t a) {
   uint4 v;
   asm volatile("ld.shared::cta.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
