@@ -96,18 +96,19 @@ constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing t
 constexpr uint32_t kSegPairBit = 1u << 6;
 constexpr int kSegNbShift = 7;
 constexpr uint32_t kSegFinFlag = 1u;
+static_assert(kSegFifo % kSegAcW == 0, "a FIFO slot always belongs to the same AC writer (arrival counts)");
 static_assert((kSegFifo & (kSegFifo - 1)) == 0 && (kSegAsm & (kSegAsm - 1)) == 0, "ring sizes are powers of two");
 static_assert(kSegAsm >= (kSegSlots + 1) / 2 + 1, "the blocks one round touches must fit the assembly ring");
 
 // shared memory of a group (32-bit words), after the CTA's copy of the lookup tables:
 //   window ring | per-lane table offsets by block-in-MCU | FIFO | block images [image][lane][32 words] |
-//   flushed-block count per lane | counters
+//   flushed-block count per lane | mbarriers
 constexpr int kSegOffTb = (kSegWords + 1) * 32;
 constexpr int kSegOffFifo = kSegOffTb + kMaxBpm * 32;
 constexpr int kSegOffAsm = kSegOffFifo + kSegFifo * kSegRoundBytes / 4;
 constexpr int kSegOffFl = kSegOffAsm + kSegAsm * 32 * 32;
-constexpr int kSegOffCtr = kSegOffFl + 32;
-constexpr int kSegGroupWords = kSegOffCtr + 32;
+constexpr int kSegOffBar = kSegOffFl + 32;    // mbarriers (2 words each)
+constexpr int kSegGroupWords = kSegOffBar + 32;
 static_assert(kSegOffFifo % 4 == 0 && kSegOffAsm % 4 == 0 && kSegGroupWords % 4 == 0, "16-byte alignment of the FIFO and the block images");
 
 B2_HD size_t segdec_smem_bytes() {
@@ -140,36 +141,45 @@ B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, 
 
 // ------------------------------------------------------------------ the FIFO between a decoder and its consumers
 // Round r lives at (r % kSegFifo) * kSegRoundBytes: kSegSlots slots of three words x 32 lanes, then one word per lane
-// (blocks finished after the round << 1 | kSegFinFlag).  ctr[0] rounds produced; ctr[1 + w] next round AC writer w
-// will READ, ctr[1 + kSegAcW] the same for the DC warp, ctr[2 + kSegAcW] for the flusher; ctr[kSegWorked + w] next round
-// AC writer w will WORK on (all its earlier rounds are in the block images), ctr[kSegWorked + kSegAcW] the same for the
-// DC warp.  st.release / ld.acquire in shared memory.
-constexpr int kSegReaders = kSegAcW + 2;      // AC writers, DC warp, flusher
-constexpr int kSegWorked = 1 + kSegReaders;   // first "worked" counter
+// (blocks finished after the round << 1 | kSegFinFlag).  Nobody polls: every hand-over is an mbarrier in shared memory,
+// a waiting warp is suspended by the hardware (spinning consumers took two fifths of the kernel's issue slots).
+//   full[s]    1 arrival: the decoder has written the round in slot s
+//   empty[s]   3 arrivals: the round's AC writer, the DC warp and the flusher have the round in registers
+//   worked[i]  2 arrivals: the AC writer and the DC warp of round r (i = r % kSegWorkedDepth) have put its values into the
+//              block images -- what the flusher waits for.  Deeper than the FIFO, so that a phase cannot complete twice
+//              before the flusher has looked at it (writers are at most kSegFifo rounds ahead of the flusher's reads).
+constexpr int kSegWorkedDepth = 8;
+constexpr int kSegBars = 2 * kSegFifo + kSegWorkedDepth;
 struct SegFifo {
   uint32_t fifo_a;           // window address of slot 0 of round 0, this lane
-  uint32_t *ctr;
+  uint32_t bar_a;            // window address of full[0]
   B2_MEMBER uint32_t round_a(uint32_t r) const { return fifo_a + (r & (uint32_t)(kSegFifo - 1)) * kSegRoundBytes; }
+  B2_MEMBER uint32_t full(uint32_t r) const { return bar_a + 8u * (r & (uint32_t)(kSegFifo - 1)); }
+  B2_MEMBER uint32_t empty(uint32_t r) const { return bar_a + 8u * ((uint32_t)kSegFifo + (r & (uint32_t)(kSegFifo - 1))); }
+  B2_MEMBER uint32_t worked(uint32_t r) const { return bar_a + 8u * ((uint32_t)(2 * kSegFifo) + (r & (uint32_t)(kSegWorkedDepth - 1))); }
+  B2_MEMBER void init() const {                                  // one thread
+    for (uint32_t s = 0; s < (uint32_t)kSegFifo; ++s) { b2_mbar_init_a(full(s), 1); b2_mbar_init_a(empty(s), 3); }
+    for (uint32_t i = 0; i < (uint32_t)kSegWorkedDepth; ++i) b2_mbar_init_a(worked(i), 2);
+  }
   // ---- producer ----
-  B2_MEMBER uint32_t readers() const {                           // the round every reader is past
-    uint32_t m = b2_ld_acquire_smem(ctr + 1);
-#pragma unroll
-    for (int c = 2; c <= kSegReaders; ++c) { const uint32_t v = b2_ld_acquire_smem(ctr + c); m = v < m ? v : m; }
-    return m;
+  B2_MEMBER void wait_room(uint32_t r) const {                   // round r may be written once round r - kSegFifo has been read
+    if (r >= (uint32_t)kSegFifo) b2_mbar_wait_a(empty(r), ((r / (uint32_t)kSegFifo) - 1u) & 1u);
   }
-  B2_MEMBER void wait_room(uint32_t r, uint32_t m) const {       // round r may be written once every reader is past round r - kSegFifo
-    while ((int)(r - m) >= kSegFifo) { b2_backoff(kSegPollNs); m = readers(); }
-  }
-  B2_MEMBER void publish(uint32_t produced, int lane) const {    // every lane's stores of the round are ordered before lane 0's release
+  B2_MEMBER void publish(uint32_t r, int lane) const {           // every lane's stores of the round are ordered before lane 0's arrive
     __syncwarp();
-    if (lane == 0) b2_st_release_smem(ctr, produced);
+    if (lane == 0) b2_mbar_arrive_a(full(r));
   }
   // ---- consumers ----
-  B2_MEMBER void wait(uint32_t r) const { while (b2_ld_acquire_smem(ctr) <= r) b2_backoff(kSegPollNs); }
-  B2_MEMBER void release(int who, uint32_t next, int lane) const {   // the warp has the round in registers
+  B2_MEMBER void wait(uint32_t r) const { b2_mbar_wait_a(full(r), (r / (uint32_t)kSegFifo) & 1u); }
+  B2_MEMBER void release(uint32_t r, int lane) const {           // the warp has the round in registers
     __syncwarp();
-    if (lane == 0) b2_st_release_smem(ctr + who, next);
+    if (lane == 0) b2_mbar_arrive_a(empty(r));
   }
+  B2_MEMBER void worked_arrive(uint32_t r, int lane) const {     // the warp's values of round r are in the block images
+    __syncwarp();
+    if (lane == 0) b2_mbar_arrive_a(worked(r));
+  }
+  B2_MEMBER void worked_wait(uint32_t r) const { b2_mbar_wait_a(worked(r), (r / (uint32_t)kSegWorkedDepth) & 1u); }
 };
 
 // =========================== the chain: codes only ===========================
@@ -233,7 +243,6 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
   };
   uint32_t r = 0;
   for (;; ++r) {
-    const uint32_t readers = ff.readers();         // read now, looked at after the top-up
     // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
     //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8 ----
     const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
@@ -244,7 +253,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
     b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
     rw += need ? 8u : 0u;
     b2_cp_async_commit();
-    ff.wait_room(r, readers);
+    ff.wait_room(r);
     const uint32_t slot_a = ff.round_a(r);
     // rw is at least 25 words ahead of the window and the round needs at most 8 more: everything but the two
     // newest groups must have landed -- copies issued two rounds (16 steps) ago
@@ -289,17 +298,17 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
     b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 128u, e);
     b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 256u, fn);
     b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | (fin ? kSegFinFlag : 0u));
-    ff.publish(r + 1u, lane);
+    ff.publish(r, lane);
     if (fin) break;
   }
   // the AC writers whose turn did not come with the last round each get an empty one that tells them to stop
   for (int k = 1; k < kSegAcW; ++k) {
     ++r;
-    ff.wait_room(r, ff.readers());
+    ff.wait_room(r);
     const uint32_t slot_a = ff.round_a(r);
     for (int u = 0; u < kSegSlots; ++u) { b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, 0u); b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, 0u); }
     b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | kSegFinFlag);
-    ff.publish(r + 1u, lane);
+    ff.publish(r, lane);
   }
 }
 
@@ -324,7 +333,7 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a,
       fn[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
     }
     const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
-    ff.release(1 + w, r + (uint32_t)kSegAcW, lane);              // every lane has read the round before it is handed back
+    ff.release(r, lane);                                          // every lane has read the round before it is handed back
     // the blocks of this round (the highest is the one in progress after it) must fit the ring of images in front of
     // the flushed ones
     while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);
@@ -355,7 +364,7 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a,
         }
       }
     }
-    ff.release(kSegWorked + w, r + (uint32_t)kSegAcW, lane);     // the round's values are in the block images
+    ff.worked_arrive(r, lane);
     if (tail & kSegFinFlag) break;
   }
 }
@@ -376,7 +385,7 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
       fn[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
     }
     const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
-    ff.release(1 + kSegAcW, r + 1u, lane);
+    ff.release(r, lane);
     while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);   // room, as for the AC writers
 #pragma unroll
     for (int u = 0; u < (B2_SEG_DIAG == 4 ? 0 : kSegSlots); ++u) {
@@ -393,7 +402,7 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
         blk = blk + 1 == L.bpm ? 0 : blk + 1;
       }
     }
-    ff.release(kSegWorked + kSegAcW, r + 1u, lane);
+    ff.worked_arrive(r, lane);
     if (tail & kSegFinFlag) break;
   }
   if (dcbad) err |= ST_DC_RANGE;
@@ -419,9 +428,8 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
   for (uint32_t r = 0;; ++r) {
     ff.wait(r);
     const uint32_t tail = b2_lds(ff.round_a(r) + (uint32_t)kSegSlots * kSegSlotBytes);
-    ff.release(2 + kSegAcW, r + 1u, lane);
-    const uint32_t *const wa = ff.ctr + kSegWorked + (int)(r % (uint32_t)kSegAcW), *const wd = ff.ctr + kSegWorked + kSegAcW;
-    while (b2_ld_acquire_smem(wa) <= r || b2_ld_acquire_smem(wd) <= r) b2_backoff(kSegPollNs);
+    ff.release(r, lane);
+    ff.worked_wait(r);
     const uint32_t upto = tail >> 1, cnt = upto - flushed;
     const uint32_t mine = flushed | (cnt << 28);
     uint32_t src[8];
@@ -459,7 +467,9 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   uint32_t *const ringl = grp + lane;                           // window ring: word j of this lane at ringl[(j & 31) * 32]
   uint32_t *const tb = grp + kSegOffTb;                         // [block-in-MCU][lane]: DC table offset | AC table offset << 16
   uint32_t *const fl = grp + kSegOffFl + lane;                  // blocks of this lane that have left the assembly ring
-  uint32_t *const ctr = grp + kSegOffCtr;
+  SegFifo ff;
+  ff.fifo_a = b2_dsm_addr(grp + kSegOffFifo) + 4u * (uint32_t)lane;
+  ff.bar_a = b2_dsm_addr(grp + kSegOffBar);
   {
     // the CTA's table set: that of its first unit (never padding)
     const int set = imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset;
@@ -475,10 +485,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       uint4 *z = reinterpret_cast<uint4 *>(lut + kHTabsPerSet * kHTab + gg * kSegGroupWords + kSegOffAsm);
       for (int k = tid; k < (kSegAsm * 32 * 32 + 32) / 4; k += kSegThreads) z[k] = make_uint4(0u, 0u, 0u, 0u);
     }
-    // an AC writer's counters start at its first round, everybody else's at 0
-    if (role == 0 && lane <= kSegWorked + kSegAcW)
-      ctr[lane] = lane >= 1 && lane <= kSegAcW ? (uint32_t)(lane - 1)
-                  : (lane >= kSegWorked && lane < kSegWorked + kSegAcW ? (uint32_t)(lane - kSegWorked) : 0u);
+    if (role == 0 && lane == 0) { ff.init(); b2_mbar_init_fence(); }
   }
   __syncthreads();
 
@@ -486,9 +493,6 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   const SegLane L = seg_lane(unit, imgs, out);
   uint32_t err = 0;
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
-  SegFifo ff;
-  ff.fifo_a = b2_dsm_addr(grp + kSegOffFifo) + 4u * (uint32_t)lane;
-  ff.ctr = ctr;
   const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
   if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);

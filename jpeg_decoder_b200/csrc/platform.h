@@ -174,6 +174,7 @@ B2_DEVICE void b2_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
 B2_DEVICE void b2_mbar_arrive_remote(uint32_t rbar) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar) : "memory");
 }
+B2_DEVICE void b2_mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 B2_DEVICE void b2_mbar_init_a(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }

@@ -274,6 +274,20 @@ static inline void b2_sts_u16(uint32_t a, uint32_t v) { const uint16_t h = (uint
 static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_base() + a, 16); return v; }
 static inline void b2_sts_v4(uint32_t a, uint4 v) { memcpy(b2_dsm_base() + a, &v, 16); }
 static inline uint32_t b2_launder(uint32_t v) { return v; }
+// mbarriers by window address (arrival counts only): [63:32] completed phases, [31:16] arrivals a phase takes, [15:0] arrivals so far
+static inline uint64_t *b2_mbar_ptr(uint32_t a) { return reinterpret_cast<uint64_t *>(b2_dsm_base() + a); }
+static inline void b2_mbar_init_a(uint32_t a, uint32_t count) { __atomic_store_n(b2_mbar_ptr(a), (uint64_t)count << 16, __ATOMIC_SEQ_CST); }
+static inline void b2_mbar_arrive_a(uint32_t a) {
+  uint64_t *p = b2_mbar_ptr(a);
+  uint64_t o = __atomic_load_n(p, __ATOMIC_SEQ_CST), n;
+  do {
+    const uint64_t need = (o >> 16) & 0xffff, got = (o & 0xffff) + 1;
+    n = got == need ? (((o >> 32) + 1) << 32) | (need << 16) : (o & ~(uint64_t)0xffff) | got;
+  } while (!__atomic_compare_exchange_n(p, &o, n, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST));
+}
+static inline void b2_mbar_wait_a(uint32_t a, uint32_t parity) {
+  while (((__atomic_load_n(b2_mbar_ptr(a), __ATOMIC_SEQ_CST) >> 32) & 1u) == parity) std::this_thread::yield();
+}
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
 static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
 static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) memcpy(b2_dsm_base() + dst_smem, src, 4); }
