@@ -378,21 +378,24 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
   for (uint32_t r = 0;; ++r) {
     ff.wait(r);
     const uint32_t ra = ff.round_a(r);
-    uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
+    // a lane opens 0.65 blocks per round: first find the round's DC symbols (bit u: slot u holds one), then visit only
+    // those -- the warp makes as many passes as its busiest lane has DC symbols (two, typically), not one per slot
+    uint32_t dcm = 0;
 #pragma unroll
     for (int u = 0; u < kSegSlots; ++u) {
-      fw[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes); fe[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 128u);
-      fn[u] = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
+      const uint32_t e = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 128u), fn = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
+      dcm |= (e != 0u && (fn & 63u) == 0u) ? 1u << u : 0u;
     }
     const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
-    ff.release(r, lane);
     while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);   // room, as for the AC writers
-#pragma unroll
-    for (int u = 0; u < (B2_SEG_DIAG == 4 ? 0 : kSegSlots); ++u) {
-      const uint32_t e = fe[u];
-      if (e != 0u && (fn[u] & 63u) == 0u) {                                       // a DC symbol opens a block
-        const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len, nblk = fn[u] >> kSegNbShift;
-        const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
+    if (B2_SEG_DIAG == 4) dcm = 0;
+    while (__any_sync(0xffffffffu, dcm != 0u)) {
+      if (dcm != 0u) {
+        const uint32_t sa = ra + (uint32_t)(__ffs((int)dcm) - 1) * kSegSlotBytes;
+        dcm &= dcm - 1u;
+        const uint32_t fw = b2_lds(sa), e = b2_lds(sa + 128u), nblk = b2_lds(sa + 256u) >> kSegNbShift;
+        const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len;
+        const uint32_t v = b2_shr(fw << len, 32u - size), t = b2_shl(1u, size) - 1u;
         const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
         const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
         const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
@@ -402,6 +405,7 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
         blk = blk + 1 == L.bpm ? 0 : blk + 1;
       }
     }
+    ff.release(r, lane);                             // the round was worked on in place
     ff.worked_arrive(r, lane);
     if (tail & kSegFinFlag) break;
   }
