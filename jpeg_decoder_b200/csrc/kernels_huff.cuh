@@ -13,7 +13,7 @@
 //            are provided, a table that needs more sets kHOverflow for the prefixes beyond them and
 //            those (pathological) codes are resolved by the per-length search huff_slow().
 //
-// entry (u32):  [4:0] adv = code length + magnitude bits (<= 27)   [8:5] len - 1 = code length - 1
+// entry (u32):  [4:0] adv = code length + magnitude bits (<= 27)   [8:5] size = magnitude bits (code length = adv - size)
 //               [15:9] zinc = how far the zig-zag index moves (run+1, run for size 0, 64 for EOB,
 //               1 for a DC symbol)   bit 16 EOB
 //               [20:17] adv2, [25:21] zinc2: level-1 entries of AC tables only -- when the symbol is followed,
@@ -40,10 +40,11 @@ constexpr uint32_t kHEob = 1u << 16, kHOverflow = 1u << 28, kHBadSize = 1u << 29
 constexpr uint32_t kHSpecial = kHOverflow | kHBadSize | kHBadCode | kHLong;
 
 B2_HD uint32_t huff_entry(uint32_t adv, uint32_t len, uint32_t zinc, uint32_t flags) {
-  return adv | ((len - 1u) << 5) | (zinc << 9) | flags;
+  return adv | ((adv - len) << 5) | (zinc << 9) | flags;
 }
 B2_HD uint32_t huff_adv(uint32_t e) { return e & 31u; }
-B2_HD uint32_t huff_len(uint32_t e) { return ((e >> 5) & 15u) + 1u; }
+B2_HD uint32_t huff_size(uint32_t e) { return (e >> 5) & 15u; }
+B2_HD uint32_t huff_len(uint32_t e) { return huff_adv(e) - huff_size(e); }
 B2_HD uint32_t huff_zinc(uint32_t e) { return (e >> 9) & 127u; }
 B2_HD uint32_t huff_adv2(uint32_t e) { return (e >> 17) & 15u; }
 B2_HD uint32_t huff_zinc2(uint32_t e) { const uint32_t z = (e >> 21) & 31u; return z ? z : 64u; }   // only if adv2 != 0

@@ -312,10 +312,20 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
   }
 }
 
-// a coefficient goes into the lane's image of block nblk: [image nblk % kSegAsm][lane][64 x int16], position ^ key as in
-// the global block (the pixel stage's swizzle), so an image is the block as it will sit in global memory
-B2_DEVICE uint32_t seg_asm_addr(uint32_t asm_a, uint32_t nblk, uint32_t pos_key) {
-  return asm_a + ((nblk & (uint32_t)(kSegAsm - 1)) << 12) + 2u * pos_key;
+// A coefficient goes into the lane's image of its block: [image][lane][64 x int16].  The image is the block as it will
+// sit in global memory, i.e. position pos at pos ^ key, key = (global block index & 7) << 3 (the pixel stage's swizzle),
+// and the image number is global block index & 7 as well, so both come out of one product: with t = gn & 7 the byte
+// address is asm_a + (2 pos ^ t * 0x1010) -- t << 12 selects the image, t << 4 is the key in bytes.
+B2_DEVICE uint32_t seg_asm_addr(uint32_t asm_a, uint32_t gn, uint32_t pos) {
+  return asm_a + ((pos + pos) ^ ((gn & (uint32_t)(kSegAsm - 1)) * 0x1010u));
+}
+static_assert(kSegAsm == 8, "image number and swizzle key share the low three bits of the global block index");
+// EXTEND (jpeg.cpp:335-343, 388-397) of the `size` bits that follow the first `len` bits of w, branch-free: the value
+// v counts from -(2^size - 1) when its first bit is 0
+B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {
+  const uint32_t x = w << len, cnt = 32u - size;
+  const uint32_t v = b2_shr(x, cnt), t = b2_shr(0xffffffffu, cnt);
+  return (int)v - (int)(t & ~(uint32_t)((int)x >> 31));
 }
 
 // =========================== AC coefficients: stateless, every kSegAcW-th round ===========================
@@ -323,6 +333,7 @@ B2_DEVICE uint32_t seg_asm_addr(uint32_t asm_a, uint32_t nblk, uint32_t pos_key)
 // needs is in its FIFO entry, so the writers keep no state between symbols and several of them work in parallel.
 B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a, uint32_t asm_a, const uint32_t *fl,
                              uint32_t g0, uint32_t &err) {
+  const uint32_t lut_r = b2_launder(lut_a);
   for (uint32_t r = (uint32_t)w;; r += (uint32_t)kSegAcW) {
     ff.wait(r);
     const uint32_t ra = ff.round_a(r);
@@ -337,33 +348,27 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a,
     // the blocks of this round (the highest is the one in progress after it) must fit the ring of images in front of
     // the flushed ones
     while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);
+    uint32_t bad = 0;
 #pragma unroll
     for (int u = 0; u < (B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
-      const uint32_t e = fe[u], z = fn[u] & 63u, nblk = fn[u] >> kSegNbShift;
+      const uint32_t e = fe[u], z = fn[u] & 63u;
       if (z != 0u && e != 0u) {                       // AC (DC symbols carry z = 0, a lane that steps in place entry 0)
-        const uint32_t key = ((g0 + nblk) & 7u) << 3;
-        const uint32_t adv = huff_adv(e), len = huff_len(e), zn = z + huff_zinc(e);
-        const uint32_t size = adv - len;
-        // EXTEND (jpeg.cpp:388-397), branch-free: v < 2^(size-1) <=> 2v <= 2^size - 1
-        const uint32_t v = b2_shr(fw[u] << len, 32u - size), t = b2_shl(1u, size) - 1u;
-        const int val = (int)v - (v + v > t ? 0 : (int)t);
-        const uint32_t pos = zn - 1u;                                             // z + run
-        if (size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, nblk, pos ^ key), (uint32_t)val);
-        // EOB, or the index ran to 64; a run that reaches past 63 is an error (jpeg.cpp:372-376)
-        if (zn >= 64u && !(e & kHEob) && !(size != 0u && zn == 64u)) err |= ST_BAD_RUN;
+        const uint32_t gn = g0 + (fn[u] >> kSegNbShift);
+        const uint32_t adv = huff_adv(e), size = huff_size(e), pos = z + huff_zinc(e) - 1u;   // z + run
+        if (size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos), (uint32_t)seg_extend(fw[u], adv - size, size));
+        // a run that reaches past 63 without being EOB is an error (jpeg.cpp:372-376); a coefficient AT 63 is not
+        bad |= (e & kHEob) ? 0u : pos + (size == 0u ? 1u : 0u);
         if (fn[u] & kSegPairBit) {
           // the second symbol of the entry: its bits follow the first one's; its details come from the same table
           const uint32_t w2 = fw[u] << adv;
-          const uint32_t e2 = b2_lds(lut_a + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-          const uint32_t adv2 = huff_adv(e2), len2 = huff_len(e2), zn2 = zn + huff_zinc(e2), size2 = adv2 - len2;
-          const uint32_t v2 = b2_shr(w2 << len2, 32u - size2), t2 = b2_shl(1u, size2) - 1u;
-          const int val2 = (int)v2 - (v2 + v2 > t2 ? 0 : (int)t2);
-          const uint32_t pos2 = zn2 - 1u;
-          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, nblk, pos2 ^ key), (uint32_t)val2);
-          if (zn2 >= 64u && !(e2 & kHEob) && !(size2 != 0u && zn2 == 64u)) err |= ST_BAD_RUN;
+          const uint32_t e2 = b2_lds_ro(lut_r + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+          const uint32_t adv2 = huff_adv(e2), size2 = huff_size(e2), pos2 = pos + huff_zinc(e2);
+          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos2), (uint32_t)seg_extend(w2, adv2 - size2, size2));
+          bad |= (e2 & kHEob) ? 0u : pos2 + (size2 == 0u ? 1u : 0u);
         }
       }
     }
+    if (bad > 63u) err |= ST_BAD_RUN;                 // (positions are below 128: OR-ing them keeps "some position > 63")
     ff.worked_arrive(r, lane);
     if (tail & kSegFinFlag) break;
   }
@@ -394,14 +399,13 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
         const uint32_t sa = ra + (uint32_t)(__ffs((int)dcm) - 1) * kSegSlotBytes;
         dcm &= dcm - 1u;
         const uint32_t fw = b2_lds(sa), e = b2_lds(sa + 128u), nblk = b2_lds(sa + 256u) >> kSegNbShift;
-        const uint32_t adv = huff_adv(e), len = huff_len(e), size = adv - len;
-        const uint32_t v = b2_shr(fw << len, 32u - size), t = b2_shl(1u, size) - 1u;
-        const int diff = (int)v - (v + v > t ? 0 : (int)t);                       // jpeg.cpp:335-343
+        const uint32_t adv = huff_adv(e), size = huff_size(e);
+        const int diff = seg_extend(fw, adv - size, size);                        // jpeg.cpp:335-343
         const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
         const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
         pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
         dcbad |= (uint32_t)(dc + 32768) >> 16;
-        b2_sts_u16(seg_asm_addr(asm_a, nblk, ((g0 + nblk) & 7u) << 3), (uint32_t)dc);   // position 0 of chunk 0 ^ key
+        b2_sts_u16(seg_asm_addr(asm_a, g0 + nblk, 0u), (uint32_t)dc);
         blk = blk + 1 == L.bpm ? 0 : blk + 1;
       }
     }
@@ -444,8 +448,9 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
       for (int i = 0; i < 8; ++i) {
         if (k < (src[i] >> 28)) {
           const uint32_t b = (src[i] & 0x0fffffffu) + k;
-          const uint32_t sa = asm_g + ((b & (uint32_t)(kSegAsm - 1)) << 12) + ((uint32_t)((lane >> 3) + 4 * i) << 7) + ((uint32_t)(lane & 7) << 4);
-          coef4[(size_t)(gsrc[i] + b) * 8 + (lane & 7)] = b2_lds_v4(sa);
+          const uint32_t gb = gsrc[i] + b;          // global block index: its low bits name the image
+          const uint32_t sa = asm_g + ((gb & (uint32_t)(kSegAsm - 1)) << 12) + ((uint32_t)((lane >> 3) + 4 * i) << 7) + ((uint32_t)(lane & 7) << 4);
+          coef4[(size_t)gb * 8 + (lane & 7)] = b2_lds_v4(sa);
           b2_sts_v4(sa, make_uint4(0u, 0u, 0u, 0u));
         }
       }
