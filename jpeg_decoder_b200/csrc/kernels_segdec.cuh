@@ -102,13 +102,14 @@ static_assert(kSegAsm >= (kSegSlots + 1) / 2 + 1, "the blocks one round touches 
 
 // shared memory of a group (32-bit words), after the CTA's copy of the lookup tables:
 //   window ring | per-lane table offsets by block-in-MCU | FIFO | block images [image][lane][32 words] |
-//   flushed-block count per lane | mbarriers
+//   flushed-block count per lane | mbarriers | flush list
 constexpr int kSegOffTb = (kSegWords + 1) * 32;
 constexpr int kSegOffFifo = kSegOffTb + kMaxBpm * 32;
 constexpr int kSegOffAsm = kSegOffFifo + kSegFifo * kSegRoundBytes / 4;
 constexpr int kSegOffFl = kSegOffAsm + kSegAsm * 32 * 32;
 constexpr int kSegOffBar = kSegOffFl + 32;    // mbarriers (2 words each)
-constexpr int kSegGroupWords = kSegOffBar + 32;
+constexpr int kSegOffList = kSegOffBar + 32;  // the flusher's list of finished blocks, a byte each
+constexpr int kSegGroupWords = kSegOffList + 32 * ((kSegSlots + 1) / 2 + 1) / 4;
 static_assert(kSegOffFifo % 4 == 0 && kSegOffAsm % 4 == 0 && kSegGroupWords % 4 == 0, "16-byte alignment of the FIFO and the block images");
 
 B2_HD size_t segdec_smem_bytes() {
@@ -417,11 +418,10 @@ B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32
 }
 
 // =========================== the way out ===========================
-// Once a round's AC writer and the DC warp are through with it, the blocks the round finished leave: thread t moves
-// 16 bytes (t & 7) of the block of lane (t >> 3) + 4 i, i = 0..7 -- eight lanes per block, whole 128-byte lines -- and
-// clears the image.
-B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t *fl,
-                           uint4 *__restrict__ coef4) {
+// Once a round's AC writer and the DC warp are through with it, the blocks the round finished leave: eight threads
+// per block, 16 bytes each -- whole 128-byte lines -- and the image is cleared.
+B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t list_a,
+                           uint32_t *fl, uint4 *__restrict__ coef4) {
   const uint32_t gblk = (uint32_t)L.gb;              // the coefficient buffer holds fewer than 2^32 blocks (512 GB)
   if (__any_sync(0xffffffffu, !L.live && L.bidx < L.bend)) {
     // a scan that is not decoded (stage U found it broken) still gets its blocks: zeros
@@ -429,9 +429,6 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
       for (uint32_t b = 0; b < (uint32_t)(L.bend - L.bidx); ++b)
         for (int c = 0; c < 8; ++c) coef4[(size_t)(gblk + b) * 8 + c] = make_uint4(0u, 0u, 0u, 0u);
   }
-  uint32_t gsrc[8];                                  // first global block of the lanes this thread flushes for
-#pragma unroll
-  for (int i = 0; i < 8; ++i) gsrc[i] = __shfl_sync(0xffffffffu, gblk, (lane >> 3) + 4 * i);
   uint32_t flushed = 0;                              // blocks of this lane that have left
   for (uint32_t r = 0;; ++r) {
     ff.wait(r);
@@ -439,20 +436,25 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
     ff.release(r, lane);
     ff.worked_wait(r);
     const uint32_t upto = tail >> 1, cnt = upto - flushed;
-    const uint32_t mine = flushed | (cnt << 28);
-    uint32_t src[8];
+    // the round's finished blocks of all lanes as one list (a byte each: lane << 3 | number among the lane's blocks), so
+    // that every pass of the copy loop moves four whole blocks whatever lanes they belong to
+    uint32_t incl = cnt;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) src[i] = __shfl_sync(0xffffffffu, mine, (lane >> 3) + 4 * i);
-    for (uint32_t k = 0; __any_sync(0xffffffffu, k < cnt); ++k) {
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); incl += lane >= d ? t : 0u; }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31), excl = incl - cnt;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (k < (src[i] >> 28)) {
-          const uint32_t b = (src[i] & 0x0fffffffu) + k;
-          const uint32_t gb = gsrc[i] + b;          // global block index: its low bits name the image
-          const uint32_t sa = asm_g + ((gb & (uint32_t)(kSegAsm - 1)) << 12) + ((uint32_t)((lane >> 3) + 4 * i) << 7) + ((uint32_t)(lane & 7) << 4);
-          coef4[(size_t)gb * 8 + (lane & 7)] = b2_lds_v4(sa);
-          b2_sts_v4(sa, make_uint4(0u, 0u, 0u, 0u));
-        }
+    for (uint32_t k = 0; k < (uint32_t)(kSegSlots + 1) / 2 + 1; ++k)
+      if (k < cnt) b2_sts_u8(list_a + excl + k, ((uint32_t)lane << 3) | k);
+    __syncwarp();
+    for (uint32_t q0 = 0; q0 < total; q0 += 4) {
+      const uint32_t q = q0 + ((uint32_t)lane >> 3);
+      const uint32_t ent = q < total ? b2_lds_u8(list_a + q) : 0u;
+      const uint32_t ls = ent >> 3;
+      const uint32_t gb = __shfl_sync(0xffffffffu, gblk + flushed, (int)ls) + (ent & 7u);   // global block index: its low bits name the image
+      if (q < total) {
+        const uint32_t sa = asm_g + ((gb & (uint32_t)(kSegAsm - 1)) << 12) + (ls << 7) + ((uint32_t)(lane & 7) << 4);
+        coef4[(size_t)gb * 8 + (lane & 7)] = b2_lds_v4(sa);
+        b2_sts_v4(sa, make_uint4(0u, 0u, 0u, 0u));
       }
     }
     flushed = upto;
@@ -507,7 +509,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);
   else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, lut_a, asm_g + ((uint32_t)lane << 7), fl, g0, err);
   else if (role == kSegAcW + 1) seg_dc_warp(ff, lane, L, asm_g + ((uint32_t)lane << 7), fl, g0, err);
-  else seg_flusher(ff, lane, L, asm_g, fl, reinterpret_cast<uint4 *>(coef));
+  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef));
   if (err) atomicOr(&out[L.img].status, err);
 }
 
