@@ -69,7 +69,7 @@ namespace b2 {
 #define B2_SEG_ACW 2
 #endif
 #ifndef B2_SEG_UNROLL
-#define B2_SEG_UNROLL 2
+#define B2_SEG_UNROLL 8
 #endif
 #ifndef B2_SEG_POLL_NS
 #define B2_SEG_POLL_NS 200
@@ -235,12 +235,8 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
     z = end ? 0u : z;
     tba = end ? tbn : tba;
     nb += end ? 1u : 0u;
-    // ---- once per lane: the segment is finished.  The last block ran past the segment's end (file.hpp:36-40),
-    //      or more than padding is left: the segment holds more blocks ----
-    const bool fin_now = end && nb == total;
-    const uint32_t fe = p > pend ? (uint32_t)ST_OVERRUN : (pend - p > 7u ? (uint32_t)ST_BLOCK_COUNT : 0u);
-    err |= fin_now ? fe : 0u;
-    done = done || fin_now;
+    // ---- once per lane: the segment is finished (a finished lane no longer moves: p stays where the last block ended) ----
+    done = done || (end && nb == total);
   };
   uint32_t r = 0;
   for (;; ++r) {
@@ -302,6 +298,8 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
     ff.publish(r, lane);
     if (fin) break;
   }
+  // the last block ran past the segment's end (file.hpp:36-40), or more than padding is left: the segment holds more blocks
+  if (L.live) err |= p > pend ? (uint32_t)ST_OVERRUN : (pend - p > 7u ? (uint32_t)ST_BLOCK_COUNT : 0u);
   // the AC writers whose turn did not come with the last round each get an empty one that tells them to stop
   for (int k = 1; k < kSegAcW; ++k) {
     ++r;
