@@ -7,7 +7,8 @@
 struct b200jpeg_ctx {
   int device = 0;
   b2::Pipeline pipe;         // the batch of prepare / run / fetch; even chunks of decode_batch
-  b2::Pipeline pipe2;        // odd chunks of decode_batch (own stream and arenas)
+  static constexpr int kExtra = 3;
+  b2::Pipeline extra[kExtra]; // further chunks of decode_batch in flight (own streams and arenas)
   bool agg_valid = false;    // counters of the last pipelined decode_batch
   b200jpeg_batch_stats agg;
   std::string last_error;
@@ -30,7 +31,8 @@ bool setup_pixel(b200jpeg_ctx *c, int f, int sms) {
   int per_sm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2::k_pixel<HS, VS, NC>, b2::kPixThreads, smem);
   if (e != cudaSuccess || per_sm < 1) { c->last_error = "k_pixel does not fit on an SM"; return false; }
-  c->pipe.pix_grid_cap[f] = c->pipe2.pix_grid_cap[f] = per_sm * sms;
+  c->pipe.pix_grid_cap[f] = per_sm * sms;
+  for (b2::Pipeline &x : c->extra) x.pix_grid_cap[f] = per_sm * sms;
   return true;
 }
 
@@ -69,8 +71,12 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
     return B200JPEG_E_CUDA;
   }
   if (cudaStreamCreateWithFlags(&c->pipe.be.stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return B200JPEG_E_CUDA; }
-  if (cudaStreamCreateWithFlags(&c->pipe2.be.stream, cudaStreamNonBlocking) != cudaSuccess) { b200jpeg_destroy(c); return B200JPEG_E_CUDA; }
-  for (int i = 0; i <= B200JPEG_T_COUNT; ++i) { cudaEventCreate(&c->pipe.ev[i]); cudaEventCreate(&c->pipe2.ev[i]); }
+  for (b2::Pipeline &x : c->extra)
+    if (cudaStreamCreateWithFlags(&x.be.stream, cudaStreamNonBlocking) != cudaSuccess) { b200jpeg_destroy(c); return B200JPEG_E_CUDA; }
+  for (int i = 0; i <= B200JPEG_T_COUNT; ++i) {
+    cudaEventCreate(&c->pipe.ev[i]);
+    for (b2::Pipeline &x : c->extra) cudaEventCreate(&x.ev[i]);
+  }
   const size_t es = b2::entropy_smem_bytes(b2::kMaxSlots, true);
   bool ok = allow_smem(b2::k_entropy_sync<true>, es, c->last_error) && allow_smem(b2::k_entropy_sync<false>, es, c->last_error) &&
             allow_smem(b2::k_entropy_write, es, c->last_error) &&
@@ -86,7 +92,7 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
 void b200jpeg_destroy(b200jpeg_ctx *c) {
   if (!c) return;
   DeviceGuard g(c->device);
-  for (b2::Pipeline *p : {&c->pipe, &c->pipe2}) {
+  for (b2::Pipeline *p : {&c->pipe, &c->extra[0], &c->extra[1], &c->extra[2]}) {
     if (p->be.stream) cudaStreamSynchronize(p->be.stream);
     p->destroy();
     for (int i = 0; i <= B200JPEG_T_COUNT; ++i) if (p->ev[i]) cudaEventDestroy(p->ev[i]);
@@ -125,17 +131,23 @@ int b200jpeg_sync(b200jpeg_ctx *c) {
   return fail(c, c->pipe.be.ok() ? 0 : B200JPEG_E_CUDA);
 }
 
-// Host buffers in, host buffers out.  Large batches are cut into chunks that alternate between two
-// pipelines (own stream, own arenas): while chunk k's RGB travels device -> host, chunk k+1's files
-// travel host -> device and its kernels run, so the call is bounded by the slower PCIe direction
-// instead of the sum of copy + decode + copy.
+// Host buffers in, host buffers out.  Large batches are cut into chunks that rotate over kSlots pipelines (own
+// stream, own arenas): while the RGB of earlier chunks travels device -> host, the files of later ones travel
+// host -> device and their kernels run, so the call is bounded by the slower PCIe direction (the RGB) instead of the
+// sum of copy + decode + copy.  Why four pipelines and small chunks: with the device -> host link saturated, host ->
+// device copies crawl (their read requests queue behind the posted writes: 19 MB took 2.1 ms in the CUPTI trace), so
+// a chunk needs about as long as a chunk's RGB copy to get ready -- with only two pipelines the RGB engine ran dry
+// for 0.6 ms per pair of chunks; and the first RGB byte leaves once the first (small) chunk is decoded.
 int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
                           const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
   if (!c || n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
-  int chunk = (n + 7) / 8;
+  constexpr int kSlots = 1 + b200jpeg_ctx::kExtra;
+  int chunk = (n + 15) / 16;
   if (chunk < 8) chunk = 8;
-  if (chunk > 64) chunk = 64;
-  if (const char *ev = getenv("B200JPEG_CHUNK")) { const int v = atoi(ev); if (v > 0) chunk = v; }   // tuning knob (images per chunk)
+  if (chunk > 32) chunk = 32;
+  int nslots = kSlots;
+  if (const char *ev = getenv("B200JPEG_CHUNK")) { const int v = atoi(ev); if (v > 0) chunk = v; }   // tuning knobs
+  if (const char *ev = getenv("B200JPEG_SLOTS")) { const int v = atoi(ev); if (v >= 2 && v <= kSlots) nslots = v; }
   if (coef_out || n <= chunk) {
     int rc = b200jpeg_batch_prepare(c, descs, n, files, sizes);
     if (rc) return rc;
@@ -144,12 +156,12 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
     return b200jpeg_batch_fetch(c, rgb_out, coef_out, status);
   }
   DeviceGuard g(c->device);
-  b2::Pipeline *slot[2] = {&c->pipe, &c->pipe2};
-  int first[2] = {0, 0};
-  bool busy[2] = {false, false};
+  b2::Pipeline *slot[kSlots] = {&c->pipe, &c->extra[0], &c->extra[1], &c->extra[2]};
+  int first[kSlots] = {0, 0, 0, 0};
+  bool busy[kSlots] = {false, false, false, false};
   b200jpeg_batch_stats a;
   memset(&a, 0, sizeof a);
-  c->pipe2.force_path = c->pipe.force_path;
+  for (b2::Pipeline &x : c->extra) x.force_path = c->pipe.force_path;
   const bool timing0 = c->pipe.timing;     // per-stage event times are a single-batch facility
   int rc = 0;
   auto drain = [&](int k) {
@@ -161,7 +173,7 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
     return r ? fail2(c, p, r) : 0;
   };
   int k = 0;
-  for (int at = 0; at < n && !rc; at += chunk, k ^= 1) {
+  for (int at = 0; at < n && !rc; at += chunk, k = (k + 1) % nslots) {
     const int cnt = n - at < chunk ? n - at : chunk;
     rc = drain(k);
     if (rc) break;
@@ -179,8 +191,10 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
     a.h2d_bytes += p.h2d_bytes;
     for (int i = 0; i < cnt; ++i) a.rgb_bytes += (int64_t)3 * p.plan.imgs[i].width * p.plan.imgs[i].height;
   }
-  const int r0 = drain(k), r1 = drain(k ^ 1);      // oldest first
-  if (!rc) rc = r0 ? r0 : r1;
+  for (int j = 0; j < nslots; ++j) {                 // oldest first
+    const int r = drain((k + j) % nslots);
+    if (!rc) rc = r;
+  }
   c->agg = a; c->agg_valid = true;
   c->pipe.timing = timing0;
   return rc;
@@ -210,7 +224,8 @@ int b200jpeg_batch_get_stats(const b200jpeg_ctx *c, b200jpeg_batch_stats *s) {
 
 int b200jpeg_set_entropy_path(b200jpeg_ctx *c, int mode) {
   if (!c || mode < 0 || mode > 2) return B200JPEG_E_ARG;
-  c->pipe.force_path = c->pipe2.force_path = mode;
+  c->pipe.force_path = mode;
+  for (b2::Pipeline &x : c->extra) x.force_path = mode;
   return B200JPEG_OK;
 }
 

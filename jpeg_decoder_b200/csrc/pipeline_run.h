@@ -318,13 +318,28 @@ struct Pipeline {
   void enqueue_rgb(uint8_t *const *rgb_out) {
     const BatchPlan &P = plan;
     if (!results_enqueued) enqueue_small_results();
-    if (rgb_out) for (int i = 0; i < P.n; ++i) if (rgb_out[i]) {
+    if (rgb_out) for (int i = 0; i < P.n;) {
+      if (!rgb_out[i]) { ++i; continue; }
       const ImageDev &im = P.imgs[i];
       const uint8_t *src = d_rgb.as<uint8_t>() + im.rgb_off;
       const size_t row = (size_t)3 * im.width;
-      if (im.rgb_pitch == row) be.d2h(rgb_out[i], src, row * im.height);
-      else be.d2h_2d(rgb_out[i], row, src, im.rgb_pitch, row, im.height);
-      d2h_bytes += (int64_t)(row * im.height);
+      if (im.rgb_pitch != row) {
+        be.d2h_2d(rgb_out[i], row, src, im.rgb_pitch, row, im.height);
+        d2h_bytes += (int64_t)(row * im.height);
+        ++i;
+        continue;
+      }
+      // dense rows: images that follow each other both on the device and in the caller's memory leave as ONE copy
+      size_t len = row * im.height;
+      int j = i + 1;
+      while (j < P.n && rgb_out[j] && P.imgs[j].rgb_pitch == (size_t)3 * P.imgs[j].width &&
+             P.imgs[j].rgb_off == im.rgb_off + len && rgb_out[j] == rgb_out[i] + len && len < ((size_t)64 << 20)) {
+        len += (size_t)3 * P.imgs[j].width * P.imgs[j].height;
+        ++j;
+      }
+      be.d2h(rgb_out[i], src, len);
+      d2h_bytes += (int64_t)len;
+      i = j;
     }
   }
 

@@ -23,18 +23,6 @@ struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__
 #define B2_SHARED __shared__
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
-// launch as thread-block clusters of `cluster` CTAs along x (grid = clusters x cluster)
-template <class... KArgs, class... Args>
-inline cudaError_t b2_launch_cluster(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t stream, int cluster,
-                                     Args... args) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = (unsigned)cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
-}
 #define B2_DYN_SMEM(type, name) extern __shared__ __align__(128) unsigned char name##_raw_[]; \
   type *name = reinterpret_cast<type *>(name##_raw_)
 #define B2_CONSTANT __constant__
@@ -152,30 +140,7 @@ B2_DEVICE uint4 b2_lds_v4(uint32_t a) {
 B2_DEVICE void b2_sts_v4(uint32_t a, uint4 v) {
   asm volatile("st.shared::cta.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-// ---- thread-block clusters: distributed shared memory between the CTAs of a cluster ----
-B2_DEVICE uint32_t b2_cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-B2_DEVICE uint32_t b2_cluster_id_x() { uint32_t r; asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r)); return r; }
-// the shared::cluster address of what sits at window address `a` in CTA `rank` of the cluster
-B2_DEVICE uint32_t b2_mapa(uint32_t a, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
-  return r;
-}
-B2_DEVICE void b2_cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// 16 bytes into ANOTHER CTA's shared memory; the store completes 16 bytes of the transaction count of an mbarrier
-// over there: no fence and no release on the producer's side, the consumer's wait on the barrier sees the data
-B2_DEVICE void b2_st_async_v4(uint32_t raddr, uint4 v, uint32_t rbar) {
-  asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];"
-               ::"r"(raddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(rbar) : "memory");
-}
-B2_DEVICE void b2_mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-B2_DEVICE void b2_mbar_arrive_remote(uint32_t rbar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(rbar) : "memory");
-}
+// ---- mbarriers by 32-bit window address (the segment decoder's hand-overs) ----
 B2_DEVICE void b2_mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 B2_DEVICE void b2_mbar_init_a(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");

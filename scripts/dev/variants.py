@@ -56,15 +56,20 @@ for p in paths:
         wall = (time.perf_counter() - t0) / a.steps * 1e3
         out = {"variant": name, "wall_ms": round(wall, 3), "bad_status": bad}
         out.update({k: round(v / a.steps, 3) for k, v in acc.items()})
-        for ch in [int(x) for x in a.e2e.split(",") if x]:
+        for spec in [x for x in a.e2e.split(",") if x]:
+            ch, _, sl = spec.partition(":")
+            ch = int(ch)
             os.environ["B200JPEG_CHUNK"] = str(ch)
+            if sl:
+                os.environ["B200JPEG_SLOTS"] = sl
             dec.decode_batch(descs, files, rgbs)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             for _ in range(5):
                 dec.decode_batch(descs, files, rgbs)
-            out["e2e_chunk%d_ms" % ch] = round((time.perf_counter() - t0) / 5 * 1e3, 2)
+            out["e2e_chunk%s_ms" % spec] = round((time.perf_counter() - t0) / 5 * 1e3, 2)
         os.environ.pop("B200JPEG_CHUNK", None)
+        os.environ.pop("B200JPEG_SLOTS", None)
         print(json.dumps(out), flush=True)
         dec.close()
     except Exception as e:  # keep going: a diagnostic build may fail on purpose
