@@ -121,7 +121,7 @@ def test_truncated_and_random_garbage_do_not_crash(dec, harness):
 
 
 def test_decode_batch_is_chunked_and_matches_single_batch(dec, harness):
-    # b200jpeg_decode_batch cuts batches of more than 8 images into chunks that alternate between two
+    # b200jpeg_decode_batch cuts batches of more than 8 images into chunks that rotate over four
     # pipelines (H2D / kernels / D2H overlap): results must equal the staged single-batch API
     import ctypes as C
     from jpeg_decoder_b200 import abi
