@@ -46,6 +46,17 @@ def test_segment_path_all_formats_and_fixtures(emul, oracle_mod, harness):
     assert info["sync_rounds"] == 0
 
 
+def test_segment_path_extreme_content(emul, oracle_mod, harness):
+    # flat pictures (DC + EOB blocks: four to five blocks per lane and FIFO round, the fullest the ring of block images
+    # gets) and white noise at q98 (long codes: the rounds' extra slot) through the segment decoder
+    rng = np.random.default_rng(5)
+    flat = np.full((48, 96, 3), 200, np.uint8)
+    noise = rng.integers(0, 256, size=(48, 96, 3), dtype=np.uint8)
+    datas = [harness.encode_rgb(flat, 90, 2, 2, False, -1), harness.encode_rgb(noise, 98, 2, 2, False, -1),
+             harness.encode_rgb(flat, 50, 1, 1, True, 2), harness.encode_rgb(noise, 98, 1, 1, False, 3)]
+    check(emul, oracle_mod, datas, flags=1, path=1)
+
+
 def test_segment_path_flags_corrupt_streams(emul, harness):
     from jpeg_decoder_b200 import abi
     good = bytearray(harness.synth_jpeg(41, 160, 96, 85, 2, 2, False, -1))

@@ -74,6 +74,28 @@ def test_mixed_batch_all_sampling_formats(dec, oracle_mod, harness):
     compare(dec, oracle_mod, datas, flags=1)
 
 
+def test_extreme_content(dec, oracle_mod, harness):
+    """Pictures at the ends of the symbol statistics, many restart segments each:
+    flat ones (every block is DC + EOB: a lane finishes four to five blocks per FIFO round -- the most the segment
+    decoder's ring of block images ever holds, its room check has to wait), white noise at q98 (long codes and large
+    magnitudes in nearly every block: the extra slot of every round is in use), and both alternating MCU by MCU."""
+    rng = np.random.default_rng(11)
+    w, h = 640, 352
+    flat = np.full((h, w, 3), 128, np.uint8)
+    black = np.zeros((h, w, 3), np.uint8)
+    noise = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+    mixed = flat.copy()
+    for y in range(0, h, 16):
+        for x in range(0, w, 16):
+            if ((x + y) // 16) % 2:
+                mixed[y:y + 16, x:x + 16] = noise[y:y + 16, x:x + 16]
+    datas = [harness.encode_rgb(flat, 90, 2, 2, False, -1), harness.encode_rgb(black, 50, 2, 2, False, 1),
+             harness.encode_rgb(noise, 98, 2, 2, False, -1), harness.encode_rgb(noise, 98, 1, 1, False, 3),
+             harness.encode_rgb(mixed, 95, 2, 2, False, -1), harness.encode_rgb(mixed, 90, 2, 1, False, 2),
+             harness.encode_rgb(flat, 90, 1, 1, True, 5), harness.encode_rgb(noise, 98, 1, 1, True, -1)]
+    compare(dec, oracle_mod, datas, flags=1)
+
+
 def test_fixtures_in_one_batch_and_repeatable(dec, oracle_mod):
     datas = [fixture_bytes(n) for n in FIXTURES]
     compare(dec, oracle_mod, datas)
