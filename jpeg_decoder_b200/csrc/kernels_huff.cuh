@@ -15,13 +15,12 @@
 //
 // entry (u32):  [4:0] adv = code length + magnitude bits (<= 27)   [8:5] size = magnitude bits (code length = adv - size)
 //               [15:9] zinc = how far the zig-zag index moves (run+1, run for size 0, 64 for EOB,
-//               1 for a DC symbol)   bit 16 EOB
-//               [20:17] adv2, [25:21] zinc2: level-1 entries of AC tables only -- when the symbol is followed,
+//               1 for a DC symbol); bit 15 (zinc = 64) doubles as the EOB flag
+//               [19:16] adv2, [24:20] zinc2, [27:25] size2: level-1 entries of AC tables only -- when the symbol is followed,
 //               inside the same kHLutBits index bits, by a SECOND complete AC symbol (code + magnitude bits),
-//               adv2 != 0 is that symbol's length and zinc2 its zig-zag advance (0 = it is EOB).  Two thirds of
-//               the symbols of a typical scan pair up, so a decoder that takes both at once makes a third fewer
-//               steps.  [27:26] the AC table's own number (whoever wants the second symbol's details looks its
-//               bits up in that table again)
+//               adv2 != 0 is that symbol's length, zinc2 its zig-zag advance (0 = it is EOB) and size2 its magnitude bits.
+//               Two thirds of the symbols of a typical scan pair up, so a decoder that takes both at once makes a third
+//               fewer steps, and whoever places the coefficients has everything about both symbols in the one entry.
 //               bit 28 overflow   bit 29 bad size (jpeg.cpp:330,381)   bit 30 no such code (jpeg.cpp:319)
 //               bit 31 long (level-1 only; [15:0] = level-2 base)
 #pragma once
@@ -36,7 +35,7 @@ constexpr int kHL2Blocks = 8;
 constexpr int kHL2 = kHL2Blocks * 64;
 constexpr int kHTab = kHL1 + kHL2;          // u32 entries per table (6 KiB)
 constexpr int kHTabsPerSet = 8;             // dc0..dc3, ac0..ac3
-constexpr uint32_t kHEob = 1u << 16, kHOverflow = 1u << 28, kHBadSize = 1u << 29, kHBadCode = 1u << 30, kHLong = 1u << 31;
+constexpr uint32_t kHEob = 1u << 15, kHOverflow = 1u << 28, kHBadSize = 1u << 29, kHBadCode = 1u << 30, kHLong = 1u << 31;
 constexpr uint32_t kHSpecial = kHOverflow | kHBadSize | kHBadCode | kHLong;
 
 B2_HD uint32_t huff_entry(uint32_t adv, uint32_t len, uint32_t zinc, uint32_t flags) {
@@ -46,9 +45,10 @@ B2_HD uint32_t huff_adv(uint32_t e) { return e & 31u; }
 B2_HD uint32_t huff_size(uint32_t e) { return (e >> 5) & 15u; }
 B2_HD uint32_t huff_len(uint32_t e) { return huff_adv(e) - huff_size(e); }
 B2_HD uint32_t huff_zinc(uint32_t e) { return (e >> 9) & 127u; }
-B2_HD uint32_t huff_adv2(uint32_t e) { return (e >> 17) & 15u; }
-B2_HD uint32_t huff_zinc2(uint32_t e) { const uint32_t z = (e >> 21) & 31u; return z ? z : 64u; }   // only if adv2 != 0
-B2_HD uint32_t huff_tslot(uint32_t e) { return (e >> 26) & 3u; }
+B2_HD uint32_t huff_adv2(uint32_t e) { return (e >> 16) & 15u; }
+B2_HD uint32_t huff_zinc2_raw(uint32_t e) { return (e >> 20) & 31u; }                                  // 0: the second symbol is EOB
+B2_HD uint32_t huff_zinc2(uint32_t e) { const uint32_t z = huff_zinc2_raw(e); return z ? z : 64u; }   // only if adv2 != 0
+B2_HD uint32_t huff_size2(uint32_t e) { return (e >> 25) & 7u; }
 // symbol -> entry, following decodeMCUComponent (jpeg.cpp:330-400)
 B2_HD uint32_t huff_symbol_entry(uint32_t sym, uint32_t len, bool is_dc) {
   if (is_dc) {
@@ -119,10 +119,9 @@ B2_GLOBAL void k_build_luts(const TableSet *__restrict__ tsets, uint32_t *__rest
         const uint32_t e2 = huff_search(spec, canon, rest << (16 - kHLutBits), 1, (int)left, false);
         if (!(e2 & kHSpecial) && huff_adv(e2) <= left) {
           const uint32_t z2 = (e2 & kHEob) ? 0u : huff_zinc(e2);                      // 0 stands for EOB
-          if ((e2 & kHEob) || (z2 >= 1u && z2 <= 16u)) e |= (huff_adv(e2) << 17) | (z2 << 21);
+          if (((e2 & kHEob) || (z2 >= 1u && z2 <= 16u)) && huff_size(e2) <= 7u) e |= (huff_adv(e2) << 16) | (z2 << 20) | (huff_size(e2) << 25);
         }
       }
-      if (!is_dc && !(e & kHLong)) e |= (uint32_t)(t - 4) << 26;   // the AC table's number rides in every direct entry
     } else {
       const uint32_t blk = (uint32_t)(idx - kHL1) >> 6, low = (uint32_t)(idx - kHL1) & 63u;
       const uint32_t prefix = p0 + blk;

@@ -243,8 +243,9 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
     // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
     //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8 ----
     const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) b2_cp_async4_if(need, ring_a + (((rw + i) & (kSegWords - 1)) << 7), us + rw + i);
+    // (rw is a multiple of 4 and so is the ring size: four consecutive words never wrap)
+    b2_cp_async4x4_if(need, ring_a + ((rw & (kSegWords - 1)) << 7), us + rw);
+    b2_cp_async4x4_if(need, ring_a + (((rw + 4u) & (kSegWords - 1)) << 7), us + rw + 4);
     // slot 32 repeats slot 0 (the window's second word is always at +128); rw is a multiple of 4
     b2_cp_async4_if(need && (rw & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw);
     b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
@@ -330,9 +331,8 @@ B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {
 // =========================== AC coefficients: stateless, every kSegAcW-th round ===========================
 // magnitude extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store into the block image; everything a symbol
 // needs is in its FIFO entry, so the writers keep no state between symbols and several of them work in parallel.
-B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a, uint32_t asm_a, const uint32_t *fl,
+B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a, const uint32_t *fl,
                              uint32_t g0, uint32_t &err) {
-  const uint32_t lut_r = b2_launder(lut_a);
   for (uint32_t r = (uint32_t)w;; r += (uint32_t)kSegAcW) {
     ff.wait(r);
     const uint32_t ra = ff.round_a(r);
@@ -358,12 +358,10 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t lut_a,
         // a run that reaches past 63 without being EOB is an error (jpeg.cpp:372-376); a coefficient AT 63 is not
         bad |= (e & kHEob) ? 0u : pos + (size == 0u ? 1u : 0u);
         if (fn[u] & kSegPairBit) {
-          // the second symbol of the entry: its bits follow the first one's; its details come from the same table
-          const uint32_t w2 = fw[u] << adv;
-          const uint32_t e2 = b2_lds_ro(lut_r + (4u + huff_tslot(e)) * (uint32_t)(kHTab * 4) + ((w2 >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-          const uint32_t adv2 = huff_adv(e2), size2 = huff_size(e2), pos2 = pos + huff_zinc(e2);
-          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos2), (uint32_t)seg_extend(w2, adv2 - size2, size2));
-          bad |= (e2 & kHEob) ? 0u : pos2 + (size2 == 0u ? 1u : 0u);
+          // the second symbol of the entry (kernels_huff.cuh): its bits follow the first one's
+          const uint32_t adv2 = huff_adv2(e), size2 = huff_size2(e), z2 = huff_zinc2_raw(e), pos2 = pos + z2;
+          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos2), (uint32_t)seg_extend(fw[u] << adv, adv2 - size2, size2));
+          bad |= z2 == 0u ? 0u : pos2 + (size2 == 0u ? 1u : 0u);    // z2 = 0: EOB
         }
       }
     }
@@ -505,7 +503,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
   if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);
-  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, lut_a, asm_g + ((uint32_t)lane << 7), fl, g0, err);
+  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, g0, err);
   else if (role == kSegAcW + 1) seg_dc_warp(ff, lane, L, asm_g + ((uint32_t)lane << 7), fl, g0, err);
   else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef));
   if (err) atomicOr(&out[L.img].status, err);

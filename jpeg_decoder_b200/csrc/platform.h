@@ -58,6 +58,16 @@ B2_DEVICE void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) {
   asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %0, 0;\n@p cp.async.ca.shared.global [%1], [%2], 4;\n}" ::"r"((int)on), "r"(dst_smem),
                "l"(__cvta_generic_to_global(src)) : "memory");
 }
+// four of them: consecutive words of global memory to shared addresses 128 bytes apart ([word][lane] layouts), one
+// address computation for all four
+B2_DEVICE void b2_cp_async4x4_if(bool on, uint32_t dst_smem, const void *src) {
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %0, 0;\n"
+               "@p cp.async.ca.shared.global [%1], [%2], 4;\n"
+               "@p cp.async.ca.shared.global [%1+128], [%2+4], 4;\n"
+               "@p cp.async.ca.shared.global [%1+256], [%2+8], 4;\n"
+               "@p cp.async.ca.shared.global [%1+384], [%2+12], 4;\n}" ::"r"((int)on), "r"(dst_smem),
+               "l"(__cvta_generic_to_global(src)) : "memory");
+}
 B2_DEVICE void b2_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> B2_DEVICE void b2_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 

@@ -292,6 +292,9 @@ static inline void b2_mbar_wait_a(uint32_t a, uint32_t parity) {
 }
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
 static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
+static inline void b2_cp_async4x4_if(bool on, uint32_t dst_smem, const void *src) {
+  if (on) for (int i = 0; i < 4; ++i) memcpy(b2_dsm_base() + dst_smem + 128 * i, static_cast<const unsigned char *>(src) + 4 * i, 4);
+}
 static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) memcpy(b2_dsm_base() + dst_smem, src, 4); }
 static inline uint32_t b2_ld_acquire_smem(const uint32_t *p) {
   std::this_thread::yield();                    // callers spin on it: one OS thread per CUDA thread here
