@@ -350,20 +350,19 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
     uint32_t bad = 0;
 #pragma unroll
     for (int u = 0; u < (B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
+      // no branch: every lane does the arithmetic of both symbols, the stores are predicated.  (A DC symbol has z = 0,
+      // a lane that steps in place entry 0, i.e. size 0: neither stores, neither trips the run check.)
       const uint32_t e = fe[u], z = fn[u] & 63u;
-      if (z != 0u && e != 0u) {                       // AC (DC symbols carry z = 0, a lane that steps in place entry 0)
-        const uint32_t gn = g0 + (fn[u] >> kSegNbShift);
-        const uint32_t adv = huff_adv(e), size = huff_size(e), pos = z + huff_zinc(e) - 1u;   // z + run
-        if (size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos), (uint32_t)seg_extend(fw[u], adv - size, size));
-        // a run that reaches past 63 without being EOB is an error (jpeg.cpp:372-376); a coefficient AT 63 is not
-        bad |= (e & kHEob) ? 0u : pos + (size == 0u ? 1u : 0u);
-        if (fn[u] & kSegPairBit) {
-          // the second symbol of the entry (kernels_huff.cuh): its bits follow the first one's
-          const uint32_t adv2 = huff_adv2(e), size2 = huff_size2(e), z2 = huff_zinc2_raw(e), pos2 = pos + z2;
-          if (size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos2), (uint32_t)seg_extend(fw[u] << adv, adv2 - size2, size2));
-          bad |= z2 == 0u ? 0u : pos2 + (size2 == 0u ? 1u : 0u);    // z2 = 0: EOB
-        }
-      }
+      const bool ac = z != 0u, two = (fn[u] & kSegPairBit) != 0u;
+      const uint32_t gn = g0 + (fn[u] >> kSegNbShift);
+      const uint32_t adv = huff_adv(e), size = huff_size(e), pos = z + huff_zinc(e) - 1u;   // z + run
+      if (ac && size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos), (uint32_t)seg_extend(fw[u], adv - size, size));
+      // a run that reaches past 63 without being EOB is an error (jpeg.cpp:372-376); a coefficient AT 63 is not
+      bad |= (e & kHEob) ? 0u : pos + (size == 0u ? 1u : 0u);
+      // the second symbol of the entry (kernels_huff.cuh): its bits follow the first one's
+      const uint32_t adv2 = huff_adv2(e), size2 = huff_size2(e), z2 = huff_zinc2_raw(e), pos2 = pos + z2;
+      if (two && size2 != 0u && pos2 < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos2), (uint32_t)seg_extend(fw[u] << adv, adv2 - size2, size2));
+      bad |= (!two || z2 == 0u) ? 0u : pos2 + (size2 == 0u ? 1u : 0u);    // z2 = 0: EOB
     }
     if (bad > 63u) err |= ST_BAD_RUN;                 // (positions are below 128: OR-ing them keeps "some position > 63")
     ff.worked_arrive(r, lane);
