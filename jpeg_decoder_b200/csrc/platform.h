@@ -104,7 +104,7 @@ B2_DEVICE void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
       "{\n"
       ".reg .pred p;\n"
       "B2_WAIT:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"
       "@p bra B2_DONE;\n"
       "bra B2_WAIT;\n"
       "B2_DONE:\n"
@@ -160,7 +160,7 @@ B2_DEVICE void b2_mbar_wait_a(uint32_t bar, uint32_t parity) {
       "{\n"
       ".reg .pred p;\n"
       "B2_WAITA:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, 0x989680;\n"   /* suspend-time hint: without it the wait comes back at once and the retry loop eats issue slots */
       "@p bra B2_DONEA;\n"
       "bra B2_WAITA;\n"
       "B2_DONEA:\n"
