@@ -8,39 +8,42 @@
 // Why this shape: a segment starts byte-aligned with the DC predictors reset (jpeg.cpp:419-425)
 // and its first block index is known a priori (k * RI * blocks-per-MCU), so nothing has to be
 // synchronised or prefix-summed -- the self-synchronising path (kernels_entropy.cuh) pays three
-// passes over the stream for that.  The price is one long dependent chain per lane and, with a few
-// thousand segments per batch, only about one warp per SM sub-partition: the kernel is bound by the
-// LATENCY of that chain (position -> window -> table entry -> position), not by issue slots or memory.
-// Two things follow.
+// passes over the stream for that.  The price is one long dependent chain per lane (position -> window -> table
+// entry -> position), and all the chains of a batch are resident at once: the kernel takes as long as one chain,
+// i.e. steps per segment x cycles per step, plus whatever else competes for the decoder's sub-partition.
 //
-// (1) Every step is the same for every lane.  Events that are rare for one lane (bit-buffer refill,
-//     end of block) happen in almost every step for SOME lane of a warp, and a branch then costs all 32:
+// (1) Every step is the same for every lane, and the eight steps of a round are one basic block.  Events that are
+//     rare for one lane (bit-buffer refill, end of block, a long code) happen in almost every step for SOME lane of a
+//     warp, and a branch then costs all 32:
 //   * no bit buffer: the 32-bit window is re-read each step from the bit position, out of a
 //     per-lane ring of the next 32 stream words in shared memory laid out [word][lane] (bank =
-//     lane: conflict-free whatever the lanes' positions);
+//     lane: conflict-free whatever the lanes' positions; slot 32 repeats slot 0, the second word is always at +128);
 //   * the ring is topped up by cp.async (LDGSTS, no register in between) under a per-lane
-//     PREDICATE once every four steps -- four steps consume at most 108 bits, one top-up brings 128;
-//   * DC and AC tables are looked up together and selected afterwards.
+//     PREDICATE once per round -- nine symbols consume at most 243 bits, one top-up brings 256;
+//   * DC or AC table by a select, block end and segment end by selects;
+//   * an entry the first-level table cannot resolve (a code longer than kHLutBits: 0.5 % of the symbols) makes the
+//     lane wait in place for the round's extra slot, where one warp-uniform branch resolves it;
+//   * AC entries that hold two complete symbols inside the index bits are taken in one step (kernels_huff.cuh).
 //
-// (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by several warps of the
+// (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by five warps of the
 //     same CTA:
 //       decoder   walks the codes -- window, table entry, advance, block/table bookkeeping -- and pushes
 //                 (window, entry, zig-zag index | block number) per lane and step into a shared-memory FIFO;
 //       AC writers take every kSegAcW-th round of the FIFO: magnitude extension (jpeg.cpp:388-397), zig-zag
 //                 position.  They keep no state between symbols -- everything they need is in the FIFO entry;
 //       DC warp   sees every round but only the DC symbols: extension, prediction per component
-//                 (jpeg.cpp:335-345), range check -- and it FLUSHES finished blocks.
-//     Hand-over is a producer counter and one consumer counter per warp (st.release / ld.acquire in shared
-//     memory), one update per round.
+//                 (jpeg.cpp:335-345), range check;
+//       flusher   sends finished blocks to global memory (3).
+//     Every hand-over is an mbarrier in shared memory: a waiting warp is suspended by the hardware.
 //
 // (3) Coefficients leave the SM as whole 128-byte blocks.  A 2-byte store per coefficient from 32 lanes that work on
 //     32 different segments is 32 sectors per instruction: one L1 tag cycle each (233 M sectors per bench step = 0.8 ms
 //     of every SM's load/store path, in front of which the decoder's shared-memory loads queue), a read-modify-write
 //     in L2 for every sector, and a 1.6 GB memset beforehand because only non-zero values were stored.  Instead the
 //     writers put the values into a per-lane ring of kSegAsm block images in SHARED memory (st.shared.u16), and the
-//     DC warp, once a round's AC writer is through, copies the blocks that round finished to global memory with
-//     128-bit stores -- eight lanes per block, full lines, zeros included, no memset, no read-modify-write -- and
-//     clears the images.  A writer checks, per lane, that the blocks of its round are less than kSegAsm ahead of the
+//     flusher, once a round's AC writer and the DC warp are through, copies the blocks that round finished to global
+//     memory with 128-bit stores -- eight threads per block, full lines, zeros included, no memset, no
+//     read-modify-write -- and clears the images.  A writer checks, per lane, that the blocks of its round are less than kSegAsm ahead of the
 //     flushed ones (they almost always are: a lane finishes 0.65 blocks per round) and waits otherwise.
 //
 //     Tried and dropped: decoders and consumers on different SMs (thread-block clusters, FIFO through DSMEM with
