@@ -103,6 +103,34 @@ B2_DEVICE void u_classify(const uint8_t *__restrict__ raw, uint32_t pos, uint32_
   }
 }
 
+// The counting pass needs only HOW MANY bytes a thread emits and how many RSTn it holds, not which: byte-lane masks and
+// two population counts per word instead of the bit masks of u_classify.  Returns false when the sixteen bytes hold
+// anything else of interest (FF D9, an illegal marker) or are the ragged end of the scan: the caller classifies in full.
+B2_DEVICE bool u_count_fast(const uint8_t *__restrict__ raw, uint32_t pos, uint32_t raw_len, uint32_t &emits, uint32_t &rsts) {
+  const bool live = pos < raw_len;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (live) v = b2_ld_nc_v4(reinterpret_cast<const uint4 *>(raw + pos));
+  uint32_t prev = __shfl_up_sync(0xffffffffu, v.w >> 24, 1);
+  if ((threadIdx.x & 31) == 0) prev = (live && pos) ? raw[pos - 1] : 0;
+  emits = rsts = 0;
+  if (!live) return true;
+  const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+  uint32_t held = 0, marks = 0, other = 0;           // byte lanes: not emitted / RSTn / anything else behind an FF
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t w = w4[j], pw = (w << 8) | prev;
+    prev = w >> 24;
+    const uint32_t fc = u_eq4(w, 0xffffffffu), fp = u_eq4(pw, 0xffffffffu), zc = u_eq4(w, 0u);
+    const uint32_t rs = u_eq4(w & 0xf8f8f8f8u, 0xd0d0d0d0u);
+    held += (uint32_t)__popc(fc | (fp & ~zc));
+    marks += (uint32_t)__popc(fp & rs);
+    other |= fp & ~(zc | rs | fc);
+  }
+  emits = 16u - (held >> 3);
+  rsts = marks >> 3;
+  return other == 0u && raw_len - pos >= 16u;
+}
+
 // U1: per-tile counts and the first EOI / first illegal marker of each image.
 B2_GLOBAL void k_unstuff_count(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ tile_base, int nimg,
                                const uint8_t *__restrict__ d_raw, uint32_t *__restrict__ tile_cnt,
@@ -113,12 +141,17 @@ B2_GLOBAL void k_unstuff_count(const ImageDev *__restrict__ imgs, const int32_t 
   const int i = s_img;
   const ImageDev im = imgs[i];
   const uint32_t pos = ((uint32_t)blockIdx.x - (uint32_t)im.tile_base) * kUTile + threadIdx.x * kUBytesPerThread;
-  UClass c;
-  u_classify(d_raw + im.raw_off, pos, im.raw_len, c);
-  if (c.end_mask) atomicMin(&out[i].end_pos, pos + (uint32_t)__ffs((int)c.end_mask) - 1);
-  if (c.err_mask) atomicMin(&out[i].err_pos, pos + (uint32_t)__ffs((int)c.err_mask) - 1);
+  uint32_t emits, rsts;
+  const bool plain = u_count_fast(d_raw + im.raw_off, pos, im.raw_len, emits, rsts);
+  if (__any_sync(0xffffffffu, !plain)) {             // rare: an end of scan, an illegal marker, the scan's last bytes
+    UClass c;
+    u_classify(d_raw + im.raw_off, pos, im.raw_len, c);
+    if (c.end_mask) atomicMin(&out[i].end_pos, pos + (uint32_t)__ffs((int)c.end_mask) - 1);
+    if (c.err_mask) atomicMin(&out[i].err_pos, pos + (uint32_t)__ffs((int)c.err_mask) - 1);
+    emits = (uint32_t)__popc(c.emit_mask); rsts = (uint32_t)__popc(c.rst_mask);
+  }
   uint32_t tot;
-  cta_excl_scan_u32((uint32_t)__popc(c.emit_mask) | ((uint32_t)__popc(c.rst_mask) << 16), &tot);
+  cta_excl_scan_u32(emits | (rsts << 16), &tot);
   if (threadIdx.x == 0) tile_cnt[blockIdx.x] = tot;   // emits in the low half, RSTs in the high half
 }
 
