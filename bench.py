@@ -293,7 +293,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                     "whole_path": {"alg_bytes": a_e2e, "achieved": a_e2e / ev_total_ms / 1e6, "frac": a_e2e / ev_total_ms / 1e6 / peak}}
         ncpu = os.cpu_count() or 1
         cpu = None
-        if world == 1 or True:
+        if world == 1:                              # the CPU baseline is a 1-GPU-run item (rank 0 at N=1 only)
             v, cores, kind, sample = cpu_reference_run(files[:min(n, max(8, min(64, ncpu)))], 2, ncpu)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
         value = world * pixels * args.steps / t_res / 1e6
