@@ -78,11 +78,11 @@ namespace b2 {
 #define B2_SEG_POLL_NS 200
 #endif
 #ifndef B2_SEG_DIAG
-#define B2_SEG_DIAG 0     // measurements only: 4 = DC warp does not compute, 5 = AC writers do not compute
+#define B2_SEG_DIAG 0     // measurements only: 5 = the writers do not compute
 #endif
 constexpr int kSegGroups = B2_SEG_GROUPS;     // groups (32 segments: one decoder warp + its consumers) per CTA
 constexpr int kSegAcW = B2_SEG_ACW;           // AC writer warps per group: writer w takes the rounds r with r % kSegAcW == w
-constexpr int kSegRoles = kSegAcW + 3;        // decoder, AC writers, DC warp, flusher
+constexpr int kSegRoles = kSegAcW + 2;        // decoder, writers, flusher
 constexpr int kSegThreads = kSegGroups * kSegRoles * 32;   // threads per CTA of k_entropy_seg
 constexpr int kSegUnits = kSegGroups * 32;    // segments per CTA
 constexpr uint32_t kSegNoUnit = 0xffffffffu;
@@ -148,9 +148,9 @@ B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, 
 // (blocks finished after the round << 1 | kSegFinFlag).  Nobody polls: every hand-over is an mbarrier in shared memory,
 // a waiting warp is suspended by the hardware (spinning consumers took two fifths of the kernel's issue slots).
 //   full[s]    1 arrival: the decoder has written the round in slot s
-//   empty[s]   3 arrivals: the round's AC writer, the DC warp and the flusher have the round in registers
-//   worked[i]  2 arrivals: the AC writer and the DC warp of round r (i = r % kSegWorkedDepth) have put its values into the
-//              block images -- what the flusher waits for.  Deeper than the FIFO, so that a phase cannot complete twice
+//   empty[s]   2 arrivals: the round's writer and the flusher have what they need of the round in registers
+//   worked[i]  1 arrival: the writer of round r (i = r % kSegWorkedDepth) has put its values into the block images --
+//              what the flusher waits for.  Deeper than the FIFO, so that a phase cannot complete twice
 //              before the flusher has looked at it (writers are at most kSegFifo rounds ahead of the flusher's reads).
 constexpr int kSegWorkedDepth = 8;
 constexpr int kSegBars = 2 * kSegFifo + kSegWorkedDepth;
@@ -162,8 +162,8 @@ struct SegFifo {
   B2_MEMBER uint32_t empty(uint32_t r) const { return bar_a + 8u * ((uint32_t)kSegFifo + (r & (uint32_t)(kSegFifo - 1))); }
   B2_MEMBER uint32_t worked(uint32_t r) const { return bar_a + 8u * ((uint32_t)(2 * kSegFifo) + (r & (uint32_t)(kSegWorkedDepth - 1))); }
   B2_MEMBER void init() const {                                  // one thread
-    for (uint32_t s = 0; s < (uint32_t)kSegFifo; ++s) { b2_mbar_init_a(full(s), 1); b2_mbar_init_a(empty(s), 3); }
-    for (uint32_t i = 0; i < (uint32_t)kSegWorkedDepth; ++i) b2_mbar_init_a(worked(i), 2);
+    for (uint32_t s = 0; s < (uint32_t)kSegFifo; ++s) { b2_mbar_init_a(full(s), 1); b2_mbar_init_a(empty(s), 2); }
+    for (uint32_t i = 0; i < (uint32_t)kSegWorkedDepth; ++i) b2_mbar_init_a(worked(i), 1);
   }
   // ---- producer ----
   B2_MEMBER void wait_room(uint32_t r) const {                   // round r may be written once round r - kSegFifo has been read
@@ -353,13 +353,14 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
     uint32_t bad = 0;
 #pragma unroll
     for (int u = 0; u < (B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
-      // no branch: every lane does the arithmetic of both symbols, the stores are predicated.  (A DC symbol has z = 0,
-      // a lane that steps in place entry 0, i.e. size 0: neither stores, neither trips the run check.)
+      // no branch: every lane does the arithmetic of both symbols, the stores are predicated.  A DC symbol is just a
+      // value for position 0 (z = 0, its entry moves the index by 1): its DIFFERENCE goes into the image, the flusher
+      // turns it into the coefficient.  (A lane that steps in place has entry 0, i.e. size 0: no store, no run error.)
       const uint32_t e = fe[u], z = fn[u] & 63u;
-      const bool ac = z != 0u, two = (fn[u] & kSegPairBit) != 0u;
+      const bool two = (fn[u] & kSegPairBit) != 0u;
       const uint32_t gn = g0 + (fn[u] >> kSegNbShift);
       const uint32_t adv = huff_adv(e), size = huff_size(e), pos = z + huff_zinc(e) - 1u;   // z + run
-      if (ac && size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos), (uint32_t)seg_extend(fw[u], adv - size, size));
+      if (size != 0u && pos < 64u) b2_sts_u16(seg_asm_addr(asm_a, gn, pos), (uint32_t)seg_extend(fw[u], adv - size, size));
       // a run that reaches past 63 without being EOB is an error (jpeg.cpp:372-376); a coefficient AT 63 is not
       bad |= (e & kHEob) ? 0u : pos + (size == 0u ? 1u : 0u);
       // the second symbol of the entry (kernels_huff.cuh): its bits follow the first one's
@@ -373,53 +374,11 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
   }
 }
 
-// =========================== DC coefficients: prediction per component ===========================
-// sees every round but only the DC symbols: extension, prediction (jpeg.cpp:335-345), range check
-B2_DEVICE void seg_dc_warp(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_a, const uint32_t *fl, uint32_t g0, uint32_t &err) {
-  int pred0 = 0, pred1 = 0, pred2 = 0;
-  int blk = 0;
-  uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
-  for (uint32_t r = 0;; ++r) {
-    ff.wait(r);
-    const uint32_t ra = ff.round_a(r);
-    // a lane opens 0.65 blocks per round: first find the round's DC symbols (bit u: slot u holds one), then visit only
-    // those -- the warp makes as many passes as its busiest lane has DC symbols (two, typically), not one per slot
-    uint32_t dcm = 0;
-#pragma unroll
-    for (int u = 0; u < kSegSlots; ++u) {
-      const uint32_t e = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 128u), fn = b2_lds(ra + (uint32_t)u * kSegSlotBytes + 256u);
-      dcm |= (e != 0u && (fn & 63u) == 0u) ? 1u << u : 0u;
-    }
-    const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
-    while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);   // room, as for the AC writers
-    if (B2_SEG_DIAG == 4) dcm = 0;
-    while (__any_sync(0xffffffffu, dcm != 0u)) {
-      if (dcm != 0u) {
-        const uint32_t sa = ra + (uint32_t)(__ffs((int)dcm) - 1) * kSegSlotBytes;
-        dcm &= dcm - 1u;
-        const uint32_t fw = b2_lds(sa), e = b2_lds(sa + 128u), nblk = b2_lds(sa + 256u) >> kSegNbShift;
-        const uint32_t adv = huff_adv(e), size = huff_size(e);
-        const int diff = seg_extend(fw, adv - size, size);                        // jpeg.cpp:335-343
-        const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-        const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff;  // jpeg.cpp:344-345
-        pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
-        dcbad |= (uint32_t)(dc + 32768) >> 16;
-        b2_sts_u16(seg_asm_addr(asm_a, g0 + nblk, 0u), (uint32_t)dc);
-        blk = blk + 1 == L.bpm ? 0 : blk + 1;
-      }
-    }
-    ff.release(r, lane);                             // the round was worked on in place
-    ff.worked_arrive(r, lane);
-    if (tail & kSegFinFlag) break;
-  }
-  if (dcbad) err |= ST_DC_RANGE;
-}
-
 // =========================== the way out ===========================
 // Once a round's AC writer and the DC warp are through with it, the blocks the round finished leave: eight threads
 // per block, 16 bytes each -- whole 128-byte lines -- and the image is cleared.
 B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t list_a,
-                           uint32_t *fl, uint4 *__restrict__ coef4) {
+                           uint32_t *fl, uint4 *__restrict__ coef4, uint32_t &err) {
   const uint32_t gblk = (uint32_t)L.gb;              // the coefficient buffer holds fewer than 2^32 blocks (512 GB)
   if (__any_sync(0xffffffffu, !L.live && L.bidx < L.bend)) {
     // a scan that is not decoded (stage U found it broken) still gets its blocks: zeros
@@ -428,12 +387,29 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
         for (int c = 0; c < 8; ++c) coef4[(size_t)(gblk + b) * 8 + c] = make_uint4(0u, 0u, 0u, 0u);
   }
   uint32_t flushed = 0;                              // blocks of this lane that have left
+  const uint32_t asm_a = asm_g + ((uint32_t)lane << 7);
+  int pred0 = 0, pred1 = 0, pred2 = 0;               // DC prediction per component (jpeg.cpp:335-345), restarted with the segment
+  int blk = 0;                                       // block-in-MCU of the lane's next block to leave
+  uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
   for (uint32_t r = 0;; ++r) {
     ff.wait(r);
     const uint32_t tail = b2_lds(ff.round_a(r) + (uint32_t)kSegSlots * kSegSlotBytes);
     ff.release(r, lane);
-    ff.worked_wait(r);
+    ff.worked_wait(r);                               // the round's writer is through
     const uint32_t upto = tail >> 1, cnt = upto - flushed;
+    // DC: the writers left each block's DC DIFFERENCE at position 0 of its image; a lane's blocks leave in order, so
+    // this is where prediction happens -- once per block, two passes per round typically
+    for (uint32_t k = 0; __any_sync(0xffffffffu, k < cnt); ++k) {
+      if (k < cnt) {
+        const uint32_t a = seg_asm_addr(asm_a, gblk + flushed + k, 0u);
+        const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+        const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + (int)(int16_t)b2_lds_u16(a);
+        pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
+        dcbad |= (uint32_t)(dc + 32768) >> 16;
+        b2_sts_u16(a, (uint32_t)dc);
+        blk = blk + 1 == L.bpm ? 0 : blk + 1;
+      }
+    }
     // the round's finished blocks of all lanes as one list (a byte each: lane << 3 | number among the lane's blocks), so
     // that every pass of the copy loop moves four whole blocks whatever lanes they belong to
     uint32_t incl = cnt;
@@ -460,6 +436,7 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
     b2_st_release_smem(fl, flushed);
     if (tail & kSegFinFlag) break;
   }
+  if (dcbad) err |= ST_DC_RANGE;
 }
 
 // units[u] = (image, segment); the units of one CTA share a table set (the planner pads each table-set group to a
@@ -471,7 +448,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
               const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef) {
   B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab], then the groups
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = warp % kSegGroups, role = warp / kSegGroups;    // role 0 decoder, 1 .. kSegAcW AC writers, kSegAcW + 1 DC warp, kSegAcW + 2 flusher
+  const int g = warp % kSegGroups, role = warp / kSegGroups;    // role 0 decoder, 1 .. kSegAcW writers, kSegAcW + 1 flusher
   uint32_t *const grp = lut + kHTabsPerSet * kHTab + g * kSegGroupWords;
   uint32_t *const ringl = grp + lane;                           // window ring: word j of this lane at ringl[(j & 31) * 32]
   uint32_t *const tb = grp + kSegOffTb;                         // [block-in-MCU][lane]: DC table offset | AC table offset << 16
@@ -506,8 +483,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
   if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);
   else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, g0, err);
-  else if (role == kSegAcW + 1) seg_dc_warp(ff, lane, L, asm_g + ((uint32_t)lane << 7), fl, g0, err);
-  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef));
+  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef), err);
   if (err) atomicOr(&out[L.img].status, err);
 }
 

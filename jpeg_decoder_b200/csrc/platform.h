@@ -140,6 +140,7 @@ B2_DEVICE uint32_t b2_lds_ro(uint32_t a) {
   return v;
 }
 B2_DEVICE void b2_sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
+B2_DEVICE uint32_t b2_lds_u16(uint32_t a) { unsigned short v; asm volatile("ld.shared::cta.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory"); return v; }
 B2_DEVICE void b2_sts_u8(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 B2_DEVICE uint32_t b2_lds_u8(uint32_t a) { uint32_t v; asm volatile("ld.shared::cta.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
 B2_DEVICE uint4 b2_lds_v4(uint32_t a) {

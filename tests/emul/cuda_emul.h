@@ -271,6 +271,7 @@ static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_base()
 static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_base() + a, &v, 4); }
 static inline uint32_t b2_lds_ro(uint32_t a) { return b2_lds(a); }
 static inline void b2_sts_u16(uint32_t a, uint32_t v) { const uint16_t h = (uint16_t)v; memcpy(b2_dsm_base() + a, &h, 2); }
+static inline uint32_t b2_lds_u16(uint32_t a) { uint16_t h; memcpy(&h, b2_dsm_base() + a, 2); return h; }
 static inline void b2_sts_u8(uint32_t a, uint32_t v) { b2_dsm_base()[a] = (unsigned char)v; }
 static inline uint32_t b2_lds_u8(uint32_t a) { return b2_dsm_base()[a]; }
 static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_base() + a, 16); return v; }
