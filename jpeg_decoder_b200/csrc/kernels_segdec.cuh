@@ -25,15 +25,15 @@
 //     lane wait in place for the round's extra slot, where one warp-uniform branch resolves it;
 //   * AC entries that hold two complete symbols inside the index bits are taken in one step (kernels_huff.cuh).
 //
-// (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by five warps of the
+// (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by four warps of the
 //     same CTA:
 //       decoder   walks the codes -- window, table entry, advance, block/table bookkeeping -- and pushes
 //                 (window, entry, zig-zag index | block number) per lane and step into a shared-memory FIFO;
-//       AC writers take every kSegAcW-th round of the FIFO: magnitude extension (jpeg.cpp:388-397), zig-zag
-//                 position.  They keep no state between symbols -- everything they need is in the FIFO entry;
-//       DC warp   sees every round but only the DC symbols: extension, prediction per component
-//                 (jpeg.cpp:335-345), range check;
-//       flusher   sends finished blocks to global memory (3).
+//       writers   take every kSegAcW-th round of the FIFO: magnitude extension (jpeg.cpp:388-397), zig-zag
+//                 position.  They keep no state between symbols -- everything they need is in the FIFO entry; a
+//                 DC symbol is a value for position 0 like any other: its DIFFERENCE goes into the block;
+//       flusher   sends finished blocks to global memory (3).  A lane's blocks pass through it in order, so this is
+//                 where the DC prediction per component (jpeg.cpp:335-345) and its range check happen.
 //     Every hand-over is an mbarrier in shared memory: a waiting warp is suspended by the hardware.
 //
 // (3) Coefficients leave the SM as whole 128-byte blocks.  A 2-byte store per coefficient from 32 lanes that work on
@@ -41,7 +41,7 @@
 //     of every SM's load/store path, in front of which the decoder's shared-memory loads queue), a read-modify-write
 //     in L2 for every sector, and a 1.6 GB memset beforehand because only non-zero values were stored.  Instead the
 //     writers put the values into a per-lane ring of kSegAsm block images in SHARED memory (st.shared.u16), and the
-//     flusher, once a round's AC writer and the DC warp are through, copies the blocks that round finished to global
+//     flusher, once a round's writer is through, copies the blocks that round finished to global
 //     memory with 128-bit stores -- eight threads per block, full lines, zeros included, no memset, no
 //     read-modify-write -- and clears the images.  A writer checks, per lane, that the blocks of its round are less than kSegAsm ahead of the
 //     flushed ones (they almost always are: a lane finishes 0.65 blocks per round) and waits otherwise.
@@ -375,7 +375,7 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
 }
 
 // =========================== the way out ===========================
-// Once a round's AC writer and the DC warp are through with it, the blocks the round finished leave: eight threads
+// Once a round's writer is through with it, the blocks the round finished leave (DC prediction first): eight threads
 // per block, 16 bytes each -- whole 128-byte lines -- and the image is cleared.
 B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t list_a,
                            uint32_t *fl, uint4 *__restrict__ coef4, uint32_t &err) {
