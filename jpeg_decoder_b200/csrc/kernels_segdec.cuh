@@ -99,7 +99,8 @@ constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing t
 constexpr uint32_t kSegPairBit = 1u << 6;
 constexpr int kSegNbShift = 7;
 constexpr uint32_t kSegFinFlag = 1u;
-static_assert(kSegFifo % kSegAcW == 0, "a FIFO slot always belongs to the same AC writer (arrival counts)");
+// a writer waits on full[s] by phase parity, so it must see EVERY phase of the slots it reads: a slot belongs to one writer
+static_assert(kSegFifo % kSegAcW == 0, "a FIFO slot always belongs to the same writer (a reader must not skip a barrier phase)");
 static_assert((kSegFifo & (kSegFifo - 1)) == 0 && (kSegAsm & (kSegAsm - 1)) == 0, "ring sizes are powers of two");
 static_assert(kSegAsm >= (kSegSlots + 1) / 2 + 1, "the blocks one round touches must fit the assembly ring");
 
