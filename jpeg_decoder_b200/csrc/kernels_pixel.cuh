@@ -94,6 +94,34 @@ B2_DEVICE void idct8(float &x0, float &x1, float &x2, float &x3, float &x4, floa
   x6 = B2_PIX_TRUNC(__fsub_rn(b1, b6)); x7 = B2_PIX_TRUNC(__fsub_rn(b0, e7));
 }
 
+// Two 1-D passes at once (two columns, or two rows): the same operations in the same order on both, the additions as
+// packed pairs (FADD2: half the instructions), the multiplications scalar (see b2_f2 in platform.h).
+#define B2_PMUL(a, b, s) b2_f2_pack(__fmul_rn(a, s), __fmul_rn(b, s))
+B2_DEVICE b2_f2 b2_f2_mul(b2_f2 v, float s) { float a, b; b2_f2_unpack(v, a, b); return B2_PMUL(a, b, s); }
+B2_DEVICE void idct8x2(float &x0, float &x1, float &x2, float &x3, float &x4, float &x5, float &x6, float &x7,
+                       float &y0, float &y1, float &y2, float &y3, float &y4, float &y5, float &y6, float &y7) {
+  const b2_f2 g0 = B2_PMUL(x0, y0, B2_S0), g1 = B2_PMUL(x4, y4, B2_S4), g2 = B2_PMUL(x2, y2, B2_S2), g3 = B2_PMUL(x6, y6, B2_S6);
+  const b2_f2 g4 = B2_PMUL(x5, y5, B2_S5), g5 = B2_PMUL(x1, y1, B2_S1), g6 = B2_PMUL(x7, y7, B2_S7), g7 = B2_PMUL(x3, y3, B2_S3);
+  const b2_f2 f4 = b2_f2_sub(g4, g7), f5 = b2_f2_add(g5, g6), f6 = b2_f2_sub(g5, g6), f7 = b2_f2_add(g4, g7);
+  const b2_f2 e2 = b2_f2_sub(g2, g3), e3 = b2_f2_add(g2, g3), e5 = b2_f2_sub(f5, f7), e7 = b2_f2_add(f5, f7);
+  const b2_f2 e8 = b2_f2_add(f4, f6);
+  const b2_f2 d2 = b2_f2_mul(e2, B2_M1), d4 = b2_f2_mul(f4, B2_M2), d5 = b2_f2_mul(e5, B2_M3);
+  const b2_f2 d6 = b2_f2_mul(f6, B2_M4), d8 = b2_f2_mul(e8, B2_M5);
+  const b2_f2 c0 = b2_f2_add(g0, g1), c1 = b2_f2_sub(g0, g1), c2 = b2_f2_sub(d2, e3), c4 = b2_f2_add(d4, d8);
+  const b2_f2 c5 = b2_f2_add(d5, e7), c6 = b2_f2_sub(d6, d8), c8 = b2_f2_sub(c5, c6);
+  const b2_f2 b0 = b2_f2_add(c0, e3), b1 = b2_f2_add(c1, c2), b2 = b2_f2_sub(c1, c2), b3 = b2_f2_sub(c0, e3);
+  const b2_f2 b4 = b2_f2_sub(c4, c8), b6 = b2_f2_sub(c6, e7);
+  float a, b;
+  b2_f2_unpack(b2_f2_add(b0, e7), a, b); x0 = B2_PIX_TRUNC(a); y0 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_add(b1, b6), a, b); x1 = B2_PIX_TRUNC(a); y1 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_add(b2, c8), a, b); x2 = B2_PIX_TRUNC(a); y2 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_add(b3, b4), a, b); x3 = B2_PIX_TRUNC(a); y3 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_sub(b3, b4), a, b); x4 = B2_PIX_TRUNC(a); y4 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_sub(b2, c8), a, b); x5 = B2_PIX_TRUNC(a); y5 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_sub(b1, b6), a, b); x6 = B2_PIX_TRUNC(a); y6 = B2_PIX_TRUNC(b);
+  b2_f2_unpack(b2_f2_sub(b0, e7), a, b); x7 = B2_PIX_TRUNC(a); y7 = B2_PIX_TRUNC(b);
+}
+
 #define B2_ZZ_LIST                                                                                      \
   0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, \
       7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, \
@@ -282,11 +310,15 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
         }
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i)                  // columns, jpeg.cpp:596-663
-        idct8(v[0 * 8 + i], v[1 * 8 + i], v[2 * 8 + i], v[3 * 8 + i], v[4 * 8 + i], v[5 * 8 + i], v[6 * 8 + i], v[7 * 8 + i]);
+      for (int i = 0; i < 8; i += 2)               // columns, two at a time, jpeg.cpp:596-663
+        idct8x2(v[0 * 8 + i], v[1 * 8 + i], v[2 * 8 + i], v[3 * 8 + i], v[4 * 8 + i], v[5 * 8 + i], v[6 * 8 + i], v[7 * 8 + i],
+                v[0 * 8 + i + 1], v[1 * 8 + i + 1], v[2 * 8 + i + 1], v[3 * 8 + i + 1], v[4 * 8 + i + 1], v[5 * 8 + i + 1],
+                v[6 * 8 + i + 1], v[7 * 8 + i + 1]);
 #pragma unroll
-      for (int i = 0; i < 8; ++i)                  // rows, jpeg.cpp:664-731
-        idct8(v[i * 8 + 0], v[i * 8 + 1], v[i * 8 + 2], v[i * 8 + 3], v[i * 8 + 4], v[i * 8 + 5], v[i * 8 + 6], v[i * 8 + 7]);
+      for (int i = 0; i < 8; i += 2)               // rows, two at a time, jpeg.cpp:664-731
+        idct8x2(v[i * 8 + 0], v[i * 8 + 1], v[i * 8 + 2], v[i * 8 + 3], v[i * 8 + 4], v[i * 8 + 5], v[i * 8 + 6], v[i * 8 + 7],
+                v[i * 8 + 8], v[i * 8 + 9], v[i * 8 + 10], v[i * 8 + 11], v[i * 8 + 12], v[i * 8 + 13], v[i * 8 + 14],
+                v[i * 8 + 15]);
       if (NC == 3 && b < C::kLuma) {               // luma lanes hand rows [kKeep,8) to the chroma lanes
         float4 *sp = reinterpret_cast<float4 *>(spill + (m * C::kLuma + b) * (8 - C::kKeep) * 32);
 #pragma unroll

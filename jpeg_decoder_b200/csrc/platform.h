@@ -46,6 +46,15 @@ B2_DEVICE uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
   return r;
 }
 
+// ---- two fp32 additions in one instruction (add.rn.f32x2, SASS FADD2; sm_100): each half is an IEEE round-to-nearest
+//      add, bit for bit what two FADDs give.  Multiplications stay scalar on purpose: ptxas contracts mul.f32x2 + add.f32x2
+//      into FFMA2 even under --fmad=false and explicit .rn, which would change the rounding. ----
+typedef unsigned long long b2_f2;
+B2_DEVICE b2_f2 b2_f2_pack(float lo, float hi) { b2_f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+B2_DEVICE void b2_f2_unpack(b2_f2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+B2_DEVICE b2_f2 b2_f2_add(b2_f2 a, b2_f2 b) { b2_f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+B2_DEVICE b2_f2 b2_f2_sub(b2_f2 a, b2_f2 b) { b2_f2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
 // ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass the register file ----
 B2_DEVICE void b2_cp_async16(void *dst, const void *src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");

@@ -261,6 +261,11 @@ static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
 }
 static inline float b2_trunc_small(float x) { return truncf(x); }
+struct b2_f2 { float lo, hi; };
+static inline b2_f2 b2_f2_pack(float lo, float hi) { return {lo, hi}; }
+static inline void b2_f2_unpack(b2_f2 v, float &lo, float &hi) { lo = v.lo; hi = v.hi; }
+static inline b2_f2 b2_f2_add(b2_f2 a, b2_f2 b) { return {__fadd_rn(a.lo, b.lo), __fadd_rn(a.hi, b.hi)}; }
+static inline b2_f2 b2_f2_sub(b2_f2 a, b2_f2 b) { return {__fsub_rn(a.lo, b.lo), __fsub_rn(a.hi, b.hi)}; }
 static inline void b2_backoff(unsigned) { std::this_thread::yield(); }
 // 32-bit window addresses of the CTA's dynamic shared memory
 static inline unsigned char *b2_dsm_base() {
