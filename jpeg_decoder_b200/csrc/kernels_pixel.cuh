@@ -408,16 +408,23 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
           }
         }
         float px[24];
+        const b2_f2 c128 = b2_f2_pack(128.0f, 128.0f);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float y = v[i * 8 + k];
+        for (int k = 0; k < 8; k += 2) {            // two pixels per packed addition (the sums in the reference's order)
+          const b2_f2 y = b2_f2_pack(v[i * 8 + k], v[i * 8 + k + 1]);
           if (NC == 3) {
-            const int j = k / HS;
-            px[3 * k] = __fadd_rn(__fadd_rn(y, p_r[j]), 128.0f);                              // jpeg.cpp:521
-            px[3 * k + 1] = __fadd_rn(__fsub_rn(__fsub_rn(y, p_g1[j]), p_g2[j]), 128.0f);     // :522
-            px[3 * k + 2] = __fadd_rn(__fadd_rn(y, p_b[j]), 128.0f);                          // :523
+            const int j0 = k / HS, j1 = (k + 1) / HS;
+            const b2_f2 r2 = b2_f2_add(b2_f2_add(y, b2_f2_pack(p_r[j0], p_r[j1])), c128);                                  // jpeg.cpp:521
+            const b2_f2 g2 = b2_f2_add(b2_f2_sub(b2_f2_sub(y, b2_f2_pack(p_g1[j0], p_g1[j1])), b2_f2_pack(p_g2[j0], p_g2[j1])), c128);   // :522
+            const b2_f2 bl2 = b2_f2_add(b2_f2_add(y, b2_f2_pack(p_b[j0], p_b[j1])), c128);                                 // :523
+            b2_f2_unpack(r2, px[3 * k], px[3 * k + 3]);
+            b2_f2_unpack(g2, px[3 * k + 1], px[3 * k + 4]);
+            b2_f2_unpack(bl2, px[3 * k + 2], px[3 * k + 5]);
           } else {                                  // Cb = Cr = 0: every product is +-0 and drops out
-            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = __fadd_rn(y, 128.0f);
+            float a, c;
+            b2_f2_unpack(b2_f2_add(y, c128), a, c);
+            px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = a;
+            px[3 * k + 3] = px[3 * k + 4] = px[3 * k + 5] = c;
           }
         }
         if (valid) {
