@@ -76,26 +76,9 @@ B2_DEVICE float f32_bits(uint32_t u) {
 #define B2_PIX_TRUNC(x) truncf(x)
 #endif
 
-// One AAN 1-D pass in place, jpeg.cpp:598-662 / 666-730.
-B2_DEVICE void idct8(float &x0, float &x1, float &x2, float &x3, float &x4, float &x5, float &x6, float &x7) {
-  const float g0 = __fmul_rn(x0, B2_S0), g1 = __fmul_rn(x4, B2_S4), g2 = __fmul_rn(x2, B2_S2), g3 = __fmul_rn(x6, B2_S6);
-  const float g4 = __fmul_rn(x5, B2_S5), g5 = __fmul_rn(x1, B2_S1), g6 = __fmul_rn(x7, B2_S7), g7 = __fmul_rn(x3, B2_S3);
-  const float f4 = __fsub_rn(g4, g7), f5 = __fadd_rn(g5, g6), f6 = __fsub_rn(g5, g6), f7 = __fadd_rn(g4, g7);
-  const float e2 = __fsub_rn(g2, g3), e3 = __fadd_rn(g2, g3), e5 = __fsub_rn(f5, f7), e7 = __fadd_rn(f5, f7);
-  const float e8 = __fadd_rn(f4, f6);
-  const float d2 = __fmul_rn(e2, B2_M1), d4 = __fmul_rn(f4, B2_M2), d5 = __fmul_rn(e5, B2_M3);
-  const float d6 = __fmul_rn(f6, B2_M4), d8 = __fmul_rn(e8, B2_M5);
-  const float c0 = __fadd_rn(g0, g1), c1 = __fsub_rn(g0, g1), c2 = __fsub_rn(d2, e3), c4 = __fadd_rn(d4, d8);
-  const float c5 = __fadd_rn(d5, e7), c6 = __fsub_rn(d6, d8), c8 = __fsub_rn(c5, c6);
-  const float b0 = __fadd_rn(c0, e3), b1 = __fadd_rn(c1, c2), b2 = __fsub_rn(c1, c2), b3 = __fsub_rn(c0, e3);
-  const float b4 = __fsub_rn(c4, c8), b6 = __fsub_rn(c6, e7);
-  x0 = B2_PIX_TRUNC(__fadd_rn(b0, e7)); x1 = B2_PIX_TRUNC(__fadd_rn(b1, b6)); x2 = B2_PIX_TRUNC(__fadd_rn(b2, c8));
-  x3 = B2_PIX_TRUNC(__fadd_rn(b3, b4)); x4 = B2_PIX_TRUNC(__fsub_rn(b3, b4)); x5 = B2_PIX_TRUNC(__fsub_rn(b2, c8));
-  x6 = B2_PIX_TRUNC(__fsub_rn(b1, b6)); x7 = B2_PIX_TRUNC(__fsub_rn(b0, e7));
-}
-
-// Two 1-D passes at once (two columns, or two rows): the same operations in the same order on both, the additions as
-// packed pairs (FADD2: half the instructions), the multiplications scalar (see b2_f2 in platform.h).
+// One AAN 1-D pass in place (jpeg.cpp:598-662 / 666-730), for TWO vectors at once (two columns, or two rows): the same
+// operations in the same order on both, the additions as packed pairs (FADD2: half the instructions), the
+// multiplications scalar (see b2_f2 in platform.h).
 #define B2_PMUL(a, b, s) b2_f2_pack(__fmul_rn(a, s), __fmul_rn(b, s))
 B2_DEVICE b2_f2 b2_f2_mul(b2_f2 v, float s) { float a, b; b2_f2_unpack(v, a, b); return B2_PMUL(a, b, s); }
 B2_DEVICE void idct8x2(float &x0, float &x1, float &x2, float &x3, float &x4, float &x5, float &x6, float &x7,
