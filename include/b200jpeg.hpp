@@ -17,7 +17,7 @@
 // prints and calls exit(1); process_image_data() runs on the GPU through b200jpeg_decode_batch() and
 // FAILS (throws) when no B200-class device is present -- there is no CPU fallback.
 // Batches: b200jpeg::Image::decode_batch() decodes many files in one call (images are independent, the
-// library chunks and double-buffers them).
+// library cuts them into chunks that rotate over four internal pipelines).
 #ifndef B200JPEG_HPP
 #define B200JPEG_HPP
 #include <cstdint>
@@ -201,7 +201,7 @@ class Image {
   void readJPEG(Context &ctx = Context::shared()) { readHeaders(); process_image_data(ctx); }
 
   // Many images, one call: headers on the host, every scan through ONE b200jpeg_decode_batch()
-  // (images are independent; the library chunks and double-buffers the batch).  Returns the per-image
+  // (images are independent; the library cuts the batch into chunks that rotate over four internal pipelines).  Returns the per-image
   // status words (0 = decoded); images[i]->rgb() holds the pixels.  Nothing throws for a corrupt scan.
   static std::vector<int> decode_batch(const std::vector<Image *> &images, Context &ctx = Context::shared()) {
     const int n = (int)images.size();
