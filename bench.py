@@ -186,7 +186,7 @@ def run_reference_arm(args, rank, world):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample + " per step"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------ GPU arm
@@ -200,7 +200,6 @@ def run_gpu_arm(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device -- the product has no CPU path")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only (NCCL prints its version there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = jd.load()
     dec = jd.Decoder(local_rank)
@@ -310,14 +309,33 @@ def run_gpu_arm(args, rank, world, local_rank):
                         "d2h_bytes_per_step": stats_e["d2h_bytes"] * world, "ms_per_step": t_e2e / args.steps * 1e3},
                 "gpu_launches": launches, "sync_rounds": stats["sync_rounds"],
                 "entropy_path": "segment-parallel" if seg else "self-synchronising", "clocks": clocks.summary()}
-        print(json.dumps(line), flush=True)
+        emit(line)
     lib.b200jpeg_host_free(rgb_ptr)
     dec.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line, on the process's real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # stdout carries the JSON line and nothing else: whatever libraries print there (NCCL announces its version on
+    # stdout under torchrun) goes to stderr instead -- file descriptor 1 is pointed at stderr, the line is written to a
+    # duplicate of the original
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
