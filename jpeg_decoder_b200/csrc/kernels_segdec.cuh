@@ -245,8 +245,11 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
   uint32_t r = 0;
   for (;; ++r) {
     // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
-    //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8 ----
-    const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8);
+    //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8.
+    //      Nothing is fetched from beyond the segment's end (+ the window's look-ahead): a lane whose data ran out
+    //      (truncated or corrupt scan) goes on over what the ring holds until its blocks are counted off, and ends
+    //      with ST_OVERRUN -- it never reads outside the scan buffer, however many blocks the header promised ----
+    const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8) && rw <= (pend >> 5) + 8u;
     // (rw is a multiple of 4 and so is the ring size: four consecutive words never wrap)
     b2_cp_async4x4_if(need, ring_a + ((rw & (kSegWords - 1)) << 7), us + rw);
     b2_cp_async4x4_if(need, ring_a + (((rw + 4u) & (kSegWords - 1)) << 7), us + rw + 4);

@@ -138,8 +138,14 @@ def test_truncated_and_random_garbage_do_not_crash(dec, harness):
         for p in pos:
             m[p] = int(rng.integers(0, 255))           # avoids 0xFF: stays a syntactically valid scan
         datas.append(bytes(m))
+    # a header that promises 1024 blocks-rows of data over a scan that stops after 1 KB: the decoders must count the
+    # blocks off without reading outside the scan buffer, and say so
+    big = harness.synth_jpeg(44, 1024, 1024, 90, 2, 2, False, 0)
+    cut = big[:big.find(b"\xff\xda") + 14 + 1000] + b"\xff\xd9"
+    datas.append(cut)
     st, rgbs, _ = dec.decode(datas)
-    assert st[0] == 0 and len(rgbs) == 7
+    assert st[0] == 0 and len(rgbs) == 8
+    assert st[7] != 0
 
 
 def test_decode_batch_is_chunked_and_matches_single_batch(dec, harness):
