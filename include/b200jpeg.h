@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define B200JPEG_ABI_VERSION 1
+#define B200JPEG_ABI_VERSION 2
 
 /* ---- return codes (calls) ---- */
 enum {
@@ -82,7 +82,11 @@ enum {
 enum {
   B200JPEG_PARSE_REFERENCE = 0, /* accept exactly what the reference accepts */
   B200JPEG_PARSE_SPEC = 1       /* superset: 1-component grey, COM/unknown
-                                   segments skipped, fill bytes before markers */
+                                   segments skipped, fill bytes before markers, any component identifiers
+                                   (the frame's first component is luma; tables bound by the scan's
+                                   component selectors, which must follow the frame's order; reference:
+                                   id 1 = luma, bound by position, jpeg.cpp:110, 241-247), 16-bit DQT
+                                   values kept whole (reference: low byte, jpeg.cpp:216) */
 };
 
 /* HuffmanTable, include/huffman.hpp:8-15.  offset[] are cumulative counts (jpeg.cpp:170-176),
@@ -140,6 +144,13 @@ typedef struct b200jpeg_ctx b200jpeg_ctx;
  * read_sos(), returning a code where the reference calls exit(1). */
 int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags, b200jpeg_image_desc *desc);
 
+/* The same for n files at once on `threads` host threads (0 = one per hardware thread, capped by the work):
+ * what a batch caller runs where the reference runs its per-byte marker reader n times (file.hpp:26-52,
+ * jpeg.cpp:826-867).  rcs[i] = the code b200jpeg_parse_header would return for file i (rcs may be NULL);
+ * returns the number of files that failed, or B200JPEG_E_ARG. */
+int b200jpeg_parse_headers(const uint8_t *const *files, const size_t *sizes, int n, int flags, int threads,
+                           b200jpeg_image_desc *descs, int32_t *rcs);
+
 /* One context per GPU: owns a stream, device arenas and pinned staging.  Use from one host
  * thread at a time. */
 int b200jpeg_create(int device, b200jpeg_ctx **ctx);
@@ -158,6 +169,30 @@ const char *b200jpeg_last_error(const b200jpeg_ctx *ctx);
 int b200jpeg_decode_batch(b200jpeg_ctx *ctx, const b200jpeg_image_desc *descs, int n,
                           const uint8_t *const *file_bytes, const size_t *file_sizes,
                           uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status);
+
+/* Several GPUs of one box: images share nothing, so a batch is cut into contiguous image ranges, one per device,
+ * each decoded by its own context on its own host thread (own stream, pinned staging and arenas); no data moves
+ * between devices.  A device may be named more than once (two contexts on it).  The reference's main() decodes
+ * the files of one process one after another (jpeg.cpp:916-929); this is that loop over N GPUs. */
+typedef struct b200jpeg_multi b200jpeg_multi;
+int b200jpeg_multi_create(const int *devices, int ndev, b200jpeg_multi **multi);
+void b200jpeg_multi_destroy(b200jpeg_multi *multi);
+int b200jpeg_multi_count(const b200jpeg_multi *multi);
+b200jpeg_ctx *b200jpeg_multi_ctx(b200jpeg_multi *multi, int k);   /* context k (for stats, entropy path, last_error) */
+/* arguments as b200jpeg_decode_batch (no coefficient output); returns the first error of any device, else 0 */
+int b200jpeg_multi_decode_batch(b200jpeg_multi *multi, const b200jpeg_image_desc *descs, int n,
+                                const uint8_t *const *file_bytes, const size_t *file_sizes,
+                                uint8_t *const *rgb_out, int32_t *status);
+/* one call, no handle: contexts for `devices` are created on first use and kept for the process */
+int b200jpeg_decode_batch_multi(const int *devices, int ndev, const b200jpeg_image_desc *descs, int n,
+                                const uint8_t *const *file_bytes, const size_t *file_sizes,
+                                uint8_t *const *rgb_out, int32_t *status);
+
+/* Measurement aid: exactly the host<->device copies b200jpeg_decode_batch would make for this batch (same chunks,
+ * same pipelines, same buffers), with no kernel launched in between -- the PCIe floor under the call.  rgb_out
+ * receives whatever the device arena holds.  *ms = wall time of the call in milliseconds. */
+int b200jpeg_copy_floor(b200jpeg_ctx *ctx, const b200jpeg_image_desc *descs, int n,
+                        const uint8_t *const *file_bytes, const size_t *file_sizes, uint8_t *const *rgb_out, float *ms);
 
 /* The same in three steps, so that a caller can keep a batch resident in HBM:
  *   prepare: plan the batch, copy the scans (and the small descriptors) host -> device

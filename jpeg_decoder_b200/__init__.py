@@ -50,6 +50,55 @@ def parse_header(data, flags=abi.PARSE_REFERENCE):
     return d
 
 
+def parse_headers(bufs, flags=abi.PARSE_REFERENCE, threads=0, descs=None):
+    """b200jpeg_parse_headers: n headers on several host threads -> ((ImageDesc*n), [rc])."""
+    n = len(bufs)
+    if descs is None:
+        descs = (ImageDesc * n)()
+    files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+    sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+    rcs = (C.c_int32 * n)()
+    load().b200jpeg_parse_headers(files, sizes, n, flags, threads, descs, rcs)
+    return descs, list(rcs)
+
+
+class MultiDecoder:
+    """One context + one host thread per entry of `devices` (b200jpeg_multi_*): a batch is cut into contiguous image
+    ranges, one per device; nothing moves between devices."""
+
+    def __init__(self, devices):
+        self.lib = load()
+        devs = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        rc = self.lib.b200jpeg_multi_create(devs, len(devices), C.byref(h))
+        if rc:
+            raise B200JpegError(rc, "b200jpeg_multi_create(%r)" % (list(devices),))
+        self.h = h
+        self.devices = list(devices)
+
+    def close(self):
+        if self.h:
+            self.lib.b200jpeg_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def decode_batch(self, descs, bufs, rgbs):
+        n = len(bufs)
+        files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+        prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
+        st = (C.c_int32 * n)()
+        rc = self.lib.b200jpeg_multi_decode_batch(self.h, descs, n, files, sizes, prgb, st)
+        if rc:
+            raise B200JpegError(rc, "multi_decode_batch")
+        return list(st)
+
+
 class Decoder:
     """One context per GPU (b200jpeg_create)."""
 
@@ -131,6 +180,16 @@ class Decoder:
         st = (C.c_int32 * n)()
         self._check(self.lib.b200jpeg_decode_batch(self.h, descs, n, files, sizes, prgb, None, st), "decode_batch")
         return list(st)
+
+    def copy_floor(self, descs, bufs, rgbs):
+        """b200jpeg_copy_floor: the copies of decode_batch without its kernels; returns milliseconds."""
+        n = len(bufs)
+        files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+        prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
+        ms = C.c_float(0)
+        self._check(self.lib.b200jpeg_copy_floor(self.h, descs, n, files, sizes, prgb, C.byref(ms)), "copy_floor")
+        return float(ms.value)
 
     # ---- one-call API -----------------------------------------------------------------------
     def decode(self, datas, flags=abi.PARSE_REFERENCE, want_coef=False):

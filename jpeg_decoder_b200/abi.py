@@ -6,7 +6,7 @@ ColorComponent (types.hpp:69-77) and Image's private state (jpeg.cpp:21-34).
 """
 import ctypes as C
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # status bits (b200jpeg.h)
 ST_BAD_MARKER = 1 << 0
@@ -72,13 +72,18 @@ EXPORTS = [
     "b200jpeg_decode_batch", "b200jpeg_batch_prepare", "b200jpeg_batch_run", "b200jpeg_batch_fetch",
     "b200jpeg_sync", "b200jpeg_device_rgb", "b200jpeg_stream", "b200jpeg_batch_get_stats",
     "b200jpeg_set_timing", "b200jpeg_last_timing", "b200jpeg_host_alloc", "b200jpeg_host_free",
-    "b200jpeg_abi_version", "b200jpeg_set_entropy_path",
+    "b200jpeg_abi_version", "b200jpeg_set_entropy_path", "b200jpeg_parse_headers", "b200jpeg_copy_floor",
+    "b200jpeg_multi_create", "b200jpeg_multi_destroy", "b200jpeg_multi_count", "b200jpeg_multi_ctx",
+    "b200jpeg_multi_decode_batch", "b200jpeg_decode_batch_multi",
 ]
 
 
 def bind_parse(lib):
     lib.b200jpeg_parse_header.restype = C.c_int
     lib.b200jpeg_parse_header.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(ImageDesc)]
+    lib.b200jpeg_parse_headers.restype = C.c_int
+    lib.b200jpeg_parse_headers.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int, C.c_int, C.c_int,
+                                           C.POINTER(ImageDesc), C.POINTER(C.c_int32)]
 
 
 def bind(lib):
@@ -120,4 +125,21 @@ def bind(lib):
     lib.b200jpeg_host_free.argtypes = [C.c_void_p]
     lib.b200jpeg_abi_version.restype = C.c_int
     lib.b200jpeg_abi_version.argtypes = []
+    lib.b200jpeg_copy_floor.restype = C.c_int
+    lib.b200jpeg_copy_floor.argtypes = [C.c_void_p, P(ImageDesc), C.c_int, P(C.c_void_p), P(C.c_size_t), P(C.c_void_p),
+                                        P(C.c_float)]
+    lib.b200jpeg_multi_create.restype = C.c_int
+    lib.b200jpeg_multi_create.argtypes = [P(C.c_int), C.c_int, P(C.c_void_p)]
+    lib.b200jpeg_multi_destroy.restype = None
+    lib.b200jpeg_multi_destroy.argtypes = [C.c_void_p]
+    lib.b200jpeg_multi_count.restype = C.c_int
+    lib.b200jpeg_multi_count.argtypes = [C.c_void_p]
+    lib.b200jpeg_multi_ctx.restype = C.c_void_p
+    lib.b200jpeg_multi_ctx.argtypes = [C.c_void_p, C.c_int]
+    lib.b200jpeg_multi_decode_batch.restype = C.c_int
+    lib.b200jpeg_multi_decode_batch.argtypes = [C.c_void_p, P(ImageDesc), C.c_int, P(C.c_void_p), P(C.c_size_t),
+                                                P(C.c_void_p), P(C.c_int32)]
+    lib.b200jpeg_decode_batch_multi.restype = C.c_int
+    lib.b200jpeg_decode_batch_multi.argtypes = [P(C.c_int), C.c_int, P(ImageDesc), C.c_int, P(C.c_void_p), P(C.c_size_t),
+                                                P(C.c_void_p), P(C.c_int32)]
     return lib

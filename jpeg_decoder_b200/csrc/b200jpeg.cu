@@ -2,7 +2,10 @@
 // No CPU path: without a usable GPU every decode entry point returns B200JPEG_E_CUDA.
 #include "pipeline_run.h"
 
+#include <chrono>
+#include <mutex>
 #include <new>
+#include <thread>
 
 struct b200jpeg_ctx {
   int device = 0;
@@ -77,9 +80,8 @@ int b200jpeg_create(int device, b200jpeg_ctx **out) {
     cudaEventCreate(&c->pipe.ev[i]);
     for (b2::Pipeline &x : c->extra) cudaEventCreate(&x.ev[i]);
   }
-  const size_t es = b2::entropy_smem_bytes(b2::kMaxSlots, true);
-  bool ok = allow_smem(b2::k_entropy_sync<true>, es, c->last_error) && allow_smem(b2::k_entropy_sync<false>, es, c->last_error) &&
-            allow_smem(b2::k_entropy_write, es, c->last_error) &&
+  const size_t es = b2::xsync_smem_bytes(b2::kHTabsPerSet);
+  bool ok = allow_smem(b2::k_xsync<true>, es, c->last_error) && allow_smem(b2::k_xsync<false>, es, c->last_error) &&
             allow_smem(b2::k_entropy_seg, b2::segdec_smem_bytes(), c->last_error);
   ok = ok && setup_pixel<1, 1, 3>(c, b2::PF_444, prop.multiProcessorCount) && setup_pixel<2, 1, 3>(c, b2::PF_422, prop.multiProcessorCount) &&
        setup_pixel<1, 2, 3>(c, b2::PF_440, prop.multiProcessorCount) && setup_pixel<2, 2, 3>(c, b2::PF_420, prop.multiProcessorCount) &&
@@ -138,17 +140,23 @@ int b200jpeg_sync(b200jpeg_ctx *c) {
 // device copies crawl (their read requests queue behind the posted writes: 19 MB took 2.1 ms in the CUPTI trace), so
 // a chunk needs about as long as a chunk's RGB copy to get ready -- with only two pipelines the RGB engine ran dry
 // for 0.6 ms per pair of chunks; and the first RGB byte leaves once the first (small) chunk is decoded.
-int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
-                          const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+// The entropy decoder is chosen ONCE, over the whole call: chunks of one call are in flight together, so what fills
+// the device is the call, not the chunk.
+// copies_only: the same copies with no kernel in between (b200jpeg_copy_floor).
+static int decode_batch_impl(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
+                             const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status,
+                             bool copies_only) {
   if (!c || n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
   constexpr int kSlots = 1 + b200jpeg_ctx::kExtra;
   int chunk = (n + 15) / 16;
   if (chunk < 8) chunk = 8;
   if (chunk > 32) chunk = 32;
   int nslots = kSlots;
-  if (const char *ev = getenv("B200JPEG_CHUNK")) { const int v = atoi(ev); if (v > 0) chunk = v; }   // tuning knobs
+#ifdef B200JPEG_TUNING                                 // measurement builds only (scripts/dev): chunking knobs
+  if (const char *ev = getenv("B200JPEG_CHUNK")) { const int v = atoi(ev); if (v > 0) chunk = v; }
   if (const char *ev = getenv("B200JPEG_SLOTS")) { const int v = atoi(ev); if (v >= 2 && v <= kSlots) nslots = v; }
-  if (coef_out || n <= chunk) {
+#endif
+  if ((coef_out || n <= chunk) && !copies_only) {
     int rc = b200jpeg_batch_prepare(c, descs, n, files, sizes);
     if (rc) return rc;
     rc = b200jpeg_batch_run(c);
@@ -161,7 +169,9 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
   bool busy[kSlots] = {false, false, false, false};
   b200jpeg_batch_stats a;
   memset(&a, 0, sizeof a);
-  for (b2::Pipeline &x : c->extra) x.force_path = c->pipe.force_path;
+  const int user_force = c->pipe.force_path;
+  const int call_path = b2::choose_path(descs, n, user_force) == b2::kPathSegment ? b2::kForceSegment : b2::kForceSync;
+  for (b2::Pipeline *p : slot) { p->force_path = call_path; p->copies_only = copies_only; }
   const bool timing0 = c->pipe.timing;     // per-stage event times are a single-batch facility
   int rc = 0;
   auto drain = [&](int k) {
@@ -195,9 +205,90 @@ int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int
     const int r = drain((k + j) % nslots);
     if (!rc) rc = r;
   }
+  for (b2::Pipeline *p : slot) { p->force_path = user_force; p->copies_only = false; }
   c->agg = a; c->agg_valid = true;
   c->pipe.timing = timing0;
   return rc;
+}
+
+int b200jpeg_decode_batch(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
+                          const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+  return decode_batch_impl(c, descs, n, files, sizes, rgb_out, coef_out, status, false);
+}
+
+int b200jpeg_copy_floor(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
+                        const size_t *sizes, uint8_t *const *rgb_out, float *ms) {
+  const auto t0 = std::chrono::steady_clock::now();
+  const int rc = decode_batch_impl(c, descs, n, files, sizes, rgb_out, nullptr, nullptr, true);
+  if (ms) *ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return rc;
+}
+
+// ---- several devices: one context + one host thread per entry of `devices`, contiguous image ranges ----
+struct b200jpeg_multi {
+  std::vector<b200jpeg_ctx *> ctx;
+  std::vector<int> devices;
+};
+
+int b200jpeg_multi_create(const int *devices, int ndev, b200jpeg_multi **out) {
+  if (!out || !devices || ndev <= 0 || ndev > 64) return B200JPEG_E_ARG;
+  *out = nullptr;
+  b200jpeg_multi *m = new (std::nothrow) b200jpeg_multi();
+  if (!m) return B200JPEG_E_NOMEM;
+  for (int k = 0; k < ndev; ++k) {
+    b200jpeg_ctx *c = nullptr;
+    const int rc = b200jpeg_create(devices[k], &c);
+    if (rc) { b200jpeg_multi_destroy(m); return rc; }
+    m->ctx.push_back(c); m->devices.push_back(devices[k]);
+  }
+  *out = m;
+  return B200JPEG_OK;
+}
+
+void b200jpeg_multi_destroy(b200jpeg_multi *m) {
+  if (!m) return;
+  for (b200jpeg_ctx *c : m->ctx) b200jpeg_destroy(c);
+  delete m;
+}
+
+int b200jpeg_multi_count(const b200jpeg_multi *m) { return m ? (int)m->ctx.size() : 0; }
+b200jpeg_ctx *b200jpeg_multi_ctx(b200jpeg_multi *m, int k) { return m && k >= 0 && k < (int)m->ctx.size() ? m->ctx[(size_t)k] : nullptr; }
+
+int b200jpeg_multi_decode_batch(b200jpeg_multi *m, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
+                                const size_t *sizes, uint8_t *const *rgb_out, int32_t *status) {
+  if (!m || m->ctx.empty() || n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
+  const int nd = (int)m->ctx.size();
+  std::vector<int> rcs((size_t)nd, 0);
+  auto part = [&](int k) {                            // images [lo, hi) of device k: sizes differ by at most one
+    const int q = n / nd, r = n % nd;
+    const int lo = k * q + (k < r ? k : r), hi = lo + q + (k < r ? 1 : 0);
+    if (hi > lo)
+      rcs[(size_t)k] = b200jpeg_decode_batch(m->ctx[(size_t)k], descs + lo, hi - lo, files + lo, sizes + lo,
+                                            rgb_out ? rgb_out + lo : nullptr, nullptr, status ? status + lo : nullptr);
+  };
+  std::vector<std::thread> pool;
+  for (int k = 1; k < nd; ++k) pool.emplace_back(part, k);
+  part(0);
+  for (std::thread &t : pool) t.join();
+  for (int k = 0; k < nd; ++k) if (rcs[(size_t)k]) return rcs[(size_t)k];
+  return B200JPEG_OK;
+}
+
+int b200jpeg_decode_batch_multi(const int *devices, int ndev, const b200jpeg_image_desc *descs, int n,
+                                const uint8_t *const *files, const size_t *sizes, uint8_t *const *rgb_out, int32_t *status) {
+  static std::mutex mu;                               // one call at a time through the process-wide contexts
+  static b200jpeg_multi *cached = nullptr;
+  if (!devices || ndev <= 0) return B200JPEG_E_ARG;
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached && (cached->devices.size() != (size_t)ndev || !std::equal(cached->devices.begin(), cached->devices.end(), devices))) {
+    b200jpeg_multi_destroy(cached);
+    cached = nullptr;
+  }
+  if (!cached) {
+    const int rc = b200jpeg_multi_create(devices, ndev, &cached);
+    if (rc) return rc;
+  }
+  return b200jpeg_multi_decode_batch(cached, descs, n, files, sizes, rgb_out, status);
 }
 
 int b200jpeg_device_rgb(b200jpeg_ctx *c, int i, void **dev_ptr, size_t *pitch) {

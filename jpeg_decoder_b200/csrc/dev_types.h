@@ -3,8 +3,10 @@
 // Vocabulary follows the reference: a "block" is one 8x8 unit (what jpeg.cpp calls an MCU
 // position, types.hpp:32-50), an "MCU" here is the JPEG MCU (hs*vs luma blocks + Cb + Cr),
 // a "segment" is the entropy-coded data between two RSTn markers (file.hpp:83-86,
-// jpeg.cpp:419-425), a "sub" (subsequence) is a fixed-size slice of the unstuffed scan that one
-// thread decodes in the self-synchronising entropy decoder.
+// jpeg.cpp:419-425), a "sub" (subsequence) is a fixed-size slice of a segment that one thread
+// walks in the self-synchronising pass, a "unit" is what one lane of the segment decoder turns into
+// coefficient blocks: a whole segment, or a run of consecutive subs whose start state the
+// self-synchronising pass has settled.
 #pragma once
 #include <stdint.h>
 
@@ -40,7 +42,7 @@ struct HuffSpec {
 
 // One distinct set of tables; images of a batch share it when their DQT/DHT are identical.
 struct TableSet {
-  uint8_t q[4][64];       // QuantizationTable::table (natural order, types.hpp:86-92), 8-bit
+  uint16_t q[4][64];      // QuantizationTable::table (natural order, types.hpp:86-92); 8-bit in the reference, 16-bit under PARSE_SPEC
   HuffSpec dc[4], ac[4];
 };
 
@@ -56,8 +58,8 @@ struct ImageDev {
   uint64_t raw_off;             // byte offset of the scan in d_raw; unstuffed copy at the same offset in d_us
   int32_t seg_base, nseg;       // segment table entries [seg_base, seg_base+nseg]
   int32_t tile_base, ntiles;    // unstuff tiles (kUTile raw bytes each)
-  int32_t sub_base, nsub_max;   // subsequences
-  int32_t cta_base, ncta;       // entropy CTAs (kCT subs each)
+  int32_t sub_base, nsub_max;   // self-synchronising path: first sub slot of the image (global numbering) / slots reserved
+  int32_t unit_base, nunit_max; // self-synchronising path: first unit slot / slots reserved
   int32_t nblocks;              // coded blocks = mcux*mcuy*bpm
   int32_t path;                 // kPathSync / kPathSegment: which entropy decoder takes this image
   int64_t coef_base;            // first block of this image in the coefficient buffer
@@ -78,6 +80,26 @@ struct ImageOut {
 
 // Per-subsequence synchronisation state.
 struct SubState { uint32_t p, blk; };           // first block start at/after the sub's end
-struct SubInfo { int32_t nb_flag, d0, d1, d2; };  // blocks / DC sums since the last segment start; bit31 = crossed one
+struct SubInfo { int32_t nb_flag, d0, d1, d2; };  // blocks / DC sums since the last segment start; bit31 = a segment starts here
+
+// What a lane of the segment decoder needs to decode a run of subs of the self-synchronising path (written by
+// k_xunits once the start states are settled): bit range, first / past-the-last block of the image, block-in-MCU phase
+// and DC predictors at the start.
+struct XUnit {
+  uint32_t p0, pend;          // first bit / where the next unit starts (the segment's end for the last one)
+  uint32_t bidx, bend;        // blocks [bidx, bend) of the image
+  int32_t pred[3];            // DC predictors at p0 (jpeg.cpp:344-345: the running sums since the segment's start)
+  uint32_t blk0;              // block-in-MCU index of the block that starts at p0
+};
+// Batch-wide parameters of the self-synchronising path (chosen by the planner from the batch's size).
+struct XParams {
+  int32_t sub_shift;          // log2 of the sub size in bits
+  int32_t unit_subs;          // subs per unit (units never span segments)
+  int32_t overlap;            // run-in in bits before a sub whose start is a guess
+  int32_t nimg;
+  int32_t nsub_slots, nunit_slots;   // totals (multiples of the CTA sizes)
+  int32_t ncta;               // CTAs of the sync kernels
+  int32_t pad;
+};
 
 }  // namespace b2

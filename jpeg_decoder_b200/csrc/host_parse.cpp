@@ -14,6 +14,9 @@
 // touched here: readImageData (file.hpp:59-104) is replaced by the unstuff kernels.
 #include "../../include/b200jpeg.h"
 #include <string.h>
+#include <atomic>
+#include <thread>
+#include <vector>
 
 namespace {
 
@@ -23,7 +26,7 @@ const int kZigZag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11,
 
 inline int be16(const uint8_t *p) { return (p[0] << 8) | p[1]; }
 
-int parse_sof(b200jpeg_image_desc *d, int marker, const uint8_t *p, int len, bool spec) {
+int parse_sof(b200jpeg_image_desc *d, int marker, const uint8_t *p, int len, bool spec, int *comp_id) {
   if (marker == 0xc2) return B200JPEG_E_PROGRESSIVE;
   if (len < 6) return B200JPEG_E_TRUNCATED;
   d->image_height = be16(p + 1);
@@ -38,9 +41,10 @@ int parse_sof(b200jpeg_image_desc *d, int marker, const uint8_t *p, int len, boo
   if (len < 6 + 3 * nc) return B200JPEG_E_TRUNCATED;
   for (int i = 0; i < nc; ++i) {
     const int id = p[6 + 3 * i];
+    comp_id[i] = id;
     if (id == 0) d->zeroBased = 1;
-    if (!d->zeroBased && id > 3) return B200JPEG_E_COMPONENT_ID;
-    if (d->zeroBased && id > 2) return B200JPEG_E_COMPONENT_ID;
+    if (!spec && !d->zeroBased && id > 3) return B200JPEG_E_COMPONENT_ID;
+    if (!spec && d->zeroBased && id > 2) return B200JPEG_E_COMPONENT_ID;
     b200jpeg_component *c = &d->color_components[i];
     c->horizontal_sampling_factor = p[7 + 3 * i] >> 4;
     c->vertical_sampling_factor = p[7 + 3 * i] & 15;
@@ -50,7 +54,9 @@ int parse_sof(b200jpeg_image_desc *d, int marker, const uint8_t *p, int len, boo
       d->horizontalSamplingFactor = d->verticalSamplingFactor = 1;
       continue;
     }
-    if (id == 1) {
+    // the reference takes identifier 1 for luma (jpeg.cpp:110); T.81 B.2.2 allows any byte, so under
+    // B200JPEG_PARSE_SPEC luma is the frame's first component
+    if (spec ? i == 0 : id == 1) {
       const int h = c->horizontal_sampling_factor, v = c->vertical_sampling_factor;
       if ((h != 1 && h != 2) || (v != 1 && v != 2)) return B200JPEG_E_SAMPLING;
       if (h == 2 && d->mcuWidth % 2 == 1) d->mcuWidthReal += 1;
@@ -91,7 +97,7 @@ int parse_dht(b200jpeg_image_desc *d, const uint8_t *p, int len) {
   return len != 0 ? B200JPEG_E_DHT : 0;
 }
 
-int parse_dqt(b200jpeg_image_desc *d, const uint8_t *p, int len) {
+int parse_dqt(b200jpeg_image_desc *d, const uint8_t *p, int len, bool spec) {
   while (len > 0) {
     const int id = p[0] & 15, wide = p[0] >> 4;
     ++p; --len;
@@ -100,6 +106,13 @@ int parse_dqt(b200jpeg_image_desc *d, const uint8_t *p, int len) {
     if (wide) {
       if (len < 128) return B200JPEG_E_TRUNCATED;
       for (int i = 0; i < 64; ++i) raw[i] = p[2 * i + 1];  // jpeg.cpp:216 keeps the low byte only
+      if (spec) {                                          // T.81 B.2.4.1, Pq = 1: the full 16-bit quantiser
+        b200jpeg_quant_table *q = &d->quantization_tables[id];
+        for (int i = 0; i < 64; ++i) q->table[kZigZag[i]] = be16(p + 2 * i);
+        q->set = 1;
+        p += 128; len -= 128;
+        continue;
+      }
       p += 128; len -= 128;
     } else {
       if (len < 64) return B200JPEG_E_TRUNCATED;
@@ -113,12 +126,15 @@ int parse_dqt(b200jpeg_image_desc *d, const uint8_t *p, int len) {
   return 0;
 }
 
-int parse_sos(b200jpeg_image_desc *d, const uint8_t *p, int len) {
+int parse_sos(b200jpeg_image_desc *d, const uint8_t *p, int len, bool spec, const int *comp_id) {
   if (len < 1) return B200JPEG_E_SOS;
   const int nc = p[0];
   if (nc != d->numComponents || (nc != 3 && nc != 1)) return B200JPEG_E_COMPONENTS;
   if (len < 1 + 2 * nc + 3) return B200JPEG_E_SOS;
   for (int i = 0; i < nc; ++i) {  // bound by position, the id byte is ignored (jpeg.cpp:241-247)
+    // B200JPEG_PARSE_SPEC: bound by component selector (T.81 B.2.3); the selectors must name the frame's
+    // components in the frame's order -- the only scan the interleaved decode loop (jpeg.cpp:415-435) takes
+    if (spec && p[1 + 2 * i] != comp_id[i]) return B200JPEG_E_SOS;
     d->color_components[i].huffmanDCTTableID = p[2 + 2 * i] >> 4;
     d->color_components[i].huffmanACTableID = p[2 + 2 * i] & 15;
   }
@@ -138,6 +154,7 @@ extern "C" int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags,
   if (len < 2 || file[0] != 0xff || file[1] != 0xd8) return B200JPEG_E_NOT_JPEG;
   size_t pos = 2;
   bool got_sos = false;
+  int comp_id[3] = {-1, -1, -1};                            // SOF component identifiers (used in SPEC mode)
   while (!got_sos) {
     if (pos >= len) return B200JPEG_E_NO_SOS;
     if (file[pos++] != 0xff) return B200JPEG_E_NO_SOS;       // jpeg.cpp:899-903
@@ -155,13 +172,13 @@ extern "C" int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags,
     if (m >= 0xe0 && m < 0xf0) continue;                     // META, file.hpp:201-207
     int rc = 0;
     switch (m) {
-      case 0xc0: case 0xc2: rc = parse_sof(d, m, p, plen, spec); break;
+      case 0xc0: case 0xc2: rc = parse_sof(d, m, p, plen, spec, comp_id); break;
       case 0xc4: rc = parse_dht(d, p, plen); break;
-      case 0xdb: rc = parse_dqt(d, p, plen); break;
+      case 0xdb: rc = parse_dqt(d, p, plen, spec); break;
       case 0xdd:
         if (plen != 2) rc = B200JPEG_E_DRI; else d->restartInterval = be16(p);
         break;
-      case 0xda: rc = parse_sos(d, p, plen); got_sos = true; break;
+      case 0xda: rc = parse_sos(d, p, plen, spec, comp_id); got_sos = true; break;
       case 0xd8: break;                                      // SOI is only logged, jpeg.cpp:838-841
       default:
         if (spec && m != 0xd9 && !(m >= 0xc1 && m <= 0xcf)) break;   // COM and friends
@@ -182,6 +199,34 @@ extern "C" int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags,
   d->scan_offset = (int64_t)pos;
   d->scan_length = (int64_t)(len - pos);
   return B200JPEG_OK;
+}
+
+// n headers on several host threads: files are handed out in blocks of 16 through one atomic counter
+extern "C" int b200jpeg_parse_headers(const uint8_t *const *files, const size_t *sizes, int n, int flags, int threads,
+                                      b200jpeg_image_desc *descs, int32_t *rcs) {
+  if (n < 0 || (n > 0 && (!files || !sizes || !descs))) return B200JPEG_E_ARG;
+  if (threads <= 0) threads = (int)std::thread::hardware_concurrency();
+  if (threads < 1) threads = 1;
+  if (threads > 64) threads = 64;
+  if (threads > (n + 31) / 32) threads = (n + 31) / 32;      // a header takes a few microseconds: no thread for less than 32
+  std::atomic<int> next(0), failed(0);
+  auto work = [&]() {
+    for (;;) {
+      const int lo = next.fetch_add(16);
+      if (lo >= n) return;
+      const int hi = lo + 16 < n ? lo + 16 : n;
+      for (int i = lo; i < hi; ++i) {
+        const int rc = b200jpeg_parse_header(files[i], sizes[i], flags, &descs[i]);
+        if (rcs) rcs[i] = rc;
+        if (rc) failed.fetch_add(1);
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < threads; ++t) pool.emplace_back(work);
+  work();
+  for (std::thread &t : pool) t.join();
+  return failed.load();
 }
 
 extern "C" int b200jpeg_abi_version(void) { return B200JPEG_ABI_VERSION; }

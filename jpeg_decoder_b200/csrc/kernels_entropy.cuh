@@ -1,306 +1,250 @@
-// kernels_entropy.cuh -- stage E: parallel Huffman decode of the unstuffed scan into
-// quantised DCT coefficients.  Replaces Image::decodeHuffman / decodeMCUComponent /
+// kernels_entropy.cuh -- stage E for scans WITHOUT (enough) restart markers: the self-synchronising pass.
+// Together with the segment decoder (kernels_segdec.cuh) it replaces Image::decodeHuffman / decodeMCUComponent /
 // getNextSymbol (jpeg.cpp:300-446) and BitStream::getBit/getBitN/align (file.hpp:130-164).
 //
-// The reference walks the scan bit by bit, one block after another.  Here the unstuffed scan
-// of every image is cut into fixed-size subsequences ("subs", kSubBits bits), one thread each:
+// The reference walks the scan bit by bit, one block after another; where a block starts is only known once every
+// block before it has been decoded.  Here every restart segment (the whole scan when the file has no RSTn) is cut into
+// fixed-size subsequences ("subs", 2^sub_shift bits, numbered batch-wide), one THREAD each:
 //
-//   sync  : each thread decodes the blocks that START inside its sub.  Its start state is
-//           (bit position, block-in-MCU index) of the first block start at/after its sub's
-//           beginning.  That state is unknown, so the thread starts kOverlapBits EARLIER from a
-//           guess (or from the last segment start, which is exact) and lets the Huffman code
-//           self-synchronise on the way: measured on 4:2:0 streams the state -- including the
-//           block-in-MCU phase -- is right after 4096 bits for 92 % of starts (4:4:4: > 99.9 %).
-//           Thread t then checks its start against thread t-1's end state; the few subs that
-//           disagree are re-decoded (Jacobi iteration, compacted so whole warps stay busy).
-//           Segment starts (RSTn) re-synchronise every decoder that reaches them.
-//   fix   : the same check across CTA boundaries (one more launch per hop; two are issued).
-//   scan  : segmented prefix sums over the per-sub block counts and DC-difference sums give
-//           every sub its first output block and its DC predictors (jpeg.cpp:344-345, 413).
-//   write : final decode from the settled states; each thread assembles whole blocks in shared
-//           memory and stores them as full 128-byte lines.
+//   plan   (k_xplan)   subs and units per segment, from the segment table stage U left behind.
+//   sync   (k_xsync<1>) each thread finds the blocks that START inside its sub: how many, the sum of their DC
+//          differences per component, and the first block start at/after the sub's end (its END STATE: bit position +
+//          block-in-MCU index).  Its own start state is the predecessor's end state, which is not known yet, so the
+//          thread starts `overlap` bits EARLIER from a guess (or from the segment's start, which is exact) and lets the
+//          Huffman code self-synchronise on the way.  Thread t then checks its start against thread t-1's end; the few
+//          subs that disagree are walked again (Jacobi iteration, compacted so that whole warps stay busy).
+//   fix    (k_xsync<0>) the same check across CTA boundaries (one more launch per hop; two are issued, the host
+//          launches more while a flag says state still moved).
+//   scan   (k_xscan)   segmented prefix sums over the CTA totals;
+//   units  (k_xunits)  ... and inside each CTA give every sub its first block and its DC predictors
+//          (jpeg.cpp:344-345: a predictor is the running sum of the differences since the segment's start).  Runs of
+//          `unit_subs` consecutive subs of a segment become UNITS (XUnit): bit range, block range, block-in-MCU phase,
+//          predictors -- exactly what a lane of the segment decoder needs.
+//   write  k_entropy_seg (kernels_segdec.cuh) decodes the units into coefficient blocks: there is ONE writer for both
+//          entropy paths.  A restart segment is simply a unit whose start state needs no synchronisation.
 //
-// Output layout: int16 coef[block][64], blocks in scan order (MCU by MCU, inside an MCU the
-// hs*vs luma blocks row-major, then Cb, then Cr -- jpeg.cpp:426-435), the 64 entries in ZIG-ZAG
-// order (the order they arrive in; stage P de-zig-zags for free when it names its registers);
-// the eight 16-byte chunks of a block are stored at chunk ^ (block & 7) so that stage P can read a
-// dense TMA copy of consecutive blocks from shared memory without bank conflicts.
-// Algorithmic bytes: scan bytes in (each pass) + 128 B per coded block out.
+// The walk itself (x_walk) is the segment decoder's chain: a round of eight identical, branch-free steps per lane (window
+// from a per-lane shared-memory ring topped up by predicated cp.async, two-level table in shared memory, paired AC
+// symbols, block end and sub end by selects), rare events (codes longer than the first-level index, the last bits of a
+// segment) resolved in the round's extra slot behind one warp-uniform branch.  It extracts no coefficients: per DC
+// symbol one magnitude extension for the sums, nothing for AC symbols.
+// Algorithmic bytes: (1 + overlap / sub size) x scan bytes in (sync) + 36 B per sub of state.
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
 #include "kernels_unstuff.cuh"   // find_owner
+#include "kernels_huff.cuh"
+#include "kernels_segdec.cuh"    // seg_extend, the ring conventions
 
 namespace b2 {
 
-#ifndef B2_SUB_BITS
-#define B2_SUB_BITS 4096
-#endif
-#ifndef B2_OVERLAP_BITS
-#define B2_OVERLAP_BITS 4096
-#endif
-constexpr int kSubBits = B2_SUB_BITS;
-constexpr int kOverlapBits = B2_OVERLAP_BITS;         // self-synchronisation run-in before a sub (see header)
-constexpr int kSubWords = kSubBits / 32;
-constexpr int kCT = 128;                    // subs (= threads) per entropy CTA
-constexpr int kLutBits = 10;
-constexpr int kLutSize = 1 << kLutBits;
-constexpr int kChunkWords = 64 + 8;          // read-ahead slack past the end of a scan: one block (<= 54 words) + queue
-constexpr int kMaxSlots = 6;                // <= 3 DC + 3 AC tables per image
+constexpr int kXT = 128;                     // subs (= threads) per CTA of the sync kernels
+constexpr int kXWarps = kXT / 32;
+constexpr int kXSteps = 8;                   // symbols per lane and round
+constexpr int kChunkWords = 64 + 8;          // read-ahead slack past the end of a scan buffer (words)
+constexpr int kXMinShift = 9, kXMaxShift = 16;
 
-// LUT entry: adv | zinc<<8 | len<<16 | run<<24 ; 0 = code longer than kLutBits (or invalid)
-//   adv  = bits consumed by code + magnitude,  len = code length,
-//   zinc = advance of the zig-zag index (64 ends the block),  run = zeros before the value.
-//   run 0xFF / 0xFE mark symbols the reference rejects (bad size / no such code).
-constexpr uint32_t kRunBadSize = 0xffu, kRunBadCode = 0xfeu;
-B2_HD uint32_t lut_entry(uint32_t adv, uint32_t zinc, uint32_t len, uint32_t run) {
-  return adv | (zinc << 8) | (len << 16) | (run << 24);
-}
-// symbol -> entry, following decodeMCUComponent (jpeg.cpp:330-400)
-B2_HD uint32_t make_entry(uint32_t sym, uint32_t len, bool is_dc) {
-  if (is_dc) {
-    if (sym > 11) return lut_entry(len, 64, len, kRunBadSize);          // jpeg.cpp:330-334
-    return lut_entry(len + sym, 1, len, 0);                             // z: 0 -> 1
-  }
-  const uint32_t run = sym >> 4, size = sym & 15;
-  if (sym == 0x00) return lut_entry(len, 64, len, 0);                   // EOB, jpeg.cpp:356-363
-  if (size == 0) {                                                      // ZRL (16) or a bare run, jpeg.cpp:368-380
-    const uint32_t z = sym == 0xf0 ? 16 : run;
-    return lut_entry(len, z, len, z);
-  }
-  if (size > 10) return lut_entry(len, 64, len, kRunBadSize);           // jpeg.cpp:381-385
-  return lut_entry(len + size, run + 1, len, run);
+// dynamic shared memory (32-bit words): the table set's used tables (compacted), then per warp the window ring
+// [word][lane] (+ the slot that repeats slot 0) and two [block-in-MCU][lane] columns: table offsets, component
+constexpr int kXRingWords = (kSegWords + 1) * 32;
+constexpr int kXWarpWords = kXRingWords + 2 * kMaxBpm * 32;
+constexpr uint32_t kXTb2Off = (uint32_t)kMaxBpm * 128u;   // bytes from a lane's table-offset entry to its component entry
+B2_HD size_t xsync_smem_bytes(int nslots) {
+  return sizeof(uint32_t) * ((size_t)nslots * kHTab + (size_t)kXWarps * kXWarpWords);
 }
 
-// Per-table data for codes longer than kLutBits: first canonical code and count per length.
-struct SlowTab {
-  uint32_t first[17];   // first[l] = first code of length l (huffman.hpp:17-29)
-  uint32_t count[17];
-  uint32_t base[17];    // index of that code's symbol
-  uint8_t symbols[176];
+// ---------------------------------------------------------------- where a sub lies
+struct XLoc {
+  bool valid, first, last;       // the slot holds a sub / it is the first / last sub of its segment
+  int img, k;                    // image, segment
+  uint32_t segp, B, lo, hi;      // segment [segp, B) and sub [lo, hi), bit positions in the image's unstuffed scan
+  uint32_t jl;                   // number of the sub inside its segment
 };
-
-struct EntropyShared {
-  SlowTab slow[kMaxSlots];
-  SubState e[kCT];                     // end state per sub
-  SubState used[kCT];                  // start state the end state was computed from
-  SubInfo info[kCT];                   // blocks / DC sums since the last segment start
-  int32_t list[kCT];                   // compacted indices of subs to re-decode
-  int32_t tab_of[kMaxBpm];             // per block-in-MCU: dc slot | ac slot << 8 | component << 16
-  uint32_t us_bits;
-  int32_t bpm, nslots, count;
-  SubState cta_in;
-  int32_t img;
-};
-
-B2_DEVICE uint32_t slow_lookup(const SlowTab &t, uint32_t w, bool is_dc) {
-  for (int l = kLutBits + 1; l <= 16; ++l) {
-    const uint32_t idx = (w >> (32 - l)) - t.first[l];
-    if (idx < t.count[l]) return make_entry(t.symbols[t.base[l] + idx], (uint32_t)l, is_dc);
+B2_DEVICE XLoc x_locate(int gsub, const XParams &xp, const int32_t *__restrict__ x_sub_base, const int32_t *__restrict__ x_img,
+                        const ImageDev *__restrict__ imgs, const uint32_t *__restrict__ seg_start,
+                        const uint32_t *__restrict__ segsub) {
+  XLoc L;
+  L.valid = L.first = L.last = false; L.img = 0; L.k = 0; L.segp = L.B = L.lo = L.hi = 0; L.jl = 0;
+  if (gsub >= xp.nsub_slots) return L;
+  const int s = find_owner(x_sub_base, xp.nimg, gsub);
+  L.img = x_img[s];
+  const ImageDev &im = imgs[L.img];
+  const uint32_t j = (uint32_t)(gsub - x_sub_base[s]);
+  const uint32_t *ss = segsub + im.seg_base;
+  if (j >= ss[im.nseg]) return L;                       // a reserved slot the image does not use
+  int a = 0, b = im.nseg - 1;                           // largest k with ss[k] <= j
+  while (a < b) {
+    const int mid = (a + b + 1) >> 1;
+    if (ss[mid] <= j) a = mid; else b = mid - 1;
   }
-  return lut_entry(16, 64, 16, kRunBadCode);                            // jpeg.cpp:319 "return -1"
+  L.k = a;
+  L.jl = j - ss[a];
+  L.segp = seg_start[im.seg_base + a]; L.B = seg_start[im.seg_base + a + 1];
+  L.lo = L.segp + (L.jl << xp.sub_shift);
+  const uint32_t h = L.lo + (1u << xp.sub_shift);
+  L.hi = h < L.B ? h : L.B;
+  L.first = L.jl == 0u; L.last = j + 1u == ss[a + 1];
+  L.valid = true;
+  return L;
 }
 
-// Cooperative build of one table's LUT + SlowTab from the DHT counts (canonical codes as
-// HuffmanTable::generateCodes, huffman.hpp:17-29; first match by increasing length as
-// getNextSymbol, jpeg.cpp:303-318).
-B2_DEVICE void build_table(const HuffSpec &spec, bool is_dc, uint32_t *lut, SlowTab &slow) {
-  if (threadIdx.x == 0) {
-    uint32_t code = 0;
-    for (int l = 1; l <= 16; ++l) {
-      slow.first[l] = code;
-      slow.count[l] = (uint32_t)spec.offset[l] - (uint32_t)spec.offset[l - 1];
-      slow.base[l] = spec.offset[l - 1];
-      code = (code + slow.count[l]) << 1;
+// ---------------------------------------------------------------- plan: subs and units per segment (one warp per image)
+B2_GLOBAL void k_xplan(XParams xp, const ImageDev *__restrict__ imgs, const ImageOut *__restrict__ out,
+                       const uint32_t *__restrict__ seg_start, uint32_t *__restrict__ segsub, uint32_t *__restrict__ segunit) {
+  const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (i >= xp.nimg) return;
+  const ImageDev &im = imgs[i];
+  const bool dead = out[i].status != 0;                 // stage U gave up on the scan: no subs, no units
+  const uint32_t *seg = seg_start + im.seg_base;
+  uint32_t cs = 0, cu = 0;
+  for (int b = 0; b <= im.nseg; b += 32) {
+    const int k = b + lane;
+    uint32_t ns = 0, nu = 0;
+    if (k < im.nseg && !dead) {
+      const uint32_t len = seg[k + 1] - seg[k];
+      ns = (len + (1u << xp.sub_shift) - 1u) >> xp.sub_shift;
+      nu = (ns + (uint32_t)xp.unit_subs - 1u) / (uint32_t)xp.unit_subs;
     }
-    slow.first[0] = slow.count[0] = slow.base[0] = 0;
-  }
-  for (int k = threadIdx.x; k < 176; k += blockDim.x) slow.symbols[k] = spec.symbols[k];
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < kLutSize; idx += blockDim.x) {
-    uint32_t e = 0;
-    for (int l = 1; l <= kLutBits; ++l) {
-      const uint32_t k = ((uint32_t)idx >> (kLutBits - l)) - slow.first[l];
-      if (k < slow.count[l]) { e = make_entry(slow.symbols[slow.base[l] + k], (uint32_t)l, is_dc); break; }
+    uint32_t is = ns, iu = nu;
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t os = __shfl_up_sync(0xffffffffu, is, d), ou = __shfl_up_sync(0xffffffffu, iu, d);
+      if (lane >= d) { is += os; iu += ou; }
     }
-    lut[idx] = e;
+    if (k <= im.nseg) { segsub[im.seg_base + k] = cs + is - ns; segunit[im.seg_base + k] = cu + iu - nu; }
+    cs += __shfl_sync(0xffffffffu, is, 31);
+    cu += __shfl_sync(0xffffffffu, iu, 31);
   }
 }
 
-// MSB-first bit reader over the (word-swapped) unstuffed scan in global memory; replaces
-// BitStream (file.hpp:122-165).  128-bit loads into a four-word register queue feed a 64-bit
-// left-aligned window: one LDG.128 per 128 bits consumed, each lane streaming through its own
-// cache lines (L1 keeps the line for the 7 following loads).
-struct BitReader {
-  const uint4 *base;      // word 0 of the image's unstuffed scan (16-byte aligned)
-  const uint4 *ptr;       // next vector to load
-  uint4 q;
-  int qn;                 // words left in q
-  uint64_t buf;
-  int avail;              // valid bits in buf
-  uint32_t wpos;          // bit index of the next word that will leave the queue
-  B2_MEMBER uint32_t next_word() {
-    if (qn == 0) { q = b2_ld_nc_v4(ptr); ++ptr; qn = 4; }
-    const uint32_t w = q.x;
-    q.x = q.y; q.y = q.z; q.z = q.w; --qn;
-    wpos += 32;
-    return w;
-  }
-  B2_MEMBER void seek(uint32_t bit) {      // bit position relative to `base`
-    const uint32_t wi = bit >> 5;
-    ptr = base + (wi >> 2);
-    q = b2_ld_nc_v4(ptr); ++ptr; qn = 4;
-    for (uint32_t k = 0; k < (wi & 3u); ++k) { q.x = q.y; q.y = q.z; q.z = q.w; --qn; }
-    wpos = wi << 5;
-    const uint64_t w0 = next_word(), w1 = next_word();
-    const uint32_t o = bit & 31u;
-    buf = ((w0 << 32) | w1) << o;
-    avail = 64 - (int)o;
-  }
-  B2_MEMBER void refill() {
-    if (avail <= 32) { const uint64_t w = next_word(); buf |= w << (32 - avail); avail += 32; }
-  }
-  B2_MEMBER uint32_t peek() const { return (uint32_t)(buf >> 32); }
-  B2_MEMBER void skip(uint32_t n) { buf <<= n; avail -= (int)n; }
-  B2_MEMBER uint32_t pos() const { return wpos - (uint32_t)avail; }
+// ---------------------------------------------------------------- the walk
+struct XWalkIn {
+  bool active;               // there is something to walk
+  bool started;              // the start is a block start inside the sub (exact or the predecessor's end state), not a run-in
+  const uint32_t *us;        // the image's unstuffed scan (words)
+  uint32_t usbits;           // its length
+  uint32_t p, blk;           // where to start: bit position, block-in-MCU index
+  uint32_t lo, hi, B;        // the sub, the end of its segment
+  int bpm;
+  const ImageDev *im;        // for the per-length search of pathological tables only
 };
+struct XWalkOut { uint32_t sp, sblk, ep, eblk; int nb, d0, d1, d2; };
 
-B2_DEVICE int extend(uint32_t w, uint32_t len, uint32_t size) {    // jpeg.cpp:335-343, 388-397
-  const uint32_t v = (w << len) >> (32 - size);
-  return (v >> (size - 1)) ? (int)v : (int)v - (int)((1u << size) - 1);
-}
-
-// True when a block that ended at bit `pe` was the last one of the segment ending at `B`:
-// it reached/passed B, or only the 1-bit padding of the last byte is left (T.81 F.1.2.3; a
-// complete Huffman code is never all ones, so padding cannot be taken for another block).
-B2_DEVICE bool segment_done(BitReader &r, uint32_t pe, uint32_t B) {
-  if (pe >= B) return true;
-  const uint32_t n = B - pe;
-  if (n > 7) return false;
-  r.refill();
-  return (r.peek() >> (32 - n)) == ((1u << n) - 1u);
-}
-
-// largest k in [lo,hi] with seg[k] <= p
-B2_DEVICE int seg_find(const uint32_t *__restrict__ seg, int lo, int hi, uint32_t p) {
-  while (lo < hi) {
-    const int mid = (lo + hi + 1) >> 1;
-    if (seg[mid] <= p) lo = mid; else hi = mid - 1;
+// All 32 lanes of a warp together.  ringl: this lane's column of the warp's window ring; tbl: this lane's column of the
+// warp's table-offset entries, already filled for the lane's image ([blk] = DC table byte offset | AC << 16, and at
+// +kXTb2Off the component).  Counts the blocks that start in [sp, ep), sp = first block start >= lo, ep = first block
+// start >= hi (or the segment's end), and sums their DC differences (jpeg.cpp:335-345) per component.
+B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, const XWalkIn &I,
+                      const TableSet *__restrict__ tsets, XWalkOut &O) {
+  (void)lane;
+  uint32_t p = I.p, z = 0, nb = 0, rw = 0;
+  int dsum = 0, d1 = 0, d2 = 0;
+  bool started = I.started, done = !I.active;
+  const uint32_t lo = I.lo, hi = I.hi, B = I.B;
+  const uint32_t *us = I.us;
+  if (I.active) {
+    rw = (p >> 5) & ~3u;
+    for (int i = 0; i < kSegWords; ++i) {
+      b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
+      if (((rw + i) & (kSegWords - 1)) == 0u) b2_cp_async4(ringl + kSegWords * 32, us + rw + i);   // slot 32 repeats slot 0
+    }
+    rw += kSegWords;
+  } else {                                              // an idle lane steps in place over entry 0 of table 0: keep its reads inside the CTA's shared memory
+    tbl[0] = 0u; tbl[kMaxBpm * 32] = 0u;
   }
-  return lo;
-}
-
-struct SubResult { SubState start, e; int nb, d0, d1, d2, flag; };
-
-// What the write pass needs on top of the walk itself.
-struct WriteCtx {
-  uint4 *stage4;          // this thread's staging block: chunk k at stage4[k * kCT]
-  int16_t *obase;         // coefficient buffer of the image
-  int bidx, limit;        // next output block, first block past the current segment's quota
-  int seg_blocks, nseg, nblocks;
-  int pred[3];
-  uint32_t err;
-};
-
-// The one decode loop of stage E: a flat loop over SYMBOLS (DC and AC alike) so that the lanes of a
-// warp stay in step; block ends are handled inside it.  Walks the blocks that start in
-// [from.p, hi).  While `lo` has not been reached the walk is only the self-synchronising run-in;
-// at the first block start >= lo the counters restart and that state is reported as R.start.
-//   WRITE=false: counts blocks and sums DC differences (per component) since the last segment
-//                start met on the way (R.flag = one was met).
-//   WRITE=true : also extracts the values into the staging block and stores finished blocks.
-template <bool WRITE>
-B2_DEVICE void decode_span(const EntropyShared &S, const uint32_t *__restrict__ luts, BitReader &r,
-                           const uint32_t *__restrict__ seg, int nseg, SubState from, uint32_t lo, uint32_t hi,
-                           SubResult &R, WriteCtx *W) {
-  uint32_t p = from.p, blk = from.blk;
-  bool started = p >= lo;
-  R.start = from; R.e = from; R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 0;
-  if (hi > S.us_bits) hi = S.us_bits;
-  if (p >= hi) return;
-  int k = seg_find(seg, 0, nseg - 1, p);
-  uint32_t B = seg[k + 1];
-  r.seek(p);
-  int tab = S.tab_of[blk];
-  uint32_t z = 0;
-  uint16_t *stage = WRITE ? reinterpret_cast<uint16_t *>(W->stage4) : nullptr;
+  b2_cp_async_commit();
+  b2_cp_async_wait<0>();
+  __syncwarp();
+  const uint32_t ring_a = b2_launder(b2_dsm_addr(ringl)), tb_a = b2_launder(b2_dsm_addr(tbl));
+  const uint32_t lut_r = b2_launder(lut_a);
+  const uint32_t tb_end = tb_a + (uint32_t)(I.active ? I.bpm : 1) * 128u;
+  uint32_t tba = tb_a + (I.active ? I.blk : 0u) * 128u;
+  uint32_t sp = p, sba = tba;
+  // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
+  auto advance = [&](uint32_t e, uint32_t w, bool is_dc, uint32_t comp) {
+    const uint32_t size = huff_size(e);
+    int diff = seg_extend(w, huff_adv(e) - size, size);            // jpeg.cpp:335-343; 0 for size 0
+    diff = is_dc ? diff : 0;
+    dsum += diff; d1 += comp == 1u ? diff : 0; d2 += comp == 2u ? diff : 0;
+    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
+    const bool pair = a2 != 0u && z + z1 < 64u;
+    p += huff_adv(e) + (pair ? a2 : 0u);
+    z += z1 + (pair ? huff_zinc2(e) : 0u);
+    const bool end = z >= 64u;
+    const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
+    z = end ? 0u : z;
+    tba = end ? tbn : tba;
+    nb += (end && p <= B) ? 1u : 0u;                               // a "block" that runs past the segment's end is padding
+    const bool ns = end && !started && p >= lo;                    // the run-in is over: the block that starts here is the sub's first
+    started = started || ns;
+    sp = ns ? p : sp; sba = ns ? tba : sba;
+    nb = ns ? 0u : nb; dsum = ns ? 0 : dsum; d1 = ns ? 0 : d1; d2 = ns ? 0 : d2;
+    done = done || (end && p >= hi);
+  };
   for (;;) {
-    r.refill();
-    const uint32_t w = r.peek();
-    const bool is_dc = z == 0;
-    const int slot = is_dc ? (tab & 0xff) : ((tab >> 8) & 0xff);
-    uint32_t e = luts[slot * kLutSize + (w >> (32 - kLutBits))];
-    if (e == 0) e = slow_lookup(S.slow[slot], w, is_dc);
-    const uint32_t adv = e & 0xff, zinc = (e >> 8) & 0xff, len = (e >> 16) & 0xff, run = e >> 24;
-    if (is_dc) {
-      const int diff = adv > len ? extend(w, len, adv - len) : 0;     // jpeg.cpp:335-345
-      const int c = tab >> 16;
-      if (WRITE) {
-        if (run >= kRunBadCode) W->err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_DC_LEN;
-        const int dc = (W->pred[c] += diff);
-        if (dc < -32768 || dc > 32767) W->err |= ST_DC_RANGE;
-        stage[0] = (uint16_t)dc;
-      } else {
-        if (c == 0) R.d0 += diff; else if (c == 1) R.d1 += diff; else R.d2 += diff;
-      }
-    } else if (WRITE) {
-      if (run >= kRunBadCode) W->err |= run == kRunBadCode ? ST_BAD_CODE : ST_BAD_AC_LEN;
-      else {
-        const uint32_t zr = z + run;
-        if (zr > 63) W->err |= ST_BAD_RUN;                               // jpeg.cpp:372-376
-        else if (adv > len) stage[(zr >> 3) * (kCT * 8) + (zr & 7)] = (uint16_t)extend(w, len, adv - len);
-      }
-    }
-    r.skip(adv);
-    z += zinc;
-    if (z < 64) continue;
-    // ---- block end ----
-    const uint32_t pe = r.pos();
-    if (WRITE) {
-      if (W->bidx < W->limit) {                  // blocks past the segment's quota are trailing garbage
-        uint4 *o = reinterpret_cast<uint4 *>(W->obase + (int64_t)W->bidx * 64);
+    // top-up, once per round: the same instructions for every lane, predicated per lane (kernels_segdec.cuh)
+    const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8) && rw <= (I.usbits >> 5) + 8u;
+    b2_cp_async4x4_if(need, ring_a + ((rw & (kSegWords - 1)) << 7), us + rw);
+    b2_cp_async4x4_if(need, ring_a + (((rw + 4u) & (kSegWords - 1)) << 7), us + rw + 4);
+    b2_cp_async4_if(need && (rw & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw);
+    b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
+    rw += need ? 8u : 0u;
+    b2_cp_async_commit();
+    b2_cp_async_wait<2>();
+    uint32_t w = 0, cur = 0, eraw = 0, comp = 0;
+    bool is_dc = false, nearf = false;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) o[q ^ (W->bidx & 7)] = W->stage4[q * kCT];   // chunk swizzle, see kernels_pixel.cuh
-      }
-#pragma unroll
-      for (int q = 0; q < 8; ++q) W->stage4[q * kCT] = make_uint4(0, 0, 0, 0);
-      ++W->bidx;
+    for (int u = 0; u < kXSteps; ++u) {
+      const uint32_t t = b2_lds_ro(tba);
+      comp = b2_lds_ro(tba + kXTb2Off);
+      is_dc = z == 0u;
+      cur = lut_r + (is_dc ? (t & 0xffffu) : (t >> 16));
+      const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
+      const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
+      w = __funnelshift_l(w1, w0, p);
+      eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+      // a block start inside the segment's last seven bits: padding or a very short block -- the extra slot decides
+      nearf = is_dc && p + 7u >= B;
+      const uint32_t e = (done || nearf || eraw >= kHOverflow) ? 0u : eraw;
+      advance(e, w, is_dc, comp);
     }
-    ++R.nb;
-    if (segment_done(r, pe, B)) {                // last block of its segment (jpeg.cpp:419-425)
-      if (WRITE) {
-        if (pe > B) W->err |= ST_OVERRUN;
-        if (W->bidx < W->limit) W->err |= ST_BLOCK_COUNT;
-        if (W->bidx > W->limit && k + 1 < W->nseg) W->err |= ST_BLOCK_COUNT;
-      }
-      p = B; blk = 0;
-      R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 1;
-      if (B < S.us_bits) {
-        ++k; B = seg[k + 1];
-        r.seek(p);
-        if (WRITE) {
-          W->bidx = k * W->seg_blocks;
-          W->limit = (k + 1 < W->nseg) ? (k + 1) * W->seg_blocks : W->nblocks;
-          W->pred[0] = W->pred[1] = W->pred[2] = 0;
+    // ---- the extra slot: lanes waiting in front of something the steps do not handle ----
+    const bool stuck = !done && (nearf || eraw >= kHOverflow);
+    if (__any_sync(0xffffffffu, stuck)) {
+      if (stuck) {
+        bool fin = false;
+        if (nearf) {
+          // T.81 F.1.2.3: the last byte of a segment is padded with 1-bits, and no code is all ones.  Anything else in
+          // those bits is taken for a block (the reference counts blocks and ignores the padding, jpeg.cpp:419-425);
+          // if it then runs past the segment's end it was padding after all (advance: p > B is not counted)
+          const uint32_t n = p < B ? B - p : 0u;
+          fin = n == 0u || (w >> (32u - n)) == ((1u << n) - 1u);
+        }
+        if (fin) {
+          if (!started) { started = true; nb = 0u; dsum = d1 = d2 = 0; sp = B; sba = tb_a; }
+          p = B; tba = tb_a; z = 0u; done = true;
+        } else {
+          uint32_t e = eraw;
+          if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+          if (e & kHOverflow) {
+            const int ci = (int)comp;
+            e = huff_slow(is_dc ? tsets[I.im->tset].dc[I.im->td[ci] & 3] : tsets[I.im->tset].ac[I.im->ta[ci] & 3], w >> 16, is_dc);
+          }
+          advance(e, w, is_dc, comp);
         }
       }
-    } else {
-      p = pe;
-      blk = blk + 1 == (uint32_t)S.bpm ? 0 : blk + 1;
     }
-    if (!started && p >= lo) {                   // the run-in is over: this is the sub's start state
-      started = true;
-      R.start.p = p; R.start.blk = blk;
-      R.nb = R.d0 = R.d1 = R.d2 = 0; R.flag = 0;
-    }
-    if (p >= hi) break;
-    tab = S.tab_of[blk];
-    z = 0;
+    if (__all_sync(0xffffffffu, done)) break;
   }
-  R.e.p = p; R.e.blk = blk;
+  b2_cp_async_wait<0>();                             // nothing of this walk lands in the ring once the next one fills it
+  O.sp = sp; O.sblk = (sba - tb_a) >> 7;
+  O.ep = p; O.eblk = (tba - tb_a) >> 7;
+  if (O.sp >= B) { O.sp = B; O.sblk = 0; }           // the segment is over: the next block is the next segment's first
+  if (O.ep >= B) { O.ep = B; O.eblk = 0; }
+  O.nb = (int)nb; O.d1 = d1; O.d2 = d2; O.d0 = dsum - d1 - d2;
+  if (!I.active) { O.sp = O.ep = I.p; O.sblk = O.eblk = I.blk; O.nb = O.d0 = O.d1 = O.d2 = 0; }
 }
 
-// Segmented-sum monoid over (flag, nb, d0, d1, d2): a flag restarts the sums.
+// ---------------------------------------------------------------- segmented sums over (flag, nb, d0, d1, d2): a flag restarts them
 struct Seg5 { int nb, d0, d1, d2, flag; };
 B2_DEVICE Seg5 seg5_zero() { Seg5 z; z.nb = z.d0 = z.d1 = z.d2 = z.flag = 0; return z; }
 B2_DEVICE Seg5 seg5_combine(const Seg5 &a, const Seg5 &b) {
@@ -338,19 +282,15 @@ B2_DEVICE SubInfo seg5_to(const Seg5 &s) {
   SubInfo i; i.nb_flag = (int32_t)((uint32_t)s.nb | ((uint32_t)s.flag << 31)); i.d0 = s.d0; i.d1 = s.d1; i.d2 = s.d2;
   return i;
 }
-B2_DEVICE SubInfo info_of(const SubResult &R) {
-  Seg5 s; s.nb = R.nb; s.d0 = R.d0; s.d1 = R.d1; s.d2 = R.d2; s.flag = R.flag;
-  return seg5_to(s);
-}
 // CTA-wide exclusive segmented scan; *total = combine of all threads' values.
 B2_DEVICE Seg5 seg5_cta_excl(const Seg5 &v, Seg5 *total) {
-  B2_SHARED Seg5 wsum[kCT / 32];
+  B2_SHARED Seg5 wsum[kXWarps];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const Seg5 inc = seg5_warp_incl(v);
   if (lane == 31) wsum[wid] = inc;
   __syncthreads();
   Seg5 base = seg5_zero(), tot = seg5_zero();
-  for (int w = 0; w < kCT / 32; ++w) { if (w < wid) base = seg5_combine(base, wsum[w]); tot = seg5_combine(tot, wsum[w]); }
+  for (int w = 0; w < kXWarps; ++w) { if (w < wid) base = seg5_combine(base, wsum[w]); tot = seg5_combine(tot, wsum[w]); }
   __syncthreads();
   Seg5 prev = seg5_shfl_up(inc, 1);
   if (lane == 0) prev = seg5_zero();
@@ -358,71 +298,131 @@ B2_DEVICE Seg5 seg5_cta_excl(const Seg5 &v, Seg5 *total) {
   return seg5_combine(base, prev);
 }
 
-// Common CTA prologue: image lookup and table build.  Returns false (uniformly) when the CTA lies
-// past the end of its image's unstuffed scan.
-B2_DEVICE bool entropy_prologue(EntropyShared &S, uint32_t *luts, const ImageDev *__restrict__ imgs,
-                                const int32_t *__restrict__ cta_base, int nimg, const TableSet *__restrict__ tsets,
-                                const ImageOut *__restrict__ out, ImageDev &im, uint32_t &chunk_bit0) {
-  if (threadIdx.x == 0) {
-    const int i = find_owner(cta_base, nimg, (int)blockIdx.x);
-    S.img = i;
-    S.us_bits = out[i].us_len * 8u;
+// ---------------------------------------------------------------- sync / fix
+struct XShared {
+  SubState e[kXT];                 // end state per sub
+  SubState used[kXT];              // start state the end state was computed from
+  SubInfo info[kXT];               // blocks / DC sums of the sub; bit 31 = first sub of its segment
+  int32_t list[kXT];               // compacted indices of subs to walk again
+  int32_t img[kXT];                // where each sub lies (x_locate), for whichever lane walks it
+  uint32_t lo[kXT], hi[kXT], B[kXT];
+  uint32_t flags[kXT];             // 1 valid, 2 first of its segment
+  int32_t tabslot[kHTabsPerSet];   // table -> slot in the CTA's compacted copy (-1: not in the set)
+  SubState cta_in;
+  int32_t count, set, skip;
+};
+
+// this lane's columns of the warp's table entries, for image `im` (DC table td -> slot, AC table ta -> slot)
+B2_DEVICE void x_set_tb(uint32_t *tbl, const ImageDev &im, const int32_t *tabslot) {
+  const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+  for (int b = 0; b < im.bpm; ++b) {
+    const int c = b < nluma ? 0 : b - nluma + 1;
+    const int sd = tabslot[im.td[c] & 3], sa = tabslot[4 + (im.ta[c] & 3)];
+    tbl[b * 32] = (uint32_t)(sd < 0 ? 0 : sd) * (kHTab * 4) | ((uint32_t)(sa < 0 ? 0 : sa) * (kHTab * 4)) << 16;
+    tbl[kMaxBpm * 32 + b * 32] = (uint32_t)c;
   }
-  __syncthreads();
-  im = imgs[S.img];
-  const uint32_t local_cta = (uint32_t)blockIdx.x - (uint32_t)im.cta_base;
-  chunk_bit0 = local_cta * (uint32_t)(kCT * kSubBits);
-  if (chunk_bit0 >= S.us_bits) return false;
-  const TableSet &ts = tsets[im.tset];
-  if (threadIdx.x == 0) {
-    // one LUT slot per distinct (class, id) used by the scan's components
-    int nslots = 0; int slot_of_dc[4] = {-1, -1, -1, -1}, slot_of_ac[4] = {-1, -1, -1, -1};
-    int cdc[3] = {0, 0, 0}, cac[3] = {0, 0, 0};
-    for (int c = 0; c < im.ncomp; ++c) {
-      const int td = im.td[c] & 3, ta = im.ta[c] & 3;
-      if (slot_of_dc[td] < 0) slot_of_dc[td] = nslots++;
-      if (slot_of_ac[ta] < 0) slot_of_ac[ta] = nslots++;
-      cdc[c] = slot_of_dc[td]; cac[c] = slot_of_ac[ta];
-    }
-    S.nslots = nslots;
-    const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
-    for (int b = 0; b < im.bpm; ++b) {
-      const int c = b < nluma ? 0 : b - nluma + 1;
-      S.tab_of[b] = cdc[c] | (cac[c] << 8) | (c << 16);
-    }
-    S.bpm = im.bpm;
-  }
-  __syncthreads();
-  {
-    bool done_dc[4] = {false, false, false, false}, done_ac[4] = {false, false, false, false};
-    for (int c = 0; c < im.ncomp; ++c) {
-      const int td = im.td[c] & 3, ta = im.ta[c] & 3;
-      const int t = S.tab_of[c == 0 ? 0 : im.bpm - im.ncomp + c];   // a block of component c
-      if (!done_dc[td]) { done_dc[td] = true; build_table(ts.dc[td], true, luts + (t & 0xff) * kLutSize, S.slow[t & 0xff]); }
-      if (!done_ac[ta]) { done_ac[ta] = true; build_table(ts.ac[ta], false, luts + ((t >> 8) & 0xff) * kLutSize, S.slow[(t >> 8) & 0xff]); }
-    }
-  }
-  __syncthreads();
-  return true;
 }
 
-B2_HD size_t entropy_smem_bytes(int nslots, bool staging) {
-  return sizeof(uint32_t) * (size_t)nslots * kLutSize + (staging ? (size_t)kCT * 128 : 0) + 16;
-}
+// FIRST=true : run-in + own sub from a guess (or an exact start), then repair inside the CTA.
+// FIRST=false: take the previous CTA's settled end state (bnd_in) and repair, if it differs from what was used.
+template <bool FIRST>
+B2_GLOBAL void __launch_bounds__(kXT)
+k_xsync(XParams xp, const ImageDev *__restrict__ imgs, const int32_t *__restrict__ x_sub_base, const int32_t *__restrict__ x_img,
+        const TableSet *__restrict__ tsets, const uint32_t *__restrict__ luts, const ImageOut *__restrict__ out,
+        const uint8_t *__restrict__ d_us, const uint32_t *__restrict__ seg_start, const uint32_t *__restrict__ segsub,
+        SubState *__restrict__ sub_e, SubState *__restrict__ sub_used, SubInfo *__restrict__ sub_info,
+        SubInfo *__restrict__ cta_tot, const SubState *__restrict__ bnd_in, SubState *__restrict__ bnd_out,
+        uint32_t *__restrict__ changed_flag) {
+  B2_DYN_SMEM(uint32_t, lut);
+  B2_SHARED XShared S;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int cta = (int)blockIdx.x, gsub = cta * kXT + tid;
+  const XLoc loc = x_locate(gsub, xp, x_sub_base, x_img, imgs, seg_start, segsub);
 
-// Jacobi repair inside a CTA: re-decode every sub whose start state differs from its predecessor's
-// end state, the needy subs compacted onto the first threads so that whole warps stay busy.
-// S.e / S.used / S.info hold the current states; thread 0's predecessor is S.cta_in if have_in.
-B2_DEVICE void entropy_repair(EntropyShared &S, const uint32_t *luts, BitReader &rd, const uint32_t *seg, int nseg,
-                              uint32_t chunk_bit0, bool have_in) {
-  const int tid = threadIdx.x;
-  for (int round = 0; round <= kCT; ++round) {
-    SubState prev; bool need = false;
-    if (tid > 0 || have_in) {
-      prev = tid == 0 ? S.cta_in : S.e[tid - 1];
-      const SubState u = S.used[tid];
-      const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
-      need = lo < S.us_bits && (prev.p != u.p || prev.blk != u.blk);
+  if (tid == 0) {
+    S.set = imgs[x_img[find_owner(x_sub_base, xp.nimg, cta * kXT)]].tset;
+    S.skip = 0;
+    if (!FIRST) {
+      // cheap uniform exit: this CTA's first sub does not depend on the previous CTA, or nothing upstream moved
+      int skip = 1;
+      if (cta > 0 && loc.valid && !loc.first) {
+        const SubState in = bnd_in[cta - 1], used = sub_used[gsub];
+        skip = in.p == used.p && in.blk == used.blk;
+        S.cta_in = in;
+      }
+      if (skip) bnd_out[cta] = bnd_in[cta];
+      S.skip = skip;
+    }
+    int n = 0;
+    for (int t = 0; t < kHTabsPerSet; ++t) {
+      const bool used = t < 4 ? tsets[S.set].dc[t].set : tsets[S.set].ac[t - 4].set;
+      S.tabslot[t] = used ? n++ : -1;
+    }
+  }
+  __syncthreads();
+  if (!FIRST && S.skip) return;
+
+  {  // the table set's tables, compacted
+    const uint4 *src = reinterpret_cast<const uint4 *>(luts + (size_t)S.set * kHTabsPerSet * kHTab);
+    uint4 *dst = reinterpret_cast<uint4 *>(lut);
+    for (int t = 0; t < kHTabsPerSet; ++t) {
+      const int slot = S.tabslot[t];
+      if (slot < 0) continue;
+      for (int k = tid; k < kHTab / 4; k += kXT) dst[slot * (kHTab / 4) + k] = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
+    }
+  }
+  int nslots = 0;
+  for (int t = 0; t < kHTabsPerSet; ++t) nslots += S.tabslot[t] >= 0;
+  uint32_t *wbase = lut + (size_t)nslots * kHTab + (size_t)warp * kXWarpWords;
+  uint32_t *ringl = wbase + lane, *tbl = wbase + kXRingWords + lane;
+  const uint32_t lut_a = b2_dsm_addr(lut);
+
+  S.img[tid] = loc.img; S.lo[tid] = loc.lo; S.hi[tid] = loc.hi; S.B[tid] = loc.B;
+  S.flags[tid] = (loc.valid ? 1u : 0u) | (loc.first ? 2u : 0u);
+  __syncthreads();                                   // tables and locations are in place
+
+  auto walk_in = [&](int j, SubState from, bool started) {
+    XWalkIn I;
+    const ImageDev &im = imgs[S.img[j]];
+    I.active = (S.flags[j] & 1u) != 0u && from.p < S.hi[j];
+    I.started = started;
+    I.us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
+    I.usbits = out[S.img[j]].us_len * 8u;
+    I.p = from.p; I.blk = from.blk;
+    I.lo = S.lo[j]; I.hi = S.hi[j]; I.B = S.B[j];
+    I.bpm = im.bpm; I.im = &im;
+    return I;
+  };
+
+  if (FIRST) {
+    SubState from; from.p = loc.lo; from.blk = 0;
+    bool started = true;
+    if (loc.valid && !loc.first) {
+      // start `overlap` bits early from a guess; from the segment's start if that is within reach (then the run-in is exact)
+      started = false;
+      from.p = (loc.lo - loc.segp > (uint32_t)xp.overlap) ? loc.lo - (uint32_t)xp.overlap : loc.segp;
+    }
+    if (loc.valid) x_set_tb(tbl, imgs[loc.img], S.tabslot);
+    const XWalkIn I = walk_in(tid, from, started);
+    XWalkOut R;
+    x_walk(lane, ringl, tbl, lut_a, I, tsets, R);
+    SubState e, u; e.p = R.ep; e.blk = R.eblk; u.p = R.sp; u.blk = R.sblk;
+    Seg5 s; s.nb = R.nb; s.d0 = R.d0; s.d1 = R.d1; s.d2 = R.d2; s.flag = loc.first ? 1 : 0;
+    if (!loc.valid) { e.p = e.blk = u.p = u.blk = 0; s = seg5_zero(); }
+    S.e[tid] = e; S.used[tid] = u; S.info[tid] = seg5_to(s);
+  } else {
+    S.e[tid] = sub_e[gsub]; S.used[tid] = sub_used[gsub]; S.info[tid] = sub_info[gsub];
+  }
+  __syncthreads();
+
+  // ---- Jacobi repair inside the CTA: walk again every sub whose start state differs from its predecessor's end state,
+  //      the needy subs compacted onto the first threads so that whole warps stay busy ----
+  const bool have_in = !FIRST;
+  for (int round = 0; round <= kXT; ++round) {
+    bool need = false;
+    if ((S.flags[tid] & 3u) == 1u && (tid > 0 || have_in)) {     // valid and not the first sub of its segment
+      const SubState prev = tid == 0 ? S.cta_in : S.e[tid - 1], u = S.used[tid];
+      need = prev.p != u.p || prev.blk != u.blk;
     }
     if (tid == 0) S.count = 0;
     __syncthreads();
@@ -433,97 +433,33 @@ B2_DEVICE void entropy_repair(EntropyShared &S, const uint32_t *luts, BitReader 
     if (tid == 0 && getenv("B2_EMU_TRACE")) fprintf(stderr, "cta %u repair round %d: %d subs\n", blockIdx.x, round, cnt);
 #endif
     if (cnt == 0) break;
-    SubResult R; int j = -1; SubState from;
-    if (tid < cnt) {
-      j = S.list[tid];
-      from = j == 0 ? S.cta_in : S.e[j - 1];
-      const uint32_t lo = chunk_bit0 + (uint32_t)j * kSubBits;
-      decode_span<false>(S, luts, rd, seg, nseg, from, lo, lo + kSubBits, R, nullptr);
-    }
-    __syncthreads();                               // every S.e read of this round precedes every write
-    if (j >= 0) { S.e[j] = R.e; S.used[j] = from; S.info[j] = info_of(R); }
-    __syncthreads();
-  }
-}
-
-// ---- sync / fix -----------------------------------------------------------------------------
-// FIRST=true : run-in + own sub from a guess (or the last segment start), then repair in the CTA.
-// FIRST=false: take the previous CTA's settled end state (bnd_in) and repair, if it differs.
-template <bool FIRST>
-B2_GLOBAL void __launch_bounds__(kCT)
-k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ cta_base, int nimg,
-               const TableSet *__restrict__ tsets, const ImageOut *__restrict__ out,
-               const uint8_t *__restrict__ d_us, const uint32_t *__restrict__ seg_start,
-               SubState *__restrict__ sub_e, SubState *__restrict__ sub_used, SubInfo *__restrict__ sub_info,
-               SubInfo *__restrict__ cta_tot, const SubState *__restrict__ bnd_in, SubState *__restrict__ bnd_out,
-               uint32_t *__restrict__ changed_flag, int nslots_max) {
-  B2_DYN_SMEM(uint32_t, luts);
-  B2_SHARED EntropyShared S;
-  const int tid = threadIdx.x;
-  (void)nslots_max;
-
-  if (!FIRST) {
-    // cheap uniform exit: nothing upstream of this CTA moved
-    B2_SHARED int s_skip;
-    if (tid == 0) {
-      const int i = find_owner(cta_base, nimg, (int)blockIdx.x);
-      const int c = (int)blockIdx.x;
-      int skip;
-      if (c == imgs[i].cta_base) skip = 1;                 // first CTA of an image starts from the truth
-      else {
-        const SubState in = bnd_in[c - 1];
-        const SubState used = sub_used[imgs[i].sub_base + (c - imgs[i].cta_base) * kCT];
-        skip = in.p == used.p && in.blk == used.blk;
+    XWalkOut R; int j = -1; SubState from; from.p = from.blk = 0;
+    if (warp * 32 < cnt) {                              // warp-uniform: the warp holds at least one sub to walk
+      XWalkIn I; I.active = false; I.started = true; I.us = nullptr; I.usbits = 0; I.p = I.blk = 0; I.lo = I.hi = I.B = 0; I.bpm = 1; I.im = &imgs[0];
+      if (tid < cnt) {
+        j = S.list[tid];
+        from = j == 0 ? S.cta_in : S.e[j - 1];
+        x_set_tb(tbl, imgs[S.img[j]], S.tabslot);
+        I = walk_in(j, from, true);
       }
-      if (skip) bnd_out[c] = bnd_in[c];
-      s_skip = skip;
+      x_walk(lane, ringl, tbl, lut_a, I, tsets, R);
+    }
+    __syncthreads();                                    // every S.e read of this round precedes every write
+    if (j >= 0) {
+      SubState e; e.p = R.ep; e.blk = R.eblk;
+      Seg5 s; s.nb = R.nb; s.d0 = R.d0; s.d1 = R.d1; s.d2 = R.d2; s.flag = 0;
+      S.e[j] = e; S.used[j] = from; S.info[j] = seg5_to(s);
     }
     __syncthreads();
-    if (s_skip) return;
   }
 
-  ImageDev im; uint32_t chunk_bit0;
-  const bool live = entropy_prologue(S, luts, imgs, cta_base, nimg, tsets, out, im, chunk_bit0);
-  const int cta = (int)blockIdx.x, local_cta = cta - im.cta_base;
-  const int gsub = im.sub_base + local_cta * kCT + tid;
-  if (!live) {
-    // beyond the end of this image's unstuffed scan: empty subs
-    if (FIRST) {
-      SubState z; z.p = S.us_bits; z.blk = 0;
-      sub_e[gsub] = z; sub_used[gsub] = z;
-      SubInfo zi; zi.nb_flag = zi.d0 = zi.d1 = zi.d2 = 0; sub_info[gsub] = zi;
-      if (tid == 0) { cta_tot[cta] = zi; bnd_out[cta] = z; }
-    } else if (tid == 0) bnd_out[cta] = bnd_in[cta];
-    return;
-  }
-  const uint32_t *seg = seg_start + im.seg_base;
-  const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
-  BitReader rd; rd.base = reinterpret_cast<const uint4 *>(d_us + im.raw_off);
-
-  if (FIRST) {
-    SubResult R;
-    SubState from; from.p = S.us_bits; from.blk = 0;
-    if (lo < S.us_bits) {
-      // start at the last segment start at or before lo if it is within reach (exact), else guess
-      const int k = seg_find(seg, 0, im.nseg - 1, lo);
-      const uint32_t sb = seg[k];
-      from.p = (lo >= (uint32_t)kOverlapBits && lo - (uint32_t)kOverlapBits > sb) ? lo - (uint32_t)kOverlapBits : sb;
-    }
-    decode_span<false>(S, luts, rd, seg, im.nseg, from, lo, lo + kSubBits, R, nullptr);
-    S.e[tid] = R.e; S.used[tid] = R.start; S.info[tid] = info_of(R);
-  } else {
-    S.e[tid] = sub_e[gsub]; S.used[tid] = sub_used[gsub]; S.info[tid] = sub_info[gsub];
-    if (tid == 0) S.cta_in = bnd_in[cta - 1];
-  }
-  __syncthreads();
-  entropy_repair(S, luts, rd, seg, im.nseg, chunk_bit0, !FIRST);
   const SubState e = S.e[tid];
   sub_e[gsub] = e; sub_used[gsub] = S.used[tid];
   const SubInfo mine = S.info[tid];
   sub_info[gsub] = mine;
   Seg5 total;
   seg5_cta_excl(seg5_from(mine), &total);
-  if (tid == kCT - 1) {
+  if (tid == kXT - 1) {
     if (!FIRST) {
       const SubState old = bnd_in[cta];
       if (old.p != e.p || old.blk != e.blk) atomicOr(changed_flag, 1u);
@@ -533,72 +469,64 @@ k_entropy_sync(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ ct
   if (tid == 0) cta_tot[cta] = seg5_to(total);
 }
 
-// ---- scan over CTA totals: one warp per image ----------------------------------------------
-B2_GLOBAL void k_entropy_scan(const ImageDev *__restrict__ imgs, int nimg, const SubInfo *__restrict__ cta_tot,
-                              SubInfo *__restrict__ cta_pre) {
-  const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-  if (i >= nimg) return;
-  const int c0 = imgs[i].cta_base, nc = imgs[i].ncta;
+// ---------------------------------------------------------------- scan over the CTA totals of the whole batch (one warp)
+B2_GLOBAL void k_xscan(int ncta, const SubInfo *__restrict__ cta_tot, SubInfo *__restrict__ cta_pre) {
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x >= 32) return;
   Seg5 carry = seg5_zero();
-  for (int b = 0; b < nc; b += 32) {
+  for (int b = 0; b < ncta; b += 32) {
     const int c = b + lane;
     Seg5 v = seg5_zero();
-    if (c < nc) v = seg5_from(cta_tot[c0 + c]);
+    if (c < ncta) v = seg5_from(cta_tot[c]);
     const Seg5 inc = seg5_warp_incl(v);
     Seg5 prev = seg5_shfl_up(inc, 1);
     if (lane == 0) prev = seg5_zero();
-    if (c < nc) cta_pre[c0 + c] = seg5_to(seg5_combine(carry, prev));
+    if (c < ncta) cta_pre[c] = seg5_to(seg5_combine(carry, prev));
     carry = seg5_combine(carry, seg5_shfl(inc, 31));
   }
 }
 
-// ---- write ------------------------------------------------------------------------------------
-B2_GLOBAL void __launch_bounds__(kCT)
-k_entropy_write(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ cta_base, int nimg,
-                const TableSet *__restrict__ tsets, ImageOut *__restrict__ out, const uint8_t *__restrict__ d_us,
-                const uint32_t *__restrict__ seg_start, const SubState *__restrict__ sub_e,
-                const SubInfo *__restrict__ sub_info, const SubInfo *__restrict__ cta_pre,
-                int16_t *__restrict__ coef, int nslots_max) {
-  B2_DYN_SMEM(uint32_t, luts);
-  B2_SHARED EntropyShared S;
-  uint4 *stage4 = reinterpret_cast<uint4 *>(luts + (size_t)nslots_max * kLutSize);
-  const int tid = threadIdx.x;
-  ImageDev im; uint32_t chunk_bit0;
-  if (!entropy_prologue(S, luts, imgs, cta_base, nimg, tsets, out, im, chunk_bit0)) return;
-  const int cta = (int)blockIdx.x, local_cta = cta - im.cta_base;
-  const int gsub = im.sub_base + local_cta * kCT + tid;
-  const uint32_t *seg = seg_start + im.seg_base;
-  const uint32_t lo = chunk_bit0 + (uint32_t)tid * kSubBits;
-
-  // first output block and DC predictors of this sub
+// ---------------------------------------------------------------- units: what the segment decoder's lanes will decode
+// Unit ul of a segment = its subs [ul * unit_subs, (ul + 1) * unit_subs).  The thread of a unit's first sub writes where
+// and in which state the unit starts, the thread of its last sub where it ends; the thread of a segment's last sub checks
+// that the segment held the blocks the header promises (RI MCUs; the rest of the image for the last segment).
+B2_GLOBAL void __launch_bounds__(kXT)
+k_xunits(XParams xp, const ImageDev *__restrict__ imgs, const int32_t *__restrict__ x_sub_base, const int32_t *__restrict__ x_img,
+         const int32_t *__restrict__ x_unit_base, ImageOut *__restrict__ out, const uint32_t *__restrict__ seg_start,
+         const uint32_t *__restrict__ segsub, const uint32_t *__restrict__ segunit, const SubState *__restrict__ sub_e,
+         const SubState *__restrict__ sub_used, const SubInfo *__restrict__ sub_info, const SubInfo *__restrict__ cta_pre,
+         XUnit *__restrict__ xunits) {
+  const int tid = threadIdx.x, cta = (int)blockIdx.x, gsub = cta * kXT + tid;
+  const XLoc loc = x_locate(gsub, xp, x_sub_base, x_img, imgs, seg_start, segsub);
+  const SubInfo mine = sub_info[gsub];
   Seg5 total;
-  Seg5 pre = seg5_cta_excl(seg5_from(sub_info[gsub]), &total);
+  Seg5 pre = seg5_cta_excl(seg5_from(mine), &total);
   pre = seg5_combine(seg5_from(cta_pre[cta]), pre);
-
-  SubState start;
-  if (local_cta == 0 && tid == 0) { start.p = 0; start.blk = 0; }
-  else start = sub_e[gsub - 1];
-
-  // staging: chunk k (8 coefficients) of thread t at stage4[k*kCT + t]
-#pragma unroll
-  for (int k = 0; k < 8; ++k) stage4[k * kCT + tid] = make_uint4(0, 0, 0, 0);
-
-  WriteCtx W;
-  W.stage4 = stage4 + tid;
-  W.obase = coef + im.coef_base * 64;
-  W.seg_blocks = im.restart_interval * im.bpm;                       // 0 when there is one segment
-  W.nseg = im.nseg; W.nblocks = im.nblocks;
-  W.err = 0;
-  if (lo < S.us_bits && start.p < lo + kSubBits && start.p < S.us_bits) {
-    const int k = seg_find(seg, 0, im.nseg - 1, start.p);
-    W.bidx = k * W.seg_blocks + pre.nb;
-    W.limit = (k + 1 < im.nseg) ? (k + 1) * W.seg_blocks : im.nblocks;
-    W.pred[0] = pre.d0; W.pred[1] = pre.d1; W.pred[2] = pre.d2;
-    BitReader rd; rd.base = reinterpret_cast<const uint4 *>(d_us + im.raw_off);
-    SubResult R;
-    decode_span<true>(S, luts, rd, seg, im.nseg, start, lo, lo + kSubBits, R, &W);
+  if (!loc.valid) return;
+  if (loc.first) pre = seg5_zero();                     // the sums before a segment's first sub belong to the segment before
+  const ImageDev &im = imgs[loc.img];
+  const int seg_blocks = im.restart_interval * im.bpm;  // 0 when there is one segment
+  const int base = loc.k * seg_blocks;
+  const int limit = (loc.k + 1 < im.nseg) ? base + seg_blocks : im.nblocks;
+  const int nb = mine.nb_flag & 0x7fffffff;
+  int first_blk = base + pre.nb, past_blk = first_blk + nb;
+  if (loc.last && past_blk != limit) atomicOr(&out[loc.img].status, (uint32_t)ST_BLOCK_COUNT);
+  first_blk = first_blk < limit ? first_blk : limit;    // whatever a corrupt scan yields, no lane writes outside its segment's blocks
+  past_blk = past_blk < limit ? past_blk : limit;
+  const uint32_t us = (uint32_t)xp.unit_subs, ul = loc.jl / us, r = loc.jl - ul * us;
+  const int s = find_owner(x_sub_base, xp.nimg, gsub);
+  XUnit &u = xunits[x_unit_base[s] + (int)segunit[im.seg_base + loc.k] + (int)ul];
+  if (r == 0u) {
+    const SubState st = sub_used[gsub];                 // == the predecessor's end state once the repair has settled
+    u.p0 = loc.first ? loc.segp : st.p;
+    u.blk0 = loc.first ? 0u : st.blk;
+    u.bidx = (uint32_t)first_blk;
+    u.pred[0] = pre.d0; u.pred[1] = pre.d1; u.pred[2] = pre.d2;
   }
-  if (W.err) atomicOr(&out[S.img].status, W.err);
+  if (r == us - 1u || loc.last) {
+    u.bend = (uint32_t)past_blk;
+    u.pend = loc.last ? loc.B : sub_e[gsub].p;
+  }
 }
 
 }  // namespace b2

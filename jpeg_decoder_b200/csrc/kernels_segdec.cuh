@@ -120,16 +120,24 @@ B2_HD size_t segdec_smem_bytes() {
   return sizeof(uint32_t) * ((size_t)kHTabsPerSet * kHTab + (size_t)kSegGroups * kSegGroupWords);
 }
 
-// What every warp of a group knows about a lane's segment before the first symbol.
+// What every warp of a group knows about a lane's unit before the first symbol.  A unit is a whole restart segment
+// (units[] = (image, segment), built by the planner: start byte-aligned, predictors zero, first block k * RI * blocks
+// per MCU -- jpeg.cpp:419-425) or, on the self-synchronising path, a run of subs whose start state
+// kernels_entropy.cuh has settled (XUnit: any bit position, any block-in-MCU phase, predictors = the running sums).
 struct SegLane {
   bool live;                 // there is something to decode
-  int img, bidx, bend;       // image, first block of the segment, first block past it
+  int img, bidx, bend;       // image, first block of the unit, first block past it
   int bpm, nluma;
   int64_t gb;                // global index of the first block in the coefficient buffer
+  uint32_t p0, pend;         // bit range in the image's unstuffed scan
+  int blk0;                  // block-in-MCU index of the first block
+  int pred[3];               // DC predictors before the first block
 };
-B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, const ImageOut *__restrict__ out) {
+B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, const ImageOut *__restrict__ out,
+                           const uint32_t *__restrict__ seg_start) {
   SegLane L;
   L.live = false; L.img = 0; L.bidx = L.bend = 0; L.bpm = 1; L.nluma = 1; L.gb = 0;
+  L.p0 = L.pend = 0; L.blk0 = 0; L.pred[0] = L.pred[1] = L.pred[2] = 0;
   if (unit.x == kSegNoUnit) return L;
   L.img = (int)unit.x;
   const ImageDev &im = imgs[L.img];
@@ -141,6 +149,29 @@ B2_DEVICE SegLane seg_lane(const uint2 unit, const ImageDev *__restrict__ imgs, 
   L.gb = im.coef_base + L.bidx;
   // a scan stage U gave up on is not decoded: its blocks read zero
   L.live = L.bidx < L.bend && !(out[L.img].status & (ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT));
+  if (L.live) { L.p0 = seg_start[im.seg_base + k]; L.pend = seg_start[im.seg_base + k + 1]; }
+  return L;
+}
+// Unit slot `slot` of the self-synchronising path: slots are numbered batch-wide, image after image in the planner's
+// table-set order (x_unit_base: n+1 prefixes, x_img: the image at each position); segunit[seg_base + nseg] is the
+// number of units the image really has.
+B2_DEVICE SegLane seg_lane_x(int slot, const ImageDev *__restrict__ imgs, const int32_t *__restrict__ x_unit_base,
+                             const int32_t *__restrict__ x_img, int nimg, const XUnit *__restrict__ xunits,
+                             const uint32_t *__restrict__ segunit) {
+  SegLane L;
+  L.live = false; L.img = 0; L.bidx = L.bend = 0; L.bpm = 1; L.nluma = 1; L.gb = 0;
+  L.p0 = L.pend = 0; L.blk0 = 0; L.pred[0] = L.pred[1] = L.pred[2] = 0;
+  const int s = find_owner(x_unit_base, nimg, slot);
+  L.img = x_img[s];
+  const ImageDev &im = imgs[L.img];
+  L.bpm = im.bpm; L.nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+  if ((uint32_t)(slot - x_unit_base[s]) >= segunit[im.seg_base + im.nseg]) return L;   // a reserved slot the image does not use
+  const XUnit u = xunits[slot];
+  L.bidx = (int)u.bidx; L.bend = (int)u.bend;
+  L.gb = im.coef_base + L.bidx;
+  L.p0 = u.p0; L.pend = u.pend; L.blk0 = (int)u.blk0;
+  L.pred[0] = u.pred[0]; L.pred[1] = u.pred[1]; L.pred[2] = u.pred[2];
+  L.live = L.bidx < L.bend;
   return L;
 }
 
@@ -194,8 +225,8 @@ struct SegFifo {
 // than kHLutBits -- one symbol in 200 --, an error entry) STAYS where it is for the rest of the round (its
 // entries read 0: no advance, nothing for the consumers) and the symbol is resolved after the last step, in the
 // round's extra slot.
-B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 unit, const ImageDev *__restrict__ imgs,
-                          const TableSet *__restrict__ tsets, const uint32_t *__restrict__ seg_start,
+B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const ImageDev *__restrict__ imgs,
+                          const TableSet *__restrict__ tsets,
                           const uint8_t *__restrict__ d_us, uint32_t *ringl, uint32_t *tb, uint32_t lut_a, uint32_t &err) {
   uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
   const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
@@ -208,8 +239,8 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
       tb[b * 32 + lane] = (uint32_t)(im.td[c] & 3) * (kHTab * 4) | ((uint32_t)(4 + (im.ta[c] & 3)) * (kHTab * 4)) << 16;
     }
     us = reinterpret_cast<const uint32_t *>(d_us + im.raw_off);
-    p = seg_start[im.seg_base + (int)unit.y];
-    pend = seg_start[im.seg_base + (int)unit.y + 1];
+    p = L.p0;
+    pend = L.pend;
     rw = (p >> 5) & ~3u;
     for (int i = 0; i < kSegWords; ++i) {
       b2_cp_async4(ringl + ((rw + i) & (kSegWords - 1)) * 32, us + rw + i);
@@ -224,7 +255,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, uint2 u
   const uint32_t ring_a = b2_launder(b2_dsm_addr(ringl)), tb_a = b2_launder(b2_dsm_addr(tb) + 4u * (uint32_t)lane);
   const uint32_t lut_r = b2_launder(lut_a);
   const uint32_t tb_end = tb_a + (uint32_t)L.bpm * 128u;
-  uint32_t tba = tb_a;                             // this lane's table entry of the current block-in-MCU
+  uint32_t tba = tb_a + (uint32_t)L.blk0 * 128u;   // this lane's table entry of the current block-in-MCU
   uint32_t z = 0, nb = 0;                          // zig-zag index, blocks finished
   // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
   auto advance = [&](uint32_t e, uint32_t &fn) {
@@ -392,8 +423,8 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
   }
   uint32_t flushed = 0;                              // blocks of this lane that have left
   const uint32_t asm_a = asm_g + ((uint32_t)lane << 7);
-  int pred0 = 0, pred1 = 0, pred2 = 0;               // DC prediction per component (jpeg.cpp:335-345), restarted with the segment
-  int blk = 0;                                       // block-in-MCU of the lane's next block to leave
+  int pred0 = L.pred[0], pred1 = L.pred[1], pred2 = L.pred[2];   // DC prediction per component (jpeg.cpp:335-345), restarted with the segment
+  int blk = L.blk0;                                  // block-in-MCU of the lane's next block to leave
   uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
   for (uint32_t r = 0;; ++r) {
     ff.wait(r);
@@ -444,12 +475,15 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
 }
 
 // units[u] = (image, segment); the units of one CTA share a table set (the planner pads each table-set group to a
-// multiple of kSegUnits with kSegNoUnit).  d_us / seg_start: stage U's output.  Every block of every unit is written
-// (whole, zeros included): the coefficient buffer needs no clearing.
+// multiple of kSegUnits with kSegNoUnit).  units == nullptr: the self-synchronising path's unit slots (seg_lane_x).
+// d_us / seg_start: stage U's output.  Every block of every unit is written (whole, zeros included): the coefficient
+// buffer needs no clearing.
 B2_GLOBAL void __launch_bounds__(kSegThreads)
 k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs, const TableSet *__restrict__ tsets,
               const uint32_t *__restrict__ luts, const uint32_t *__restrict__ seg_start,
-              const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef) {
+              const uint8_t *__restrict__ d_us, ImageOut *__restrict__ out, int16_t *__restrict__ coef,
+              const int32_t *__restrict__ x_unit_base, const int32_t *__restrict__ x_img, int nimg,
+              const XUnit *__restrict__ xunits, const uint32_t *__restrict__ segunit) {
   B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab], then the groups
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = warp % kSegGroups, role = warp / kSegGroups;    // role 0 decoder, 1 .. kSegAcW writers, kSegAcW + 1 flusher
@@ -462,7 +496,8 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   ff.bar_a = b2_dsm_addr(grp + kSegOffBar);
   {
     // the CTA's table set: that of its first unit (never padding)
-    const int set = imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset;
+    const int set = units ? imgs[units[(size_t)blockIdx.x * kSegUnits].x].tset
+                          : imgs[x_img[find_owner(x_unit_base, nimg, (int)blockIdx.x * kSegUnits)]].tset;
     const uint4 *src = reinterpret_cast<const uint4 *>(luts + (size_t)set * kHTabsPerSet * kHTab);
     uint4 *dst = reinterpret_cast<uint4 *>(lut);
     for (int t = 0; t < kHTabsPerSet; ++t) {
@@ -479,13 +514,14 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   }
   __syncthreads();
 
-  const uint2 unit = units[(size_t)blockIdx.x * kSegUnits + g * 32 + lane];
-  const SegLane L = seg_lane(unit, imgs, out);
+  const int slot = (int)blockIdx.x * kSegUnits + g * 32 + lane;
+  const SegLane L = units ? seg_lane(units[slot], imgs, out, seg_start)
+                          : seg_lane_x(slot, imgs, x_unit_base, x_img, nimg, xunits, segunit);
   uint32_t err = 0;
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
   const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
-  if (role == 0) seg_decode(ff, lane, L, unit, imgs, tsets, seg_start, d_us, ringl, tb, lut_a, err);
+  if (role == 0) seg_decode(ff, lane, L, imgs, tsets, d_us, ringl, tb, lut_a, err);
   else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, g0, err);
   else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef), err);
   if (err) atomicOr(&out[L.img].status, err);

@@ -19,8 +19,9 @@
 #include "platform.h"
 #include "dev_types.h"
 #include "kernels_unstuff.cuh"
-#include "kernels_entropy.cuh"
+#include "kernels_huff.cuh"
 #include "kernels_segdec.cuh"
+#include "kernels_entropy.cuh"
 #include "kernels_pixel.cuh"
 
 namespace b2 {
@@ -124,18 +125,42 @@ struct BatchPlan {
   int n = 0;
   std::vector<ImageDev> imgs;
   std::vector<TableSet> tsets;
-  std::vector<int32_t> tile_base, cta_base;           // n+1 exclusive prefixes
+  std::vector<int32_t> tile_base;                     // n+1 exclusive prefixes
   std::vector<int32_t> grp_img[PF_COUNT], grp_pre[PF_COUNT];
   PixUni uni[PF_COUNT];                               // arithmetic tile lookup for uniform groups
   std::vector<int> bwr, bhr;                          // reference block grid (coef export)
   size_t raw_bytes = 0, rgb_bytes = 0;
   int64_t nblocks = 0, pixels = 0, scan_bytes = 0;
-  int ntiles = 0, nsubs = 0, nctas = 0, nsegs = 0, nslots_max = 2;
-  // entropy path of the batch (kPathSegment: one thread per restart segment, kernels_segdec.cuh)
+  int ntiles = 0, nsegs = 0, nslots_max = 2;
+  // entropy path of the batch (kPathSegment: one lane per restart segment; kPathSync: self-synchronising subs first)
   int path = kPathSync;
-  std::vector<uint2> units;                           // (image, segment), grouped by table set, padded per group
-  int nunit_ctas = 0;
+  std::vector<uint2> units;                           // segment path: (image, segment), grouped by table set, padded per group
+  int nunit_ctas = 0;                                 // CTAs of k_entropy_seg (either path)
+  // self-synchronising path (kernels_entropy.cuh): sub and unit slots, numbered batch-wide in table-set order
+  XParams x;
+  std::vector<int32_t> x_img, x_sub_base, x_unit_base;   // image at each position; n+1 prefixes of the reserved slots
 };
+
+// Sub and unit sizes of the self-synchronising path, from the batch's scan bits.  The sync pass wants enough subs to
+// fill the device (one thread each, ~150 k in flight) but pays `overlap` extra bits per sub, so subs grow with the
+// batch; the write pass wants a few waves of its 148 x 128 lanes, and chains short enough that the last wave is short.
+inline void choose_x_params(int64_t total_bits, XParams &x) {
+#ifdef B2_X_FORCE_SHIFT                                // test builds: tiny subs, no run-in (exercises repair and fix)
+  x.sub_shift = B2_X_FORCE_SHIFT; x.unit_subs = 2; x.overlap = 0;
+  (void)total_bits;
+#else
+  int us = 11;                                         // unit bits = 2^us
+  while (us < 14 && (total_bits >> us) > (int64_t)148 * 128 * 4) ++us;
+  int ss = 11;
+  while (ss < us && (total_bits >> ss) > 150000) ++ss;
+  x.sub_shift = ss; x.unit_subs = 1 << (us - ss); x.overlap = 4096;
+#ifdef B200JPEG_TUNING
+  if (const char *ev = getenv("B200JPEG_XSUB")) { const int v = atoi(ev); if (v >= kXMinShift && v <= kXMaxShift) x.sub_shift = v; }
+  if (const char *ev = getenv("B200JPEG_XUNIT")) { const int v = atoi(ev); if (v >= 1 && v <= 64) x.unit_subs = v; }
+  if (const char *ev = getenv("B200JPEG_XOVERLAP")) { const int v = atoi(ev); if (v >= 0 && v <= 65536) x.overlap = v; }
+#endif
+#endif
+}
 
 // Which entropy decoder takes the batch.  The segment path runs one long dependent chain per
 // segment: its time is ~0.55 us per byte of the LONGEST segment (measured: 4.8 ms for 8.8 KB segments)
@@ -168,11 +193,17 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
   P.path = choose_path(descs, n, force_path);
   P.imgs.resize(n);
   P.tile_base.assign(n + 1, 0);
-  P.cta_base.assign(n + 1, 0);
   P.bwr.resize(n); P.bhr.resize(n);
   int64_t coef_base = 0;
   size_t raw_off = 0, rgb_off = 0;
-  int seg_base = 0, sub_base = 0;
+  int seg_base = 0;
+  memset(&P.x, 0, sizeof P.x);
+  P.x.nimg = n;
+  if (P.path == kPathSync) {
+    int64_t bits = 0;
+    for (int i = 0; i < n; ++i) bits += (int64_t)(descs[i].scan_length > 0 ? descs[i].scan_length : 0) * 8;
+    choose_x_params(bits, P.x);
+  }
   for (int i = 0; i < n; ++i) {
     const b200jpeg_image_desc &d = descs[i];
     ImageDev &im = P.imgs[i];
@@ -196,6 +227,13 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     im.mcuy = (d.mcuHeight + im.vs - 1) / im.vs;
     im.restart_interval = d.restartInterval;
     for (int c = 0; c < nc; ++c) {
+      const b200jpeg_component &cc = d.color_components[c];
+      if (cc.quantizationTableID < 0 || cc.quantizationTableID > 3 || cc.huffmanDCTTableID < 0 || cc.huffmanDCTTableID > 3 ||
+          cc.huffmanACTableID < 0 || cc.huffmanACTableID > 3)
+        return B200JPEG_E_TABLE_ID;                        // jpeg.cpp:156-160, 205-209
+      if (!d.quantization_tables[cc.quantizationTableID].set || !d.huffmanDCTTable[cc.huffmanDCTTableID].set ||
+          !d.huffmanACTable[cc.huffmanACTableID].set)
+        return B200JPEG_E_TABLE_MISSING;                   // jpeg.cpp:757-774
       im.tq[c] = (int8_t)d.color_components[c].quantizationTableID;
       im.td[c] = (int8_t)d.color_components[c].huffmanDCTTableID;
       im.ta[c] = (int8_t)d.color_components[c].huffmanACTableID;
@@ -203,10 +241,18 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     // table set, shared with earlier images when byte-identical
     TableSet ts; memset(&ts, 0, sizeof ts);
     for (int t = 0; t < 4; ++t) {
-      if (d.quantization_tables[t].set) for (int k = 0; k < 64; ++k) ts.q[t][k] = (uint8_t)d.quantization_tables[t].table[k];
+      if (d.quantization_tables[t].set) for (int k = 0; k < 64; ++k) {
+        const int32_t q = d.quantization_tables[t].table[k];
+        if (q < 0 || q > 65535) return B200JPEG_E_ARG;     // 8-bit in the reference (types.hpp:86-92), 16-bit at most (T.81 B.2.4.1)
+        ts.q[t][k] = (uint16_t)q;
+      }
       const b200jpeg_huffman_table *src[2] = {&d.huffmanDCTTable[t], &d.huffmanACTable[t]};
       HuffSpec *dst[2] = {&ts.dc[t], &ts.ac[t]};
       for (int k = 0; k < 2; ++k) if (src[k]->set) {
+        // descriptors may be hand-built (C ABI, b200jpeg.hpp) without b200jpeg_parse_header's checks: the device
+        // code indexes symbols[] by these counts (jpeg.cpp:170-181 bounds them the same way)
+        if (src[k]->offset[0] != 0 || src[k]->offset[16] > 176) return B200JPEG_E_DHT;
+        for (int l = 1; l <= 16; ++l) if (src[k]->offset[l] < src[k]->offset[l - 1]) return B200JPEG_E_DHT;
         memcpy(dst[k]->offset, src[k]->offset, 17); memcpy(dst[k]->symbols, src[k]->symbols, 176); dst[k]->set = 1;
       }
     }
@@ -216,11 +262,8 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     if (found < 0) { P.tsets.push_back(ts); found = (int)P.tsets.size() - 1; }
     im.tset = found;
     {
-      int nslots = 0; bool dcu[4] = {false, false, false, false}, acu[4] = {false, false, false, false};
-      for (int c = 0; c < nc; ++c) {
-        if (!dcu[im.td[c] & 3]) { dcu[im.td[c] & 3] = true; ++nslots; }
-        if (!acu[im.ta[c] & 3]) { acu[im.ta[c] & 3] = true; ++nslots; }
-      }
+      int nslots = 0;                                  // tables the set holds: what an entropy CTA keeps in shared memory
+      for (int t = 0; t < 4; ++t) nslots += (P.tsets[found].dc[t].set != 0) + (P.tsets[found].ac[t].set != 0);
       if (nslots > P.nslots_max) P.nslots_max = nslots;
     }
     im.raw_len = (uint32_t)d.scan_length;
@@ -232,10 +275,10 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     im.ntiles = (int)((d.scan_length + kUTile - 1) / kUTile);
     im.tile_base = P.tile_base[i]; P.tile_base[i + 1] = im.tile_base + im.ntiles;
     im.path = P.path;
-    im.nsub_max = P.path == kPathSync ? (int)(((int64_t)d.scan_length * 8 + kSubBits - 1) / kSubBits) : 0;
-    im.ncta = (im.nsub_max + kCT - 1) / kCT;
-    im.sub_base = sub_base; sub_base += im.ncta * kCT;
-    im.cta_base = P.cta_base[i]; P.cta_base[i + 1] = im.cta_base + im.ncta;
+    // slots reserved on the self-synchronising path: the unstuffed scan is at most as long as the stuffed one, and
+    // every segment ends with at most one partial sub / unit (bases are assigned below, in table-set order)
+    im.nsub_max = P.path == kPathSync ? (int)((((int64_t)d.scan_length * 8) >> P.x.sub_shift) + im.nseg + 1) : 0;
+    im.nunit_max = P.path == kPathSync ? im.nsub_max / P.x.unit_subs + im.nseg + 1 : 0;
     im.nblocks = (int32_t)(mcus * im.bpm);
     im.coef_base = coef_base; coef_base += (im.nblocks + 7) & ~7;   // multiple of 8: the chunk swizzle key is (block & 7)
     im.rgb_pitch = (uint32_t)align_up((size_t)3 * im.width, 16);
@@ -273,10 +316,30 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     u.magic_tpr = (((uint64_t)1 << 40) + (uint64_t)tpr - 1) / (uint64_t)tpr;
     u.coef_base0 = a.coef_base; u.coef_stride = cstride; u.rgb_off0 = a.rgb_off; u.rgb_stride = rstride;
   }
-  if (P.path == kPathSegment) {                       // units grouped by table set; every CTA sees one set
-    std::vector<int> order(n);
-    for (int i = 0; i < n; ++i) order[i] = i;
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return P.imgs[a].tset < P.imgs[b].tset; });
+  std::vector<int> order(n);                          // images by table set: every entropy CTA sees one set
+  for (int i = 0; i < n; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return P.imgs[a].tset < P.imgs[b].tset; });
+  if (P.path == kPathSync) {
+    // sub slots and unit slots batch-wide, image after image; where the table set changes the numbering skips to the
+    // next multiple of the CTA size (the skipped slots belong to the image before them and stay unused)
+    P.x_img.assign(order.begin(), order.end());
+    P.x_sub_base.assign(n + 1, 0); P.x_unit_base.assign(n + 1, 0);
+    int64_t sb = 0, ub = 0;
+    for (int oi = 0; oi < n; ++oi) {
+      ImageDev &im = P.imgs[order[oi]];
+      if (oi > 0 && im.tset != P.imgs[order[oi - 1]].tset) { sb = (int64_t)align_up((size_t)sb, kXT); ub = (int64_t)align_up((size_t)ub, kSegUnits); }
+      im.sub_base = (int32_t)sb; im.unit_base = (int32_t)ub;
+      P.x_sub_base[oi] = (int32_t)sb; P.x_unit_base[oi] = (int32_t)ub;
+      sb += im.nsub_max; ub += im.nunit_max;
+      if (sb > (int64_t)1 << 30 || ub > (int64_t)1 << 30) return B200JPEG_E_UNSUPPORTED;
+    }
+    sb = (int64_t)align_up((size_t)sb, kXT); ub = (int64_t)align_up((size_t)ub, kSegUnits);
+    P.x_sub_base[n] = (int32_t)sb; P.x_unit_base[n] = (int32_t)ub;
+    P.x.nsub_slots = (int32_t)sb; P.x.nunit_slots = (int32_t)ub;
+    P.x.ncta = (int32_t)(sb / kXT);
+    P.nunit_ctas = (int)(ub / kSegUnits);
+  }
+  if (P.path == kPathSegment) {                       // units grouped by table set
     int cur_set = -1;
     for (int oi = 0; oi < n; ++oi) {
       const ImageDev &im = P.imgs[order[oi]];
@@ -290,7 +353,7 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
     P.nunit_ctas = (int)(P.units.size() / kSegUnits);
   }
   P.raw_bytes = raw_off; P.rgb_bytes = rgb_off; P.nblocks = coef_base;
-  P.ntiles = P.tile_base[n]; P.nctas = P.cta_base[n]; P.nsubs = sub_base; P.nsegs = seg_base;
+  P.ntiles = P.tile_base[n]; P.nsegs = seg_base;
   return 0;
 }
 

@@ -13,11 +13,13 @@ struct Pipeline {
   BatchPlan plan;
   bool prepared = false, ran = false;
   // arenas
-  DevBuf d_raw, d_us, d_imgs, d_tsets, d_out, d_tile_base, d_cta_base, d_tile_cnt, d_tile_pre, d_seg;
+  DevBuf d_raw, d_us, d_imgs, d_tsets, d_out, d_tile_base, d_tile_cnt, d_tile_pre, d_seg;
   DevBuf d_sub_e, d_sub_used, d_sub_info, d_cta_tot, d_cta_pre, d_bnd[2], d_flags, d_coef, d_rgb, d_export;
+  DevBuf d_segsub, d_segunit, d_x_img, d_x_sub_base, d_x_unit_base, d_xunits;   // self-synchronising path
   DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
   DevBuf d_units, d_luts;
   int force_path = kForceAuto;
+  bool copies_only = false;             // b200jpeg_copy_floor: run() launches nothing
   // small results (per-image ImageOut, convergence flags) land in PINNED host memory, copied right behind
   // the kernels and BEFORE the bulk RGB copies: a pageable read-back would queue behind the other
   // pipeline's RGB traffic in the D2H engine and stall the host for milliseconds
@@ -35,9 +37,10 @@ struct Pipeline {
 #endif
 
   void destroy() {
-    DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_cta_base, &d_tile_cnt, &d_tile_pre,
+    DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_tile_cnt, &d_tile_pre,
                      &d_seg, &d_sub_e, &d_sub_used, &d_sub_info, &d_cta_tot, &d_cta_pre, &d_bnd[0], &d_bnd[1],
-                     &d_flags, &d_coef, &d_rgb, &d_export, &d_units, &d_luts};
+                     &d_flags, &d_coef, &d_rgb, &d_export, &d_units, &d_luts,
+                     &d_segsub, &d_segunit, &d_x_img, &d_x_sub_base, &d_x_unit_base, &d_xunits};
     for (DevBuf *b : all) b->destroy(be);
     for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
     be.host_release(h_out); be.host_release(h_flags);
@@ -76,17 +79,24 @@ struct Pipeline {
     ok &= d_tsets.reserve(be, sizeof(TableSet) * P.tsets.size());
     ok &= d_out.reserve(be, sizeof(ImageOut) * n);
     ok &= d_tile_base.reserve(be, 4 * (size_t)(n + 1));
-    ok &= d_cta_base.reserve(be, 4 * (size_t)(n + 1));
     ok &= d_tile_cnt.reserve(be, 4 * (size_t)P.ntiles);
     ok &= d_tile_pre.reserve(be, 8 * (size_t)P.ntiles);
     ok &= d_seg.reserve(be, 4 * (size_t)P.nsegs);
-    ok &= d_sub_e.reserve(be, sizeof(SubState) * (size_t)P.nsubs);
-    ok &= d_sub_used.reserve(be, sizeof(SubState) * (size_t)P.nsubs);
-    ok &= d_sub_info.reserve(be, sizeof(SubInfo) * (size_t)P.nsubs);
-    ok &= d_cta_tot.reserve(be, sizeof(SubInfo) * (size_t)P.nctas);
-    ok &= d_cta_pre.reserve(be, sizeof(SubInfo) * (size_t)P.nctas);
-    ok &= d_bnd[0].reserve(be, sizeof(SubState) * (size_t)P.nctas);
-    ok &= d_bnd[1].reserve(be, sizeof(SubState) * (size_t)P.nctas);
+    if (P.path == kPathSync) {
+      ok &= d_sub_e.reserve(be, sizeof(SubState) * (size_t)P.x.nsub_slots);
+      ok &= d_sub_used.reserve(be, sizeof(SubState) * (size_t)P.x.nsub_slots);
+      ok &= d_sub_info.reserve(be, sizeof(SubInfo) * (size_t)P.x.nsub_slots);
+      ok &= d_cta_tot.reserve(be, sizeof(SubInfo) * (size_t)P.x.ncta);
+      ok &= d_cta_pre.reserve(be, sizeof(SubInfo) * (size_t)P.x.ncta);
+      ok &= d_bnd[0].reserve(be, sizeof(SubState) * (size_t)P.x.ncta);
+      ok &= d_bnd[1].reserve(be, sizeof(SubState) * (size_t)P.x.ncta);
+      ok &= d_segsub.reserve(be, 4 * (size_t)P.nsegs);
+      ok &= d_segunit.reserve(be, 4 * (size_t)P.nsegs);
+      ok &= d_x_img.reserve(be, 4 * (size_t)n);
+      ok &= d_x_sub_base.reserve(be, 4 * (size_t)(n + 1));
+      ok &= d_x_unit_base.reserve(be, 4 * (size_t)(n + 1));
+      ok &= d_xunits.reserve(be, sizeof(XUnit) * (size_t)P.x.nunit_slots);
+    }
     ok &= d_flags.reserve(be, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
     ok &= d_coef.reserve(be, 128 * (size_t)P.nblocks);
     ok &= d_rgb.reserve(be, P.rgb_bytes);
@@ -114,9 +124,14 @@ struct Pipeline {
     be.h2d(d_imgs.p, P.imgs.data(), sizeof(ImageDev) * n);
     be.h2d(d_tsets.p, P.tsets.data(), sizeof(TableSet) * P.tsets.size());
     be.h2d(d_tile_base.p, P.tile_base.data(), 4 * (size_t)(n + 1));
-    be.h2d(d_cta_base.p, P.cta_base.data(), 4 * (size_t)(n + 1));
+    if (P.path == kPathSync) {
+      be.h2d(d_x_img.p, P.x_img.data(), 4 * (size_t)n);
+      be.h2d(d_x_sub_base.p, P.x_sub_base.data(), 4 * (size_t)(n + 1));
+      be.h2d(d_x_unit_base.p, P.x_unit_base.data(), 4 * (size_t)(n + 1));
+      h2d_bytes += (int64_t)(4 * (size_t)(3 * n + 2));
+    }
     if (!P.units.empty()) { be.h2d(d_units.p, P.units.data(), sizeof(uint2) * P.units.size()); h2d_bytes += (int64_t)(sizeof(uint2) * P.units.size()); }
-    h2d_bytes += (int64_t)(sizeof(ImageDev) * n + sizeof(TableSet) * P.tsets.size() + 8 * (size_t)(n + 1));
+    h2d_bytes += (int64_t)(sizeof(ImageDev) * n + sizeof(TableSet) * P.tsets.size() + 4 * (size_t)(n + 1));
     for (int f = 0; f < PF_COUNT; ++f) if (!P.grp_img[f].empty()) {
       be.h2d(d_grp_img[f].p, P.grp_img[f].data(), 4 * P.grp_img[f].size());
       be.h2d(d_grp_pre[f].p, P.grp_pre[f].data(), 4 * P.grp_pre[f].size());
@@ -190,27 +205,36 @@ struct Pipeline {
 
   void launch_fix(int k) {   // k-th repair launch: reads boundary states k-1, writes k
     const BatchPlan &P = plan;
-    const size_t smem = entropy_smem_bytes(P.nslots_max, false);
-    B2_LAUNCH((k_entropy_sync<false>), P.nctas, kCT, smem, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(),
-              P.n, d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
+    B2_LAUNCH((k_xsync<false>), P.x.ncta, kXT, xsync_smem_bytes(P.nslots_max), be.stream, P.x, d_imgs.as<ImageDev>(),
+              d_x_sub_base.as<int32_t>(), d_x_img.as<int32_t>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(),
+              d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(), d_segsub.as<uint32_t>(),
               d_sub_e.as<SubState>(), d_sub_used.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_tot.as<SubInfo>(),
-              d_bnd[(k + 1) & 1].as<SubState>(), d_bnd[k & 1].as<SubState>(), d_flags.as<uint32_t>() + k, P.nslots_max);
+              d_bnd[(k + 1) & 1].as<SubState>(), d_bnd[k & 1].as<SubState>(), d_flags.as<uint32_t>() + k);
     ++launches; ++sync_rounds;
   }
 
-  void launch_tail(int last_fix) {   // scan + write + pixel
+  void launch_seg(bool xunits) {   // the one writer of coefficient blocks: restart segments, or the units of the self-synchronising path
+    const BatchPlan &P = plan;
+    if (P.nunit_ctas <= 0) return;
+    B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream,
+              xunits ? (const uint2 *)nullptr : d_units.as<uint2>(), d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(),
+              d_luts.as<uint32_t>(), d_seg.as<uint32_t>(), d_us.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>(),
+              d_x_unit_base.as<int32_t>(), d_x_img.as<int32_t>(), P.n, d_xunits.as<XUnit>(), d_segunit.as<uint32_t>());
+    ++launches;
+  }
+
+  void launch_tail(int last_fix) {   // scan + units + write + pixel
     const BatchPlan &P = plan;
     (void)last_fix;
-    B2_LAUNCH(k_entropy_scan, (P.n + 7) / 8, 256, 0, be.stream, d_imgs.as<ImageDev>(), P.n, d_cta_tot.as<SubInfo>(),
-              d_cta_pre.as<SubInfo>());
+    B2_LAUNCH(k_xscan, 1, 32, 0, be.stream, P.x.ncta, d_cta_tot.as<SubInfo>(), d_cta_pre.as<SubInfo>());
     ++launches;
     mark(2);
-    const size_t smem_w = entropy_smem_bytes(P.nslots_max, true);
-    B2_LAUNCH(k_entropy_write, P.nctas, kCT, smem_w, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(), P.n,
-              d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
-              d_sub_e.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_pre.as<SubInfo>(), d_coef.as<int16_t>(),
-              P.nslots_max);
+    B2_LAUNCH(k_xunits, P.x.ncta, kXT, 0, be.stream, P.x, d_imgs.as<ImageDev>(), d_x_sub_base.as<int32_t>(),
+              d_x_img.as<int32_t>(), d_x_unit_base.as<int32_t>(), d_out.as<ImageOut>(), d_seg.as<uint32_t>(),
+              d_segsub.as<uint32_t>(), d_segunit.as<uint32_t>(), d_sub_e.as<SubState>(), d_sub_used.as<SubState>(),
+              d_sub_info.as<SubInfo>(), d_cta_pre.as<SubInfo>(), d_xunits.as<XUnit>());
     ++launches;
+    launch_seg(true);
     mark(3);
     launch_pixels();
   }
@@ -230,6 +254,11 @@ struct Pipeline {
     const BatchPlan &P = plan;
     launches = 0; sync_rounds = 0;
     results_enqueued = false;
+    if (copies_only) {                   // the copies of a batch without its kernels: flags read "converged"
+      be.fill(d_flags.p, 0, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
+      ran = true;
+      return be.ok() ? 0 : B200JPEG_E_CUDA;
+    }
     mark(0);
     // ImageOut: end_pos/err_pos = kNone, the rest 0
     be.fill(d_out.p, 0xff, sizeof(ImageOut) * P.n);
@@ -254,12 +283,7 @@ struct Pipeline {
     mark(1);
     if (P.path == kPathSegment) {
       mark(2);
-      if (P.nunit_ctas > 0) {
-        B2_LAUNCH(k_entropy_seg, P.nunit_ctas, kSegThreads, segdec_smem_bytes(), be.stream, d_units.as<uint2>(),
-                  d_imgs.as<ImageDev>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(), d_seg.as<uint32_t>(),
-                  d_us.as<uint8_t>(), d_out.as<ImageOut>(), d_coef.as<int16_t>());
-        ++launches;
-      }
+      launch_seg(false);
       mark(3);
       launch_pixels();
       mark(5);
@@ -267,12 +291,15 @@ struct Pipeline {
       ran = true;
       return be.ok() ? 0 : B200JPEG_E_CUDA;
     }
-    if (P.nctas > 0) {
-      const size_t smem = entropy_smem_bytes(P.nslots_max, false);
-      B2_LAUNCH((k_entropy_sync<true>), P.nctas, kCT, smem, be.stream, d_imgs.as<ImageDev>(), d_cta_base.as<int32_t>(),
-                P.n, d_tsets.as<TableSet>(), d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(),
+    if (P.x.ncta > 0) {
+      B2_LAUNCH(k_xplan, (P.n + 7) / 8, 256, 0, be.stream, P.x, d_imgs.as<ImageDev>(), d_out.as<ImageOut>(),
+                d_seg.as<uint32_t>(), d_segsub.as<uint32_t>(), d_segunit.as<uint32_t>());
+      ++launches;
+      B2_LAUNCH((k_xsync<true>), P.x.ncta, kXT, xsync_smem_bytes(P.nslots_max), be.stream, P.x, d_imgs.as<ImageDev>(),
+                d_x_sub_base.as<int32_t>(), d_x_img.as<int32_t>(), d_tsets.as<TableSet>(), d_luts.as<uint32_t>(),
+                d_out.as<ImageOut>(), d_us.as<uint8_t>(), d_seg.as<uint32_t>(), d_segsub.as<uint32_t>(),
                 d_sub_e.as<SubState>(), d_sub_used.as<SubState>(), d_sub_info.as<SubInfo>(), d_cta_tot.as<SubInfo>(),
-                (const SubState *)nullptr, d_bnd[1].as<SubState>(), d_flags.as<uint32_t>(), P.nslots_max);
+                (const SubState *)nullptr, d_bnd[1].as<SubState>(), d_flags.as<uint32_t>());
       ++launches;
       for (int k = 0; k < kFixLaunches; ++k) launch_fix(k);   // launch k reads d_bnd[(k+1)&1], writes d_bnd[k&1]
       launch_tail(kFixLaunches - 1);
@@ -293,9 +320,10 @@ struct Pipeline {
       be.sync();
       results_enqueued = false;
       if (!be.ok()) return B200JPEG_E_CUDA;
-      if (P.path != kPathSync || P.nctas == 0 || h_flags[k] == 0) break;
+      if (P.path != kPathSync || P.x.ncta == 0 || h_flags[k] == 0) break;
       if (k + 1 >= kFixLaunches + kMaxExtraFix) {
         B2_LAUNCH(k_raise_status, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n, (uint32_t)ST_NOT_CONVERGED);
+        launch_pixels();                 // the images are dead now (kStDead): their pixels leave as zeros
         enqueue_small_results();
         be.sync();
         results_enqueued = false;
@@ -367,6 +395,12 @@ struct Pipeline {
       const size_t bytes = (size_t)P.bwr[i] * P.bhr[i] * 3 * 64 * sizeof(int16_t);
       if (!d_export.reserve(be, bytes)) return B200JPEG_E_NOMEM;
       be.fill(d_export.p, 0, bytes);   // MCU[] is value-initialised, jpeg.cpp:407
+      if (h_out[i].status & kStDead) {  // blocks of this image were not all written this batch: zeros, never an earlier batch's
+        be.d2h(coef_out[i], d_export.p, bytes);
+        be.sync();
+        d2h_bytes += (int64_t)bytes;
+        continue;
+      }
       #ifdef B200JPEG_EMU
       const int egrid = 4;
 #else

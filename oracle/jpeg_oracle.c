@@ -67,6 +67,7 @@ typedef struct {
   int flags;
   int width, height, bw, bh, bwr, bhr, hs, vs, ncomp, ri, zero_based;
   comp_t comp[3];
+  int comp_id[3];             /* SOF component identifiers (only ORACLE_F_SPEC binds tables by them) */
   qtab_t q[4];
   htab_t dc[4], ac[4];
   /* BitStream state, file.hpp:122-165 */
@@ -90,13 +91,16 @@ static int read_sof(dec_t *D, int marker, const uint8_t *p, int len) {
   if (len < 6 + 3 * nc) return ORACLE_E_TRUNCATED;
   for (int i = 0; i < nc; i++) {
     const int id = p[6 + 3 * i];
+    D->comp_id[i] = id;
     if (id == 0) D->zero_based = 1;                          /* :91-94 */
-    if (!D->zero_based && id > 3) return ORACLE_E_COMPONENT_ID;
-    if (D->zero_based && id > 2) return ORACLE_E_COMPONENT_ID;
+    if (!spec && !D->zero_based && id > 3) return ORACLE_E_COMPONENT_ID;
+    if (!spec && D->zero_based && id > 2) return ORACLE_E_COMPONENT_ID;
     comp_t *c = &D->comp[i];
     c->h = p[7 + 3 * i] >> 4; c->v = p[7 + 3 * i] & 15; c->tq = p[8 + 3 * i]; /* :105-109 */
     if (nc == 1) { c->h = c->v = 1; D->hs = D->vs = 1; continue; } /* T.81 A.2.2: one block per MCU */
-    if (id == 1) {                                           /* :110-128 */
+    /* the reference takes "identifier 1" for the luma component (:110); T.81 B.2.2 lets identifiers be any
+     * byte, so under ORACLE_F_SPEC it is the FIRST component of the frame */
+    if (spec ? i == 0 : id == 1) {                           /* :110-128 */
       if ((c->h != 1 && c->h != 2) || (c->v != 1 && c->v != 2)) return ORACLE_E_SAMPLING;
       if (c->h == 2 && D->bw % 2 == 1) D->bwr += 1;
       if (c->v == 2 && D->bh % 2 == 1) D->bhr += 1;
@@ -133,6 +137,11 @@ static int read_dqt(dec_t *D, const uint8_t *p, int len) {   /* jpeg.cpp:197-231
     if (wide) {
       if (len < 128) return ORACLE_E_TRUNCATED;
       for (int i = 0; i < 64; i++) raw[i] = (unsigned char)((p[2 * i] << 8) + p[2 * i + 1]); /* :216 keeps the low byte */
+      if (D->flags & ORACLE_F_SPEC) {                         /* T.81 B.2.4.1, Pq = 1: the full 16-bit quantiser */
+        for (int i = 0; i < 64; i++) D->q[id].table[oracle_zigzag[i]] = (p[2 * i] << 8) + p[2 * i + 1];
+        D->q[id].set = 1; p += 128; len -= 128;
+        continue;
+      }
       p += 128; len -= 128;
     } else {
       if (len < 64) return ORACLE_E_TRUNCATED;
@@ -150,6 +159,9 @@ static int read_sos(dec_t *D, const uint8_t *p, int len) {   /* jpeg.cpp:233-287
   if (nc != D->ncomp || (nc != 3 && nc != 1)) return ORACLE_E_COMPONENTS; /* :236-240 */
   if (len < 1 + 2 * nc + 3) return ORACLE_E_SOS;
   for (int i = 0; i < nc; i++) {                              /* tables bound by position, :241-247 */
+    /* ORACLE_F_SPEC: by component selector (T.81 B.2.3); the selectors must name the frame's components in
+     * the frame's order, anything else is not a scan the interleaved decode loop (:415-435) can take */
+    if ((D->flags & ORACLE_F_SPEC) && p[1 + 2 * i] != D->comp_id[i]) return ORACLE_E_SOS;
     D->comp[i].td = p[2 + 2 * i] >> 4; D->comp[i].ta = p[2 + 2 * i] & 15;
   }
   const uint8_t *q = p + 1 + 2 * nc;

@@ -41,8 +41,11 @@ enum {
 /* ORACLE_F_SPEC: behave as ITU-T T.81 where the reference deviates or rejects (SURVEY.md
  * 8(f) rank 1): restart every RI JPEG-MCUs regardless of sampling (reference: jpeg.cpp:414,419
  * is wrong for 4:2:0 unless RI is whole MCU rows), 1-component grayscale accepted
- * (reference: jpeg.cpp:83-87 rejects), COM/unknown segments skipped.  Without the flag the
- * port reproduces the reference verbatim, quirks included. */
+ * (reference: jpeg.cpp:83-87 rejects), COM/unknown segments skipped, component identifiers may be any
+ * byte -- the first frame component is the (possibly subsampled) luma, and the scan's selectors must name
+ * the frame's components in order (reference: identifier 1 is luma, tables bound by position,
+ * jpeg.cpp:95-110, 241-247), a 16-bit DQT (Pq = 1) keeps its full values (reference: low byte,
+ * jpeg.cpp:216).  Without the flag the port reproduces the reference verbatim, quirks included. */
 enum { ORACLE_F_SPEC = 1 };
 
 typedef struct {

@@ -43,7 +43,7 @@ def build(force=False):
             os.path.getmtime(PORT_SO) < os.path.getmtime(os.path.join(_HERE, "jpeg_oracle.c"))):
         subprocess.check_call(["make", "-s", "-C", _HERE, "port"])
     if os.path.exists("/root/reference/jpeg.cpp") and (force or not os.path.exists(REF_BIN) or (
-            os.path.getmtime(REF_BIN) < os.path.getmtime(os.path.join(_HERE, "ref_wrapper.cpp")))):
+            os.path.getmtime(REF_BIN) < os.path.getmtime(os.path.join(_HERE, "ref_wrapper_post.h")))):
         subprocess.check_call(["make", "-s", "-C", _HERE, "ref"])
 
 

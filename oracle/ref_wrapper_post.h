@@ -1,46 +1,4 @@
-// oracle/ref_wrapper.cpp -- TEST INFRASTRUCTURE (parity oracle + CPU baseline), not product code.
-//
-// Compiles the UNTOUCHED reference translation unit (/root/reference/jpeg.cpp and its six
-// headers, included from where they lie) into a headless command-line tool, oracle/_ref/ref_decode.
-// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-// execute it.  Nothing under jpeg_decoder_b200/ links or calls it.
-//
-// Accommodations:
-//   * oracle/stubs/X11/Xlib.h stands in for libX11 (display.hpp:1); XOpenDisplay() returns NULL.
-//   * -U_FORTIFY_SOURCE: utils.hpp:18-23 sprintf()s 3 bytes into new unsigned char[2].
-//   * `#define class struct` so the private stages of `Image` (jpeg.cpp:19-789) can be driven
-//     one at a time and the MCU array dumped between decodeHuffman() (jpeg.cpp:405-446) and
-//     dequantize()/inverseDCT()/YCbCrToRGB() (jpeg.cpp:563-590, 735-753, 544-561).
-//   * No -march=native / -mfma / -ffast-math: FMA contraction changes ~3 ppm of samples.
-//
-// Modes
-//   ref_decode dump  <in.jpg> <out.coef> <out.rgb>
-//        out.coef = raw MCU[bwR*bhR] after decodeHuffman(): int32 [pos][3][64]   (types.hpp:32-50)
-//        out.rgb  = uint8 [H][W][3] gathered as display.hpp:19-34 does
-//        prints one JSON line with the geometry and per-stage milliseconds
-//   ref_decode full  <in.jpg> <out.rgb>
-//        runs the reference's own readJPEG() (jpeg.cpp:826-907) end to end, then gathers RGB
-//   ref_decode bench <reps> <file>...
-//        times ctor + readJPEG() (parse + unstuff + Huffman + dequant + IDCT + colour) per file;
-//        prints one JSON line {"images":..,"pixels":..,"seconds":..}
-#include <iostream>
-#include <fstream>
-#include <string>
-#include <cstring>
-#include <math.h>
-#include <map>
-#include <vector>
-#include <chrono>
-#include <thread>
-#include <stdio.h>
-#include <stdlib.h>
-#include <stdint.h>
-#include <sstream>
-#include "X11/Xlib.h"
-
-#define class struct
-#define main ref_main
-#include "jpeg.cpp"
+// oracle/ref_wrapper_post.h -- TEST INFRASTRUCTURE: second half of the wrapper TU (see ref_wrapper_pre.h).
 #undef main
 #undef class
 

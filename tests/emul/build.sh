@@ -5,7 +5,7 @@ cd "$(dirname "$0")/../.."
 mkdir -p tests/emul/_build
 FLAGS="-std=c++20 -O1 -g -pthread -fPIC -shared -Wall -Wno-unused-function -Wno-unknown-pragmas -ffp-contract=off"
 # stress variant: tiny subs and no run-in, so that nearly every sub needs the Jacobi repair path
-g++ $FLAGS -DB2_SUB_BITS=512 -DB2_OVERLAP_BITS=0 -o tests/emul/_build/libb200jpeg_emul_stress.so \
+g++ $FLAGS -DB2_X_FORCE_SHIFT=9 -o tests/emul/_build/libb200jpeg_emul_stress.so \
     tests/emul/emul_lib.cpp jpeg_decoder_b200/csrc/host_parse.cpp
 g++ -std=c++20 -O1 -g -pthread -fPIC -shared -Wall -Wno-unused-function -Wno-unknown-pragmas -ffp-contract=off \
     -o tests/emul/_build/libb200jpeg_emul.so tests/emul/emul_lib.cpp jpeg_decoder_b200/csrc/host_parse.cpp
