@@ -1,18 +1,22 @@
 #!/usr/bin/env python
 """bench.py -- decoded megapixels/s of the scan-to-pixels path (BASELINE.json metric).
 
-Workload (config.workload): BASELINE.json configs[1] -- a batch of 256 synthetic 1920x1080 YCbCr
-4:2:0 q90 baseline JPEGs with a restart interval of one MCU row, made by the bundled encoder.
-A "step" is one pass of the whole path (unstuff -> entropy decode -> fused pixel stage) over that
-batch.  `value`: inputs already resident in HBM.  `e2e`: the same through the C ABI with HOST
-buffers (pinned), H2D of the files and D2H of the RGB inside the timed region.
-Multi-GPU (torchrun, one process per GPU): every rank decodes its own batch (weak scaling), no
-collective on the data path; time = max over ranks.
+Workloads (--workload, BASELINE.json configs[1..4]; all made by the bundled deterministic encoder):
+  C2       256 x 1920x1080 4:2:0 q90, restart interval = 1 MCU row            (default; the metric's config)
+  C3       1 x 8192x8192 4:4:4 q95, no restart markers (self-synchronising decode of one long scan)
+  C4-gray  8 x 4096x4096 1-component  | C4-422  8 x 4096x4096 4:2:2 | C4-444  8 x 4096x4096 4:4:4   (--quality 50|90)
+  C5       16384 x 512x512 4:2:0 q85, no restart markers, sharded over the GPUs (strong scaling)
+A "step" is one pass of the whole path (unstuff -> entropy decode -> fused pixel stage) over the workload.
+`value`: inputs already resident in HBM.  `e2e`: the same through the C ABI with HOST buffers (pinned): header
+parse, H2D of the files and D2H of the RGB inside the timed region; `e2e.copy_floor_ms` = the same copies with
+no kernels.  Multi-GPU (torchrun, one process per GPU), no collective on the data path, time = max over ranks:
+C2 weak scaling (every rank its own batch), C5 strong scaling (the 16384 images are sharded), C3/C4 replicas.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--images 256]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload C2] [--images N] [--quality Q]
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import subprocess
@@ -27,36 +31,69 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-W, H, QUALITY = 1920, 1080, 90
 METRIC = "decoded megapixels/s (baseline 4:2:0 JPEG)"
 UNIT = "MP/s"
 
+# name -> images, geometry, encoder settings, first seed, scaling over GPUs
+WORKLOADS = {
+    "C2": dict(n=256, w=1920, h=1080, q=90, hs=2, vs=2, gray=False, restart=-1, seed0=1000, scaling="weak",
+               name="C2: %d x 1920x1080 4:2:0 q90 baseline JPEG, DRI = 1 MCU row (bundled encoder, synthetic)"),
+    "C3": dict(n=1, w=8192, h=8192, q=95, hs=1, vs=1, gray=False, restart=0, seed0=3001, scaling="replicas",
+               name="C3: %d x 8192x8192 4:4:4 q95 baseline JPEG, no restart markers (bundled encoder, synthetic)"),
+    "C4-gray": dict(n=8, w=4096, h=4096, q=90, hs=1, vs=1, gray=True, restart=0, seed0=4300, scaling="replicas",
+                    name="C4: %d x 4096x4096 grayscale q%d baseline JPEG, no restart markers (bundled encoder, synthetic)"),
+    "C4-422": dict(n=8, w=4096, h=4096, q=90, hs=2, vs=1, gray=False, restart=0, seed0=4100, scaling="replicas",
+                   name="C4: %d x 4096x4096 4:2:2 q%d baseline JPEG, no restart markers (bundled encoder, synthetic)"),
+    "C4-444": dict(n=8, w=4096, h=4096, q=90, hs=1, vs=1, gray=False, restart=0, seed0=4200, scaling="replicas",
+                   name="C4: %d x 4096x4096 4:4:4 q%d baseline JPEG, no restart markers (bundled encoder, synthetic)"),
+    "C5": dict(n=16384, w=512, h=512, q=85, hs=2, vs=2, gray=False, restart=0, seed0=5000, scaling="strong",
+               name="C5: %d x 512x512 4:2:0 q85 baseline JPEG, no restart markers (bundled encoder, synthetic)"),
+}
 
-def workload_name(n):
-    return "C2: %d x 1920x1080 4:2:0 q90 baseline JPEG, DRI = 1 MCU row (bundled encoder, synthetic)" % n
+
+def workload(args):
+    wl = dict(WORKLOADS[args.workload])
+    if args.images:
+        wl["n"] = args.images
+    if args.quality:
+        wl["q"] = args.quality
+    wl["label"] = wl["name"] % ((wl["n"], wl["q"]) if wl["name"].count("%d") == 2 else wl["n"])
+    wl["flags"] = 1 if wl["gray"] else 0          # the reference rejects 1-component files (jpeg.cpp:83-87): PARSE_SPEC
+    return wl
 
 
-def make_batch(n, seed0, pinned_alloc=None):
-    """n synthetic JPEGs packed back to back (256-byte aligned) in one buffer -> (arena, views)."""
+def make_files(wl, lo, hi):
+    """JPEGs [lo, hi) of the workload as a list of uint8 arrays (seed = seed0 + index)."""
     from jpeg_decoder_b200.harness import synth_jpeg, build_harness
     build_harness()
-    cap = W * H  # generous per-image bound (~0.29 B/px expected)
-    tmp = [np.empty(cap, np.uint8) for _ in range(n)]
+    cap = wl["w"] * wl["h"] * (3 if wl["q"] > 92 else 1) + 65536
+    tl = threading.local()
+
+    def one(i):
+        if not hasattr(tl, "buf"):
+            tl.buf = np.empty(cap, np.uint8)
+        n = synth_jpeg(wl["seed0"] + i, wl["w"], wl["h"], wl["q"], wl["hs"], wl["vs"], wl["gray"], wl["restart"], out=tl.buf)
+        return tl.buf[:n].copy()
+
     with ThreadPoolExecutor(max_workers=max(1, min(32, os.cpu_count() or 1))) as ex:
-        lens = list(ex.map(lambda i: synth_jpeg(seed0 + i, W, H, QUALITY, 2, 2, False, -1, out=tmp[i]), range(n)))
-    total = sum((l + 255) // 256 * 256 for l in lens) + 4096
-    if pinned_alloc is not None:
-        ptr = pinned_alloc(total)
+        return list(ex.map(one, range(lo, hi)))
+
+
+def pack(files, alloc=None):
+    """The files back to back (256-byte aligned) in one buffer (pinned when `alloc` is given) -> (arena, views)."""
+    total = sum((f.size + 255) // 256 * 256 for f in files) + 4096
+    if alloc is not None:
+        ptr = alloc(total)
         if not ptr:
             raise MemoryError("pinned allocation of %d bytes failed" % total)
         arena = np.ctypeslib.as_array((C.c_uint8 * total).from_address(ptr))
     else:
         arena = np.empty(total, np.uint8)
     views, off = [], 0
-    for i in range(n):
-        arena[off:off + lens[i]] = tmp[i][:lens[i]]
-        views.append(arena[off:off + lens[i]])
-        off += (lens[i] + 255) // 256 * 256
+    for f in files:
+        arena[off:off + f.size] = f
+        views.append(arena[off:off + f.size])
+        off += (f.size + 255) // 256 * 256
     return arena, views
 
 
@@ -116,36 +153,36 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(kernel, images):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json);
-    None when the capture was taken on another batch size or does not hold the kernel."""
+def ncu_capture(workload_key, images):
+    """Per-kernel figures of the committed `ncu --set full` capture of this workload (profiles/traffic.json):
+    DRAM bytes per launch, IPC, ALU pipe %, lanes per instruction.  {} when none was taken at this size."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        k = t["kernels"][kernel]
-        return k["read"] + k["write"] if t["images"] == images else None
+        w = t.get("workloads", {}).get(workload_key) or (t if workload_key == "C2" and "kernels" in t else None)
+        return w["kernels"] if w and w.get("images") == images else {}
     except (OSError, KeyError, ValueError):
-        return None
+        return {}
 
 
-# ------------------------------------------------------------------ CPU side (oracle as baseline)
-def cpu_reference_run(files, per_worker, workers):
+# ------------------------------------------------------------------ CPU side (the reference, timed on the host cores)
+def cpu_reference_run(files, per_worker, workers, flags=0):
     """Time the reference's own CPU path on `workers` processes, `per_worker` images each.
 
-    kind "reference": oracle/_ref/ref_decode = the UNTOUCHED jpeg.cpp compiled headless; the timed
-    region per image is ctor + readJPEG() (parse + unstuff + Huffman + dequant + IDCT + colour).
-    Falls back to the C restatement (kind "port", 1 thread) when the binary is absent.
-    Returns (MP/s, cores, kind, sample description)."""
+    kind "reference": oracle/_ref/ref_decode = the reference's jpeg.cpp compiled headless; the timed region per image
+    is ctor + readJPEG() (per-byte file read + parse + unstuff + Huffman + dequant + IDCT + colour).
+    kind "port": the C restatement (1 thread) -- for what the reference rejects (grey, jpeg.cpp:83-87) or when the binary
+    is absent.  Returns (MP/s, cores, kind, sample description)."""
     from oracle import oracle
     oracle.build()
-    with tempfile.TemporaryDirectory() as td:
-        paths = []
-        for i, v in enumerate(files):
-            p = os.path.join(td, "f%04d.jpg" % i)
-            with open(p, "wb") as f:
-                f.write(v.tobytes())
-            paths.append(p)
-        if oracle.have_ref():
+    if oracle.have_ref() and not flags:
+        with tempfile.TemporaryDirectory() as td:
+            paths = []
+            for i, v in enumerate(files):
+                p = os.path.join(td, "f%04d.jpg" % i)
+                with open(p, "wb") as f:
+                    f.write(v.tobytes())
+                paths.append(p)
             procs = []
             for w in range(workers):
                 mine = [paths[(w * per_worker + k) % len(paths)] for k in range(per_worker)]
@@ -155,34 +192,44 @@ def cpu_reference_run(files, per_worker, workers):
                 raise RuntimeError("reference bench worker failed")
             pixels = sum(o["pixels"] for o in outs)
             secs = max(o["seconds"] for o in outs)
-            return pixels / secs / 1e6, workers, "reference", "%d worker processes x %d images of the workload" % (workers, per_worker)
-        t0 = time.time()
-        pixels = 0
-        for k in range(per_worker):
-            rc, info, _, _ = oracle.port_decode(files[k % len(files)].tobytes(), want_coef=False)
-            assert rc == 0
-            pixels += info["width"] * info["height"]
-        return pixels / (time.time() - t0) / 1e6, 1, "port", "%d images of the workload, 1 thread" % per_worker
+            return pixels / secs / 1e6, workers, "reference", "%d worker process%s x %d image%s of the workload" % (
+                workers, "" if workers == 1 else "es", per_worker, "" if per_worker == 1 else "s")
+    t0 = time.time()
+    pixels = 0
+    for k in range(per_worker):
+        rc, info, _, _ = oracle.port_decode(files[k % len(files)].tobytes(), flags=flags, want_coef=False)
+        assert rc == 0
+        pixels += info["width"] * info["height"]
+    return pixels / (time.time() - t0) / 1e6, 1, "port", "%d image%s of the workload, 1 thread (C restatement: the reference rejects this format)" % (
+        per_worker, "" if per_worker == 1 else "s")
+
+
+def cpu_sample_shape(wl, ncpu):
+    """Workers x images of the bounded CPU sample: ~2 s of one core per worker, at most 16 GB of reference heap."""
+    mp = wl["w"] * wl["h"] / 1e6
+    per_worker = max(1, min(32, int(2.0 * 15.0 / mp)))            # ~15 MP/s per core
+    workers = max(1, min(ncpu, int(16e9 / (mp * 1e6 * 30))))      # ~30 B of heap per pixel (MCU[] + per-byte chunks)
+    return workers, per_worker
 
 
 def run_reference_arm(args, rank, world):
     if rank != 0:
         return
+    wl = workload(args)
     ncpu = os.cpu_count() or 1
-    workers = max(1, ncpu)
-    per_worker = 2
-    _, files = make_batch(min(args.images, max(8, min(64, workers))), 1000)
+    workers, per_worker = cpu_sample_shape(wl, ncpu)
+    files = make_files(wl, 0, min(wl["n"], workers * per_worker, 64))
     vals = []
     for s in range(args.warmup + args.steps):
-        v, cores, kind, sample = cpu_reference_run(files, per_worker, workers)
+        v, cores, kind, sample = cpu_reference_run(files, per_worker, workers, wl["flags"])
         if s >= args.warmup:
             vals.append(v)
     value = float(np.mean(vals))
-    pixels_step = workers * per_worker * W * H
+    pixels_step = (workers if kind == "reference" else 1) * per_worker * wl["w"] * wl["h"]
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": pixels_step / value / 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+int32", "data": "synthetic",
-            "config": {"workload": workload_name(args.images), "step": "bounded sample: " + sample},
+            "config": {"workload": wl["label"], "step": "bounded sample: " + sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample + " per step"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -190,6 +237,27 @@ def run_reference_arm(args, rank, world):
 
 
 # ------------------------------------------------------------------ GPU arm
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def rank_parity_check(dec, abi):
+    """Every rank decodes golden synthetic streams on ITS device through both entropy decoders and compares the
+    coefficients and the pixels with the digests the reference binary produced (tests/golden/golden.json)."""
+    from jpeg_decoder_b200.harness import synth_jpeg
+    with open(os.path.join(ROOT, "tests", "golden", "golden.json")) as f:
+        g = json.load(f)["synthetic"]
+    names = ["s420_rstrow_200x120", "s444_norst_123x77", "s422_rst7_200x120", "s420_512_q85"]
+    datas = [synth_jpeg(**g[n]["args"]) for n in names]
+    for mode in (abi.ENTROPY_SYNC, abi.ENTROPY_SEGMENT):
+        dec.set_entropy_path(mode)
+        st, rgbs, coefs = dec.decode(datas, want_coef=True)
+        for n, s, r, c in zip(names, st, rgbs, coefs):
+            if s != 0 or sha(c.astype(np.int32)) != g[n]["coef_sha256"] or sha(r) != g[n]["rgb_sha256"]:
+                return False
+    return True
+
+
 def run_gpu_arm(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -203,14 +271,27 @@ def run_gpu_arm(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = jd.load()
     dec = jd.Decoder(local_rank)
+    wl = workload(args)
+    ok = rank_parity_check(dec, abi)
+    okt = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+    if world > 1:
+        dist.all_reduce(okt)
+    parity_ranks = int(okt.item())
+    assert parity_ranks == world, "parity check failed on %d of %d ranks" % (world - parity_ranks, world)
     dec.set_entropy_path({"auto": abi.ENTROPY_AUTO, "segment": abi.ENTROPY_SEGMENT, "sync": abi.ENTROPY_SYNC}[args.entropy])
-    n = args.images
-    seed0, _ = sharding.weak_shard(n, rank)
-    arena, files = make_batch(n, seed0, pinned_alloc=lib.b200jpeg_host_alloc)   # pinned host files
-    descs = (abi.ImageDesc * n)()
-    for i, b in enumerate(files):
-        rc = lib.b200jpeg_parse_header(b.ctypes.data, b.size, 0, C.byref(descs[i]))
-        assert rc == 0, rc
+
+    # this rank's images: weak = its own batch, strong = its shard of the one batch, replicas = the same batch
+    if wl["scaling"] == "weak":
+        lo, hi = rank * wl["n"], (rank + 1) * wl["n"]
+    elif wl["scaling"] == "strong":
+        lo, hi = sharding.shard_range(wl["n"], rank, world)
+    else:
+        lo, hi = 0, wl["n"]
+    n = hi - lo
+    arena, files = pack(make_files(wl, lo, hi), alloc=lib.b200jpeg_host_alloc)   # pinned host files
+    W, H = wl["w"], wl["h"]
+    descs, rcs = jd.parse_headers(files, wl["flags"])
+    assert not any(rcs), rcs[:8]
     pixels = n * W * H
     rgb_bytes = 3 * W * H
     rgb_ptr = lib.b200jpeg_host_alloc(n * rgb_bytes)                                          # pinned host RGB
@@ -225,6 +306,12 @@ def run_gpu_arm(args, rank, world, local_rank):
 
     def max_over_ranks(x):
         return sharding.max_over_ranks(x, device="cuda")
+
+    def sum_over_ranks(x):
+        t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t)
+        return float(t.item())
 
     # ---- device-resident: value ----
     dec.set_timing(True)
@@ -248,20 +335,33 @@ def run_gpu_arm(args, rank, world, local_rank):
     launches = stats["kernel_launches"] * args.steps
     ev_total_ms = stage["total"] / args.steps
 
-    # ---- end to end through the C ABI with host buffers: e2e ----
+    # ---- end to end through the C ABI with host buffers: e2e.  Inside the timed region, every step: header parse of
+    #      every file (host threads), H2D of every scan + descriptors, all kernels, D2H of every RGB image + status ----
+    def e2e_step():
+        d, r = jd.parse_headers(files, wl["flags"], descs=descs)
+        return dec.decode_batch(d, files, rgbs)
     for _ in range(min(2, args.warmup)):
-        dec.decode_batch(descs, files, rgbs)
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        # the reference-facing call: H2D of every scan + descriptors, all kernels, D2H of every RGB image +
-        # status, chunked and double-buffered inside the library
-        st = dec.decode_batch(descs, files, rgbs)
+        st = e2e_step()
     barrier()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
     stats_e = dec.stats()
     assert all(s == 0 for s in st)
+    # the same copies, same chunks, same buffers, no kernels: the PCIe floor under the call at this N
+    floors = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        dec.copy_floor(descs, files, rgbs)
+        barrier()
+        floors.append(max_over_ranks(time.perf_counter() - t0))
+    floor_ms = float(np.median(floors)) * 1e3
 
+    total_pixels = sum_over_ranks(pixels)
+    h2d = sum_over_ranks(stats_e["h2d_bytes"]); d2h = sum_over_ranks(stats_e["d2h_bytes"])
     if rank == 0:
         peak, peak_src = measured_peaks()
         blocks = stats["coded_blocks"]
@@ -270,44 +370,62 @@ def run_gpu_arm(args, rank, world, local_rank):
         a_e2e = stats["scan_bytes"] + 3 * pixels
         ms = {k: v / args.steps for k, v in stage.items()}
         seg = stats["entropy_path"] == 1
-        ent_name = "k_entropy_seg" if seg else "k_entropy_write"
+        pix_name = "k_pixel<%d,%d,%d>" % ((1, 1, 1) if wl["gray"] else (wl["hs"], wl["vs"], 3))
+        cap = ncu_capture(args.workload, n)
+
+        def kern(name, t_ms, alg):
+            k = {"name": name, "ms": t_ms, "alg_bytes": alg, "gbs": alg / t_ms / 1e6 if t_ms > 0 else None,
+                 "frac": alg / t_ms / 1e6 / peak if t_ms > 0 else None}
+            c = cap.get(name.split("+")[-1])
+            if c:
+                k["traffic"] = c.get("read", 0) + c.get("write", 0)
+                k["issue"] = {kk: c[kk] for kk in ("ipc", "alu_pipe_pct", "lanes_per_inst", "issue_active_pct") if kk in c}
+            return k
         kernels = {
-            "pixel": {"name": "k_pixel<2,2,3>", "ms": ms["pixel"], "alg_bytes": a_pix, "gbs": a_pix / ms["pixel"] / 1e6,
-                      "frac": a_pix / ms["pixel"] / 1e6 / peak},
-            "entropy_decode": {"name": ent_name, "ms": ms["write"], "alg_bytes": a_ent, "gbs": a_ent / ms["write"] / 1e6,
-                               "frac": a_ent / ms["write"] / 1e6 / peak},
-            "unstuff": {"name": "k_unstuff_count+scan+scatter", "ms": ms["unstuff"], "alg_bytes": 3 * stats["scan_bytes"],
-                        "gbs": 3 * stats["scan_bytes"] / ms["unstuff"] / 1e6},
+            "pixel": kern(pix_name, ms["pixel"], a_pix),
+            "entropy_decode": kern("k_entropy_seg" if seg else "k_xunits+k_entropy_seg", ms["write"], a_ent),
+            "unstuff": kern("k_unstuff_count+scan+scatter", ms["unstuff"], 3 * stats["scan_bytes"]),
         }
         if not seg:
-            kernels["entropy_sync"] = {"name": "k_entropy_sync<1>+<0>x2+scan", "ms": ms["sync"], "alg_bytes": 3 * stats["scan_bytes"],
-                                       "gbs": 3 * stats["scan_bytes"] / ms["sync"] / 1e6}
-        dom = max(("pixel", "entropy_decode"), key=lambda k: kernels[k]["ms"])
-        roofline = {"kernel": kernels[dom]["name"], "bound": "hbm",
-                    "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s", "frac": kernels[dom]["frac"],
-                    "traffic": ncu_traffic(kernels[dom]["name"], n), "peak_source": peak_src,
-                    "note": "entropy decoding is latency/issue bound (one dependent chain per stream), see DESIGN.md; "
-                            "the HBM-bound kernel of the path is the pixel kernel",
+            kernels["entropy_sync"] = kern("k_xplan+k_xsync<0>x2+k_xscan+k_xsync<1>", ms["sync"], stats["scan_bytes"])
+        dom = max((k for k in kernels if k != "unstuff"), key=lambda k: kernels[k]["ms"])
+        d = kernels[dom]
+        entropy_dom = dom != "pixel"
+        roofline = {"kernel": d["name"], "bound": "hbm", "achieved": d["gbs"], "peak": peak, "unit": "GB/s", "frac": d["frac"],
+                    "traffic": d.get("traffic"), "peak_source": peak_src,
+                    "real_bound": "integer issue (one dependent chain per stream: position -> window -> table -> position)"
+                                  if entropy_dom else "hbm, then fp32 issue of the mandated operation order",
+                    "issue": dict(d.get("issue", {}), unit="warp instructions per cycle and SM", peak=4.0,
+                                  frac=(d["issue"]["ipc"] / 4.0 if d.get("issue", {}).get("ipc") else None)),
                     "pixel_kernel": {"achieved": kernels["pixel"]["gbs"], "frac": kernels["pixel"]["frac"]},
                     "whole_path": {"alg_bytes": a_e2e, "achieved": a_e2e / ev_total_ms / 1e6, "frac": a_e2e / ev_total_ms / 1e6 / peak}}
         ncpu = os.cpu_count() or 1
         cpu = None
         if world == 1:                              # the CPU baseline is a 1-GPU-run item (rank 0 at N=1 only)
-            v, cores, kind, sample = cpu_reference_run(files[:min(n, max(8, min(64, ncpu)))], 2, ncpu)
-            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
-        value = world * pixels * args.steps / t_res / 1e6
-        e2e = world * pixels * args.steps / t_e2e / 1e6
+            workers, per_worker = cpu_sample_shape(wl, ncpu)
+            sample_files = files[:min(n, workers * per_worker, 64)]
+            v, cores, kind, sample = cpu_reference_run(sample_files, per_worker, workers, wl["flags"])
+            v1, _, _, sample1 = cpu_reference_run(sample_files, per_worker, 1, wl["flags"])
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                   "one_core": {"value": v1, "unit": UNIT, "cores": 1, "sample": sample1}, "host_cores": ncpu}
+        value = total_pixels * args.steps / t_res / 1e6
+        e2e = total_pixels * args.steps / t_e2e / 1e6
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "strong" if wl["scaling"] == "strong" else "weak", "vs_baseline": None,
                 "dtype": "int32 entropy + f32 IDCT/colour", "data": "synthetic",
-                "config": {"workload": workload_name(n), "images_per_gpu": n, "parallelism": "images sharded, no collective",
+                "config": {"workload": wl["label"], "images_per_gpu": n,
+                           "parallelism": {"weak": "images sharded (every rank its own batch), no collective",
+                                           "strong": "the batch's images sharded over the ranks, no collective",
+                                           "replicas": "replicas only (a single scan is not split across GPUs)"}[wl["scaling"]],
                            "l2": "working set per step (scan %.0f MB, coefficients %.0f MB, RGB %.0f MB) exceeds the 126 MB L2"
                                  % (stats["scan_bytes"] / 1e6, 128 * blocks / 1e6, 3 * pixels / 1e6),
                            "timed": "K steps bracketed by barrier + stream sync; each step = all kernels + status readback"},
                 "event_ms_per_step": ev_total_ms, "kernels": kernels, "roofline": roofline, "cpu_baseline": cpu,
-                "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": stats_e["h2d_bytes"] * world,
-                        "d2h_bytes_per_step": stats_e["d2h_bytes"] * world, "ms_per_step": t_e2e / args.steps * 1e3},
-                "gpu_launches": launches, "sync_rounds": stats["sync_rounds"],
+                "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "ms_per_step": t_e2e / args.steps * 1e3, "copy_floor_ms": floor_ms,
+                        "timed": "header parse of every file + H2D + kernels + D2H per step"},
+                "gpu_launches": launches, "sync_rounds": stats["sync_rounds"], "parity_checked_ranks": parity_ranks,
                 "entropy_path": "segment-parallel" if seg else "self-synchronising", "clocks": clocks.summary()}
         emit(line)
     lib.b200jpeg_host_free(rgb_ptr)
@@ -341,7 +459,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--images", type=int, default=256, help="images per GPU per step")
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--images", type=int, default=0, help="images per step (C2: per GPU); 0 = the workload's own count")
+    ap.add_argument("--quality", type=int, default=0, help="encoder quality; 0 = the workload's own (C4: 50 or 90)")
     ap.add_argument("--entropy", default="auto", choices=["auto", "segment", "sync"],
                     help="entropy decoder (auto = the library's own choice; the others are for measurements)")
     args = ap.parse_args()

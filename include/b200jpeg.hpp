@@ -20,12 +20,14 @@
 // library cuts them into chunks that rotate over four internal pipelines).
 #ifndef B200JPEG_HPP
 #define B200JPEG_HPP
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "b200jpeg.h"
@@ -93,6 +95,63 @@ struct MCU {
   int *operator[](int index) { return index == 0 ? y : index == 1 ? cb : index == 2 ? cr : nullptr; }
 };
 
+// include/file.hpp:167-181.  Same enumerators, same values.
+enum MarkerType { SOI = 0xd8, APP = 0xe0, DQT = 0xdb, SOF = 0xc0, DHT = 0xc4, SOS = 0xda, EOI = 0xd9, DRI = 0xdd, DRM = 0xd0,
+                  META = -2, PAD = 0x00, INVALID = -1 };
+
+// include/file.hpp:183-280 over a file that is already in memory: the byte after an 0xFF is classified exactly as
+// Marker::Marker does (PAD, META for APPn, DRM for RSTn with length = n, SOS, the table/frame markers, INVALID for the
+// rest -- COM included, file.hpp:252-253), `length` counts its own two bytes, `data` is the payload.  Nothing is copied
+// and nothing leaks (the reference allocates per read, file.hpp:267); at SOS the scan is NOT consumed (the reference runs
+// readImageData() there, file.hpp:214-219): `scan` is where the entropy-coded bytes start, for the GPU to unstuff.
+class Marker {
+  int _data_pointer = 0;
+
+ public:
+  unsigned char marker = 0;
+  int length = 0;
+  const unsigned char *data = nullptr;
+  int type = MarkerType::INVALID;
+  size_t scan = 0;     // SOS only: offset of the first entropy-coded byte in the file
+  size_t next = 0;     // offset of the byte after this marker segment
+
+  // `pos`: offset of the marker byte (the one after 0xFF) in file[0, n)
+  Marker(const unsigned char *file, size_t n, size_t pos) {
+    if (pos >= n) throw Error(B200JPEG_E_TRUNCATED, "marker reader: end of file");
+    marker = file[pos];
+    next = pos + 1;
+    if (marker == 0x00) { type = MarkerType::PAD; return; }
+    if (marker >= 0xd0 && marker < 0xd8) { type = MarkerType::DRM; length = marker - 0xd0; return; }
+    // SOI / EOI stand alone (T.81 B.1.1.3); the reference would take the two bytes behind them for a length
+    // (file.hpp:255-256) but never meets SOI (the constructor consumes it, jpeg.cpp:797-807) and stops at EOI
+    if (marker == 0xd8) { type = MarkerType::SOI; return; }
+    if (marker == 0xd9) { type = MarkerType::EOI; return; }
+    if (pos + 3 > n) throw Error(B200JPEG_E_TRUNCATED, "marker reader: segment length past the end of the file");
+    length = (file[pos + 1] << 8) + file[pos + 2];
+    if (length < 2 || pos + 1 + (size_t)length > n) throw Error(B200JPEG_E_TRUNCATED, "marker reader: segment past the end of the file");
+    data = file + pos + 3;
+    next = pos + 1 + (size_t)length;
+    if (marker >= 224 && marker < 240) type = MarkerType::META;
+    else if (marker == 0xda) { type = MarkerType::SOS; scan = next; }
+    else switch (marker) {
+      case 0xdb: type = MarkerType::DQT; break;
+      case 0xc0: case 0xc2: type = MarkerType::SOF; break;
+      case 0xc4: type = MarkerType::DHT; break;
+      case 0xd9: type = MarkerType::EOI; break;
+      case 0xd8: type = MarkerType::SOI; break;
+      case 0xdd: type = MarkerType::DRI; break;
+      default: type = MarkerType::INVALID;
+    }
+  }
+  // file.hpp:260-274: the next n payload bytes (nullptr past the end, where the reference logs an error)
+  const unsigned char *read(int n = 1) {
+    if (_data_pointer + n > length - 2) return nullptr;
+    const unsigned char *res = data + _data_pointer;
+    _data_pointer += n;
+    return res;
+  }
+};
+
 // One GPU context per device, shared by the Images of a process (b200jpeg_create / _destroy).
 class Context {
   b200jpeg_ctx *ctx_ = nullptr;
@@ -106,8 +165,113 @@ class Context {
   Context(const Context &) = delete;
   Context &operator=(const Context &) = delete;
   b200jpeg_ctx *get() const { return ctx_; }
-  static Context &shared() { static Context c(0); return c; }
+  static Context &shared() { static Context c(0); return c; }   // device 0; other devices: Context(k), or decode_files(.., devices)
 };
+
+// Pinned host memory (b200jpeg_host_alloc): copies to and from it are asynchronous, which is what lets the library
+// overlap the files going in, the kernels and the pixels coming out.
+class PinnedBuffer {
+  uint8_t *p_ = nullptr;
+  size_t n_ = 0;
+
+ public:
+  PinnedBuffer() = default;
+  explicit PinnedBuffer(size_t n) : p_(static_cast<uint8_t *>(b200jpeg_host_alloc(n))), n_(n) {
+    if (!p_) throw Error(B200JPEG_E_NOMEM, "b200jpeg_host_alloc");
+  }
+  ~PinnedBuffer() { b200jpeg_host_free(p_); }
+  PinnedBuffer(const PinnedBuffer &) = delete;
+  PinnedBuffer &operator=(const PinnedBuffer &) = delete;
+  PinnedBuffer(PinnedBuffer &&o) noexcept : p_(o.p_), n_(o.n_) { o.p_ = nullptr; o.n_ = 0; }
+  PinnedBuffer &operator=(PinnedBuffer &&o) noexcept { if (this != &o) { b200jpeg_host_free(p_); p_ = o.p_; n_ = o.n_; o.p_ = nullptr; o.n_ = 0; } return *this; }
+  uint8_t *data() const { return p_; }
+  size_t size() const { return n_; }
+};
+
+// What the reference's main() does for one path (jpeg.cpp:916-929: Image ctor, readJPEG) for MANY files in one go, the
+// way the device wants to be fed: every file read straight into ONE pinned arena by a pool of
+// host threads (the reference reads byte by byte through an ifstream, file.hpp:26-52), every header parsed on host
+// threads (b200jpeg_parse_headers), every scan decoded by b200jpeg_decode_batch -- over several GPUs when `devices`
+// names more than one (contiguous image ranges, one context + host thread each) -- into ONE pinned RGB arena.
+class Batch {
+ public:
+  std::vector<std::string> paths;
+  std::vector<b200jpeg_image_desc> descs;
+  std::vector<int32_t> parse_rc, status;       // per file: header parse code (0 = ok), decode status bits (0 = decoded)
+  std::vector<size_t> file_off, file_len, rgb_off;
+  PinnedBuffer files, pixels;
+  int width(size_t i) const { return descs[i].image_width; }
+  int height(size_t i) const { return descs[i].image_height; }
+  bool ok(size_t i) const { return parse_rc[i] == 0 && status[i] == 0; }
+  const uint8_t *rgb(size_t i) const { return pixels.data() + rgb_off[i]; }   // interleaved R,G,B, pitch 3*width
+  void savePPM(size_t i, const std::string &filename) const {
+    std::ofstream o(filename, std::ios::binary);
+    o << "P6\n" << width(i) << " " << height(i) << "\n255\n";
+    o.write(reinterpret_cast<const char *>(rgb(i)), (std::streamsize)3 * width(i) * height(i));
+  }
+};
+
+inline Batch decode_files(const std::vector<std::string> &paths, const std::vector<int> &devices = std::vector<int>(1, 0),
+                          int parse_flags = B200JPEG_PARSE_REFERENCE, int host_threads = 0) {
+  Batch b;
+  b.paths = paths;
+  const size_t n = paths.size();
+  b.descs.resize(n); b.parse_rc.assign(n, 0); b.status.assign(n, 0);
+  b.file_off.assign(n, 0); b.file_len.assign(n, 0); b.rgb_off.assign(n, 0);
+  if (n == 0) return b;
+  if (host_threads <= 0) host_threads = (int)std::thread::hardware_concurrency();
+  if (host_threads < 1) host_threads = 1;
+  if ((size_t)host_threads > n) host_threads = (int)n;
+  auto parallel = [&](auto &&fn) {                     // fn(i) for every file, files handed out through one counter
+    std::atomic<size_t> next(0);
+    auto work = [&]() { for (size_t i; (i = next.fetch_add(1)) < n;) fn(i); };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < host_threads; ++t) pool.emplace_back(work);
+    work();
+    for (std::thread &t : pool) t.join();
+  };
+  parallel([&](size_t i) {                             // sizes first: the arena is allocated once
+    std::ifstream f(paths[i], std::ios::binary | std::ios::ate);
+    b.file_len[i] = f ? (size_t)f.tellg() : 0;
+  });
+  size_t total = 0;
+  for (size_t i = 0; i < n; ++i) { b.file_off[i] = total; total += (b.file_len[i] + 255) / 256 * 256; }
+  b.files = PinnedBuffer(total + 256);
+  parallel([&](size_t i) {
+    std::ifstream f(paths[i], std::ios::binary);
+    if (f && b.file_len[i]) f.read(reinterpret_cast<char *>(b.files.data() + b.file_off[i]), (std::streamsize)b.file_len[i]);
+    if (!f) b.file_len[i] = 0;
+  });
+  std::vector<const uint8_t *> fptr(n);
+  for (size_t i = 0; i < n; ++i) fptr[i] = b.files.data() + b.file_off[i];
+  b200jpeg_parse_headers(fptr.data(), b.file_len.data(), (int)n, parse_flags, host_threads, b.descs.data(), b.parse_rc.data());
+  // the images whose header parsed go to the device; the others keep their parse code
+  std::vector<size_t> live;
+  size_t rgb_total = 0;
+  for (size_t i = 0; i < n; ++i) if (b.parse_rc[i] == 0) {
+    live.push_back(i);
+    b.rgb_off[i] = rgb_total;
+    rgb_total += ((size_t)3 * b.descs[i].image_width * b.descs[i].image_height + 255) / 256 * 256;
+  }
+  b.pixels = PinnedBuffer(rgb_total + 256);
+  if (live.empty()) return b;
+  const size_t m = live.size();
+  std::vector<b200jpeg_image_desc> d(m);
+  std::vector<const uint8_t *> f(m);
+  std::vector<size_t> sz(m);
+  std::vector<uint8_t *> out(m);
+  std::vector<int32_t> st(m, 0);
+  for (size_t k = 0; k < m; ++k) {
+    const size_t i = live[k];
+    d[k] = b.descs[i]; f[k] = fptr[i]; sz[k] = b.file_len[i]; out[k] = b.pixels.data() + b.rgb_off[i];
+  }
+  const std::vector<int> devs = devices.empty() ? std::vector<int>(1, 0) : devices;
+  const int rc = b200jpeg_decode_batch_multi(devs.data(), (int)devs.size(), d.data(), (int)m, f.data(), sz.data(),
+                                             out.data(), st.data());
+  if (rc) throw Error(rc, "decode_files: b200jpeg_decode_batch_multi failed (no usable sm_100 GPU? there is no CPU fallback)");
+  for (size_t k = 0; k < m; ++k) b.status[live[k]] = st[k];
+  return b;
+}
 
 class Image {
   std::string filename_;
@@ -219,6 +383,54 @@ class Image {
     if (n == 0) return std::vector<int>();
     const int rc = b200jpeg_decode_batch(ctx.get(), descs.data(), n, files.data(), sizes.data(), out.data(), nullptr, st.data());
     if (rc) throw Error(rc, std::string("decode_batch: ") + b200jpeg_last_error(ctx.get()));
+    for (int i = 0; i < n; ++i) { images[(size_t)i]->status_ = st[(size_t)i]; images[(size_t)i]->decoded_ = st[(size_t)i] == 0; }
+    return std::vector<int>(st.begin(), st.end());
+  }
+
+  // The marker segments of the file up to and including SOS, as the reference's marker reader classifies them
+  // (Marker, include/file.hpp:183-258) -- the loop of readJPEG (jpeg.cpp:826-867) without the dispatch.
+  std::vector<Marker> markers() const {
+    std::vector<Marker> out;
+    size_t pos = 2;                                    // behind SOI, where readJPEG starts (jpeg.cpp:797-807, 826)
+    while (pos + 1 < file_.size()) {
+      if (file_[pos] != 0xff) break;                   // jpeg.cpp:899-903: "Invalid Marker"
+      Marker m(file_.data(), file_.size(), pos + 1);
+      out.push_back(m);
+      pos = m.next;
+      if (m.type == MarkerType::SOS || m.type == MarkerType::EOI || m.type == MarkerType::INVALID) break;
+    }
+    return out;
+  }
+
+  // Results decoded elsewhere (b200jpeg::decode_files) handed to an Image, for its sinks (saveToBMP, mcus, ...).
+  void adopt(const b200jpeg_image_desc &d, const uint8_t *rgb) {
+    desc_ = d;
+    image_width = d.image_width; image_height = d.image_height;
+    mcuWidthReal = d.mcuWidthReal; mcuHeightReal = d.mcuHeightReal;
+    restartInterval = d.restartInterval;
+    load_tables();
+    rgb_.assign(rgb, rgb + (size_t)3 * image_width * image_height);
+    parsed_ = decoded_ = true; status_ = 0;
+  }
+
+  // Many images over several GPUs: contiguous ranges of `images`, one context + host thread per device
+  // (b200jpeg_decode_batch_multi).  Same results as decode_batch(images).
+  static std::vector<int> decode_batch(const std::vector<Image *> &images, const std::vector<int> &devices) {
+    const int n = (int)images.size();
+    if (n == 0) return std::vector<int>();
+    std::vector<b200jpeg_image_desc> descs((size_t)n);
+    std::vector<const uint8_t *> files((size_t)n);
+    std::vector<size_t> sizes((size_t)n);
+    std::vector<uint8_t *> out((size_t)n);
+    std::vector<int32_t> st((size_t)n, 0);
+    for (int i = 0; i < n; ++i) {
+      Image &im = *images[(size_t)i];
+      if (!im.parsed_) im.readHeaders();
+      im.rgb_.assign((size_t)3 * im.image_width * im.image_height, 0);
+      descs[(size_t)i] = im.desc_; files[(size_t)i] = im.file_.data(); sizes[(size_t)i] = im.file_.size(); out[(size_t)i] = im.rgb_.data();
+    }
+    const int rc = b200jpeg_decode_batch_multi(devices.data(), (int)devices.size(), descs.data(), n, files.data(), sizes.data(), out.data(), st.data());
+    if (rc) throw Error(rc, "decode_batch: b200jpeg_decode_batch_multi failed (no usable sm_100 GPU? there is no CPU fallback)");
     for (int i = 0; i < n; ++i) { images[(size_t)i]->status_ = st[(size_t)i]; images[(size_t)i]->decoded_ = st[(size_t)i] == 0; }
     return std::vector<int>(st.begin(), st.end());
   }

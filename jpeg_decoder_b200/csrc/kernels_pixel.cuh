@@ -165,7 +165,7 @@ struct PixUni {
 // An image whose coefficient blocks were not ALL written this batch (stage U gave up on the scan, or the entropy stage
 // did not find the blocks the header promises) gets black pixels: the coefficient and RGB arenas are reused from batch
 // to batch, and nothing of an earlier batch -- possibly another caller's picture -- may come back for a corrupt upload.
-constexpr uint32_t kStDead = ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT | ST_BLOCK_COUNT | ST_NOT_CONVERGED;
+constexpr uint32_t kStDead = ST_BAD_MARKER | ST_NO_EOI | ST_BAD_RST_COUNT | ST_BLOCK_COUNT | ST_OVERRUN | ST_NOT_CONVERGED;
 B2_DEVICE uint32_t pix_dead(const ImageOut *__restrict__ out, int img) { return (out[img].status & kStDead) != 0; }
 B2_DEVICE int pix_qkey(const ImageDev &im) {
   return (im.tset << 6) | (im.tq[0] & 3) | ((im.tq[1] & 3) << 2) | ((im.tq[2] & 3) << 4);

@@ -15,6 +15,12 @@ PROBE = r"""
 int main(int argc, char **argv) {
   try {
     b200jpeg::Image img(argv[1]);
+    if (argc > 2 && std::string(argv[2]) == "markers") {
+      for (b200jpeg::Marker &m : img.markers()) {
+        std::cout << "M " << m.type << " " << (int)m.marker << " " << m.length << " " << (m.read(1) ? (int)m.read(0)[-1] : -1) << " " << m.scan << std::endl;
+      }
+      return 0;
+    }
     img.readHeaders();
     std::cout << img.image_width << " " << img.image_height << " " << img.mcuWidthReal << " " << img.mcuHeightReal << " "
               << img.restartInterval << " " << img.color_components[0].horizontal_sampling_factor
@@ -114,3 +120,50 @@ def test_cli_writes_the_oracles_pixels(cli, oracle_mod, tmp_path):
 def test_image_readjpeg_decodes(probe):
     rc, out, err = run([probe, os.path.join(GOLDEN_DIR, "img3.jpg"), "decode"])
     assert rc == 0 and "decoded" in out, err
+
+
+def test_marker_reader_classifies_like_the_reference(probe, harness, tmp_path):
+    # Marker / MarkerType (include/file.hpp:167-258): APPn -> META (-2), COM -> INVALID (-1), SOF0/SOF2 -> SOF (0xc0),
+    # `length` counts its own two bytes, the payload starts behind it; SOS reports where the scan starts
+    from tests import jpeg_craft as jc
+    for name in ["img.jpg", "img4.jpg"]:
+        path = os.path.join(GOLDEN_DIR, name)
+        data = open(path, "rb").read()
+        rc, out, err = run([probe, path, "markers"])
+        assert rc == 0, err
+        got = [[int(x) for x in l.split()[1:]] for l in out.splitlines() if l.startswith("M ")]
+        segs = jc.segments(data)
+        kinds = {0xdb: 0xdb, 0xc0: 0xc0, 0xc2: 0xc0, 0xc4: 0xc4, 0xda: 0xda, 0xdd: 0xdd, 0xd9: 0xd9}
+        assert len(got) == len(segs)
+        for g, (m, off, n) in zip(got, segs):
+            t = -2 if 0xe0 <= m < 0xf0 else kinds.get(m, -1)
+            assert g[0] == t and g[1] == m and g[2] == n + 2 and g[3] == data[off]
+            assert g[4] == (off + n if m == 0xda else 0)
+    com = tmp_path / "com.jpg"
+    good = harness.synth_jpeg(6, 64, 48, 80, 2, 2, False, 0)
+    com.write_bytes(good[:2] + b"\xff\xfe\x00\x04hi" + good[2:])
+    rc, out, err = run([probe, str(com), "markers"])
+    assert rc == 0 and [l.split()[1] for l in out.splitlines() if l.startswith("M ")][-1] == "-1"   # COM ends parsing, file.hpp:252-253
+
+
+@pytest.mark.gpu
+def test_cli_many_files_through_the_pinned_feed(cli, oracle_mod, harness, tmp_path):
+    # b200jpeg::decode_files: files read into one pinned arena by host threads, headers parsed on host threads, one
+    # b200jpeg_decode_batch_multi call; --gpus takes as many devices as the box has (1 here)
+    import torch
+    n = 40
+    datas = [harness.synth_jpeg(1500 + i, 320 + 16 * (i % 3), 200, 88, 2, 2, False, -1 if i % 2 else 0) for i in range(n)]
+    paths = []
+    for i, d in enumerate(datas):
+        p = tmp_path / ("f%03d.jpg" % i)
+        p.write_bytes(d)
+        paths.append(str(p))
+    (tmp_path / "broken.jpg").write_bytes(b"\xff\xd8\xff\xd9")
+    gpus = min(2, torch.cuda.device_count())
+    rc, out, err = run([cli] + paths + [str(tmp_path / "broken.jpg"), "--out-dir", str(tmp_path), "--gpus", str(gpus)])
+    assert rc == 1 and "broken.jpg: not decodable" in err and "%d of %d files decoded" % (n, n + 1) in out, (out, err)
+    for i in (0, 19, 20, 39):
+        _, _, _, orgb = oracle_mod.port_decode(datas[i])
+        raw = open(tmp_path / ("f%03d.ppm" % i), "rb").read()
+        head = b"P6\n%d %d\n255\n" % (orgb.shape[1], orgb.shape[0])
+        assert raw.startswith(head) and np.array_equal(np.frombuffer(raw[len(head):], np.uint8).reshape(orgb.shape), orgb), i

@@ -102,3 +102,39 @@ def test_repair_and_fix_paths_under_stress(emul, oracle_mod, harness):
              fixture_bytes("img2.jpg")]
     info = check(emul, oracle_mod, datas, stress=True)
     assert info["sync_rounds"] >= 2
+
+
+def test_zero_padded_restart_segments_decode_on_both_paths(emul, oracle_mod, harness):
+    # a non-conforming stream the reference decodes (it counts blocks and never looks at the padding, jpeg.cpp:419-425):
+    # both entropy decoders must take it, with the same status and the same result
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(61, 200, 120, 85, 1, 1, False, 3)
+    rc, _, c0, r0 = oracle_mod.port_decode(d)
+
+    def same(x):
+        rc, _, c, r = oracle_mod.port_decode(x)
+        return rc == 0 and np.array_equal(c, c0) and np.array_equal(r, r0)
+    z, cleared = jc.with_zero_padding(d, same)
+    assert cleared > 100
+    for path in (1, 2):
+        st, rgbs, coefs, _ = emul.decode([z, d], path=path)
+        assert st == [0, 0]
+        assert np.array_equal(coefs[0].astype(np.int32), c0) and np.array_equal(rgbs[0], r0)
+        assert np.array_equal(rgbs[1], r0)
+
+
+def test_spec_superset_component_ids_and_16bit_dqt(emul, oracle_mod, harness):
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(63, 120, 88, 85, 2, 2, False, 4)
+    ids = jc.with_component_ids(d, (7, 9, 200))
+    wide = jc.with_wide_dqt(d, lambda t, i, v: min(65535, v * 40) if i > 20 else v)
+    check(emul, oracle_mod, [ids, wide, d], flags=1)
+    check(emul, oracle_mod, [ids, wide, d], flags=1, path=1)
+    check(emul, oracle_mod, [jc.with_wide_dqt(harness.synth_jpeg(64, 96, 40, 80, 1, 1, False, 0))])   # REFERENCE mode: low byte
+
+
+def test_sub_sizes_of_the_self_synchronising_path(emul, oracle_mod, harness):
+    # several CTAs of subs, units of more than one sub, restart segments shorter and longer than a sub
+    datas = [harness.synth_jpeg(71, 512, 384, 92, 2, 2, False, 0), harness.synth_jpeg(72, 400, 300, 90, 2, 1, False, 11),
+             harness.synth_jpeg(73, 256, 256, 95, 1, 1, False, 1), fixture_bytes("img4.jpg")]
+    check(emul, oracle_mod, datas, flags=1)

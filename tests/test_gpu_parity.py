@@ -168,3 +168,83 @@ def test_decode_batch_is_chunked_and_matches_single_batch(dec, harness):
         assert np.array_equal(a, b)
     s = dec.stats()
     assert s["images"] == n and s["rgb_bytes"] == sum(w.size for w in want) and s["d2h_bytes"] == s["rgb_bytes"]
+
+
+def test_zero_padded_restart_segments(dec, oracle_mod, harness):
+    # a stream padded with 0-bits before RSTn is non-conforming, but the reference decodes it (block count +
+    # align(), jpeg.cpp:419-425; pinned in tests/test_oracle.py): both decoders must take it, status 0, same result
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(61, 200, 120, 85, 1, 1, False, 3)
+    rc, _, c0, r0 = oracle_mod.port_decode(d)
+
+    def same(x):
+        rc, _, c, r = oracle_mod.port_decode(x)
+        return rc == 0 and np.array_equal(c, c0) and np.array_equal(r, r0)
+    z, cleared = jc.with_zero_padding(d, same)
+    assert cleared > 100
+    st, rgbs, coefs = dec.decode([z, d], want_coef=True)
+    assert st == [0, 0]
+    assert np.array_equal(coefs[0].astype(np.int32), c0) and np.array_equal(rgbs[0], r0) and np.array_equal(rgbs[1], r0)
+
+
+def test_spec_superset_component_ids_and_16bit_dqt(dec, oracle_mod, harness):
+    # SURVEY.md 8(f) rank 1, "port only" (the reference rejects / truncates these): any component identifiers, 16-bit DQT
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(63, 120, 88, 85, 2, 2, False, 4)
+    ids = jc.with_component_ids(d, (7, 9, 200))
+    wide = jc.with_wide_dqt(d, lambda t, i, v: min(65535, v * 40) if i > 20 else v)
+    compare(dec, oracle_mod, [ids, wide, d], flags=1)
+    compare(dec, oracle_mod, [jc.with_wide_dqt(harness.synth_jpeg(64, 96, 40, 80, 1, 1, False, 0))])   # REFERENCE mode: low byte
+
+
+def test_no_pixels_of_an_earlier_batch_come_back(dec, harness):
+    # the device arenas are reused from batch to batch; an image the decoder gives up on must not
+    # return what an earlier batch -- possibly another caller's picture -- left in its slot
+    rng = np.random.default_rng(5)
+    noise = rng.integers(1, 256, size=(256, 256, 3), dtype=np.uint8)
+    first = [harness.encode_rgb(noise, 95, 2, 2, False, 0)] * 3
+    st, rgbs, _ = dec.decode(first)
+    assert st == [0, 0, 0] and rgbs[0].any()
+    good = harness.synth_jpeg(45, 256, 256, 90, 2, 2, False, 0)
+    body = good.find(b"\xff\xda") + 14
+    no_eoi = good[:-2] + b"\x00\x00"
+    cut = good[:body + 700] + b"\xff\xd9"                        # the header promises 1024 MCUs, the scan holds a few
+    bad_marker = bytearray(good); bad_marker[body + 300:body + 302] = b"\xff\xc4"
+    st, rgbs, coefs = dec.decode([no_eoi, cut, bytes(bad_marker)], want_coef=True)
+    assert all(s != 0 for s in st)
+    for r, c in zip(rgbs, coefs):
+        assert not r.any(), "pixels of the earlier batch came back"
+        assert not c.any(), "coefficients of the earlier batch came back"
+
+
+def test_multi_device_entry_point(lib_so, oracle_mod, harness):
+    # b200jpeg_multi_*: one context + one host thread per entry; on a one-GPU box the two entries are two contexts on
+    # device 0 (the threading and the range arithmetic are what is under test); with more devices, the first two
+    import ctypes as C
+    import torch
+    import jpeg_decoder_b200 as jd
+    from jpeg_decoder_b200 import abi
+    devs = [0, 1] if torch.cuda.device_count() >= 2 else [0, 0]
+    datas = [harness.synth_jpeg(800 + i, 160 + 16 * (i % 4), 96, 85, 2, 2, False, -1 if i % 2 else 0) for i in range(37)]
+    bufs = [np.frombuffer(d, dtype=np.uint8) for d in datas]
+    descs, rcs = jd.parse_headers(bufs)
+    assert not any(rcs)
+    rgbs = [np.zeros((descs[i].image_height, descs[i].image_width, 3), np.uint8) for i in range(len(datas))]
+    m = jd.MultiDecoder(devs)
+    st = m.decode_batch(descs, bufs, rgbs)
+    m.close()
+    assert st == [0] * len(datas)
+    for i in (0, 18, 19, 36):                                      # both sides of the range boundary
+        rc, _, _, orgb = oracle_mod.port_decode(datas[i])
+        assert rc == 0 and np.array_equal(rgbs[i], orgb), i
+    # the handle-free form
+    lib = jd.load()
+    n = len(datas)
+    files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+    sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+    again = [np.zeros_like(r) for r in rgbs]
+    prgb = (C.c_void_p * n)(*[r.ctypes.data for r in again])
+    st2 = (C.c_int32 * n)()
+    dv = (C.c_int * len(devs))(*devs)
+    assert lib.b200jpeg_decode_batch_multi(dv, len(devs), descs, n, files, sizes, prgb, st2) == 0
+    assert list(st2) == [0] * n and all(np.array_equal(a, b) for a, b in zip(again, rgbs))

@@ -101,3 +101,71 @@ def test_decoder_fails_loudly_without_gpu(lib):
     with pytest.raises(j.B200JpegError) as e:
         j.Decoder(0)
     assert e.value.code == abi.E_CUDA     # no CPU fallback exists
+
+
+def test_spec_parser_component_ids_and_wide_dqt(lib, harness):
+    """under B200JPEG_PARSE_SPEC component identifiers may be any byte (tables bound by the scan's
+    selectors, the frame's first component is luma) and a 16-bit DQT keeps its full values; REFERENCE mode keeps the
+    reference's rules (identifier <= 3, jpeg.cpp:95-104; low byte, jpeg.cpp:216)."""
+    import jpeg_decoder_b200 as j
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(61, 200, 120, 85, 2, 1, False, 0)
+    ids = jc.with_component_ids(d, (7, 9, 200))
+    with pytest.raises(j.B200JpegError) as e:
+        j.parse_header(ids)
+    assert e.value.code == abi.E_COMPONENT_ID
+    a, b = j.parse_header(d, abi.PARSE_SPEC), j.parse_header(ids, abi.PARSE_SPEC)
+    assert (b.horizontalSamplingFactor, b.verticalSamplingFactor) == (2, 1)
+    assert bytes(a)[:C.sizeof(abi.ImageDesc) - 16] == bytes(b)[:C.sizeof(abi.ImageDesc) - 16]   # same state at the seam
+    sos = [s for s in jc.segments(ids) if s[0] == 0xDA][0]
+    bad = bytearray(ids); bad[sos[1] + 3] = 8                                    # a selector the frame does not hold
+    with pytest.raises(j.B200JpegError) as e:
+        j.parse_header(bytes(bad), abi.PARSE_SPEC)
+    assert e.value.code == abi.E_SOS
+    w = jc.with_wide_dqt(d, lambda t, i, v: min(65535, v * 40) if i > 20 else v)
+    lo, hi = j.parse_header(w), j.parse_header(w, abi.PARSE_SPEC)
+    tq = lo.color_components[0].quantizationTableID
+    t_lo, t_hi = list(lo.quantization_tables[tq].table), list(hi.quantization_tables[tq].table)
+    assert max(t_hi) > 255 and t_lo == [v & 255 for v in t_hi]
+
+
+def test_parse_headers_batch_equals_single(lib, harness):
+    import jpeg_decoder_b200 as j
+    datas = [harness.synth_jpeg(900 + i, 64 + 8 * (i % 7), 48, 80, 2, 2, False, i % 3) for i in range(150)]
+    datas[17] = b"\x00\x01garbage"
+    datas[99] = fixture_bytes("prograssive-sample-2.jpg")
+    bufs = [np.frombuffer(d, dtype=np.uint8) for d in datas]
+    for threads in (0, 1, 5):
+        descs, rcs = j.parse_headers(bufs, threads=threads)
+        assert rcs[17] == abi.E_NOT_JPEG and rcs[99] == abi.E_PROGRESSIVE
+        for i, d in enumerate(datas):
+            if i in (17, 99):
+                continue
+            assert rcs[i] == 0 and bytes(descs[i]) == bytes(j.parse_header(d)), i
+
+
+def test_plan_rejects_malformed_hand_built_tables(lib, harness):
+    """Descriptors may be hand-built through the C ABI: a Huffman table whose cumulative counts are not monotone, or a
+    table id outside 0..3, must be refused before anything reaches the device (no GPU needed to see the refusal order:
+    without a device the call fails with E_CUDA at create, so this checks the planner through the emulation build)."""
+    from tests.emul import emul_harness
+    emul_harness.build()
+    L = emul_harness._load()
+    d = np.frombuffer(harness.synth_jpeg(62, 64, 48, 80, 2, 2, False, 0), dtype=np.uint8).copy()
+    for kind in ("offsets", "table_id", "quant"):
+        desc = (abi.ImageDesc * 1)()
+        assert L.b200jpeg_parse_header(d.ctypes.data, d.size, 0, C.byref(desc[0])) == 0
+        if kind == "offsets":
+            desc[0].huffmanACTable[0].offset[5] = 200
+        elif kind == "table_id":
+            desc[0].color_components[1].huffmanDCTTableID = 9
+        else:
+            desc[0].quantization_tables[0].table[3] = 70000
+        files = (C.c_void_p * 1)(d.ctypes.data)
+        sizes = (C.c_size_t * 1)(d.size)
+        rgb = np.zeros((48, 64, 3), np.uint8)
+        prgb = (C.c_void_p * 1)(rgb.ctypes.data)
+        st = (C.c_int32 * 1)()
+        info = (C.c_int32 * 3)()
+        rc = L.emu_decode_batch(desc, 1, files, sizes, prgb, None, st, info)
+        assert rc == {"offsets": abi.E_DHT, "table_id": abi.E_TABLE_ID, "quant": abi.E_ARG}[kind], (kind, rc)

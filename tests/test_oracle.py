@@ -88,3 +88,29 @@ def test_gray_equals_444_with_zero_chroma(oracle_mod, harness):
     assert rc1 == 0 and rc3 == 0
     assert np.array_equal(c1[:, 0], c3[:, 0])
     assert np.abs(r1.astype(int) - r3.astype(int)).max() <= 1
+
+
+def test_port_matches_live_reference_on_quirk_inputs(oracle_mod, harness):
+    """Two reference quirks no encoder exercises, pinned against the reference binary: a 16-bit DQT keeps only the low
+    byte of every entry (jpeg.cpp:216), and the padding bits before an RSTn marker are never looked at (segments end by
+    block count + align(), jpeg.cpp:419-425) -- 0-bits decode like 1-bits."""
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref/ref_decode not built (reference sources absent)")
+    from tests import jpeg_craft as jc
+    d = harness.synth_jpeg(61, 200, 120, 85, 1, 1, False, 3)
+    rc, _, c0, r0 = oracle_mod.port_decode(d)
+    assert rc == 0
+
+    def same(x):
+        rc, _, c, r = oracle_mod.port_decode(x)
+        return rc == 0 and np.array_equal(c, c0) and np.array_equal(r, r0)
+    z, cleared = jc.with_zero_padding(d, same)
+    assert cleared > 100
+    _, c, r = oracle_mod.ref_dump(z)
+    assert np.array_equal(c, c0) and np.array_equal(r, r0)
+    w = jc.with_wide_dqt(d, lambda t, i, v: min(65535, v * 40) if i > 20 else v)
+    _, c, r = oracle_mod.ref_dump(w)
+    rc, _, pc, pr = oracle_mod.port_decode(w)
+    assert rc == 0 and np.array_equal(c, pc) and np.array_equal(r, pr)
+    rc, _, sc, sr = oracle_mod.port_decode(w, flags=oracle_mod.F_SPEC)       # T.81: the whole 16-bit value
+    assert rc == 0 and np.array_equal(sc, pc) and not np.array_equal(sr, pr)

@@ -1,8 +1,10 @@
 // b200jpeg_cli -- the reference's main() (jpeg.cpp:916-929) over the B200 path:
-//   ./b200jpeg <image_path> [more images ...] [--out-dir DIR] [--bmp] [--spec]
-// Reads each JPEG, decodes it on GPU 0 and writes <name>.ppm (or .bmp) next to --out-dir instead
-// of opening an X11 window (display.hpp:49-120 has no headless equivalent).  Exit code 1 on a usage
-// error or an undecodable file, like the reference.
+//   ./b200jpeg <image_path> [more images ...] [--out-dir DIR] [--bmp] [--spec] [--gpus N] [--no-write]
+// Reads the JPEGs (all of them at once: one pinned arena, host threads), decodes them on N GPUs (contiguous ranges of
+// the files, one context and host thread per GPU) and writes <name>.ppm (or .bmp) into --out-dir instead of opening an
+// X11 window (display.hpp:49-120; unavailable on this box).  Exit code 1 on a usage error or an undecodable file, like
+// the reference.
+#include <chrono>
 #include <iostream>
 #include <string>
 #include <vector>
@@ -11,39 +13,48 @@
 
 int main(int argc, char **argv) {
   if (argc < 2) {
-    std::cerr << "Usage: " << argv[0] << " <image_path> [...] [--out-dir DIR] [--bmp] [--spec]" << std::endl;
+    std::cerr << "Usage: " << argv[0] << " <image_path> [...] [--out-dir DIR] [--bmp] [--spec] [--gpus N] [--no-write]" << std::endl;
     return 1;
   }
   std::string out_dir = ".";
-  bool bmp = false, spec = false;
+  bool bmp = false, spec = false, write = true;
+  int gpus = 1;
   std::vector<std::string> paths;
   for (int i = 1; i < argc; ++i) {
     const std::string a = argv[i];
     if (a == "--out-dir" && i + 1 < argc) out_dir = argv[++i];
+    else if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);
     else if (a == "--bmp") bmp = true;
     else if (a == "--spec") spec = true;
+    else if (a == "--no-write") write = false;
     else paths.push_back(a);
   }
+  if (gpus < 1 || paths.empty()) { std::cerr << "ERROR: nothing to do" << std::endl; return 1; }
   try {
-    std::vector<b200jpeg::Image> images;
-    images.reserve(paths.size());
-    for (const std::string &p : paths) {
-      images.emplace_back(p);
-      if (spec) images.back().parse_flags = B200JPEG_PARSE_SPEC;
-      images.back().readHeaders();
-    }
-    std::vector<b200jpeg::Image *> ptrs;
-    for (b200jpeg::Image &im : images) ptrs.push_back(&im);
-    const std::vector<int> st = b200jpeg::Image::decode_batch(ptrs);
+    std::vector<int> devices;
+    for (int k = 0; k < gpus; ++k) devices.push_back(k);
+    const auto t0 = std::chrono::steady_clock::now();
+    const b200jpeg::Batch b = b200jpeg::decode_files(paths, devices, spec ? B200JPEG_PARSE_SPEC : B200JPEG_PARSE_REFERENCE);
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     int bad = 0;
-    for (size_t i = 0; i < images.size(); ++i) {
+    double mp = 0;
+    for (size_t i = 0; i < paths.size(); ++i) {
       std::string base = paths[i].substr(paths[i].find_last_of('/') + 1);
       base = base.substr(0, base.find_last_of('.'));
-      if (st[i]) { std::cerr << paths[i] << ": corrupt scan, status bits " << st[i] << std::endl; ++bad; continue; }
+      if (b.parse_rc[i]) { std::cerr << paths[i] << ": not decodable, b200jpeg error " << b.parse_rc[i] << std::endl; ++bad; continue; }
+      if (b.status[i]) { std::cerr << paths[i] << ": corrupt scan, status bits " << b.status[i] << std::endl; ++bad; continue; }
+      mp += 1e-6 * b.width(i) * b.height(i);
+      if (!write) continue;
       const std::string out = out_dir + "/" + base + (bmp ? ".bmp" : ".ppm");
-      if (bmp) images[i].saveToBMP(out); else images[i].savePPM(out);
-      std::cout << paths[i] << ": " << images[i].image_width << "x" << images[i].image_height << " -> " << out << std::endl;
+      if (bmp) {                                     // through Image: jpeg.cpp:809-816 with the byte order put right
+        b200jpeg::Image im(b.files.data() + b.file_off[i], b.file_len[i]);
+        im.adopt(b.descs[i], b.rgb(i));
+        im.saveToBMP(out);
+      } else b.savePPM(i, out);
+      std::cout << paths[i] << ": " << b.width(i) << "x" << b.height(i) << " -> " << out << std::endl;
     }
+    std::cout << paths.size() - (size_t)bad << " of " << paths.size() << " files decoded on " << gpus << " GPU(s): " << mp << " MP in " << ms
+              << " ms (files read + headers + decode, host to host)" << std::endl;
     return bad ? 1 : 0;
   } catch (const b200jpeg::Error &e) {
     std::cerr << "ERROR: " << e.what() << std::endl;
