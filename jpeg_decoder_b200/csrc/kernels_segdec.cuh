@@ -169,9 +169,11 @@ B2_DEVICE SegLane seg_lane_x(int slot, const ImageDev *__restrict__ imgs, const 
   const XUnit u = xunits[slot];
   L.bidx = (int)u.bidx; L.bend = (int)u.bend;
   L.gb = im.coef_base + L.bidx;
+  L.live = L.bidx < L.bend;
+  if (!L.live) return L;     // a unit without a block start (a segment's short tail inside its last block): nothing to decode,
+                             // and the idle lane must step in place over row 0 of its table column -- the only row it writes
   L.p0 = u.p0; L.pend = u.pend; L.blk0 = (int)u.blk0;
   L.pred[0] = u.pred[0]; L.pred[1] = u.pred[1]; L.pred[2] = u.pred[2];
-  L.live = L.bidx < L.bend;
   return L;
 }
 

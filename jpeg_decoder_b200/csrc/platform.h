@@ -21,8 +21,22 @@ struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__
 #define B2_COLD __device__ __noinline__            /* rare paths stay out of the hot loops' instruction footprint */
 #define B2_GLOBAL __global__
 #define B2_SHARED __shared__
+#ifdef B200JPEG_TUNING   /* measurement / debugging builds only (scripts/build_variant.sh): B200JPEG_SYNC_EACH=1 waits after every
+                            launch and names the kernel a fault belongs to (compute-sanitizer is closed on this pool) */
+#include <stdio.h>
+#include <stdlib.h>
+#define B2_LAUNCH(kernel, grid, block, smem, stream, ...)                                                      \
+  do {                                                                                                         \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                                                \
+    if (getenv("B200JPEG_SYNC_EACH")) {                                                                        \
+      const cudaError_t e_ = cudaStreamSynchronize(stream);                                                    \
+      if (e_ != cudaSuccess) fprintf(stderr, "B2_LAUNCH %s grid %d: %s\n", #kernel, (int)(grid), cudaGetErrorString(e_)); \
+    }                                                                                                          \
+  } while (0)
+#else
 #define B2_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
 #define B2_DYN_SMEM(type, name) extern __shared__ __align__(128) unsigned char name##_raw_[]; \
   type *name = reinterpret_cast<type *>(name##_raw_)
 #define B2_CONSTANT __constant__

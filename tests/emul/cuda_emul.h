@@ -55,7 +55,7 @@ void launch(dim3 grid, dim3 block, size_t smem, F body) {
   const unsigned nt = block.x * block.y * block.z;
   if (grid.x == 0 || nt == 0) return;
   Cta c; cta() = &c;
-  c.dyn_smem.assign(smem + 128, 0);
+  c.dyn_smem.assign(smem + 128, 0xCD);   // poison: a read of shared memory nobody wrote must not look like a valid zero
   c.vote[0] = c.vote[1] = 0; c.count[0] = c.count[1] = 0;
   std::barrier<> outer(nt);
   auto setup = [&]() {
@@ -272,18 +272,29 @@ static inline unsigned char *b2_dsm_base() {
   return reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(emu::cta()->dyn_smem.data()) + 127) & ~uintptr_t(127));
 }
 static inline uint32_t b2_dsm_addr(const void *p) { return (uint32_t)(reinterpret_cast<const unsigned char *>(p) - b2_dsm_base()); }
-static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_base() + a, 4); return v; }
-static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_base() + a, &v, 4); }
+// every access through a window address is checked: inside the CTA's dynamic shared memory and naturally aligned (the GPU
+// faults with "misaligned address" / reads another CTA's memory where this emulation would silently go on)
+static inline unsigned char *b2_dsm_at(uint32_t a, uint32_t bytes, const char *what) {
+  const size_t cap = emu::cta()->dyn_smem.size() - 128;
+  if ((a & (bytes - 1)) != 0 || (size_t)a + bytes > cap) {
+    fprintf(stderr, "emulation: %s of %u bytes at shared window address %u (cta %u thread %u): %s\n", what, bytes, a,
+            blockIdx.x, emu::linear_tid(), (a & (bytes - 1)) ? "misaligned" : "outside the CTA's shared memory");
+    abort();
+  }
+  return b2_dsm_base() + a;
+}
+static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_at(a, 4, "ld.shared.u32"), 4); return v; }
+static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_at(a, 4, "st.shared.u32"), &v, 4); }
 static inline uint32_t b2_lds_ro(uint32_t a) { return b2_lds(a); }
-static inline void b2_sts_u16(uint32_t a, uint32_t v) { const uint16_t h = (uint16_t)v; memcpy(b2_dsm_base() + a, &h, 2); }
-static inline uint32_t b2_lds_u16(uint32_t a) { uint16_t h; memcpy(&h, b2_dsm_base() + a, 2); return h; }
-static inline void b2_sts_u8(uint32_t a, uint32_t v) { b2_dsm_base()[a] = (unsigned char)v; }
-static inline uint32_t b2_lds_u8(uint32_t a) { return b2_dsm_base()[a]; }
-static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_base() + a, 16); return v; }
-static inline void b2_sts_v4(uint32_t a, uint4 v) { memcpy(b2_dsm_base() + a, &v, 16); }
+static inline void b2_sts_u16(uint32_t a, uint32_t v) { const uint16_t h = (uint16_t)v; memcpy(b2_dsm_at(a, 2, "st.shared.u16"), &h, 2); }
+static inline uint32_t b2_lds_u16(uint32_t a) { uint16_t h; memcpy(&h, b2_dsm_at(a, 2, "ld.shared.u16"), 2); return h; }
+static inline void b2_sts_u8(uint32_t a, uint32_t v) { *b2_dsm_at(a, 1, "st.shared.u8") = (unsigned char)v; }
+static inline uint32_t b2_lds_u8(uint32_t a) { return *b2_dsm_at(a, 1, "ld.shared.u8"); }
+static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_at(a, 16, "ld.shared.v4"), 16); return v; }
+static inline void b2_sts_v4(uint32_t a, uint4 v) { memcpy(b2_dsm_at(a, 16, "st.shared.v4"), &v, 16); }
 static inline uint32_t b2_launder(uint32_t v) { return v; }
 // mbarriers by window address (arrival counts only): [63:32] completed phases, [31:16] arrivals a phase takes, [15:0] arrivals so far
-static inline uint64_t *b2_mbar_ptr(uint32_t a) { return reinterpret_cast<uint64_t *>(b2_dsm_base() + a); }
+static inline uint64_t *b2_mbar_ptr(uint32_t a) { return reinterpret_cast<uint64_t *>(b2_dsm_at(a, 8, "mbarrier")); }
 static inline void b2_mbar_init_a(uint32_t a, uint32_t count) { __atomic_store_n(b2_mbar_ptr(a), (uint64_t)count << 16, __ATOMIC_SEQ_CST); }
 static inline void b2_mbar_arrive_a(uint32_t a) {
   uint64_t *p = b2_mbar_ptr(a);
@@ -298,10 +309,13 @@ static inline void b2_mbar_wait_a(uint32_t a, uint32_t parity) {
 }
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
 static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
-static inline void b2_cp_async4x4_if(bool on, uint32_t dst_smem, const void *src) {
-  if (on) for (int i = 0; i < 4; ++i) memcpy(b2_dsm_base() + dst_smem + 128 * i, static_cast<const unsigned char *>(src) + 4 * i, 4);
+static inline void b2_cp_async_src_check(const void *src) {
+  if (reinterpret_cast<uintptr_t>(src) & 3u) { fprintf(stderr, "emulation: cp.async from a misaligned global address\n"); abort(); }
 }
-static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) memcpy(b2_dsm_base() + dst_smem, src, 4); }
+static inline void b2_cp_async4x4_if(bool on, uint32_t dst_smem, const void *src) {
+  if (on) { b2_cp_async_src_check(src); for (int i = 0; i < 4; ++i) memcpy(b2_dsm_at(dst_smem + 128 * i, 4, "cp.async"), static_cast<const unsigned char *>(src) + 4 * i, 4); }
+}
+static inline void b2_cp_async4_if(bool on, uint32_t dst_smem, const void *src) { if (on) { b2_cp_async_src_check(src); memcpy(b2_dsm_at(dst_smem, 4, "cp.async"), src, 4); } }
 static inline uint32_t b2_ld_acquire_smem(const uint32_t *p) {
   std::this_thread::yield();                    // callers spin on it: one OS thread per CUDA thread here
   return __atomic_load_n(p, __ATOMIC_ACQUIRE);
