@@ -58,8 +58,9 @@ enum {
   B200JPEG_E_TABLE_MISSING = -19, /* jpeg.cpp:757-774 */
   B200JPEG_E_TRUNCATED = -20,     /* header runs past the end of the buffer */
   B200JPEG_E_COMPONENT_ID = -21,  /* jpeg.cpp:95-104 */
-  B200JPEG_E_UNSUPPORTED = -22    /* accepted by the reference's parser but outside the kernels:
+  B200JPEG_E_UNSUPPORTED = -22,   /* accepted by the reference's parser but outside the kernels:
                                      the subsampled component is not the first one */
+  B200JPEG_E_TOO_LARGE = -23      /* b200jpeg_export_coefficients_noalloc: beyond B200JPEG_NOALLOC_MAX_BYTES */
 };
 
 /* ---- per-image status bits written by the kernels (status[i] == 0: decoded) ---- */
@@ -233,6 +234,19 @@ enum { B200JPEG_T_UNSTUFF = 0, B200JPEG_T_SYNC = 1, B200JPEG_T_WRITE = 2, B200JP
        B200JPEG_T_TOTAL = 4, B200JPEG_T_COUNT = 5 };
 int b200jpeg_set_timing(b200jpeg_ctx *ctx, int enabled);
 int b200jpeg_last_timing(b200jpeg_ctx *ctx, float *ms, int count);
+
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The coefficients of image i of the CURRENT batch (after b200jpeg_batch_run) in the layout b200jpeg_batch_fetch()
+ * gives for coef_out[i] -- int16 [mcuWidthReal*mcuHeightReal][3][64], natural order, the MCU array after
+ * decodeHuffman() -- but staged in a fixed array of B200JPEG_NOALLOC_MAX_BYTES that lives in the library's device
+ * image (every GPU that loads the library holds it until exit) instead of a buffer allocated on demand: the call
+ * performs NO allocation of any kind.  coef_out is a host buffer of coef_out_bytes >= positions * 384 bytes.
+ * An image whose array is larger is refused with B200JPEG_E_TOO_LARGE (text in b200jpeg_last_error).
+ * All calls on one GPU share the array: calls that overlap on the same GPU (other host threads, other contexts on
+ * that device) race -- serialise them.  Returns 0 or a B200JPEG_E_* code. */
+#define B200JPEG_NOALLOC_MAX_BYTES (16u << 20)   /* 43,690 block positions: e.g. 1920x1080 4:2:0 (12.5 MB) */
+int b200jpeg_export_coefficients_noalloc(b200jpeg_ctx *ctx, int i, int16_t *coef_out, size_t coef_out_bytes);
 
 /* Pinned host memory helpers (cudaHostAlloc / cudaFreeHost) for zero-staging copies. */
 void *b200jpeg_host_alloc(size_t bytes);

@@ -181,6 +181,13 @@ class Decoder:
         self._check(self.lib.b200jpeg_decode_batch(self.h, descs, n, files, sizes, prgb, None, st), "decode_batch")
         return list(st)
 
+    def export_coefficients_noalloc(self, i, out):
+        """b200jpeg_export_coefficients_noalloc: coefficients of image i of the current batch through the library's
+        static device scratch (no allocation).  `out`: int16 numpy array [positions, 3, 64]."""
+        rc = self.lib.b200jpeg_export_coefficients_noalloc(self.h, i, out.ctypes.data, out.nbytes)
+        self._check(rc, "export_coefficients_noalloc")
+        return out
+
     def copy_floor(self, descs, bufs, rgbs):
         """b200jpeg_copy_floor: the copies of decode_batch without its kernels; returns milliseconds."""
         n = len(bufs)

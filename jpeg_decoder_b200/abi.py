@@ -25,6 +25,8 @@ ST_UNSUPPORTED = 1 << 11
 E_ARG, E_CUDA, E_NOMEM, E_STATE = -1, -2, -3, -4
 E_NOT_JPEG, E_PROGRESSIVE, E_COMPONENTS, E_SAMPLING, E_TABLE_ID, E_DHT = -10, -11, -12, -13, -14, -15
 E_SOS, E_DRI, E_NO_SOS, E_TABLE_MISSING, E_TRUNCATED, E_COMPONENT_ID, E_UNSUPPORTED = -16, -17, -18, -19, -20, -21, -22
+E_TOO_LARGE = -23
+NOALLOC_MAX_BYTES = 16 << 20
 
 PARSE_REFERENCE, PARSE_SPEC = 0, 1
 ENTROPY_AUTO, ENTROPY_SEGMENT, ENTROPY_SYNC = 0, 1, 2
@@ -74,7 +76,7 @@ EXPORTS = [
     "b200jpeg_set_timing", "b200jpeg_last_timing", "b200jpeg_host_alloc", "b200jpeg_host_free",
     "b200jpeg_abi_version", "b200jpeg_set_entropy_path", "b200jpeg_parse_headers", "b200jpeg_copy_floor",
     "b200jpeg_multi_create", "b200jpeg_multi_destroy", "b200jpeg_multi_count", "b200jpeg_multi_ctx",
-    "b200jpeg_multi_decode_batch", "b200jpeg_decode_batch_multi",
+    "b200jpeg_multi_decode_batch", "b200jpeg_decode_batch_multi", "b200jpeg_export_coefficients_noalloc",
 ]
 
 
@@ -125,6 +127,8 @@ def bind(lib):
     lib.b200jpeg_host_free.argtypes = [C.c_void_p]
     lib.b200jpeg_abi_version.restype = C.c_int
     lib.b200jpeg_abi_version.argtypes = []
+    lib.b200jpeg_export_coefficients_noalloc.restype = C.c_int
+    lib.b200jpeg_export_coefficients_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
     lib.b200jpeg_copy_floor.restype = C.c_int
     lib.b200jpeg_copy_floor.argtypes = [C.c_void_p, P(ImageDesc), C.c_int, P(C.c_void_p), P(C.c_size_t), P(C.c_void_p),
                                         P(C.c_float)]

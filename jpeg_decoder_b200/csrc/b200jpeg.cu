@@ -341,3 +341,79 @@ void *b200jpeg_host_alloc(size_t bytes) {
 void b200jpeg_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------------
+// b200jpeg_export_coefficients_noalloc -- no counterpart in the reference; added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// A variant of ONE kernel that uses scratch memory: k_export_coef, which rebuilds the reference's MCU[] layout
+// (types.hpp:32-50) from the device's scan-order coefficient blocks.  b200jpeg_batch_fetch() stages that array in
+// Pipeline::d_export, a buffer it cudaMalloc()s on demand; here the staging area is the file-scope array below, which
+// every GPU that loads this library holds until the process exits (B200JPEG_NOALLOC_MAX_BYTES = 16 MiB: block
+// positions x 384 bytes, i.e. images up to 43,690 block positions -- 1920x1080 4:2:0 needs 12.5 MB).
+//
+// In host code `g_noalloc_scratch` is a host-side stand-in, NOT a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress(), asked once per device with that device current (noalloc_scratch_of).
+// The call allocates nothing: no cudaMalloc / cudaFree / cudaHostAlloc, no allocating library routine.  Every call on a
+// device shares the one array and the array keeps the last call's contents, so each call clears the bytes it is about
+// to use first (MCU[] is value-initialised, jpeg.cpp:407: positions the scan never writes must read zero).  Calls that
+// overlap on the same GPU -- two host threads, two contexts on one device -- RACE on it: serialise them.
+namespace {
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200JPEG_NOALLOC_MAX_BYTES];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_addr[kNoAllocMaxDevices];          // device address of the array on each device, once asked
+bool g_noalloc_known[kNoAllocMaxDevices];
+
+// set-up, once per device, with that device current
+void *noalloc_scratch_of(int device, std::string &err) {
+  if (device < 0 || device >= kNoAllocMaxDevices) { err = "device index out of range"; return nullptr; }
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_known[device]) {
+    void *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      err = std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e);
+      cudaGetLastError();
+      return nullptr;
+    }
+    g_noalloc_addr[device] = ptr;
+    g_noalloc_known[device] = true;
+  }
+  return g_noalloc_addr[device];
+}
+
+}  // namespace
+
+extern "C" int b200jpeg_export_coefficients_noalloc(b200jpeg_ctx *c, int i, int16_t *coef_out, size_t coef_out_bytes) {
+  if (!c || !coef_out) return B200JPEG_E_ARG;
+  b2::Pipeline &p = c->pipe;
+  if (!p.prepared || !p.ran) return B200JPEG_E_STATE;                 // needs a batch that b200jpeg_batch_run() has launched
+  if (i < 0 || i >= p.plan.n) return B200JPEG_E_ARG;
+  const size_t bytes = (size_t)p.plan.bwr[(size_t)i] * p.plan.bhr[(size_t)i] * 3 * 64 * sizeof(int16_t);
+  if (bytes > (size_t)B200JPEG_NOALLOC_MAX_BYTES) {
+    c->last_error = "b200jpeg_export_coefficients_noalloc: the image's MCU array (" + std::to_string(bytes) +
+                    " bytes) exceeds the static scratch of " + std::to_string((size_t)B200JPEG_NOALLOC_MAX_BYTES) +
+                    " bytes (B200JPEG_NOALLOC_MAX_BYTES); use b200jpeg_batch_fetch()";
+    return B200JPEG_E_TOO_LARGE;
+  }
+  if (coef_out_bytes < bytes) { c->last_error = "b200jpeg_export_coefficients_noalloc: output buffer too small"; return B200JPEG_E_ARG; }
+  DeviceGuard g(c->device);
+  void *scratch = noalloc_scratch_of(c->device, c->last_error);
+  if (!scratch) return B200JPEG_E_CUDA;
+  const int rc = p.finish();                                          // waits for the batch; reads status into pinned memory prepare() holds
+  if (rc) return fail(c, rc);
+  const b2::ImageDev &im = p.plan.imgs[(size_t)i];
+  p.be.fill(scratch, 0, bytes);                                       // the array keeps the last call's contents
+  if (!(p.h_out[i].status & b2::kStDead)) {                           // blocks not all written this batch: zeros, as batch_fetch
+    const int egrid = im.nblocks / 4 + 1 < 2368 ? im.nblocks / 4 + 1 : 2368;
+    B2_LAUNCH(b2::k_export_coef, egrid, 256, 0, p.be.stream, im, p.plan.bwr[(size_t)i], p.d_coef.as<int16_t>(),
+              static_cast<int16_t *>(scratch));
+  }
+  p.be.d2h(coef_out, scratch, bytes);
+  p.be.sync();
+  p.be.check("b200jpeg_export_coefficients_noalloc");
+  return fail(c, p.be.ok() ? 0 : B200JPEG_E_CUDA);
+}
