@@ -272,12 +272,12 @@ def run_gpu_arm(args, rank, world, local_rank):
     lib = jd.load()
     dec = jd.Decoder(local_rank)
     wl = workload(args)
-    ok = rank_parity_check(dec, abi)
+    ok = True if args.skip_parity else rank_parity_check(dec, abi)
     okt = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
     if world > 1:
         dist.all_reduce(okt)
-    parity_ranks = int(okt.item())
-    assert parity_ranks == world, "parity check failed on %d of %d ranks" % (world - parity_ranks, world)
+    parity_ranks = 0 if args.skip_parity else int(okt.item())
+    assert args.skip_parity or parity_ranks == world, "parity check failed on %d of %d ranks" % (world - parity_ranks, world)
     dec.set_entropy_path({"auto": abi.ENTROPY_AUTO, "segment": abi.ENTROPY_SEGMENT, "sync": abi.ENTROPY_SYNC}[args.entropy])
 
     # this rank's images: weak = its own batch, strong = its shard of the one batch, replicas = the same batch
@@ -462,6 +462,8 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--images", type=int, default=0, help="images per step (C2: per GPU); 0 = the workload's own count")
     ap.add_argument("--quality", type=int, default=0, help="encoder quality; 0 = the workload's own (C4: 50 or 90)")
+    ap.add_argument("--skip-parity", action="store_true",
+                    help="profiling runs only (ncu -c N should capture the workload's launches, not the parity decodes)")
     ap.add_argument("--entropy", default="auto", choices=["auto", "segment", "sync"],
                     help="entropy decoder (auto = the library's own choice; the others are for measurements)")
     args = ap.parse_args()

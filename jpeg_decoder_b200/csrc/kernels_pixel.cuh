@@ -10,22 +10,22 @@
 // double->float initialisers produce (types.hpp:5-19).  int16 coefficient x 8-bit quantiser
 // is < 2^24, so float(c)*float(q) is exact and equals the reference's int product converted.
 //
-// Mapping (v2, warp-autonomous and persistent): every WARP owns a private slice of shared memory
-// and walks the tile list with stride (warps in the grid).  A tile is kTM consecutive MCUs of one
-// MCU row = at most 32 consecutive coded blocks (30 for 4:2:0 / 4:4:4), i.e. one contiguous run of
-// the coefficient buffer.  Per tile:
-//   load   lane 0 starts a TMA 1-D bulk copy (cp.async.bulk -> mbarrier) of the tile's coefficients
-//          into one of two stage buffers -- issued one tile AHEAD, so HBM latency hides behind the
-//          previous tile's arithmetic and no register is spent on prefetching;
-//   idct   one lane per coded block, all 64 values in registers: de-zig-zag by register naming,
-//          dequantise, column pass, row pass.  The entropy stage stores each block's eight 16-byte
-//          chunks XOR-swizzled by (block & 7) so that the lanes' 128-bit reads of a dense copy are
-//          bank-conflict free.  Chroma lanes publish their block as an fp32 plane in shared memory
-//          (same XOR on its chunks); luma blocks never leave their registers;
-//   colour every luma lane converts its own 8x8 block: nearest-neighbour chroma from the planes
-//          (jpeg.cpp:518-520), the four chroma products once per chroma sample, colour sums,
-//          truncate + clamp, 24 bytes per row into the (now free) stage buffer as RGB staging;
-//   store  the staged rows leave as fully coalesced 128-bit streaming stores.
+// Mapping (warp-autonomous and persistent): every WARP owns a private slice of shared memory and walks the tile list with
+// stride (warps in the grid).  A tile is kTM consecutive MCUs of one MCU row = at most 32 consecutive coded blocks
+// (30 for 4:2:0 / 4:4:4), i.e. one contiguous run of the coefficient buffer.  Per tile:
+//   load   lane 0 starts a TMA 1-D bulk copy (cp.async.bulk -> mbarrier) of the tile's coefficients into one of two
+//          stage buffers -- issued one tile AHEAD, so HBM latency hides behind the previous tile's arithmetic and no
+//          register is spent on prefetching;
+//   idct   one lane per coded block, all 64 values in registers: de-zig-zag by register naming, dequantise, column
+//          pass, row pass.  The entropy stage stores each block's eight 16-byte chunks XOR-swizzled by (block & 7) so
+//          that the lanes' 128-bit reads of a dense copy are bank-conflict free.  Chroma lanes publish their block as
+//          an fp32 plane in shared memory (same XOR on its chunks);
+//   colour the 8 * kLuma luma rows of an MCU are shared out over ALL its lanes: a luma lane keeps rows [0, kKeep) and
+//          hands the rest to the MCU's two chroma lanes through shared memory (transposed [chunk][slot] layout,
+//          pix_spill_slot), so no lane idles; nearest-neighbour chroma from the planes (jpeg.cpp:518-520), the four
+//          chroma products once per chroma sample, colour sums, truncate + clamp + pack, RGB rows into the (now free)
+//          stage buffer;
+//   store  the staged tile leaves through ONE TMA tensor store (uniform batches) or one TMA bulk copy per row.
 // Only __syncwarp() separates the phases; there is no CTA-wide barrier in the kernel.
 // Algorithmic bytes per tile: 128 B per coded block in + 3 B per pixel out.
 #pragma once
@@ -69,12 +69,11 @@ B2_DEVICE float f32_bits(uint32_t u) {
 #ifndef B2_PIX_MAXCTAS
 #define B2_PIX_MAXCTAS 4
 #endif
-#ifndef B2_PIX_TMA_STORE
-#define B2_PIX_TMA_STORE 1
-#endif
-#ifndef B2_PIX_TRUNC
+// Truncation toward zero after each 1-D pass (the reference assigns float to int, jpeg.cpp:655-662): truncf = one FRND
+// on the quarter-rate XU pipe.  Measured alternatives (profiles/r02_experiments.md): truncation by FADD.RZ against 2^23
+// (no XU instruction, three on the FMA/ALU pipes) is 5 % SLOWER, int16 -> float through the mantissa of 1.5 * 2^23
+// instead of I2F is neutral -- the kernel is bound by issue slots, not by the XU pipe -- so neither is kept.
 #define B2_PIX_TRUNC(x) truncf(x)
-#endif
 
 // One AAN 1-D pass in place (jpeg.cpp:598-662 / 666-730), for TWO vectors at once (two columns, or two rows): the same
 // operations in the same order on both, the additions as packed pairs (FADD2: half the instructions), the
@@ -111,6 +110,16 @@ B2_DEVICE void idct8x2(float &x0, float &x1, float &x2, float &x3, float &x4, fl
       31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63
 B2_CONSTANT uint8_t c_zigzag[64] = {B2_ZZ_LIST};   // zig-zag position -> natural index (types.hpp:23-31)
 
+// Luma rows handed from the luma lanes to the chroma lanes ("spill"): 16-byte chunk c (row r - kKeep, left / right half)
+// of luma block `lb` of MCU m.  Transposed layout [chunk][slot], slots in the order the READERS walk them, so that both
+// the 128-bit stores of the luma lanes and the 128-bit loads of the chroma lanes touch consecutive 16-byte words
+// (measured before, with [block][row] at 64 / 128-byte lane strides: 10 wavefronts per instruction where 2-3 suffice).
+template <int HS, int VS, int TM>
+B2_DEVICE int pix_spill_slot(int m, int lb) {
+  if (HS * VS == 4) return (lb & 1) * (TM * 2) + m * 2 + (lb >> 1);   // a chroma lane reads block 2*cidx + (i >> 1): (m, cidx) consecutive
+  return m * (HS * VS) + lb;                                          // 4:2:2 / 4:4:0: block cidx; 4:4:4: block 0
+}
+
 template <int HS, int VS, int NC>
 struct PixCfg {
   static constexpr int kLuma = NC == 1 ? 1 : HS * VS;
@@ -134,10 +143,6 @@ struct PixCfg {
   // resident CTAs per SM the register budget must allow (shared memory allows this many)
   static constexpr int kMinCtas = (int)(232448 / (kSmemBytes + 1024)) > B2_PIX_MAXCTAS ? B2_PIX_MAXCTAS : (int)(232448 / (kSmemBytes + 1024));
 };
-
-B2_DEVICE uint32_t pack4(uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  return __byte_perm(__byte_perm(a, b, 0x0040), __byte_perm(c, d, 0x0040), 0x5410);
-}
 
 struct PixTile {
   int img, my, mx0, nm;
@@ -305,11 +310,12 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
                 v[i * 8 + 8], v[i * 8 + 9], v[i * 8 + 10], v[i * 8 + 11], v[i * 8 + 12], v[i * 8 + 13], v[i * 8 + 14],
                 v[i * 8 + 15]);
       if (NC == 3 && b < C::kLuma) {               // luma lanes hand rows [kKeep,8) to the chroma lanes
-        float4 *sp = reinterpret_cast<float4 *>(spill + (m * C::kLuma + b) * (8 - C::kKeep) * 32);
+        float4 *sp = reinterpret_cast<float4 *>(spill) + pix_spill_slot<HS, VS, C::kTM>(m, b);
+        constexpr int kSlots = C::kTM * C::kLuma;
 #pragma unroll
         for (int r = C::kKeep; r < 8; ++r) {
-          sp[(r - C::kKeep) * 2] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
-          sp[(r - C::kKeep) * 2 + 1] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
+          sp[((r - C::kKeep) * 2) * kSlots] = make_float4(v[r * 8 + 0], v[r * 8 + 1], v[r * 8 + 2], v[r * 8 + 3]);
+          sp[((r - C::kKeep) * 2 + 1) * kSlots] = make_float4(v[r * 8 + 4], v[r * 8 + 5], v[r * 8 + 6], v[r * 8 + 7]);
         }
       }
       if (NC == 3 && b >= C::kLuma) {              // chroma lanes publish their block: plane 2m (Cb), 2m+1 (Cr)
@@ -341,8 +347,9 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
           else if (HS * VS == 2) { lb = cidx; r = 4 + i; }
           else { lb = 0; r = 3 + 3 * cidx + i; }
           if (i < C::kTake && r < 8) {
-            const float4 *sp = reinterpret_cast<const float4 *>(spill + (((m * C::kLuma + lb) * (8 - C::kKeep)) + (r - C::kKeep)) * 32);
-            const float4 a = sp[0], c = sp[1];
+            const float4 *sp = reinterpret_cast<const float4 *>(spill) + pix_spill_slot<HS, VS, C::kTM>(m, lb);
+            constexpr int kSlots = C::kTM * C::kLuma;
+            const float4 a = sp[((r - C::kKeep) * 2) * kSlots], c = sp[((r - C::kKeep) * 2 + 1) * kSlots];
             v[i * 8 + 0] = a.x; v[i * 8 + 1] = a.y; v[i * 8 + 2] = a.z; v[i * 8 + 3] = a.w;
             v[i * 8 + 4] = c.x; v[i * 8 + 5] = c.y; v[i * 8 + 6] = c.z; v[i * 8 + 7] = c.w;
           }
@@ -436,7 +443,6 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
       int rowb = (cur.nm * 8 * HS * 3 + 15) & ~15;
       if (rowb > room) rowb = room;
       uint8_t *gbase = rgb + cur.rgb_off + (uint64_t)gy0 * pitch + (uint64_t)gx0 * 3;
-#if B2_PIX_TMA_STORE
       // one TMA bulk store per row, issued by the lane of that row number; the group is drained
       // (source read) before the stage buffer is handed back to the load pipeline
       b2_fence_proxy_async();
@@ -454,26 +460,6 @@ k_pixel(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ grp_img, 
         b2_bulk_commit();
         b2_bulk_wait_read();
       }
-#else
-      if (gx0 < width && rows > 0) {
-        if (rowb == C::kRowBytes) {
-          constexpr int cpr = C::kRowBytes / 16;
-          const int total = rows * cpr;
-          for (int idx = lane; idx < total; idx += 32) {
-            const int row = idx / cpr, ch = idx - row * cpr;
-            const uint4 w = *reinterpret_cast<const uint4 *>(st_cur + idx * 16);
-            b2_st_cs_v4(reinterpret_cast<uint4 *>(gbase + (uint64_t)row * pitch) + ch, w);
-          }
-        } else {
-          const int cpr = rowb >> 4;
-          for (int row = 0; row < rows; ++row)
-            for (int ch = lane; ch < cpr; ch += 32) {
-              const uint4 w = *reinterpret_cast<const uint4 *>(st_cur + row * C::kRowBytes + ch * 16);
-              b2_st_cs_v4(reinterpret_cast<uint4 *>(gbase + (uint64_t)row * pitch) + ch, w);
-            }
-        }
-      }
-#endif
     }
     __syncwarp();      // the stage buffer is the target of the copy started at the top of the next iteration
 

@@ -141,19 +141,21 @@ struct BatchPlan {
   std::vector<int32_t> x_img, x_sub_base, x_unit_base;   // image at each position; n+1 prefixes of the reserved slots
 };
 
-// Sub and unit sizes of the self-synchronising path, from the batch's scan bits.  The sync pass wants enough subs to
-// fill the device (one thread each, ~150 k in flight) but pays `overlap` extra bits per sub, so subs grow with the
-// batch; the write pass wants a few waves of its 148 x 128 lanes, and chains short enough that the last wave is short.
+// Sub and unit sizes of the self-synchronising path, from the batch's scan bits (measured: profiles/r02_xsweep.md).
+// Both passes are bound by instruction issue along one dependent chain per lane, so what matters is (a) how many bits a
+// lane walks -- sub + run-in for the sync pass, unit for the write pass: the shorter, the sooner the last wave ends -- and
+// (b) that there are enough lanes to fill the device once (148 SMs x 4 CTAs x 128 threads = 75,776 sync threads).  So:
+// sub = unit = the smallest power of two that keeps the batch within one wave of sync threads, between 2^9 (a single
+// small picture: latency is one chain) and 2^13 (beyond that the write pass's tail grows faster than the sync pass's
+// run-in overhead shrinks); run-in 2048 bits (4096 converges no better: the same one repair round, rarely two).
 inline void choose_x_params(int64_t total_bits, XParams &x) {
 #ifdef B2_X_FORCE_SHIFT                                // test builds: tiny subs, no run-in (exercises repair and fix)
   x.sub_shift = B2_X_FORCE_SHIFT; x.unit_subs = 2; x.overlap = 0;
   (void)total_bits;
 #else
-  int us = 11;                                         // unit bits = 2^us
-  while (us < 14 && (total_bits >> us) > (int64_t)148 * 128 * 4) ++us;
-  int ss = 11;
-  while (ss < us && (total_bits >> ss) > 150000) ++ss;
-  x.sub_shift = ss; x.unit_subs = 1 << (us - ss); x.overlap = 4096;
+  int ss = kXMinShift;
+  while (ss < 13 && (total_bits >> ss) > (int64_t)148 * 4 * kXT) ++ss;
+  x.sub_shift = ss; x.unit_subs = 1; x.overlap = 2048;
 #ifdef B200JPEG_TUNING
   if (const char *ev = getenv("B200JPEG_XSUB")) { const int v = atoi(ev); if (v >= kXMinShift && v <= kXMaxShift) x.sub_shift = v; }
   if (const char *ev = getenv("B200JPEG_XUNIT")) { const int v = atoi(ev); if (v >= 1 && v <= 64) x.unit_subs = v; }

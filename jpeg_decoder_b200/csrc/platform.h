@@ -43,13 +43,6 @@ struct B2TensorMap { CUtensorMap map; };                 // kernel parameter (__
 
 B2_DEVICE uint32_t b2_ld_nc_u32(const uint32_t *p) { return __ldg(p); }
 B2_DEVICE uint4 b2_ld_nc_v4(const uint4 *p) { return __ldg(p); }
-// float -> uint8 with truncation toward zero and saturation to [0,255] in one F2I
-B2_DEVICE uint32_t b2_f2u8_rz_sat(float x) {
-  uint32_t r;
-  asm("cvt.rzi.u8.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
-B2_DEVICE void b2_st_cs_v4(uint4 *p, uint4 v) { __stcs(p, v); }
 // four floats -> truncate toward zero, clamp to [0,255], pack a | b<<8 | c<<16 | d<<24.
 // cvt.rzi.s32.f32 + cvt.pack.sat.u8.s32 fuse into two F2IP.U8.F32.TRUNC (two floats each, merged): no PRMT.
 B2_DEVICE uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
@@ -69,10 +62,7 @@ B2_DEVICE void b2_f2_unpack(b2_f2 v, float &lo, float &hi) { asm("mov.b64 {%0, %
 B2_DEVICE b2_f2 b2_f2_add(b2_f2 a, b2_f2 b) { b2_f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 B2_DEVICE b2_f2 b2_f2_sub(b2_f2 a, b2_f2 b) { b2_f2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 
-// ---- cp.async (LDGSTS): 16-byte global -> shared copies that bypass the register file ----
-B2_DEVICE void b2_cp_async16(void *dst, const void *src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
-}
+// ---- cp.async (LDGSTS): global -> shared copies that bypass the register file ----
 B2_DEVICE void b2_cp_async4(void *dst, const void *src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(__cvta_generic_to_global(src)) : "memory");
 }
@@ -193,13 +183,6 @@ B2_DEVICE void b2_mbar_wait_a(uint32_t bar, uint32_t parity) {
 B2_DEVICE uint32_t b2_launder(uint32_t v) { asm volatile("" : "+r"(v) :: "memory"); return v; }
 // shifts that give 0 for counts >= 32 (PTX semantics; undefined in C++)
 B2_DEVICE uint32_t b2_shr(uint32_t v, uint32_t n) { uint32_t r; asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
-B2_DEVICE uint32_t b2_shl(uint32_t v, uint32_t n) { uint32_t r; asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
-// float -> integer-valued float, toward zero, for |x| < 2^23, without the XU pipe (FRND):
-// |x| + 2^23 rounded toward zero is floor(|x|) + 2^23 exactly; subtract and restore the sign.
-B2_DEVICE float b2_trunc_small(float x) {
-  const float a = __fadd_rz(fabsf(x), 8388608.0f);
-  return copysignf(__fsub_rn(a, 8388608.0f), x);
-}
 #else
 // ------------------------------------------------------------------ emulation
 #include "../../tests/emul/cuda_emul.h"

@@ -14,7 +14,7 @@ import jpeg_decoder_b200 as jd  # noqa: E402
 from jpeg_decoder_b200 import abi  # noqa: E402
 import bench  # noqa: E402
 
-CASES = {"C2": ("C2", 256), "C3": ("C3", 1), "C5": ("C5", 2048), "C4": ("C4-422", 4)}
+CASES = {"C2": ("C2", 256), "C3": ("C3", 1), "C5": ("C5", 2048), "C4": ("C4-422", 4), "C1": ("C1", 1)}
 
 
 def main():
@@ -27,14 +27,20 @@ def main():
 
         class A:
             workload, images, quality = key, n, 0
-        wl = bench.workload(A)
-        files = bench.make_files(wl, 0, n)
-        descs, rcs = jd.parse_headers(files, wl["flags"])
-        for sub in (11, 12, 13, 14):
-            for unit_bits in (11, 12, 13, 14, 15):
+        if key == "C1":                                # BASELINE config 1: the reference's own fixture, one small picture
+            files = [np.frombuffer(open(os.path.join(ROOT, "tests", "golden", "img.jpg"), "rb").read(), np.uint8)]
+            descs, rcs = jd.parse_headers(files, 0)
+            subs, units, ovs = (9, 10, 11, 12), (9, 10, 11, 12), (512, 1024, 2048, 4096)
+        else:
+            wl = bench.workload(A)
+            files = bench.make_files(wl, 0, n)
+            descs, rcs = jd.parse_headers(files, wl["flags"])
+            subs, units, ovs = (11, 12, 13, 14), (11, 12, 13, 14, 15), (2048, 4096)
+        for sub in subs:
+            for unit_bits in units:
                 if unit_bits < sub:
                     continue
-                for ov in (2048, 4096):
+                for ov in ovs:
                     os.environ["B200JPEG_XSUB"] = str(sub)
                     os.environ["B200JPEG_XUNIT"] = str(1 << (unit_bits - sub))
                     os.environ["B200JPEG_XOVERLAP"] = str(ov)

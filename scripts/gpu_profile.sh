@@ -28,16 +28,16 @@ fi
 if [[ $PH == *n* ]]; then
   timeout 300 python bench.py --steps 2 --warmup 1 > $OUT/plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv \
-      python bench.py --steps 2 --warmup 1 > $OUT/ncu_launches.log 2>&1
+      python bench.py --steps 2 --warmup 1 --skip-parity > $OUT/ncu_launches.log 2>&1
   echo "ncu launches exit $?"
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_pixel|k_entropy_seg|k_unstuff_(count|scatter)' -c 8 \
-      -o $OUT/prof_C2 python bench.py --steps 1 --warmup 1 > $OUT/ncu_full_C2.log 2>&1
+      -o $OUT/prof_C2 python bench.py --steps 1 --warmup 1 --skip-parity > $OUT/ncu_full_C2.log 2>&1
   echo "ncu full C2 exit $?"
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_xsync|k_entropy_seg|k_xunits|k_pixel' -c 10 \
-      -o $OUT/prof_C3 python bench.py --workload C3 --steps 1 --warmup 1 > $OUT/ncu_full_C3.log 2>&1
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_xsync|k_entropy_seg|k_xunits|k_pixel' -c 8 \
+      -o $OUT/prof_C3 python bench.py --workload C3 --steps 1 --warmup 1 --skip-parity > $OUT/ncu_full_C3.log 2>&1
   echo "ncu full C3 exit $?"
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:'k_xsync|k_entropy_seg' -c 8 \
-      -o $OUT/prof_C2sync python bench.py --entropy sync --steps 1 --warmup 1 > $OUT/ncu_full_C2sync.log 2>&1
+      -o $OUT/prof_C2sync python bench.py --entropy sync --steps 1 --warmup 1 --skip-parity > $OUT/ncu_full_C2sync.log 2>&1
   echo "ncu full C2 sync exit $?"
   for P in C2 C3 C2sync; do
     ncu -i $OUT/prof_$P.ncu-rep --page raw --csv > $OUT/raw_$P.csv 2>/dev/null

@@ -229,15 +229,14 @@ template <class T> static inline T min(T a, T b) { return a < b ? a : b; }
 template <class T> static inline T max(T a, T b) { return a > b ? a : b; }
 static inline uint32_t b2_ld_nc_u32(const uint32_t *p) { return *p; }
 static inline uint4 b2_ld_nc_v4(const uint4 *p) { return *p; }
-static inline uint32_t b2_f2u8_rz_sat(float x) {
+static inline uint32_t emu_f2u8_rz_sat(float x) {
   if (!(x == x)) return 0;
   if (x <= 0.0f) return 0;
   if (x >= 255.0f) return 255;
   return (uint32_t)(int)x;
 }
-static inline void b2_st_cs_v4(uint4 *p, uint4 v) { *p = v; }
 static inline uint32_t b2_f4_to_u8x4(float a, float b, float c, float d) {
-  return b2_f2u8_rz_sat(a) | (b2_f2u8_rz_sat(b) << 8) | (b2_f2u8_rz_sat(c) << 16) | (b2_f2u8_rz_sat(d) << 24);
+  return emu_f2u8_rz_sat(a) | (emu_f2u8_rz_sat(b) << 8) | (emu_f2u8_rz_sat(c) << 16) | (emu_f2u8_rz_sat(d) << 24);
 }
 // mbarrier / bulk copy: the barrier word counts completed phases; the copy is done by the issuing thread
 static inline void b2_mbar_init(uint64_t *bar, uint32_t) { __atomic_store_n(bar, (uint64_t)0, __ATOMIC_SEQ_CST); }
@@ -247,7 +246,6 @@ static inline void b2_bulk_load(void *dst, const void *src, uint32_t bytes, uint
   memcpy(dst, src, bytes);
   __atomic_fetch_add(bar, (uint64_t)1, __ATOMIC_SEQ_CST);
 }
-static inline void b2_cp_async16(void *dst, const void *src) { memcpy(dst, src, 16); }
 static inline void b2_cp_async4(void *dst, const void *src) { memcpy(dst, src, 4); }
 static inline void b2_cp_async_commit() {}
 template <int N> static inline void b2_cp_async_wait() {}
@@ -260,7 +258,6 @@ static inline void b2_bulk_wait_read() {}
 static inline void b2_mbar_wait(uint64_t *bar, uint32_t parity) {
   while ((__atomic_load_n(bar, __ATOMIC_SEQ_CST) & 1u) == parity) std::this_thread::yield();
 }
-static inline float b2_trunc_small(float x) { return truncf(x); }
 struct b2_f2 { float lo, hi; };
 static inline b2_f2 b2_f2_pack(float lo, float hi) { return {lo, hi}; }
 static inline void b2_f2_unpack(b2_f2 v, float &lo, float &hi) { lo = v.lo; hi = v.hi; }
@@ -308,7 +305,6 @@ static inline void b2_mbar_wait_a(uint32_t a, uint32_t parity) {
   while (((__atomic_load_n(b2_mbar_ptr(a), __ATOMIC_SEQ_CST) >> 32) & 1u) == parity) std::this_thread::yield();
 }
 static inline uint32_t b2_shr(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v >> n; }
-static inline uint32_t b2_shl(uint32_t v, uint32_t n) { return n >= 32 ? 0u : v << n; }
 static inline void b2_cp_async_src_check(const void *src) {
   if (reinterpret_cast<uintptr_t>(src) & 3u) { fprintf(stderr, "emulation: cp.async from a misaligned global address\n"); abort(); }
 }
