@@ -159,7 +159,7 @@ def ncu_capture(workload_key, images):
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f)
-        w = t.get("workloads", {}).get(workload_key) or (t if workload_key == "C2" and "kernels" in t else None)
+        w = t.get("workloads", {}).get(workload_key)
         return w["kernels"] if w and w.get("images") == images else {}
     except (OSError, KeyError, ValueError):
         return {}
@@ -229,11 +229,20 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": pixels_step / value / 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+int32", "data": "synthetic",
-            "config": {"workload": wl["label"], "step": "bounded sample: " + sample},
+            "config": gpu_config(wl, wl["n"] if wl["scaling"] != "strong" else wl["n"] // max(1, args.gpus)),
+            "notes": {"step": "bounded sample of the workload: " + sample},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample + " per step"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
+
+
+def gpu_config(wl, images_per_gpu):
+    """`config` of the JSON line -- the same for both arms (the driver compares them)."""
+    return {"workload": wl["label"], "images_per_gpu": images_per_gpu,
+            "parallelism": {"weak": "images sharded (every rank its own batch), no collective",
+                            "strong": "the batch's images sharded over the ranks, no collective",
+                            "replicas": "replicas only (a single scan is not split across GPUs)"}[wl["scaling"]]}
 
 
 # ------------------------------------------------------------------ GPU arm
@@ -371,20 +380,20 @@ def run_gpu_arm(args, rank, world, local_rank):
         ms = {k: v / args.steps for k, v in stage.items()}
         seg = stats["entropy_path"] == 1
         pix_name = "k_pixel<%d,%d,%d>" % ((1, 1, 1) if wl["gray"] else (wl["hs"], wl["vs"], 3))
-        cap = ncu_capture(args.workload, n)
+        cap = ncu_capture(args.workload + ("-sync" if args.entropy == "sync" else ""), n)
 
         def kern(name, t_ms, alg):
             k = {"name": name, "ms": t_ms, "alg_bytes": alg, "gbs": alg / t_ms / 1e6 if t_ms > 0 else None,
                  "frac": alg / t_ms / 1e6 / peak if t_ms > 0 else None}
-            c = cap.get(name.split("+")[-1])
+            c = cap.get(name.split("+")[-1].replace(" ", ""))   # the stage's main kernel in the committed ncu capture
             if c:
                 k["traffic"] = c.get("read", 0) + c.get("write", 0)
-                k["issue"] = {kk: c[kk] for kk in ("ipc", "alu_pipe_pct", "lanes_per_inst", "issue_active_pct") if kk in c}
+                k["issue"] = {kk: c[kk] for kk in ("ipc", "alu_pipe_pct", "fma_pipe_pct", "xu_pipe_pct", "lanes_per_inst") if kk in c}
             return k
         kernels = {
             "pixel": kern(pix_name, ms["pixel"], a_pix),
             "entropy_decode": kern("k_entropy_seg" if seg else "k_xunits+k_entropy_seg", ms["write"], a_ent),
-            "unstuff": kern("k_unstuff_count+scan+scatter", ms["unstuff"], 3 * stats["scan_bytes"]),
+            "unstuff": kern("k_unstuff_count+k_unstuff_scan+k_unstuff_scatter", ms["unstuff"], 3 * stats["scan_bytes"]),
         }
         if not seg:
             kernels["entropy_sync"] = kern("k_xplan+k_xsync<0>x2+k_xscan+k_xsync<1>", ms["sync"], stats["scan_bytes"])
@@ -414,13 +423,10 @@ def run_gpu_arm(args, rank, world, local_rank):
                 "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True,
                 "scaling": "strong" if wl["scaling"] == "strong" else "weak", "vs_baseline": None,
                 "dtype": "int32 entropy + f32 IDCT/colour", "data": "synthetic",
-                "config": {"workload": wl["label"], "images_per_gpu": n,
-                           "parallelism": {"weak": "images sharded (every rank its own batch), no collective",
-                                           "strong": "the batch's images sharded over the ranks, no collective",
-                                           "replicas": "replicas only (a single scan is not split across GPUs)"}[wl["scaling"]],
-                           "l2": "working set per step (scan %.0f MB, coefficients %.0f MB, RGB %.0f MB) exceeds the 126 MB L2"
-                                 % (stats["scan_bytes"] / 1e6, 128 * blocks / 1e6, 3 * pixels / 1e6),
-                           "timed": "K steps bracketed by barrier + stream sync; each step = all kernels + status readback"},
+                "config": gpu_config(wl, n),
+                "notes": {"l2": "working set per step (scan %.0f MB, coefficients %.0f MB, RGB %.0f MB) exceeds the 126 MB L2"
+                                % (stats["scan_bytes"] / 1e6, 128 * blocks / 1e6, 3 * pixels / 1e6),
+                          "timed": "K steps bracketed by barrier + stream sync; each step = all kernels + status readback"},
                 "event_ms_per_step": ev_total_ms, "kernels": kernels, "roofline": roofline, "cpu_baseline": cpu,
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": t_e2e / args.steps * 1e3, "copy_floor_ms": floor_ms,
