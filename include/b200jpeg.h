@@ -195,6 +195,40 @@ int b200jpeg_decode_batch_multi(const int *devices, int ndev, const b200jpeg_ima
 int b200jpeg_copy_floor(b200jpeg_ctx *ctx, const b200jpeg_image_desc *descs, int n,
                         const uint8_t *const *file_bytes, const size_t *file_sizes, uint8_t *const *rgb_out, float *ms);
 
+/* ---- progressive DCT files (SOF2): SURVEY.md 8(f) rank 4.  The reference REFUSES them (jpeg.cpp:69-73, "Progressive
+ * JPEG not supported") although it ships two as fixtures (images/prograssive-sample*.jpg); b200jpeg_parse_header keeps
+ * returning B200JPEG_E_PROGRESSIVE for them, and these two calls lift the refusal.  A progressive file is a frame
+ * (same fields as SOF0, jpeg.cpp:50-138) followed by several scans (ITU-T T.81 Annex G), each a band of coefficients
+ * (Ss..Se) at a bit position (Ah, Al) for one or all components, each with the Huffman tables in force when it starts
+ * (DHT segments may redefine a table between scans, hence the pool).  After the last scan the coefficients are what a
+ * baseline file of the same picture holds, and the rest of the path (dequantize, inverseDCT, YCbCrToRGB) is the same. */
+#define B200JPEG_PROG_MAX_SCANS 48
+#define B200JPEG_PROG_MAX_TABLES 48
+typedef struct {
+  int32_t ns;                          /* components in the scan: 1, or all of them for DC scans */
+  int32_t comp[3];                     /* index into frame.color_components */
+  int32_t dc_table[3], ac_table[3];    /* per scan component: index into tables[], -1 where the scan needs none */
+  int32_t ss, se, ah, al;              /* spectral selection and successive approximation (T.81 B.2.3) */
+  int32_t restart_interval;            /* DRI in force (jpeg.cpp:285-298), in MCUs of THIS scan */
+  int64_t offset, length;              /* the scan's entropy-coded bytes in the file: stuffed, RSTn included, up to the next marker */
+} b200jpeg_scan;
+typedef struct {
+  b200jpeg_image_desc frame;           /* geometry, components (sampling, quantisation ids), quantisation tables; its Huffman
+                                          tables are unused, scan_offset/scan_length span from the first scan to the end of the file */
+  int32_t nscans, ntables;
+  b200jpeg_scan scans[B200JPEG_PROG_MAX_SCANS];
+  b200jpeg_huffman_table tables[B200JPEG_PROG_MAX_TABLES];
+} b200jpeg_progressive_desc;
+/* host only; B200JPEG_E_UNSUPPORTED for frames the kernels do not take (only the first component may be subsampled, by 1 or
+ * 2; more scans / tables than the limits above), B200JPEG_E_NOT_JPEG .. as b200jpeg_parse_header, B200JPEG_E_ARG for a
+ * baseline (SOF0) file */
+int b200jpeg_parse_progressive(const uint8_t *file, size_t len, b200jpeg_progressive_desc *desc);
+/* arguments as b200jpeg_decode_batch.  One GPU thread walks one scan of one image (scans of an image run one after another,
+ * images side by side): correct, not fast -- see DESIGN.md. */
+int b200jpeg_decode_progressive(b200jpeg_ctx *ctx, const b200jpeg_progressive_desc *descs, int n,
+                                const uint8_t *const *file_bytes, const size_t *file_sizes,
+                                uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status);
+
 /* The same in three steps, so that a caller can keep a batch resident in HBM:
  *   prepare: plan the batch, copy the scans (and the small descriptors) host -> device
  *   run    : launch every kernel of the path on the context's stream (asynchronous)

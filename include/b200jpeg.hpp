@@ -253,7 +253,34 @@ inline Batch decode_files(const std::vector<std::string> &paths, const std::vect
     b.rgb_off[i] = rgb_total;
     rgb_total += ((size_t)3 * b.descs[i].image_width * b.descs[i].image_height + 255) / 256 * 256;
   }
+  // progressive files (refused by b200jpeg_parse_headers like the reference refuses them): under B200JPEG_PARSE_SPEC they
+  // are parsed as such and decoded by b200jpeg_decode_progressive on the first device, after the baseline ones
+  std::vector<size_t> prog;
+  std::vector<b200jpeg_progressive_desc> pd;
+  if (parse_flags & B200JPEG_PARSE_SPEC)
+    for (size_t i = 0; i < n; ++i) if (b.parse_rc[i] == B200JPEG_E_PROGRESSIVE) {
+      pd.emplace_back();
+      const int rc = b200jpeg_parse_progressive(fptr[i], b.file_len[i], &pd.back());
+      if (rc) { b.parse_rc[i] = rc; pd.pop_back(); continue; }
+      b.parse_rc[i] = 0;
+      b.descs[i] = pd.back().frame;
+      prog.push_back(i);
+      b.rgb_off[i] = rgb_total;
+      rgb_total += ((size_t)3 * b.descs[i].image_width * b.descs[i].image_height + 255) / 256 * 256;
+    }
   b.pixels = PinnedBuffer(rgb_total + 256);
+  if (!prog.empty()) {
+    const size_t m = prog.size();
+    std::vector<const uint8_t *> f(m);
+    std::vector<size_t> sz(m);
+    std::vector<uint8_t *> out(m);
+    std::vector<int32_t> st(m, 0);
+    for (size_t k = 0; k < m; ++k) { f[k] = fptr[prog[k]]; sz[k] = b.file_len[prog[k]]; out[k] = b.pixels.data() + b.rgb_off[prog[k]]; }
+    Context own(devices.empty() ? 0 : devices[0]);
+    const int rc = b200jpeg_decode_progressive(own.get(), pd.data(), (int)m, f.data(), sz.data(), out.data(), nullptr, st.data());
+    if (rc) throw Error(rc, std::string("decode_files (progressive): ") + b200jpeg_last_error(own.get()));
+    for (size_t k = 0; k < m; ++k) b.status[prog[k]] = st[k];
+  }
   if (live.empty()) return b;
   const size_t m = live.size();
   std::vector<b200jpeg_image_desc> d(m);
@@ -362,7 +389,40 @@ class Image {
   }
 
   // jpeg.cpp:826-907: headers, then the scan (the reference calls process_image_data at SOS, :858-863).
-  void readJPEG(Context &ctx = Context::shared()) { readHeaders(); process_image_data(ctx); }
+  // Progressive files (SOF2): the reference refuses them (jpeg.cpp:69-73) and so does this call under
+  // B200JPEG_PARSE_REFERENCE; with parse_flags = B200JPEG_PARSE_SPEC the refusal is lifted (readProgressive).
+  void readJPEG(Context &ctx = Context::shared()) {
+    b200jpeg_image_desc probe;
+    if ((parse_flags & B200JPEG_PARSE_SPEC) &&
+        b200jpeg_parse_header(file_.data(), file_.size(), parse_flags, &probe) == B200JPEG_E_PROGRESSIVE) { readProgressive(ctx); return; }
+    readHeaders();
+    process_image_data(ctx);
+  }
+
+  // SOF2: frame + scans through b200jpeg_parse_progressive / b200jpeg_decode_progressive (T.81 Annex G on the GPU).
+  void readProgressive(Context &ctx = Context::shared()) {
+    std::vector<b200jpeg_progressive_desc> pd(1);
+    int rc = b200jpeg_parse_progressive(file_.data(), file_.size(), &pd[0]);
+    if (rc) throw Error(rc, "readJPEG (progressive): " + filename_);
+    desc_ = pd[0].frame;
+    image_width = desc_.image_width; image_height = desc_.image_height;
+    mcuWidthReal = desc_.mcuWidthReal; mcuHeightReal = desc_.mcuHeightReal;
+    restartInterval = desc_.restartInterval;
+    load_tables();
+    parsed_ = true;
+    rgb_.assign((size_t)3 * image_width * image_height, 0);
+    const uint8_t *files[1] = {file_.data()};
+    const size_t sizes[1] = {file_.size()};
+    uint8_t *out[1] = {rgb_.data()};
+    int16_t *co[1] = {nullptr};
+    if (keep_coefficients) { coef_.assign((size_t)mcuWidthReal * mcuHeightReal * 3 * 64, 0); co[0] = coef_.data(); }
+    int32_t st = 0;
+    rc = b200jpeg_decode_progressive(ctx.get(), pd.data(), 1, files, sizes, out, keep_coefficients ? co : nullptr, &st);
+    if (rc) throw Error(rc, std::string("readJPEG (progressive): ") + b200jpeg_last_error(ctx.get()));
+    status_ = st;
+    if (st) throw Error(B200JPEG_E_STATE, "readJPEG (progressive): corrupt scan, status bits " + std::to_string(st));
+    decoded_ = true;
+  }
 
   // Many images, one call: headers on the host, every scan through ONE b200jpeg_decode_batch()
   // (images are independent; the library cuts the batch into chunks that rotate over four internal pipelines).  Returns the per-image

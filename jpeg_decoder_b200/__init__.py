@@ -188,6 +188,27 @@ class Decoder:
         self._check(rc, "export_coefficients_noalloc")
         return out
 
+    def decode_progressive(self, datas, want_coef=False):
+        """Progressive (SOF2) files: b200jpeg_parse_progressive + b200jpeg_decode_progressive.
+        Returns (status list, rgb arrays [H,W,3], coef arrays or None) like decode()."""
+        n = len(datas)
+        descs = (abi.ProgressiveDesc * n)()
+        bufs = [np.frombuffer(d, dtype=np.uint8) for d in datas]
+        for i, b in enumerate(bufs):
+            rc = self.lib.b200jpeg_parse_progressive(b.ctypes.data, b.size, C.byref(descs[i]))
+            if rc:
+                raise B200JpegError(rc, "parse_progressive(image %d)" % i)
+        fr = [descs[i].frame for i in range(n)]
+        rgbs = [np.empty((f.image_height, f.image_width, 3), np.uint8) for f in fr]
+        coefs = [np.empty((f.mcuWidthReal * f.mcuHeightReal, 3, 64), np.int16) for f in fr] if want_coef else None
+        files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        sizes = (C.c_size_t * n)(*[b.size for b in bufs])
+        prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
+        pco = (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None
+        st = (C.c_int32 * n)()
+        self._check(self.lib.b200jpeg_decode_progressive(self.h, descs, n, files, sizes, prgb, pco, st), "decode_progressive")
+        return list(st), rgbs, coefs
+
     def copy_floor(self, descs, bufs, rgbs):
         """b200jpeg_copy_floor: the copies of decode_batch without its kernels; returns milliseconds."""
         n = len(bufs)

@@ -61,6 +61,20 @@ class ImageDesc(C.Structure):
                 ("scan_offset", C.c_int64), ("scan_length", C.c_int64)]
 
 
+PROG_MAX_SCANS, PROG_MAX_TABLES = 48, 48
+
+
+class Scan(C.Structure):
+    _fields_ = [("ns", C.c_int32), ("comp", C.c_int32 * 3), ("dc_table", C.c_int32 * 3), ("ac_table", C.c_int32 * 3),
+                ("ss", C.c_int32), ("se", C.c_int32), ("ah", C.c_int32), ("al", C.c_int32), ("restart_interval", C.c_int32),
+                ("offset", C.c_int64), ("length", C.c_int64)]
+
+
+class ProgressiveDesc(C.Structure):
+    _fields_ = [("frame", ImageDesc), ("nscans", C.c_int32), ("ntables", C.c_int32), ("scans", Scan * PROG_MAX_SCANS),
+                ("tables", HuffmanTable * PROG_MAX_TABLES)]
+
+
 class BatchStats(C.Structure):
     _fields_ = [("images", C.c_int64), ("pixels", C.c_int64), ("scan_bytes", C.c_int64),
                 ("coded_blocks", C.c_int64), ("rgb_bytes", C.c_int64), ("h2d_bytes", C.c_int64),
@@ -77,12 +91,15 @@ EXPORTS = [
     "b200jpeg_abi_version", "b200jpeg_set_entropy_path", "b200jpeg_parse_headers", "b200jpeg_copy_floor",
     "b200jpeg_multi_create", "b200jpeg_multi_destroy", "b200jpeg_multi_count", "b200jpeg_multi_ctx",
     "b200jpeg_multi_decode_batch", "b200jpeg_decode_batch_multi", "b200jpeg_export_coefficients_noalloc",
+    "b200jpeg_parse_progressive", "b200jpeg_decode_progressive",
 ]
 
 
 def bind_parse(lib):
     lib.b200jpeg_parse_header.restype = C.c_int
     lib.b200jpeg_parse_header.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(ImageDesc)]
+    lib.b200jpeg_parse_progressive.restype = C.c_int
+    lib.b200jpeg_parse_progressive.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(ProgressiveDesc)]
     lib.b200jpeg_parse_headers.restype = C.c_int
     lib.b200jpeg_parse_headers.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int, C.c_int, C.c_int,
                                            C.POINTER(ImageDesc), C.POINTER(C.c_int32)]
@@ -129,6 +146,9 @@ def bind(lib):
     lib.b200jpeg_abi_version.argtypes = []
     lib.b200jpeg_export_coefficients_noalloc.restype = C.c_int
     lib.b200jpeg_export_coefficients_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+    lib.b200jpeg_decode_progressive.restype = C.c_int
+    lib.b200jpeg_decode_progressive.argtypes = [C.c_void_p, P(ProgressiveDesc), C.c_int, P(C.c_void_p), P(C.c_size_t),
+                                                P(C.c_void_p), P(C.c_void_p), P(C.c_int32)]
     lib.b200jpeg_copy_floor.restype = C.c_int
     lib.b200jpeg_copy_floor.argtypes = [C.c_void_p, P(ImageDesc), C.c_int, P(C.c_void_p), P(C.c_size_t), P(C.c_void_p),
                                         P(C.c_float)]

@@ -291,6 +291,20 @@ int b200jpeg_decode_batch_multi(const int *devices, int ndev, const b200jpeg_ima
   return b200jpeg_multi_decode_batch(cached, descs, n, files, sizes, rgb_out, status);
 }
 
+// Progressive files (SOF2): see b200jpeg.h and kernels_prog.cuh.
+int b200jpeg_decode_progressive(b200jpeg_ctx *c, const b200jpeg_progressive_desc *descs, int n, const uint8_t *const *files,
+                                const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+  if (!c || n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
+  DeviceGuard g(c->device);
+  c->pipe.be.err.clear();
+  c->agg_valid = false;
+  int rc = c->pipe.prepare_progressive(descs, n, files, sizes);
+  if (rc) return fail(c, rc);
+  rc = c->pipe.run_progressive();
+  if (rc) return fail(c, rc);
+  return fail(c, c->pipe.fetch(rgb_out, coef_out, status));
+}
+
 int b200jpeg_device_rgb(b200jpeg_ctx *c, int i, void **dev_ptr, size_t *pitch) {
   if (!c || !c->pipe.prepared || i < 0 || i >= c->pipe.plan.n) return B200JPEG_E_ARG;
   if (dev_ptr) *dev_ptr = c->pipe.d_rgb.as<uint8_t>() + c->pipe.plan.imgs[i].rgb_off;

@@ -201,6 +201,106 @@ extern "C" int b200jpeg_parse_header(const uint8_t *file, size_t len, int flags,
   return B200JPEG_OK;
 }
 
+// Progressive files (SOF2): frame + scan list + table pool, see b200jpeg.h.  The marker walk is the one above; SOF2 has
+// the layout of SOF0 (T.81 B.2.2), every DHT appends to the pool, every SOS records which pool entries are in force.
+extern "C" int b200jpeg_parse_progressive(const uint8_t *file, size_t len, b200jpeg_progressive_desc *P) {
+  if (!file || !P) return B200JPEG_E_ARG;
+  memset(P, 0, sizeof *P);
+  if (len < 2 || file[0] != 0xff || file[1] != 0xd8) return B200JPEG_E_NOT_JPEG;
+  b200jpeg_image_desc *d = &P->frame;
+  int comp_id[3] = {-1, -1, -1}, cur_dc[4] = {-1, -1, -1, -1}, cur_ac[4] = {-1, -1, -1, -1};
+  bool got_frame = false;
+  size_t pos = 2;
+  while (pos + 1 < len) {
+    if (file[pos] != 0xff) return B200JPEG_E_NO_SOS;
+    const int m = file[pos + 1];
+    if (m == 0xff) { ++pos; continue; }
+    pos += 2;
+    if (m == 0xd9) break;
+    if (m == 0x00 || (m >= 0xd0 && m <= 0xd8)) continue;
+    if (pos + 2 > len) return B200JPEG_E_TRUNCATED;
+    const int seglen = be16(file + pos);
+    const uint8_t *p = file + pos + 2;
+    const int plen = seglen - 2;
+    if (plen < 0 || pos + (size_t)seglen > len) return B200JPEG_E_TRUNCATED;
+    pos += (size_t)seglen;
+    int rc = 0;
+    switch (m) {
+      case 0xc0: return B200JPEG_E_ARG;                      // a baseline file: b200jpeg_parse_header
+      case 0xc2: rc = parse_sof(d, 0xc0, p, plen, true, comp_id); got_frame = rc == 0; break;
+      case 0xc1: case 0xc3: case 0xc5: case 0xc6: case 0xc7: case 0xc9: case 0xca: case 0xcb: case 0xcd: case 0xce: case 0xcf:
+        return B200JPEG_E_UNSUPPORTED;                       // extended / lossless / arithmetic frames
+      case 0xdb: rc = parse_dqt(d, p, plen, true); break;
+      case 0xdd: if (plen != 2) rc = B200JPEG_E_DRI; else d->restartInterval = be16(p); break;
+      case 0xc4: {                                           // every table of the segment goes to the pool
+        const uint8_t *q = p; int left = plen;
+        while (left > 0) {
+          if (left < 17) return B200JPEG_E_DHT;
+          int all = 0;
+          for (int i = 1; i <= 16; ++i) all += q[i];
+          if (all > 176 || left < 17 + all) return B200JPEG_E_DHT;
+          if (P->ntables >= B200JPEG_PROG_MAX_TABLES) return B200JPEG_E_UNSUPPORTED;
+          b200jpeg_image_desc tmp_holder;                    // parse_dht writes into a descriptor: borrow its slot 0 / class
+          memset(&tmp_holder, 0, sizeof tmp_holder);
+          uint8_t one[17 + 176];
+          memcpy(one, q, (size_t)(17 + all));
+          const int id = q[0] & 15, is_ac = q[0] >> 4;
+          if (id > 3) return B200JPEG_E_TABLE_ID;
+          rc = parse_dht(&tmp_holder, one, 17 + all);
+          if (rc) return rc;
+          P->tables[P->ntables] = is_ac ? tmp_holder.huffmanACTable[id] : tmp_holder.huffmanDCTTable[id];
+          (is_ac ? cur_ac : cur_dc)[id] = P->ntables++;
+          q += 17 + all; left -= 17 + all;
+        }
+        break;
+      }
+      case 0xda: {
+        if (!got_frame) return B200JPEG_E_NO_SOS;
+        if (P->nscans >= B200JPEG_PROG_MAX_SCANS) return B200JPEG_E_UNSUPPORTED;
+        if (plen < 1) return B200JPEG_E_SOS;
+        b200jpeg_scan *S = &P->scans[P->nscans];
+        S->ns = p[0];
+        if (S->ns < 1 || S->ns > d->numComponents || plen != 1 + 2 * S->ns + 3) return B200JPEG_E_SOS;
+        const uint8_t *q = p + 1 + 2 * S->ns;
+        S->ss = q[0]; S->se = q[1]; S->ah = q[2] >> 4; S->al = q[2] & 15;
+        if (S->ss > S->se || S->se > 63 || (S->ss == 0 && S->se != 0) || (S->ss != 0 && S->ns != 1) || S->al > 13) return B200JPEG_E_SOS;
+        for (int j = 0; j < 3; ++j) { S->comp[j] = 0; S->dc_table[j] = S->ac_table[j] = -1; }
+        for (int j = 0; j < S->ns; ++j) {
+          int ci = -1;
+          for (int i = 0; i < d->numComponents; ++i) if (comp_id[i] == p[1 + 2 * j]) ci = i;
+          if (ci < 0) return B200JPEG_E_SOS;
+          const int td = p[2 + 2 * j] >> 4, ta = p[2 + 2 * j] & 15;
+          if (td > 3 || ta > 3) return B200JPEG_E_TABLE_ID;
+          S->comp[j] = ci;
+          if (S->ss == 0 && S->ah == 0) { if (cur_dc[td] < 0) return B200JPEG_E_TABLE_MISSING; S->dc_table[j] = cur_dc[td]; }
+          if (S->ss != 0) { if (cur_ac[ta] < 0) return B200JPEG_E_TABLE_MISSING; S->ac_table[j] = cur_ac[ta]; }
+        }
+        S->restart_interval = d->restartInterval;
+        S->offset = (int64_t)pos;
+        size_t e = pos;                                      // the scan runs up to the next marker that is not RSTn / stuffing
+        while (e + 1 < len && !(file[e] == 0xff && file[e + 1] != 0x00 && file[e + 1] != 0xff && !(file[e + 1] >= 0xd0 && file[e + 1] <= 0xd7))) ++e;
+        if (e + 1 >= len) e = len;
+        S->length = (int64_t)(e - pos);
+        if (P->nscans == 0) d->scan_offset = (int64_t)pos;
+        pos = e;
+        ++P->nscans;
+        break;
+      }
+      default: break;                                        // APPn, COM, ...
+    }
+    if (rc) return rc;
+  }
+  if (!got_frame || P->nscans == 0) return B200JPEG_E_NO_SOS;
+  if (d->numComponents == 0 || d->horizontalSamplingFactor == 0 || d->verticalSamplingFactor == 0) return B200JPEG_E_SAMPLING;
+  for (int i = 0; i < d->numComponents; ++i) {
+    const int tq = d->color_components[i].quantizationTableID;
+    if (tq < 0 || tq > 3) return B200JPEG_E_TABLE_ID;
+    if (!d->quantization_tables[tq].set) return B200JPEG_E_TABLE_MISSING;
+  }
+  d->scan_length = (int64_t)len - d->scan_offset;
+  return B200JPEG_OK;
+}
+
 // n headers on several host threads: files are handed out in blocks of 16 through one atomic counter
 extern "C" int b200jpeg_parse_headers(const uint8_t *const *files, const size_t *sizes, int n, int flags, int threads,
                                       b200jpeg_image_desc *descs, int32_t *rcs) {

@@ -23,6 +23,7 @@
 #include "kernels_segdec.cuh"
 #include "kernels_entropy.cuh"
 #include "kernels_pixel.cuh"
+#include "kernels_prog.cuh"
 
 namespace b2 {
 
@@ -189,7 +190,10 @@ inline int choose_path(const b200jpeg_image_desc *descs, int n, int force) {
 }
 
 // Build the plan.  Returns 0 or a B200JPEG_E_* code.
-inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file_sizes, BatchPlan &P, int force_path = kForceAuto) {
+// progressive: the descriptors are the FRAMES of progressive files (b200jpeg_progressive_desc::frame): Huffman tables travel
+// with the scans, not with the frame, and the entropy stage is kernels_prog.cuh
+inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file_sizes, BatchPlan &P, int force_path = kForceAuto,
+                     bool progressive = false) {
   P = BatchPlan();
   P.n = n;
   P.path = choose_path(descs, n, force_path);
@@ -233,8 +237,8 @@ inline int make_plan(const b200jpeg_image_desc *descs, int n, const size_t *file
       if (cc.quantizationTableID < 0 || cc.quantizationTableID > 3 || cc.huffmanDCTTableID < 0 || cc.huffmanDCTTableID > 3 ||
           cc.huffmanACTableID < 0 || cc.huffmanACTableID > 3)
         return B200JPEG_E_TABLE_ID;                        // jpeg.cpp:156-160, 205-209
-      if (!d.quantization_tables[cc.quantizationTableID].set || !d.huffmanDCTTable[cc.huffmanDCTTableID].set ||
-          !d.huffmanACTable[cc.huffmanACTableID].set)
+      if (!d.quantization_tables[cc.quantizationTableID].set ||
+          (!progressive && (!d.huffmanDCTTable[cc.huffmanDCTTableID].set || !d.huffmanACTable[cc.huffmanACTableID].set)))
         return B200JPEG_E_TABLE_MISSING;                   // jpeg.cpp:757-774
       im.tq[c] = (int8_t)d.color_components[c].quantizationTableID;
       im.td[c] = (int8_t)d.color_components[c].huffmanDCTTableID;

@@ -16,6 +16,8 @@ struct Pipeline {
   DevBuf d_raw, d_us, d_imgs, d_tsets, d_out, d_tile_base, d_tile_cnt, d_tile_pre, d_seg;
   DevBuf d_sub_e, d_sub_used, d_sub_info, d_cta_tot, d_cta_pre, d_bnd[2], d_flags, d_coef, d_rgb, d_export;
   DevBuf d_segsub, d_segunit, d_x_img, d_x_sub_base, d_x_unit_base, d_xunits;   // self-synchronising path
+  DevBuf d_pimgs, d_ptables;                                                      // progressive files (kernels_prog.cuh)
+  int prog_max_scans = 0;
   DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
   DevBuf d_units, d_luts;
   int force_path = kForceAuto;
@@ -40,7 +42,7 @@ struct Pipeline {
     DevBuf *all[] = {&d_raw, &d_us, &d_imgs, &d_tsets, &d_out, &d_tile_base, &d_tile_cnt, &d_tile_pre,
                      &d_seg, &d_sub_e, &d_sub_used, &d_sub_info, &d_cta_tot, &d_cta_pre, &d_bnd[0], &d_bnd[1],
                      &d_flags, &d_coef, &d_rgb, &d_export, &d_units, &d_luts,
-                     &d_segsub, &d_segunit, &d_x_img, &d_x_sub_base, &d_x_unit_base, &d_xunits};
+                     &d_segsub, &d_segunit, &d_x_img, &d_x_sub_base, &d_x_unit_base, &d_xunits, &d_pimgs, &d_ptables};
     for (DevBuf *b : all) b->destroy(be);
     for (int f = 0; f < PF_COUNT; ++f) { d_grp_img[f].destroy(be); d_grp_pre[f].destroy(be); }
     be.host_release(h_out); be.host_release(h_flags);
@@ -64,10 +66,11 @@ struct Pipeline {
   }
 
   // plan + H2D of the scans and descriptors
-  int prepare(const b200jpeg_image_desc *descs, int n, const uint8_t *const *files, const size_t *sizes) {
+  int prepare(const b200jpeg_image_desc *descs, int n, const uint8_t *const *files, const size_t *sizes, bool progressive = false) {
     prepared = ran = false;
+    prog_max_scans = 0;
     if (n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
-    const int rc = make_plan(descs, n, sizes, plan, force_path);
+    const int rc = make_plan(descs, n, sizes, plan, progressive ? (int)kForceSegment : force_path, progressive);
     if (rc) return rc;
     const BatchPlan &P = plan;
     bool ok = true;
@@ -140,6 +143,92 @@ struct Pipeline {
     if (!be.ok()) return B200JPEG_E_CUDA;
     prepared = true;
     return 0;
+  }
+
+  // Progressive files: the plan comes from the frames; the scans and their tables go to the device beside it.
+  int prepare_progressive(const b200jpeg_progressive_desc *descs, int n, const uint8_t *const *files, const size_t *sizes) {
+    if (n <= 0 || !descs || !files || !sizes) return B200JPEG_E_ARG;
+    std::vector<b200jpeg_image_desc> frames((size_t)n);
+    std::vector<ProgImageDev> pimgs((size_t)n);
+    std::vector<HuffSpec> tables;
+    int max_scans = 0;
+    for (int i = 0; i < n; ++i) {
+      const b200jpeg_progressive_desc &d = descs[i];
+      if (d.nscans < 1 || d.nscans > kProgMaxScans || d.ntables < 0 || d.ntables > B200JPEG_PROG_MAX_TABLES) return B200JPEG_E_ARG;
+      frames[(size_t)i] = d.frame;
+      ProgImageDev &pi = pimgs[(size_t)i];
+      memset(&pi, 0, sizeof pi);
+      pi.nscans = d.nscans; pi.width = d.frame.image_width; pi.height = d.frame.image_height;
+      const int tbase = (int)tables.size();
+      for (int t = 0; t < d.ntables; ++t) {
+        const b200jpeg_huffman_table &src = d.tables[t];
+        if (src.offset[0] != 0 || src.offset[16] > 176) return B200JPEG_E_DHT;
+        for (int l = 1; l <= 16; ++l) if (src.offset[l] < src.offset[l - 1]) return B200JPEG_E_DHT;
+        HuffSpec h; memset(&h, 0, sizeof h);
+        memcpy(h.offset, src.offset, 17); memcpy(h.symbols, src.symbols, 176); h.set = 1;
+        tables.push_back(h);
+      }
+      for (int k = 0; k < d.nscans; ++k) {
+        const b200jpeg_scan &S = d.scans[k];
+        ProgScanDev &o = pi.scans[k];
+        if (S.ns < 1 || S.ns > d.frame.numComponents || S.ss < 0 || S.ss > S.se || S.se > 63 || (S.ss == 0 && S.se != 0) ||
+            (S.ss != 0 && S.ns != 1) || S.al < 0 || S.al > 13 || S.ah < 0 || S.ah > 13 || S.restart_interval < 0)
+          return B200JPEG_E_SOS;
+        if (S.offset < d.frame.scan_offset || S.length < 0 || (size_t)(S.offset + S.length) > sizes[i]) return B200JPEG_E_ARG;
+        o.ns = S.ns; o.ss = S.ss; o.se = S.se; o.ah = S.ah; o.al = S.al; o.restart_interval = S.restart_interval;
+        o.offset = (uint32_t)(S.offset - d.frame.scan_offset); o.length = (uint32_t)S.length;
+        for (int j = 0; j < 3; ++j) {
+          o.comp[j] = 0; o.dc_table[j] = o.ac_table[j] = -1;
+          if (j >= S.ns) continue;
+          if (S.comp[j] < 0 || S.comp[j] >= d.frame.numComponents) return B200JPEG_E_SOS;
+          o.comp[j] = S.comp[j];
+          const bool need_dc = S.ss == 0 && S.ah == 0, need_ac = S.ss != 0;
+          if ((need_dc && (S.dc_table[j] < 0 || S.dc_table[j] >= d.ntables)) || (need_ac && (S.ac_table[j] < 0 || S.ac_table[j] >= d.ntables)))
+            return B200JPEG_E_TABLE_MISSING;
+          if (need_dc) o.dc_table[j] = tbase + S.dc_table[j];
+          if (need_ac) o.ac_table[j] = tbase + S.ac_table[j];
+        }
+      }
+      if (d.nscans > max_scans) max_scans = d.nscans;
+    }
+    const int rc = prepare(frames.data(), n, files, sizes, true);
+    if (rc) return rc;
+    prepared = false;
+    bool ok = d_pimgs.reserve(be, sizeof(ProgImageDev) * (size_t)n) && d_ptables.reserve(be, sizeof(HuffSpec) * (tables.size() + 1));
+    if (!ok) return be.ok() ? B200JPEG_E_NOMEM : B200JPEG_E_CUDA;
+    be.h2d(d_pimgs.p, pimgs.data(), sizeof(ProgImageDev) * (size_t)n);
+    if (!tables.empty()) be.h2d(d_ptables.p, tables.data(), sizeof(HuffSpec) * tables.size());
+    be.sync();                                     // pimgs / tables are host temporaries
+    h2d_bytes += (int64_t)(sizeof(ProgImageDev) * (size_t)n + sizeof(HuffSpec) * tables.size());
+    if (!be.ok()) return B200JPEG_E_CUDA;
+    prog_max_scans = max_scans;
+    prepared = true;
+    return 0;
+  }
+
+  int run_progressive() {
+    if (!prepared || prog_max_scans <= 0) return B200JPEG_E_STATE;
+    const BatchPlan &P = plan;
+    launches = 0; sync_rounds = 0;
+    results_enqueued = false;
+    mark(0);
+    be.fill(d_out.p, 0xff, sizeof(ImageOut) * P.n);
+    be.fill(d_flags.p, 0, 4 * (size_t)(kFixLaunches + kMaxExtraFix + 2));
+    B2_LAUNCH(k_reset_out, (P.n + 255) / 256, 256, 0, be.stream, d_out.as<ImageOut>(), P.n);
+    ++launches;
+    be.fill(d_coef.p, 0, 128 * (size_t)P.nblocks);   // scans only ever write the coefficients they carry (MCU[] starts at zero, jpeg.cpp:407)
+    mark(1); mark(2);
+    for (int k = 0; k < prog_max_scans; ++k) {        // scan k of every image; later scans refine what earlier ones wrote
+      B2_LAUNCH(k_prog_scan, (P.n + 31) / 32, 32, 0, be.stream, d_imgs.as<ImageDev>(), d_pimgs.as<ProgImageDev>(), P.n, k,
+                d_ptables.as<HuffSpec>(), d_raw.as<uint8_t>(), d_coef.as<int16_t>(), d_out.as<ImageOut>());
+      ++launches;
+    }
+    mark(3);
+    launch_pixels();
+    mark(5);
+    be.check("kernel launch");
+    ran = true;
+    return be.ok() ? 0 : B200JPEG_E_CUDA;
   }
 
   void mark(int k) {

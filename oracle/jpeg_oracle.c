@@ -346,6 +346,52 @@ static double now_ms(void) {
   return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
+/* dequantize + inverseDCT + YCbCrToRGB + the RGB gather over a decoded MCU array (jpeg.cpp:785-788 after decodeHuffman,
+ * display.hpp:19-34); shared by the baseline and the progressive decoder.  tt = times after dequant / idct / colour. */
+static void finish_pixels(dec_t *D, int32_t *mcus, int32_t **coef_out, uint8_t **rgb_out, double tt[3]) {
+  const size_t npos = (size_t)D->bwr * D->bhr;
+  if (coef_out) {
+    *coef_out = (int32_t *)malloc(npos * 3 * 64 * sizeof(int32_t));
+    memcpy(*coef_out, mcus, npos * 3 * 64 * sizeof(int32_t));
+  }
+  /* dequantize(), jpeg.cpp:572-590 -- same loop nest as decodeHuffman */
+  for (int y = 0; y < D->bh; y += D->vs)
+    for (int x = 0; x < D->bw; x += D->hs)
+      for (int i = 0; i < D->ncomp; ++i)
+        for (int v = 0; v < D->comp[i].v; ++v)
+          for (int h = 0; h < D->comp[i].h; ++h)
+            oracle_dequant_block(PLANE(mcus, POS(D, y + v, x + h), i), D->q[D->comp[i].tq].table);
+  tt[0] = now_ms();
+  /* inverseDCT(), jpeg.cpp:735-753 */
+  for (int y = 0; y < D->bh; y += D->vs)
+    for (int x = 0; x < D->bw; x += D->hs)
+      for (int i = 0; i < D->ncomp; ++i)
+        for (int v = 0; v < D->comp[i].v; ++v)
+          for (int h = 0; h < D->comp[i].h; ++h)
+            oracle_idct_block(PLANE(mcus, POS(D, y + v, x + h), i));
+  tt[1] = now_ms();
+  /* YCbCrToRGB(), jpeg.cpp:544-561: v,h descending so the anchor block converts last */
+  for (int y = 0; y < D->bh; y += D->vs)
+    for (int x = 0; x < D->bw; x += D->hs) {
+      const size_t cpos = POS(D, y, x);
+      for (unsigned v = D->vs - 1; v < (unsigned)D->vs; --v)
+        for (unsigned h = D->hs - 1; h < (unsigned)D->hs; --h)
+          ycc_block(D, mcus, POS(D, y + v, x + h), cpos, v, h);
+    }
+  tt[2] = now_ms();
+  if (rgb_out) {                                                       /* display.hpp:19-34 */
+    uint8_t *rgb = (uint8_t *)malloc((size_t)D->width * D->height * 3);
+    for (int y = 0; y < D->height; ++y)
+      for (int x = 0; x < D->width; ++x) {
+        const size_t pos = POS(D, y / 8, x / 8); const int p = (y % 8) * 8 + (x % 8);
+        uint8_t *o = rgb + ((size_t)y * D->width + x) * 3;
+        o[0] = (uint8_t)PLANE(mcus, pos, 0)[p]; o[1] = (uint8_t)PLANE(mcus, pos, 1)[p];
+        o[2] = (uint8_t)PLANE(mcus, pos, 2)[p];
+      }
+    *rgb_out = rgb;
+  }
+}
+
 int oracle_decode(const uint8_t *file, size_t len, int flags, oracle_info *info, int32_t **coef_out,
                   uint8_t **rgb_out) {
   init_consts();
@@ -413,46 +459,9 @@ int oracle_decode(const uint8_t *file, size_t len, int flags, oracle_info *info,
   rc = decode_huffman(D, mcus);
   if (rc) goto done;
   const double t2 = now_ms();
-  if (coef_out) {
-    *coef_out = (int32_t *)malloc(npos * 3 * 64 * sizeof(int32_t));
-    memcpy(*coef_out, mcus, npos * 3 * 64 * sizeof(int32_t));
-  }
-  /* dequantize(), jpeg.cpp:572-590 -- same loop nest as decodeHuffman */
-  for (int y = 0; y < D->bh; y += D->vs)
-    for (int x = 0; x < D->bw; x += D->hs)
-      for (int i = 0; i < D->ncomp; ++i)
-        for (int v = 0; v < D->comp[i].v; ++v)
-          for (int h = 0; h < D->comp[i].h; ++h)
-            oracle_dequant_block(PLANE(mcus, POS(D, y + v, x + h), i), D->q[D->comp[i].tq].table);
-  const double t3 = now_ms();
-  /* inverseDCT(), jpeg.cpp:735-753 */
-  for (int y = 0; y < D->bh; y += D->vs)
-    for (int x = 0; x < D->bw; x += D->hs)
-      for (int i = 0; i < D->ncomp; ++i)
-        for (int v = 0; v < D->comp[i].v; ++v)
-          for (int h = 0; h < D->comp[i].h; ++h)
-            oracle_idct_block(PLANE(mcus, POS(D, y + v, x + h), i));
-  const double t4 = now_ms();
-  /* YCbCrToRGB(), jpeg.cpp:544-561: v,h descending so the anchor block converts last */
-  for (int y = 0; y < D->bh; y += D->vs)
-    for (int x = 0; x < D->bw; x += D->hs) {
-      const size_t cpos = POS(D, y, x);
-      for (unsigned v = D->vs - 1; v < (unsigned)D->vs; --v)
-        for (unsigned h = D->hs - 1; h < (unsigned)D->hs; --h)
-          ycc_block(D, mcus, POS(D, y + v, x + h), cpos, v, h);
-    }
-  const double t5 = now_ms();
-  if (rgb_out) {                                                       /* display.hpp:19-34 */
-    uint8_t *rgb = (uint8_t *)malloc((size_t)D->width * D->height * 3);
-    for (int y = 0; y < D->height; ++y)
-      for (int x = 0; x < D->width; ++x) {
-        const size_t pos = POS(D, y / 8, x / 8); const int p = (y % 8) * 8 + (x % 8);
-        uint8_t *o = rgb + ((size_t)y * D->width + x) * 3;
-        o[0] = (uint8_t)PLANE(mcus, pos, 0)[p]; o[1] = (uint8_t)PLANE(mcus, pos, 1)[p];
-        o[2] = (uint8_t)PLANE(mcus, pos, 2)[p];
-      }
-    *rgb_out = rgb;
-  }
+  double tt[3];
+  finish_pixels(D, mcus, coef_out, rgb_out, tt);
+  const double t3 = tt[0], t4 = tt[1], t5 = tt[2];
   if (info) {
     info->ms_parse_unstuff = t1 - t0; info->ms_huffman = t2 - t1; info->ms_dequant = t3 - t2;
     info->ms_idct = t4 - t3; info->ms_colour = t5 - t4;
@@ -463,6 +472,219 @@ done:
     info->width = D->width; info->height = D->height; info->bw = D->bw; info->bh = D->bh;
     info->bwr = D->bwr; info->bhr = D->bhr; info->hs = D->hs; info->vs = D->vs;
     info->ncomp = D->ncomp; info->restart_interval = D->ri;
+  }
+  free(clean); free(mcus); free(D);
+  return rc;
+}
+
+/* ======================================================================================================================
+ * Progressive DCT (SOF2) -- ITU-T T.81 Annex G restatement.  PORT ONLY: the reference rejects SOF2 (jpeg.cpp:69-73), so
+ * there is no reference run of these functions.  What pins them instead (tests/test_oracle.py): a progressive file and
+ * its baseline twin written by the same encoder from the same pixels carry the SAME quantised coefficients, and the twin
+ * IS decoded by the reference binary -- coefficient dump and RGB must be identical.  Everything after the coefficients
+ * (dequantize, inverseDCT, YCbCrToRGB) is the reference's own path above (finish_pixels).
+ * Supported frames are the ones the rest of the port supports: 1 component, or 3 with only the first one subsampled.
+ * ==================================================================================================================== */
+typedef struct { int ns, ci[3], ss, se, ah, al; } pscan_t;
+
+/* entropy-coded bytes of ONE scan: FF00 -> FF, RSTn dropped (file.hpp:78-86), stops in front of any other marker */
+static long prog_unstuff(const uint8_t *s, size_t n, uint8_t *out, size_t *consumed) {
+  size_t i = 0, o = 0;
+  while (i < n) {
+    const unsigned char c = s[i];
+    if (c != 0xff) { out[o++] = c; i++; continue; }
+    if (i + 1 >= n) break;
+    const unsigned char m = s[i + 1];
+    if (m == 0x00) { out[o++] = 0xff; i += 2; }
+    else if (m >= 0xd0 && m <= 0xd7) i += 2;
+    else if (m == 0xff) i += 1;
+    else break;
+  }
+  *consumed = i;
+  return (long)o;
+}
+
+static int prog_receive_extend(dec_t *D, int s) {            /* T.81 F.2.2.1 EXTEND, as jpeg.cpp:335-343 */
+  int v = get_bit_n(D, s);
+  if (s != 0 && v < (1 << (s - 1))) v -= (1 << s) - 1;
+  return v;
+}
+
+/* G.1.2.1 / G.1.2.2 / G.1.2.3: one 8x8 block of one scan.  c = natural-order coefficients of the block. */
+static int prog_block(dec_t *D, const pscan_t *S, int32_t *c, int *pred, const htab_t *dct, const htab_t *act, int *eobrun) {
+  if (S->ss == 0) {                                           /* DC scan */
+    if (S->ah == 0) {
+      const int s = next_symbol(D, dct);
+      if (D->err) return D->err;
+      if (s > 11) return ORACLE_E_DC_LENGTH;
+      *pred += prog_receive_extend(D, s);
+      c[0] = *pred * (1 << S->al);
+    } else if (get_bit(D)) c[0] |= 1 << S->al;
+    return D->err;
+  }
+  if (S->ah == 0) {                                           /* AC first scan, G.1.2.2 */
+    if (*eobrun > 0) { --*eobrun; return 0; }
+    for (int k = S->ss; k <= S->se; ++k) {
+      const int rs = next_symbol(D, act);
+      if (D->err) return D->err;
+      const int r = rs >> 4, sz = rs & 15;
+      if (sz) {
+        k += r;
+        if (k > 63) return ORACLE_E_AC_RUN;
+        c[oracle_zigzag[k]] = prog_receive_extend(D, sz) * (1 << S->al);
+      } else if (r == 15) k += 15;
+      else { *eobrun = 1 << r; if (r) *eobrun += get_bit_n(D, r); --*eobrun; break; }
+    }
+    return D->err;
+  }
+  /* AC refinement scan, G.1.2.3 */
+  const int p1 = 1 << S->al, m1 = -(1 << S->al);
+  int k = S->ss;
+  if (*eobrun == 0) {
+    for (; k <= S->se; ++k) {
+      const int rs = next_symbol(D, act);
+      if (D->err) return D->err;
+      int r = rs >> 4, sz = rs & 15;
+      if (sz) sz = get_bit(D) ? p1 : m1;                      /* a newly non-zero coefficient: its sign */
+      else if (r != 15) { *eobrun = 1 << r; if (r) *eobrun += get_bit_n(D, r); break; }
+      do {                                                    /* skip r still-zero coefficients; correction bits for the others */
+        int32_t *q = &c[oracle_zigzag[k]];
+        if (*q != 0) { if (get_bit(D) && (*q & p1) == 0) *q += *q >= 0 ? p1 : m1; }
+        else if (--r < 0) break;
+        ++k;
+      } while (k <= S->se);
+      if (sz && k <= 63) c[oracle_zigzag[k]] = sz;
+    }
+  }
+  if (*eobrun > 0) {                                          /* rest of the band: correction bits only */
+    for (; k <= S->se; ++k) {
+      int32_t *q = &c[oracle_zigzag[k]];
+      if (*q != 0 && get_bit(D) && (*q & p1) == 0) *q += *q >= 0 ? p1 : m1;
+    }
+    --*eobrun;
+  }
+  return D->err;
+}
+
+static int prog_scan(dec_t *D, const pscan_t *S, int32_t *mcus) {
+  int pred[3] = {0, 0, 0}, eobrun = 0;
+  long unit = 0;                                              /* MCUs decoded in this scan, for the restart interval (E.2.4) */
+#define PROG_RESTART() do { if (D->ri && unit && unit % D->ri == 0) { pred[0] = pred[1] = pred[2] = 0; eobrun = 0; D->st_c = -1; } } while (0)
+  if (S->ns > 1) {                                            /* interleaved (DC scans): MCU order as jpeg.cpp:415-435 */
+    for (int y = 0; y < D->bh; y += D->vs)
+      for (int x = 0; x < D->bw; x += D->hs, ++unit) {
+        PROG_RESTART();
+        for (int j = 0; j < S->ns; ++j) {
+          const int i = S->ci[j];
+          for (int v = 0; v < D->comp[i].v; ++v)
+            for (int h = 0; h < D->comp[i].h; ++h) {
+              const int e = prog_block(D, S, PLANE(mcus, POS(D, y + v, x + h), i), &pred[i], &D->dc[D->comp[i].td],
+                                       &D->ac[D->comp[i].ta], &eobrun);
+              if (e) return e;
+            }
+        }
+      }
+    return 0;
+  }
+  /* one component: its blocks in raster order over ceil(component size / 8) (A.2.3); a chroma block lives at the anchor
+   * position of its MCU in the reference's layout (jpeg.cpp:426-435) */
+  const int i = S->ci[0];
+  const int lum = D->comp[i].h == D->hs && D->comp[i].v == D->vs && (i == 0);
+  const int cw = lum ? D->width : (D->width + D->hs - 1) / D->hs, ch = lum ? D->height : (D->height + D->vs - 1) / D->vs;
+  const int nbx = (cw + 7) / 8, nby = (ch + 7) / 8;
+  for (int by = 0; by < nby; ++by)
+    for (int bx = 0; bx < nbx; ++bx, ++unit) {
+      PROG_RESTART();
+      const size_t pos = lum ? POS(D, by, bx) : POS(D, by * D->vs, bx * D->hs);
+      const int e = prog_block(D, S, PLANE(mcus, pos, i), &pred[i], &D->dc[D->comp[i].td], &D->ac[D->comp[i].ta], &eobrun);
+      if (e) return e;
+    }
+  return 0;
+#undef PROG_RESTART
+}
+
+int oracle_decode_progressive(const uint8_t *file, size_t len, int flags, oracle_info *info, int32_t **coef_out,
+                              uint8_t **rgb_out) {
+  init_consts();
+  dec_t *D = (dec_t *)calloc(1, sizeof(dec_t));
+  D->d = file; D->n = len; D->flags = flags | ORACLE_F_SPEC; D->st_c = -1;
+  int rc = 0, got_frame = 0, nscans = 0;
+  uint8_t *clean = NULL; int32_t *mcus = NULL;
+  if (coef_out) *coef_out = NULL;
+  if (rgb_out) *rgb_out = NULL;
+  if (len < 2 || file[0] != 0xff || file[1] != 0xd8) { rc = ORACLE_E_NOT_JPEG; goto done; }
+  size_t pos = 2;
+  clean = (uint8_t *)malloc(len + 1);
+  for (;;) {
+    if (pos + 1 >= len) break;
+    if (file[pos] != 0xff) { rc = ORACLE_E_NO_SOS; goto done; }
+    const int m = file[pos + 1];
+    if (m == 0xff) { pos += 1; continue; }
+    pos += 2;
+    if (m == 0xd9) break;                                     /* EOI */
+    if (m == 0x00 || (m >= 0xd0 && m <= 0xd8)) continue;
+    if (pos + 2 > len) { rc = ORACLE_E_TRUNCATED; goto done; }
+    const int seglen = be16(file + pos);
+    const uint8_t *p = file + pos + 2;
+    const int plen = seglen - 2;
+    if (plen < 0 || pos + (size_t)seglen > len) { rc = ORACLE_E_TRUNCATED; goto done; }
+    pos += seglen;
+    switch (m) {
+      case 0xc2:                                              /* SOF2: same layout as SOF0 (B.2.2) */
+        rc = read_sof(D, 0xc0, p, plen); got_frame = 1;
+        if (!rc) mcus = (int32_t *)calloc((size_t)D->bwr * D->bhr * 3 * 64, sizeof(int32_t));
+        break;
+      case 0xc0: rc = ORACLE_E_PROGRESSIVE; break;            /* a baseline file: use oracle_decode */
+      case 0xc4: rc = read_dht(D, p, plen); break;
+      case 0xdb: rc = read_dqt(D, p, plen); break;
+      case 0xdd: if (plen != 2) rc = ORACLE_E_DRI; else D->ri = be16(p); break;
+      case 0xda: {
+        if (!got_frame || !mcus) { rc = ORACLE_E_NO_SOS; break; }
+        pscan_t S;
+        if (plen < 1) { rc = ORACLE_E_SOS; break; }
+        S.ns = p[0];
+        if (S.ns < 1 || S.ns > D->ncomp || plen != 1 + 2 * S.ns + 3) { rc = ORACLE_E_SOS; break; }
+        for (int j = 0; j < S.ns && !rc; ++j) {
+          int ci = -1;
+          for (int i = 0; i < D->ncomp; ++i) if (D->comp_id[i] == p[1 + 2 * j]) ci = i;
+          if (ci < 0) { rc = ORACLE_E_SOS; break; }
+          S.ci[j] = ci;
+          D->comp[ci].td = p[2 + 2 * j] >> 4; D->comp[ci].ta = p[2 + 2 * j] & 15;
+          if (D->comp[ci].td > 3 || D->comp[ci].ta > 3) rc = ORACLE_E_TABLE_ID;
+        }
+        if (rc) break;
+        const uint8_t *q = p + 1 + 2 * S.ns;
+        S.ss = q[0]; S.se = q[1]; S.ah = q[2] >> 4; S.al = q[2] & 15;
+        if (S.ss > S.se || S.se > 63 || (S.ss == 0 && S.se != 0) || (S.ss != 0 && S.ns != 1) || S.al > 13) { rc = ORACLE_E_SOS; break; }
+        for (int j = 0; j < S.ns; ++j) {                      /* the tables this scan names must exist (jpeg.cpp:757-774) */
+          const comp_t *c = &D->comp[S.ci[j]];
+          if (S.ss == 0 && S.ah == 0 && !D->dc[c->td].set) rc = ORACLE_E_TABLE_MISSING;
+          if (S.ss != 0 && !D->ac[c->ta].set) rc = ORACLE_E_TABLE_MISSING;
+        }
+        if (rc) break;
+        size_t used = 0;
+        const long n = prog_unstuff(file + pos, len - pos, clean, &used);
+        D->clean = clean; D->clean_n = (size_t)n; D->clean_pos = 0; D->st_c = -1; D->err = 0;
+        rc = prog_scan(D, &S, mcus);
+        pos += used; ++nscans;
+        break;
+      }
+      default: break;                                         /* APPn, COM, ... */
+    }
+    if (rc) goto done;
+  }
+  if (!got_frame || !nscans) { rc = ORACLE_E_NO_SOS; goto done; }
+  for (int i = 0; i < D->ncomp; i++) if (D->comp[i].tq > 3 || !D->q[D->comp[i].tq].set) { rc = ORACLE_E_TABLE_MISSING; goto done; }
+  {
+    double tt[3];
+    finish_pixels(D, mcus, coef_out, rgb_out, tt);
+  }
+done:
+  if (info) {
+    memset(info, 0, sizeof *info);
+    info->width = D->width; info->height = D->height; info->bw = D->bw; info->bh = D->bh;
+    info->bwr = D->bwr; info->bhr = D->bhr; info->hs = D->hs; info->vs = D->vs;
+    info->ncomp = D->ncomp; info->restart_interval = D->ri; info->scan_unstuffed = nscans;
   }
   free(clean); free(mcus); free(D);
   return rc;

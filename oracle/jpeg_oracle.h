@@ -66,6 +66,11 @@ typedef struct {
  * as display.hpp:19-34.  Free both with oracle_free(). */
 int oracle_decode(const uint8_t *file, size_t len, int flags, oracle_info *info,
                   int32_t **coef, uint8_t **rgb);
+/* Progressive DCT (SOF2), T.81 Annex G.  PORT ONLY: the reference rejects SOF2 (jpeg.cpp:69-73); pinned through baseline
+ * twins of the same coefficients that the reference binary does decode (tests/test_oracle.py).  Same outputs as
+ * oracle_decode; info->scan_unstuffed holds the number of scans. */
+int oracle_decode_progressive(const uint8_t *file, size_t len, int flags, oracle_info *info,
+                              int32_t **coef, uint8_t **rgb);
 void oracle_free(void *p);
 
 /* Stage-level entry points for unit tests. */

@@ -61,6 +61,8 @@ def _port():
                                       ctypes.POINTER(OracleInfo),
                                       ctypes.POINTER(ctypes.POINTER(ctypes.c_int32)),
                                       ctypes.POINTER(ctypes.POINTER(ctypes.c_uint8))]
+        lib.oracle_decode_progressive.restype = ctypes.c_int
+        lib.oracle_decode_progressive.argtypes = lib.oracle_decode.argtypes
         lib.oracle_free.argtypes = [ctypes.c_void_p]
         lib.oracle_idct_block.argtypes = [ctypes.c_void_p]
         lib.oracle_dequant_block.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
@@ -76,7 +78,12 @@ def have_ref():
     return os.path.exists(REF_BIN)
 
 
-def port_decode(data, flags=0, want_coef=True, want_rgb=True):
+def port_decode_progressive(data, want_coef=True, want_rgb=True):
+    """Progressive (SOF2) files through the Annex-G restatement (port only: the reference rejects them)."""
+    return port_decode(data, 0, want_coef, want_rgb, _fn="oracle_decode_progressive")
+
+
+def port_decode(data, flags=0, want_coef=True, want_rgb=True, _fn="oracle_decode"):
     """Decode ``data`` (bytes) with the C restatement.
 
     Returns ``(rc, info_dict, coef, rgb)``; ``coef`` is int32 ``[bwr*bhr, 3, 64]`` in the reference's
@@ -87,7 +94,7 @@ def port_decode(data, flags=0, want_coef=True, want_rgb=True):
     info = OracleInfo()
     pc = ctypes.POINTER(ctypes.c_int32)()
     pr = ctypes.POINTER(ctypes.c_uint8)()
-    rc = lib.oracle_decode(buf, len(data), flags, ctypes.byref(info),
+    rc = getattr(lib, _fn)(buf, len(data), flags, ctypes.byref(info),
                            ctypes.byref(pc) if want_coef else None,
                            ctypes.byref(pr) if want_rgb else None)
     coef = rgb = None

@@ -22,6 +22,14 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def golden_prog():
+    """Progressive fixtures (tests/golden/prog, made by make_prog_golden.py): digests the REFERENCE BINARY produced on the
+    baseline twin of each progressive file (same quantised coefficients, written as one scan)."""
+    with open(os.path.join(GOLDEN_DIR, "golden_prog.json")) as f:
+        return json.load(f)
+
+
+@pytest.fixture(scope="session")
 def oracle_mod():
     """The parity oracle (test infrastructure): C port always, reference binary when built."""
     from oracle import oracle

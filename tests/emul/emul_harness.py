@@ -58,3 +58,28 @@ def decode(datas, flags=0, want_coef=True, stress=False, path=0):
     if rc:
         raise RuntimeError("emu_decode_batch rc=%d" % rc)
     return list(st), rgbs, (coefs if want_coef else None), {"launches": info[0], "sync_rounds": info[1]}
+
+
+def decode_progressive(datas, want_coef=True):
+    """Progressive (SOF2) files through the emulation: same contract as Decoder.decode_progressive."""
+    L = _load()
+    L.emu_decode_progressive.restype = C.c_int
+    n = len(datas)
+    descs = (abi.ProgressiveDesc * n)()
+    bufs = [np.frombuffer(d, dtype=np.uint8).copy() for d in datas]
+    for i, b in enumerate(bufs):
+        rc = L.b200jpeg_parse_progressive(b.ctypes.data, len(b), C.byref(descs[i]))
+        if rc:
+            raise RuntimeError("parse_progressive rc=%d" % rc)
+    fr = [descs[i].frame for i in range(n)]
+    files = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+    sizes = (C.c_size_t * n)(*[len(b) for b in bufs])
+    rgbs = [np.zeros((f.image_height, f.image_width, 3), np.uint8) for f in fr]
+    coefs = [np.zeros((f.mcuWidthReal * f.mcuHeightReal, 3, 64), np.int16) for f in fr]
+    prgb = (C.c_void_p * n)(*[r.ctypes.data for r in rgbs])
+    pco = (C.c_void_p * n)(*[c.ctypes.data for c in coefs]) if want_coef else None
+    st = (C.c_int32 * n)()
+    rc = L.emu_decode_progressive(descs, n, files, sizes, prgb, pco, st)
+    if rc:
+        raise RuntimeError("emu_decode_progressive rc=%d" % rc)
+    return list(st), rgbs, (coefs if want_coef else None)

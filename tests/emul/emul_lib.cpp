@@ -20,3 +20,15 @@ extern "C" int emu_decode_batch(const b200jpeg_image_desc *descs, int n, const u
   P.destroy();
   return rc;
 }
+
+extern "C" int emu_decode_progressive(const b200jpeg_progressive_desc *descs, int n, const uint8_t *const *files, const size_t *sizes,
+                                      uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status) {
+  b2::Pipeline P;
+  int rc = P.prepare_progressive(descs, n, files, sizes);
+  if (rc) return rc;
+  rc = P.run_progressive();
+  if (rc) return rc;
+  rc = P.fetch(rgb_out, coef_out, status);
+  P.destroy();
+  return rc;
+}

@@ -167,3 +167,17 @@ def test_cli_many_files_through_the_pinned_feed(cli, oracle_mod, harness, tmp_pa
         raw = open(tmp_path / ("f%03d.ppm" % i), "rb").read()
         head = b"P6\n%d %d\n255\n" % (orgb.shape[1], orgb.shape[0])
         assert raw.startswith(head) and np.array_equal(np.frombuffer(raw[len(head):], np.uint8).reshape(orgb.shape), orgb), i
+
+
+@pytest.mark.gpu
+def test_cli_spec_mode_lifts_the_progressive_refusal(cli, oracle_mod, tmp_path):
+    # `b200jpeg file.jpg` refuses a progressive file like the reference (jpeg.cpp:69-73); `--spec` decodes it
+    src = os.path.join(GOLDEN_DIR, "prograssive-sample-2.jpg")
+    rc, out, err = run([cli, src, "--out-dir", str(tmp_path)])
+    assert rc == 1 and "not decodable, b200jpeg error -11" in err
+    rc, out, err = run([cli, src, os.path.join(GOLDEN_DIR, "img2.jpg"), "--out-dir", str(tmp_path), "--spec"])
+    assert rc == 0, err
+    _, _, _, orgb = oracle_mod.port_decode_progressive(open(src, "rb").read())
+    raw = open(tmp_path / "prograssive-sample-2.ppm", "rb").read()
+    head = b"P6\n%d %d\n255\n" % (orgb.shape[1], orgb.shape[0])
+    assert raw.startswith(head) and np.array_equal(np.frombuffer(raw[len(head):], np.uint8).reshape(orgb.shape), orgb)

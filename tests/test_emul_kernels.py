@@ -138,3 +138,20 @@ def test_sub_sizes_of_the_self_synchronising_path(emul, oracle_mod, harness):
     datas = [harness.synth_jpeg(71, 512, 384, 92, 2, 2, False, 0), harness.synth_jpeg(72, 400, 300, 90, 2, 1, False, 11),
              harness.synth_jpeg(73, 256, 256, 95, 1, 1, False, 1), fixture_bytes("img4.jpg")]
     check(emul, oracle_mod, datas, flags=1)
+
+
+def test_progressive_scans_against_reference_digests(emul, oracle_mod, golden_prog):
+    # kernels_prog.cuh (T.81 Annex G) through the emulation: the digests are the reference binary's, taken on each file's
+    # baseline twin (tests/golden/make_prog_golden.py); plus one of the reference's own progressive fixtures against the port
+    import hashlib
+    import os
+    from tests.conftest import GOLDEN_DIR
+    names = sorted(golden_prog)
+    datas = [open(os.path.join(GOLDEN_DIR, "prog", n + ".jpg"), "rb").read() for n in names] + [fixture_bytes("prograssive-sample-2.jpg")]
+    st, rgbs, coefs = emul.decode_progressive(datas)
+    assert st == [0] * len(datas)
+    sha = lambda a: hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+    for n, r, c in zip(names, rgbs, coefs):
+        assert sha(c.astype(np.int32)) == golden_prog[n]["coef_sha256"] and sha(r) == golden_prog[n]["rgb_sha256"], n
+    rc, _, oc, orgb = oracle_mod.port_decode_progressive(datas[-1])
+    assert rc == 0 and np.array_equal(coefs[-1].astype(np.int32), oc) and np.array_equal(rgbs[-1], orgb)

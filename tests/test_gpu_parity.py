@@ -248,3 +248,36 @@ def test_multi_device_entry_point(lib_so, oracle_mod, harness):
     dv = (C.c_int * len(devs))(*devs)
     assert lib.b200jpeg_decode_batch_multi(dv, len(devs), descs, n, files, sizes, prgb, st2) == 0
     assert list(st2) == [0] * n and all(np.array_equal(a, b) for a, b in zip(again, rgbs))
+
+
+def test_progressive_files(lib_so, oracle_mod, golden_prog):
+    """SOF2 files, which the reference refuses (jpeg.cpp:69-73).  Coefficients and pixels against the
+    digests the REFERENCE BINARY produced on each fixture's baseline twin; the reference's own two progressive fixtures
+    (427x640 and 2832x4256) against the Annex-G port ("port only"); a batch mixing sizes, formats, grey and restarts."""
+    import os
+    import jpeg_decoder_b200 as jd
+    from tests.conftest import GOLDEN_DIR
+    dec = jd.Decoder(0)
+    try:
+        names = sorted(golden_prog)
+        datas = [open(os.path.join(GOLDEN_DIR, "prog", n + ".jpg"), "rb").read() for n in names]
+        own = [fixture_bytes("prograssive-sample-2.jpg"), fixture_bytes("prograssive-sample.jpg")]
+        for rep in range(2):                                         # twice: the arenas are reused
+            st, rgbs, coefs = dec.decode_progressive(datas + own, want_coef=True)
+            assert st == [0] * (len(datas) + 2)
+            for n, r, c in zip(names, rgbs, coefs):
+                assert sha(c.astype(np.int32)) == golden_prog[n]["coef_sha256"], n
+                assert sha(r) == golden_prog[n]["rgb_sha256"], n
+        for d, r, c in zip(own, rgbs[len(datas):], coefs[len(datas):]):
+            rc, _, oc, orgb = oracle_mod.port_decode_progressive(d)
+            assert rc == 0 and np.array_equal(c.astype(np.int32), oc) and np.array_equal(r, orgb)
+        # a baseline batch right after, in the same context
+        st, rgbs, _ = dec.decode([fixture_bytes("img2.jpg")])
+        rc, _, _, orgb = oracle_mod.port_decode(fixture_bytes("img2.jpg"))
+        assert st == [0] and np.array_equal(rgbs[0], orgb)
+        # corrupt progressive scan: status bits, no crash
+        bad = bytearray(datas[0]); k = bad.rfind(b"\xff\xda"); bad[k + 20:k + 60] = bytes(40)
+        st, _, _ = dec.decode_progressive([bytes(bad), datas[1]])
+        assert st[1] == 0
+    finally:
+        dec.close()

@@ -31,13 +31,13 @@ def test_library_exports_every_declared_symbol(lib):
 def test_struct_sizes_match_header(lib_so):
     # compile a tiny C probe against the header and compare sizeof with the ctypes mirror
     import subprocess, tempfile
-    src = '#include "b200jpeg.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu\\n",sizeof(b200jpeg_huffman_table),sizeof(b200jpeg_quant_table),sizeof(b200jpeg_component),sizeof(b200jpeg_image_desc),sizeof(b200jpeg_batch_stats));return 0;}'
+    src = '#include "b200jpeg.h"\n#include <stdio.h>\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n",sizeof(b200jpeg_huffman_table),sizeof(b200jpeg_quant_table),sizeof(b200jpeg_component),sizeof(b200jpeg_image_desc),sizeof(b200jpeg_batch_stats),sizeof(b200jpeg_scan),sizeof(b200jpeg_progressive_desc));return 0;}'
     with tempfile.TemporaryDirectory() as td:
         open(os.path.join(td, "p.c"), "w").write(src)
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(td, "p"), os.path.join(td, "p.c")])
         got = [int(x) for x in subprocess.check_output([os.path.join(td, "p")]).split()]
     want = [C.sizeof(abi.HuffmanTable), C.sizeof(abi.QuantTable), C.sizeof(abi.Component), C.sizeof(abi.ImageDesc),
-            C.sizeof(abi.BatchStats)]
+            C.sizeof(abi.BatchStats), C.sizeof(abi.Scan), C.sizeof(abi.ProgressiveDesc)]
     assert got == want
 
 
@@ -169,3 +169,33 @@ def test_plan_rejects_malformed_hand_built_tables(lib, harness):
         info = (C.c_int32 * 3)()
         rc = L.emu_decode_batch(desc, 1, files, sizes, prgb, None, st, info)
         assert rc == {"offsets": abi.E_DHT, "table_id": abi.E_TABLE_ID, "quant": abi.E_ARG}[kind], (kind, rc)
+
+
+def test_parse_progressive(lib, golden_prog, harness):
+    """b200jpeg_parse_progressive: frame + scan list + table pool of SOF2 files; the baseline parser keeps the reference's
+    refusal (jpeg.cpp:69-73)."""
+    import jpeg_decoder_b200 as j
+    from tests.conftest import GOLDEN_DIR
+    for name, g in golden_prog.items():
+        data = open(os.path.join(GOLDEN_DIR, "prog", name + ".jpg"), "rb").read()
+        with pytest.raises(j.B200JpegError) as e:
+            j.parse_header(data, abi.PARSE_SPEC)
+        assert e.value.code == abi.E_PROGRESSIVE
+        buf = np.frombuffer(data, np.uint8)
+        d = abi.ProgressiveDesc()
+        assert lib.b200jpeg_parse_progressive(buf.ctypes.data, buf.size, C.byref(d)) == 0
+        assert (d.frame.image_width, d.frame.image_height, d.nscans) == (g["w"], g["h"], g["scans"])
+        assert d.ntables >= 2 and d.frame.scan_offset == d.scans[0].offset
+        end = 0
+        for k in range(d.nscans):
+            s = d.scans[k]
+            assert s.offset >= end and s.length > 0 and data[s.offset - 2 * s.ns - 7] == 0xDA            # right behind its SOS header
+            assert data[s.offset + s.length] == 0xFF and data[s.offset + s.length + 1] not in (0x00, 0xFF) + tuple(range(0xD0, 0xD8))
+            assert (s.ss == 0) == (s.se == 0) and (s.ns == 1 or s.ss == 0)
+            end = s.offset + s.length
+        if "rst" in name:
+            assert d.scans[0].restart_interval > 0
+    base = np.frombuffer(harness.synth_jpeg(6, 64, 48, 80, 2, 2, False, 0), np.uint8)
+    assert lib.b200jpeg_parse_progressive(base.ctypes.data, base.size, C.byref(abi.ProgressiveDesc())) == abi.E_ARG
+    junk = np.frombuffer(b"\x00\x01\x02", np.uint8)
+    assert lib.b200jpeg_parse_progressive(junk.ctypes.data, junk.size, C.byref(abi.ProgressiveDesc())) == abi.E_NOT_JPEG

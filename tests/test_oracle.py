@@ -114,3 +114,33 @@ def test_port_matches_live_reference_on_quirk_inputs(oracle_mod, harness):
     assert rc == 0 and np.array_equal(c, pc) and np.array_equal(r, pr)
     rc, _, sc, sr = oracle_mod.port_decode(w, flags=oracle_mod.F_SPEC)       # T.81: the whole 16-bit value
     assert rc == 0 and np.array_equal(sc, pc) and not np.array_equal(sr, pr)
+
+
+def test_progressive_port_is_pinned_through_baseline_twins(oracle_mod, golden_prog):
+    """SOF2 (T.81 Annex G) restatement.  The reference refuses progressive files (jpeg.cpp:69-73), so the witness is
+    indirect: Pillow wrote each fixture twice from the same pixels, progressive and baseline -- the same quantised
+    coefficients -- and the digests in golden_prog.json come from the REFERENCE BINARY on the baseline twin."""
+    import os
+    from tests.conftest import GOLDEN_DIR
+    for name, g in golden_prog.items():
+        prog = open(os.path.join(GOLDEN_DIR, "prog", name + ".jpg"), "rb").read()
+        twin = open(os.path.join(GOLDEN_DIR, "prog", name + "_twin.jpg"), "rb").read()
+        assert hashlib.sha256(prog).hexdigest() == g["prog_sha256"] and hashlib.sha256(twin).hexdigest() == g["twin_sha256"]
+        assert oracle_mod.port_decode(prog, flags=1)[0] == -2                      # the baseline entry point still refuses it
+        rc, info, coef, rgb = oracle_mod.port_decode_progressive(prog)
+        assert rc == 0 and info["scan_unstuffed"] == g["scans"]
+        assert sha(coef) == g["coef_sha256"] and sha(rgb) == g["rgb_sha256"], name
+        rc, _, tc, tr = oracle_mod.port_decode(twin, flags=1)
+        assert rc == 0 and np.array_equal(tc, coef) and np.array_equal(tr, rgb), name
+        if oracle_mod.have_ref() and g["witness"].startswith("reference"):
+            _, rcf, rrgb = oracle_mod.ref_dump(twin)                                # the live reference binary, here
+            assert sha(rcf) == g["coef_sha256"] and sha(rrgb) == g["rgb_sha256"], name
+
+
+def test_progressive_port_decodes_the_references_own_fixtures(oracle_mod):
+    # images/prograssive-sample*.jpg: the files the reference ships and refuses.  No pixel oracle exists for them; this
+    # checks geometry, scan count and that the result is a picture (low-frequency energy in every component)
+    for name, (w, h, scans) in {"prograssive-sample-2.jpg": (427, 640, 8), "prograssive-sample.jpg": (2832, 4256, 10)}.items():
+        rc, info, coef, rgb = oracle_mod.port_decode_progressive(fixture_bytes(name))
+        assert rc == 0 and (info["width"], info["height"], info["scan_unstuffed"]) == (w, h, scans)
+        assert rgb.std() > 20 and np.abs(coef[:, 0, 0]).max() > 100

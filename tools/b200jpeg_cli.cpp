@@ -3,7 +3,8 @@
 // Reads the JPEGs (all of them at once: one pinned arena, host threads), decodes them on N GPUs (contiguous ranges of
 // the files, one context and host thread per GPU) and writes <name>.ppm (or .bmp) into --out-dir instead of opening an
 // X11 window (display.hpp:49-120; unavailable on this box).  Exit code 1 on a usage error or an undecodable file, like
-// the reference.
+// the reference.  --spec: the superset of what the reference accepts (grey, COM segments, any component ids, 16-bit DQT)
+// INCLUDING progressive files, which the reference refuses (jpeg.cpp:69-73).
 #include <chrono>
 #include <iostream>
 #include <string>
