@@ -7,12 +7,18 @@
 // leave there -- int16 coef[block][64], blocks in the interleaved MCU order, zig-zag order inside a block, 16-byte chunks
 // XOR-swizzled by (block & 7) -- and the pixel stage (kernels_pixel.cuh) runs unchanged.
 //
-// Shape: ONE THREAD per (image, scan); the scans of an image are launched one after another (a refinement scan reads what
-// the scans before it wrote), the images of a batch side by side.  Nothing here is parallel inside a scan: end-of-band runs
-// and correction bits make the position of every symbol depend on coefficient VALUES decoded earlier, so the
-// self-synchronising construction of kernels_entropy.cuh does not carry over as is.  Correct, not fast: a first version.
-// The bit reader walks the STUFFED bytes (FF00 -> FF inline; RSTn at restart boundaries: file.hpp:78-86), so stage U is
-// not needed.  Symbols are found by the canonical per-length search (huffman.hpp:17-29 / jpeg.cpp:303-318).
+// Shape: ONE WARP per (image, scan); lane 0 walks the scan, all 32 lanes build its lookup tables and fetch its blocks.
+// Scans are launched by dependency LEVEL: a scan depends on the earlier scans of the same component whose band overlaps
+// its own (a refinement reads what they wrote); scans that touch disjoint (component, band) sets -- the DC scan, the first
+// AC bands of Y, Cb, Cr -- run side by side, as do the images of a batch.  The usual ten-scan script has three levels.
+// Nothing is parallel INSIDE a scan: end-of-band runs and correction bits make the position of every symbol depend on
+// coefficient VALUES decoded earlier, so the self-synchronising construction of kernels_entropy.cuh does not carry over as
+// is.  Correct first, then quick where it was cheap: a 9-bit symbol table per Huffman table in shared memory (longer codes
+// by the canonical per-length search, huffman.hpp:17-29 / jpeg.cpp:303-318), the stuffed bytes pulled as 16-byte
+// vectors (FF00 -> FF inline; RSTn at restart boundaries: file.hpp:78-86; stage U is not needed), and for refinement scans
+// a 64-bit non-zero mask of the block from eight independent vector loads instead of one dependent load per coefficient.
+// Measured (profiles/r02_progressive_time.jsonl): these took a 12-megapixel file from 3.2 s to 1.5 s; a software prefetch
+// of the blocks ahead changed nothing -- the limit is the instruction chain of one thread, not memory latency.
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -26,6 +32,8 @@ struct ProgScanDev {
   int32_t ss, se, ah, al;
   int32_t restart_interval;
   uint32_t offset, length;              // the scan's stuffed bytes, relative to the image's first scan byte in d_raw
+  int32_t level;                        // dependency level: runs after every overlapping earlier scan of its components
+  int32_t pad;
 };
 constexpr int kProgMaxScans = 48;       // B200JPEG_PROG_MAX_SCANS
 struct ProgImageDev {
@@ -35,20 +43,35 @@ struct ProgImageDev {
 };
 
 struct ProgBits {
-  const uint8_t *p, *end;
+  const uint4 *base;    // 16-byte aligned; positions below are byte offsets from it
+  uint32_t pos, end;
+  uint4 c;              // the vector that holds byte `cidx * 16 ...`
+  uint32_t cidx;
   uint32_t buf;         // left-aligned: the next bit is bit 31
   int cnt;              // valid bits in buf
-  B2_MEMBER void init(const uint8_t *b, const uint8_t *e) { p = b; end = e; buf = 0; cnt = 0; }
+  B2_MEMBER void init(const uint8_t *b, uint32_t len) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(b);
+    base = reinterpret_cast<const uint4 *>(a & ~(uintptr_t)15);
+    pos = (uint32_t)(a & 15); end = pos + len;
+    cidx = 0xffffffffu; buf = 0; cnt = 0;
+    c = make_uint4(0, 0, 0, 0);
+  }
+  B2_MEMBER uint32_t byte_at(uint32_t q) {            // q < end (the scan buffer has slack behind the last image)
+    if ((q >> 4) != cidx) { cidx = q >> 4; c = b2_ld_nc_v4(base + cidx); }
+    const uint32_t k = (q >> 2) & 3u;
+    const uint32_t w = k == 0 ? c.x : (k == 1 ? c.y : (k == 2 ? c.z : c.w));
+    return (w >> (8u * (q & 3u))) & 0xffu;
+  }
   B2_MEMBER void fill() {
     while (cnt <= 24) {
       uint32_t byte = 0;
-      if (p < end) {
-        byte = *p;
+      if (pos < end) {
+        byte = byte_at(pos);
         if (byte == 0xffu) {
-          const uint32_t nx = p + 1 < end ? p[1] : 0xd9u;
-          if (nx == 0u) p += 2;                       // stuffed zero (file.hpp:78-82)
-          else { byte = 0; }                          // a marker (RSTn or the end of the scan): feed zeros, stay in front of it
-        } else ++p;
+          const uint32_t nx = pos + 1 < end ? byte_at(pos + 1) : 0xd9u;
+          if (nx == 0u) pos += 2;                     // stuffed zero (file.hpp:78-82)
+          else byte = 0;                              // a marker (RSTn or the end of the scan): feed zeros, stay in front of it
+        } else ++pos;
       }
       buf |= byte << (24 - cnt);
       cnt += 8;
@@ -66,13 +89,33 @@ struct ProgBits {
   B2_MEMBER uint32_t bit() { return bits(1); }
   B2_MEMBER void restart() {                          // byte-align (BitStream::align, file.hpp:161-164) and step over RSTn
     buf = 0; cnt = 0;
-    if (p + 1 < end && p[0] == 0xffu && p[1] >= 0xd0u && p[1] <= 0xd7u) p += 2;
+    if (pos + 1 < end && byte_at(pos) == 0xffu) { const uint32_t m = byte_at(pos + 1); if (m >= 0xd0u && m <= 0xd7u) pos += 2; }
   }
 };
 
-// one Huffman symbol: first match by increasing length (jpeg.cpp:303-318); 0x100 | flags when no code matches
-B2_DEVICE uint32_t prog_symbol(ProgBits &B, const HuffSpec &spec) {
+// A Huffman table as the scan walker sees it: 512 entries on the next 9 bits (length << 8 | symbol; 0 = a longer code) in
+// shared memory, the DHT data behind it for the rest.
+constexpr int kProgLutBits = 9;
+struct ProgTable { const uint16_t *lut; const HuffSpec *spec; };
+B2_DEVICE void prog_build_lut(uint16_t *lut, const HuffSpec &spec, int lane) {   // all 32 lanes of the warp
+  for (int idx = lane; idx < (1 << kProgLutBits); idx += 32) {
+    uint32_t code = 0, e = 0;
+    for (int l = 1; l <= kProgLutBits; ++l) {
+      const uint32_t cnt = (uint32_t)spec.offset[l] - (uint32_t)spec.offset[l - 1];
+      const uint32_t k = ((uint32_t)idx >> (kProgLutBits - l)) - code;
+      if (k < cnt) { e = ((uint32_t)l << 8) | spec.symbols[spec.offset[l - 1] + k]; break; }
+      code = (code + cnt) << 1;
+    }
+    lut[idx] = (uint16_t)e;
+  }
+}
+
+// one Huffman symbol: first match by increasing length (jpeg.cpp:303-318); 0x100 when no code matches
+B2_DEVICE uint32_t prog_symbol(ProgBits &B, const ProgTable &T) {
   const uint32_t w = B.peek16();
+  const uint32_t e = T.lut[w >> (16 - kProgLutBits)];
+  if (e) { B.skip((int)(e >> 8)); return e & 0xffu; }
+  const HuffSpec &spec = *T.spec;
   uint32_t code = 0;
   for (int l = 1; l <= 16; ++l) {
     const uint32_t cnt = (uint32_t)spec.offset[l] - (uint32_t)spec.offset[l - 1];
@@ -93,8 +136,24 @@ B2_DEVICE int16_t *prog_coef(int16_t *coef, int64_t gb, int k) {
 }
 
 // one block of one scan; returns status bits
-B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, int64_t gb, int &pred, const HuffSpec *dct,
-                              const HuffSpec *act, int &eobrun) {
+// 64-bit map of the block's non-zero coefficients (bit k = zig-zag index k), from eight independent 16-byte loads
+B2_DEVICE uint64_t prog_nonzero_mask(const int16_t *coef, int64_t gb) {
+  const uint4 *b = reinterpret_cast<const uint4 *>(coef + gb * 64);
+  uint64_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint4 v = b[j ^ (int)(gb & 7)];             // logical chunk j (zig-zag 8j .. 8j+7) sits at j ^ (block & 7)
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t bits = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) bits |= ((w[q] & 0xffffu) ? 1u : 0u) << (2 * q) | ((w[q] >> 16) ? 1u : 0u) << (2 * q + 1);
+    m |= (uint64_t)bits << (8 * j);
+  }
+  return m;
+}
+
+B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, int64_t gb, int &pred, const ProgTable *dct,
+                              const ProgTable *act, int &eobrun) {
   if (S.ss == 0) {                                    // DC scans, G.1.2.1
     if (S.ah == 0) {
       const uint32_t s = prog_symbol(B, *dct);
@@ -122,8 +181,10 @@ B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, 
     }
     return 0;
   }
-  // AC refinement scan, G.1.2.3
+  // AC refinement scan, G.1.2.3.  Which coefficients are already non-zero decides where every bit goes: one mask up front
+  // (a coefficient this scan makes non-zero is never revisited by it, so the mask stays valid for the block)
   const int p1 = 1 << S.al, m1 = -(1 << S.al);
+  const uint64_t nz = prog_nonzero_mask(coef, gb);
   int k = S.ss;
   if (eobrun == 0) {
     for (; k <= S.se; ++k) {
@@ -133,39 +194,44 @@ B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, 
       if (sz) sz = B.bit() ? p1 : m1;                 // a newly non-zero coefficient: its sign
       else if (r != 15) { eobrun = 1 << r; if (r) eobrun += (int)B.bits(r); break; }
       do {                                            // skip r still-zero coefficients; correction bits for the others
-        int16_t *q = prog_coef(coef, gb, k);
-        const int c = *q;
-        if (c != 0) { if (B.bit() && (c & p1) == 0) *q = (int16_t)(c + (c >= 0 ? p1 : m1)); }
-        else if (--r < 0) break;
+        if ((nz >> k) & 1u) {
+          if (B.bit()) { int16_t *q = prog_coef(coef, gb, k); const int c = *q; if ((c & p1) == 0) *q = (int16_t)(c + (c >= 0 ? p1 : m1)); }
+        } else if (--r < 0) break;
         ++k;
       } while (k <= S.se);
       if (sz && k <= 63) *prog_coef(coef, gb, k) = (int16_t)sz;
     }
   }
   if (eobrun > 0) {                                   // rest of the band: correction bits only
-    for (; k <= S.se; ++k) {
-      int16_t *q = prog_coef(coef, gb, k);
-      const int c = *q;
-      if (c != 0 && B.bit() && (c & p1) == 0) *q = (int16_t)(c + (c >= 0 ? p1 : m1));
-    }
+    for (; k <= S.se; ++k)
+      if (((nz >> k) & 1u) && B.bit()) { int16_t *q = prog_coef(coef, gb, k); const int c = *q; if ((c & p1) == 0) *q = (int16_t)(c + (c >= 0 ? p1 : m1)); }
     --eobrun;
   }
   return 0;
 }
 
-// scan number `scan_no` of every image that has one; thread t = image t
-B2_GLOBAL void k_prog_scan(const ImageDev *__restrict__ imgs, const ProgImageDev *__restrict__ pimgs, int nimg, int scan_no,
-                           const HuffSpec *__restrict__ tables, const uint8_t *__restrict__ d_raw, int16_t *__restrict__ coef,
-                           ImageOut *__restrict__ out) {
-  const int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+// One warp per (image, scan slot); only the scans of dependency level `level` run.  Lane 0 walks the scan.
+B2_GLOBAL void __launch_bounds__(32)
+k_prog_scan(const ImageDev *__restrict__ imgs, const ProgImageDev *__restrict__ pimgs, int nimg, int max_scans, int level,
+            const HuffSpec *__restrict__ tables, const uint8_t *__restrict__ d_raw, int16_t *__restrict__ coef,
+            ImageOut *__restrict__ out) {
+  B2_SHARED uint16_t s_lut[3][1 << kProgLutBits];
+  const int i = (int)blockIdx.x / max_scans, scan_no = (int)blockIdx.x % max_scans, lane = threadIdx.x;
   if (i >= nimg) return;
   const ProgImageDev &pi = pimgs[i];
-  if (scan_no >= pi.nscans) return;
+  if (scan_no >= pi.nscans || pi.scans[scan_no].level != level) return;
   const ImageDev &im = imgs[i];
   const ProgScanDev &S = pi.scans[scan_no];
+  ProgTable T[3];                                     // per scan component: the one table the scan needs of it (DC first: DC, AC scans: AC)
+  for (int j = 0; j < 3; ++j) {
+    const int t = j < S.ns ? (S.ss == 0 ? S.dc_table[j] : S.ac_table[j]) : -1;
+    T[j].lut = s_lut[j]; T[j].spec = t >= 0 ? &tables[t] : nullptr;
+    if (t >= 0) prog_build_lut(s_lut[j], tables[t], lane);
+  }
+  __syncwarp();
+  if (lane != 0) return;
   ProgBits B;
-  const uint8_t *base = d_raw + im.raw_off;
-  B.init(base + S.offset, base + S.offset + S.length);
+  B.init(d_raw + im.raw_off + S.offset, S.length);
   const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
   int pred[3] = {0, 0, 0}, eobrun = 0;
   uint32_t err = 0;
@@ -178,8 +244,7 @@ B2_GLOBAL void k_prog_scan(const ImageDev *__restrict__ imgs, const ProgImageDev
         const int c = S.comp[j];
         const int first = c == 0 ? 0 : nluma + c - 1, cnt = c == 0 ? nluma : 1;
         for (int b = 0; b < cnt && !err; ++b)
-          err |= prog_block(B, S, coef, im.coef_base + m * im.bpm + first + b, pred[c],
-                            S.dc_table[j] >= 0 ? &tables[S.dc_table[j]] : nullptr, S.ac_table[j] >= 0 ? &tables[S.ac_table[j]] : nullptr, eobrun);
+          err |= prog_block(B, S, coef, im.coef_base + m * im.bpm + first + b, pred[c], &T[j], &T[j], eobrun);
       }
     }
   } else {                                            // one component: its blocks in raster order over ceil(component size / 8) (A.2.3)
@@ -187,15 +252,15 @@ B2_GLOBAL void k_prog_scan(const ImageDev *__restrict__ imgs, const ProgImageDev
     const bool lum = c == 0;
     const int cw = lum ? im.width : (im.width + im.hs - 1) / im.hs, ch = lum ? im.height : (im.height + im.vs - 1) / im.vs;
     const int nbx = (cw + 7) / 8, nby = (ch + 7) / 8;
-    const HuffSpec *dct = S.dc_table[0] >= 0 ? &tables[S.dc_table[0]] : nullptr, *act = S.ac_table[0] >= 0 ? &tables[S.ac_table[0]] : nullptr;
+    auto block_of = [&](int by, int bx) -> int64_t {
+      if (lum && im.ncomp == 3) return ((int64_t)(by / im.vs) * im.mcux + bx / im.hs) * im.bpm + (by % im.vs) * im.hs + bx % im.hs;
+      if (lum) return (int64_t)by * im.mcux + bx;
+      return ((int64_t)by * im.mcux + bx) * im.bpm + nluma + c - 1;
+    };
     for (int by = 0; by < nby && !err; ++by)
       for (int bx = 0; bx < nbx && !err; ++bx, ++unit) {
         if (S.restart_interval && unit && unit % S.restart_interval == 0) { pred[0] = pred[1] = pred[2] = 0; eobrun = 0; B.restart(); }
-        int64_t blk;
-        if (lum && im.ncomp == 3) blk = ((int64_t)(by / im.vs) * im.mcux + bx / im.hs) * im.bpm + (by % im.vs) * im.hs + bx % im.hs;
-        else if (lum) blk = (int64_t)by * im.mcux + bx;
-        else blk = ((int64_t)by * im.mcux + bx) * im.bpm + nluma + c - 1;
-        err |= prog_block(B, S, coef, im.coef_base + blk, pred[c], dct, act, eobrun);
+        err |= prog_block(B, S, coef, im.coef_base + block_of(by, bx), pred[c], &T[0], &T[0], eobrun);
       }
   }
   if (err) atomicOr(&out[i].status, err);

@@ -17,7 +17,7 @@ struct Pipeline {
   DevBuf d_sub_e, d_sub_used, d_sub_info, d_cta_tot, d_cta_pre, d_bnd[2], d_flags, d_coef, d_rgb, d_export;
   DevBuf d_segsub, d_segunit, d_x_img, d_x_sub_base, d_x_unit_base, d_xunits;   // self-synchronising path
   DevBuf d_pimgs, d_ptables;                                                      // progressive files (kernels_prog.cuh)
-  int prog_max_scans = 0;
+  int prog_max_scans = 0, prog_levels = 0;
   DevBuf d_grp_img[PF_COUNT], d_grp_pre[PF_COUNT];
   DevBuf d_units, d_luts;
   int force_path = kForceAuto;
@@ -151,7 +151,7 @@ struct Pipeline {
     std::vector<b200jpeg_image_desc> frames((size_t)n);
     std::vector<ProgImageDev> pimgs((size_t)n);
     std::vector<HuffSpec> tables;
-    int max_scans = 0;
+    int max_scans = 0, max_levels = 0;
     for (int i = 0; i < n; ++i) {
       const b200jpeg_progressive_desc &d = descs[i];
       if (d.nscans < 1 || d.nscans > kProgMaxScans || d.ntables < 0 || d.ntables > B200JPEG_PROG_MAX_TABLES) return B200JPEG_E_ARG;
@@ -188,6 +188,15 @@ struct Pipeline {
           if (need_dc) o.dc_table[j] = tbase + S.dc_table[j];
           if (need_ac) o.ac_table[j] = tbase + S.ac_table[j];
         }
+        // dependency level: after every earlier scan that shares a component and whose band overlaps this one
+        o.level = 0;
+        for (int t = 0; t < k; ++t) {
+          const ProgScanDev &e = pi.scans[t];
+          bool shares = false;
+          for (int a = 0; a < o.ns; ++a) for (int b = 0; b < e.ns; ++b) shares = shares || o.comp[a] == e.comp[b];
+          if (shares && o.ss <= e.se && e.ss <= o.se && e.level + 1 > o.level) o.level = e.level + 1;
+        }
+        if (o.level + 1 > max_levels) max_levels = o.level + 1;
       }
       if (d.nscans > max_scans) max_scans = d.nscans;
     }
@@ -201,7 +210,7 @@ struct Pipeline {
     be.sync();                                     // pimgs / tables are host temporaries
     h2d_bytes += (int64_t)(sizeof(ProgImageDev) * (size_t)n + sizeof(HuffSpec) * tables.size());
     if (!be.ok()) return B200JPEG_E_CUDA;
-    prog_max_scans = max_scans;
+    prog_max_scans = max_scans; prog_levels = max_levels;
     prepared = true;
     return 0;
   }
@@ -218,9 +227,9 @@ struct Pipeline {
     ++launches;
     be.fill(d_coef.p, 0, 128 * (size_t)P.nblocks);   // scans only ever write the coefficients they carry (MCU[] starts at zero, jpeg.cpp:407)
     mark(1); mark(2);
-    for (int k = 0; k < prog_max_scans; ++k) {        // scan k of every image; later scans refine what earlier ones wrote
-      B2_LAUNCH(k_prog_scan, (P.n + 31) / 32, 32, 0, be.stream, d_imgs.as<ImageDev>(), d_pimgs.as<ProgImageDev>(), P.n, k,
-                d_ptables.as<HuffSpec>(), d_raw.as<uint8_t>(), d_coef.as<int16_t>(), d_out.as<ImageOut>());
+    for (int lv = 0; lv < prog_levels; ++lv) {        // one warp per (image, scan); a level's scans do not depend on each other
+      B2_LAUNCH(k_prog_scan, P.n * prog_max_scans, 32, 0, be.stream, d_imgs.as<ImageDev>(), d_pimgs.as<ProgImageDev>(), P.n,
+                prog_max_scans, lv, d_ptables.as<HuffSpec>(), d_raw.as<uint8_t>(), d_coef.as<int16_t>(), d_out.as<ImageOut>());
       ++launches;
     }
     mark(3);
