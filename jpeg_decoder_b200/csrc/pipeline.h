@@ -155,7 +155,7 @@ inline void choose_x_params(int64_t total_bits, XParams &x) {
   (void)total_bits;
 #else
   int ss = kXMinShift;
-  while (ss < 13 && (total_bits >> ss) > (int64_t)148 * 4 * kXT) ++ss;
+  while (ss < 13 && (total_bits >> ss) > (int64_t)148 * 4 * kXT * 11 / 10) ++ss;   // up to 10 % over one wave: 78 k subs of 2^12 beat 39 k of 2^13 (C4)
   x.sub_shift = ss; x.unit_subs = 1; x.overlap = 2048;
 #ifdef B200JPEG_TUNING
   if (const char *ev = getenv("B200JPEG_XSUB")) { const int v = atoi(ev); if (v >= kXMinShift && v <= kXMaxShift) x.sub_shift = v; }
