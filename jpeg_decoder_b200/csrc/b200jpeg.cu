@@ -140,8 +140,9 @@ int b200jpeg_sync(b200jpeg_ctx *c) {
 // device copies crawl (their read requests queue behind the posted writes: 19 MB took 2.1 ms in the CUPTI trace), so
 // a chunk needs about as long as a chunk's RGB copy to get ready -- with only two pipelines the RGB engine ran dry
 // for 0.6 ms per pair of chunks; and the first RGB byte leaves once the first (small) chunk is decoded.
-// The entropy decoder is chosen ONCE, over the whole call: chunks of one call are in flight together, so what fills
-// the device is the call, not the chunk.
+// The entropy decoder is chosen ONCE per call, for what is resident on the device at a time: nslots chunks (not one chunk,
+// which would ignore its neighbours in flight; not the whole call, whose chunks never meet: a 16-image chunk handed to the
+// segment decoder takes a full chain's time, 1.7 ms, for 1088 segments -- measured 31.39 ms per C2 call against 31.12).
 // copies_only: the same copies with no kernel in between (b200jpeg_copy_floor).
 static int decode_batch_impl(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, int n, const uint8_t *const *files,
                              const size_t *sizes, uint8_t *const *rgb_out, int16_t *const *coef_out, int32_t *status,
@@ -170,7 +171,8 @@ static int decode_batch_impl(b200jpeg_ctx *c, const b200jpeg_image_desc *descs, 
   b200jpeg_batch_stats a;
   memset(&a, 0, sizeof a);
   const int user_force = c->pipe.force_path;
-  const int call_path = b2::choose_path(descs, n, user_force) == b2::kPathSegment ? b2::kForceSegment : b2::kForceSync;
+  const int window = n < chunk * nslots ? n : chunk * nslots;
+  const int call_path = b2::choose_path(descs, window, user_force) == b2::kPathSegment ? b2::kForceSegment : b2::kForceSync;
   for (b2::Pipeline *p : slot) { p->force_path = call_path; p->copies_only = copies_only; }
   const bool timing0 = c->pipe.timing;     // per-stage event times are a single-batch facility
   int rc = 0;
