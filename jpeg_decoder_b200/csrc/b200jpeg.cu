@@ -433,3 +433,12 @@ extern "C" int b200jpeg_export_coefficients_noalloc(b200jpeg_ctx *c, int i, int1
   p.be.check("b200jpeg_export_coefficients_noalloc");
   return fail(c, p.be.ok() ? 0 : B200JPEG_E_CUDA);
 }
+
+#if B2_SEG_DIAG == 7
+// measurements only (build_variant.sh -DB2_SEG_DIAG=7): the decoder warps' cycle counters, read and cleared
+extern "C" int b200jpeg_debug_seg_diag(unsigned long long *out24) {
+  unsigned long long z[24] = {};
+  if (cudaMemcpyFromSymbol(out24, b2::g_seg_diag, sizeof z) != cudaSuccess) return -1;
+  return cudaMemcpyToSymbol(b2::g_seg_diag, z, sizeof z) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -22,7 +22,10 @@
 //     PREDICATE once per round -- nine symbols consume at most 243 bits, one top-up brings 256;
 //   * DC or AC table by a select, block end and segment end by selects;
 //   * an entry the first-level table cannot resolve (a code longer than kHLutBits: 0.5 % of the symbols) makes the
-//     lane wait in place for the round's extra slot, where one warp-uniform branch resolves it;
+//     lane wait in place for the round's NINTH step, which is a step like the others plus a predicated look into the
+//     table's second level: the waiting lane gets its symbol, every other lane one more symbol (a branch taken by
+//     "whoever is stuck" ran in 72 % of the rounds and cost as much as one and a half steps while decoding nothing for
+//     31 lanes: 5.8 % of the kernel);
 //   * AC entries that hold two complete symbols inside the index bits are taken in one step (kernels_huff.cuh).
 //
 // (2) Only what the chain needs stays on the chain.  A group of 32 segments is worked on by four warps of the
@@ -33,8 +36,13 @@
 //                 position.  They keep no state between symbols -- everything they need is in the FIFO entry; a
 //                 DC symbol is a value for position 0 like any other: its DIFFERENCE goes into the block;
 //       flusher   sends finished blocks to global memory (3).  A lane's blocks pass through it in order, so this is
-//                 where the DC prediction per component (jpeg.cpp:335-345) and its range check happen.
+//                 where the DC prediction per component (jpeg.cpp:335-345) and its range check happen.  It never
+//                 touches the FIFO: the writer of a round passes on what the flusher needs of it (blocks finished per
+//                 lane, last round or not), so that the decoder waits for the writers only.
 //     Every hand-over is an mbarrier in shared memory: a waiting warp is suspended by the hardware.
+//     What bounds the kernel (ncu, profiles/): the four warps of a group share one SM sub-partition, whose integer
+//     pipe takes one warp instruction every two cycles and is busy 66-74 % of the time -- the decoder's chain and the
+//     consumers' arithmetic compete for it, and instruction COUNT, not latency hiding, is what is left to gain.
 //
 // (3) Coefficients leave the SM as whole 128-byte blocks.  A 2-byte store per coefficient from 32 lanes that work on
 //     32 different segments is 32 sectors per instruction: one L1 tag cycle each (233 M sectors per bench step = 0.8 ms
@@ -89,21 +97,26 @@ constexpr uint32_t kSegNoUnit = 0xffffffffu;
 constexpr int kSegWords = 32;                 // stream words per lane in the window ring (+ one slot that repeats slot 0)
 constexpr int kSegFifo = B2_SEG_FIFO;         // rounds the FIFO holds
 constexpr int kSegSteps = 8;                  // symbols per lane and round: the per-round work (top-up, hand-over) is paid once per 8 steps
-constexpr int kSegSlots = kSegSteps + 1;      // FIFO slots per round: the steps + one for symbols the first-level table does not resolve
+constexpr int kSegSlots = kSegSteps + 1;      // FIFO slots per round: the steps + the ninth, which also looks into the tables' second level
 constexpr int kSegSlotBytes = 3 * 128;        // one slot: (window, entry, zig-zag index | block number) x 32 lanes
-constexpr int kSegRoundBytes = kSegSlots * kSegSlotBytes + 128;   // + per lane: blocks finished after the round << 1 | decoder has finished
+constexpr int kSegRoundBytes = kSegSlots * kSegSlotBytes + 128;   // + the round's last word per lane (kSegTailNbShift)
+constexpr int kSegMaxFin = (kSegSlots + 1) / 2;   // blocks a lane can FINISH in one round: a block is a DC symbol and at least one more
+constexpr int kSegCopyDepth = 3;              // blocks per thread-octet and pass of the flusher's copy loop (2, 3, 4: the same time)
 constexpr int kSegAsm = 8;                    // block images per lane in the assembly ring; a round touches at most 6 blocks of a lane
 constexpr int kSegUnroll = B2_SEG_UNROLL;     // how far the decoder's step loop is unrolled (instruction-cache footprint)
 constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
 // third FIFO word of a step: zig-zag index before the symbol | two symbols taken << 6 | block number << 7
 constexpr uint32_t kSegPairBit = 1u << 6;
 constexpr int kSegNbShift = 7;
+// last word of a round, per lane: blocks finished after the round << 4 | blocks finished IN the round << 1 | the decoder has finished
 constexpr uint32_t kSegFinFlag = 1u;
+constexpr int kSegTailNbShift = 4;
 // a writer waits on full[s] by phase parity, so it must see EVERY phase of the slots it reads: a slot belongs to one writer
 static_assert(kSegFifo % kSegAcW == 0, "a FIFO slot always belongs to the same writer (a reader must not skip a barrier phase)");
 static_assert((kSegFifo & (kSegFifo - 1)) == 0 && (kSegAsm & (kSegAsm - 1)) == 0, "ring sizes are powers of two");
 static_assert(kSegAsm >= (kSegSlots + 1) / 2 + 1, "the blocks one round touches must fit the assembly ring");
 
+constexpr int kSegWorkedDepth = 8;            // rounds between a writer and the flusher (worked[] barriers, side ring)
 // shared memory of a group (32-bit words), after the CTA's copy of the lookup tables:
 //   window ring | per-lane table offsets by block-in-MCU | FIFO | block images [image][lane][32 words] |
 //   flushed-block count per lane | mbarriers | flush list
@@ -113,7 +126,8 @@ constexpr int kSegOffAsm = kSegOffFifo + kSegFifo * kSegRoundBytes / 4;
 constexpr int kSegOffFl = kSegOffAsm + kSegAsm * 32 * 32;
 constexpr int kSegOffBar = kSegOffFl + 32;    // mbarriers (2 words each)
 constexpr int kSegOffList = kSegOffBar + 32;  // the flusher's list of finished blocks, a byte each
-constexpr int kSegGroupWords = kSegOffList + 32 * ((kSegSlots + 1) / 2 + 1) / 4;
+constexpr int kSegOffSide = kSegOffList + 32 * ((kSegSlots + 1) / 2 + 1) / 4;   // what the flusher needs of a round, a byte per lane (below)
+constexpr int kSegGroupWords = kSegOffSide + kSegWorkedDepth * 32 / 4;
 static_assert(kSegOffFifo % 4 == 0 && kSegOffAsm % 4 == 0 && kSegGroupWords % 4 == 0, "16-byte alignment of the FIFO and the block images");
 
 B2_HD size_t segdec_smem_bytes() {
@@ -179,15 +193,20 @@ B2_DEVICE SegLane seg_lane_x(int slot, const ImageDev *__restrict__ imgs, const 
 
 // ------------------------------------------------------------------ the FIFO between a decoder and its consumers
 // Round r lives at (r % kSegFifo) * kSegRoundBytes: kSegSlots slots of three words x 32 lanes, then one word per lane
-// (blocks finished after the round << 1 | kSegFinFlag).  Nobody polls: every hand-over is an mbarrier in shared memory,
+// (kSegTailNbShift).  Nobody polls: every hand-over is an mbarrier in shared memory,
 // a waiting warp is suspended by the hardware (spinning consumers took two fifths of the kernel's issue slots).
 //   full[s]    1 arrival: the decoder has written the round in slot s
-//   empty[s]   2 arrivals: the round's writer and the flusher have what they need of the round in registers
-//   worked[i]  1 arrival: the writer of round r (i = r % kSegWorkedDepth) has put its values into the block images --
-//              what the flusher waits for.  Deeper than the FIFO, so that a phase cannot complete twice
-//              before the flusher has looked at it (writers are at most kSegFifo rounds ahead of the flusher's reads).
-constexpr int kSegWorkedDepth = 8;
+//   empty[s]   1 arrival: the round's writer has the round in registers.  The flusher does not read the FIFO: with two
+//              rounds of depth, a decoder that had to wait for the flusher to START a round before it could write the
+//              next but one found no room in five rounds out of six.  What the flusher needs of a round -- how many
+//              blocks each lane finished in it, and whether it is the last -- the writer passes on, a byte per lane,
+//              in a ring as deep as worked[] (side)
+//   worked[i]  1 arrival: the writer of round r (i = r % kSegWorkedDepth) has put its values into the block images and
+//              its byte into the side ring -- what the flusher waits for.  A writer does not begin round r before the
+//              flusher has finished round r - kSegWorkedDepth (the flusher's round counter, next to the barriers), so
+//              a phase cannot complete twice before the flusher has looked at it
 constexpr int kSegBars = 2 * kSegFifo + kSegWorkedDepth;
+static_assert(2 * kSegBars + 1 <= 32, "the mbarriers and the flusher's round counter share 32 words");
 struct SegFifo {
   uint32_t fifo_a;           // window address of slot 0 of round 0, this lane
   uint32_t bar_a;            // window address of full[0]
@@ -196,12 +215,15 @@ struct SegFifo {
   B2_MEMBER uint32_t empty(uint32_t r) const { return bar_a + 8u * ((uint32_t)kSegFifo + (r & (uint32_t)(kSegFifo - 1))); }
   B2_MEMBER uint32_t worked(uint32_t r) const { return bar_a + 8u * ((uint32_t)(2 * kSegFifo) + (r & (uint32_t)(kSegWorkedDepth - 1))); }
   B2_MEMBER void init() const {                                  // one thread
-    for (uint32_t s = 0; s < (uint32_t)kSegFifo; ++s) { b2_mbar_init_a(full(s), 1); b2_mbar_init_a(empty(s), 2); }
+    for (uint32_t s = 0; s < (uint32_t)kSegFifo; ++s) { b2_mbar_init_a(full(s), 1); b2_mbar_init_a(empty(s), 1); }
     for (uint32_t i = 0; i < (uint32_t)kSegWorkedDepth; ++i) b2_mbar_init_a(worked(i), 1);
   }
   // ---- producer ----
   B2_MEMBER void wait_room(uint32_t r) const {                   // round r may be written once round r - kSegFifo has been read
     if (r >= (uint32_t)kSegFifo) b2_mbar_wait_a(empty(r), ((r / (uint32_t)kSegFifo) - 1u) & 1u);
+  }
+  B2_MEMBER bool has_room(uint32_t r) const {                    // the same question without waiting
+    return r < (uint32_t)kSegFifo || b2_mbar_test_a(empty(r), ((r / (uint32_t)kSegFifo) - 1u) & 1u);
   }
   B2_MEMBER void publish(uint32_t r, int lane) const {           // every lane's stores of the round are ordered before lane 0's arrive
     __syncwarp();
@@ -220,16 +242,23 @@ struct SegFifo {
   B2_MEMBER void worked_wait(uint32_t r) const { b2_mbar_wait_a(worked(r), (r / (uint32_t)kSegWorkedDepth) & 1u); }
 };
 
+#if B2_SEG_DIAG == 7
+// measurements only: cycles the decoder warps spend per part of a round (summed over warps), rounds, warps
+__device__ unsigned long long g_seg_diag[24];   // decoder 0..8, writers 10..13, flusher 16..19
+#define B2_SEG_TICK(k) do { const long long t_ = clock64(); diag[k] += (unsigned long long)(t_ - tprev); tprev = t_; } while (0)
+#else
+#define B2_SEG_TICK(k) do { } while (0)
+#endif
 // =========================== the chain: codes only ===========================
 // The eight steps of a round are ONE basic block: no branch, table and window loads that the compiler may
 // schedule freely (b2_lds_ro), so the off-chain work of step i overlaps the chain of step i+1.  What needs a
 // branch is taken out of the steps: a lane that meets an entry the first-level table cannot resolve (code longer
 // than kHLutBits -- one symbol in 200 --, an error entry) STAYS where it is for the rest of the round (its
-// entries read 0: no advance, nothing for the consumers) and the symbol is resolved after the last step, in the
-// round's extra slot.
+// entries read 0: no advance, nothing for the consumers) and the symbol is resolved in the round's ninth step.
 B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const ImageDev *__restrict__ imgs,
                           const TableSet *__restrict__ tsets,
-                          const uint8_t *__restrict__ d_us, uint32_t *ringl, uint32_t *tb, uint32_t lut_a, uint32_t &err) {
+                          const uint8_t *__restrict__ d_us, uint32_t *ringl, uint32_t *tb, uint32_t lut_a, bool ovf_possible,
+                          uint32_t &err) {
   uint32_t p = 0, pend = 0, rw = 0;    // bit position / end of the segment / next word to fetch (all in the unstuffed scan)
   const uint32_t *us = reinterpret_cast<const uint32_t *>(d_us);
   const uint32_t total = L.live ? (uint32_t)(L.bend - L.bidx) : 0u;
@@ -276,7 +305,13 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     done = done || (end && nb == total);
   };
   uint32_t r = 0;
+#if B2_SEG_DIAG == 7
+  unsigned long long diag[6] = {0, 0, 0, 0, 0, 0};
+  long long tprev = clock64();
+  uint32_t nroom = 0;
+#endif
   for (;; ++r) {
+    const bool room = ff.has_room(r);     // asked before the top-up, needed after it: the barrier's answer takes ~90 cycles
     // ---- top-up: once per round, the same instructions for every lane, predicated per lane (no branch).
     //      A round consumes at most 9 x 27 bits < 8 words; a top-up brings 8.
     //      Nothing is fetched from beyond the segment's end (+ the window's look-ahead): a lane whose data ran out
@@ -291,12 +326,19 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     b2_cp_async4_if(need && ((rw + 4u) & (kSegWords - 1)) == 0u, ring_a + (kSegWords << 7), us + rw + 4);
     rw += need ? 8u : 0u;
     b2_cp_async_commit();
-    ff.wait_room(r);
+    B2_SEG_TICK(0);
+    if (!room) ff.wait_room(r);
+#if B2_SEG_DIAG == 7
+    nroom += room ? 0u : 1u;
+#endif
+    B2_SEG_TICK(1);
     const uint32_t slot_a = ff.round_a(r);
     // rw is at least 25 words ahead of the window and the round needs at most 8 more: everything but the two
     // newest groups must have landed -- copies issued two rounds (16 steps) ago
     b2_cp_async_wait<2>();
+    B2_SEG_TICK(2);
     uint32_t w = 0, cur = 0, eraw = 0;
+    const uint32_t nb0 = nb;                       // blocks finished before this round
 #pragma unroll kSegUnroll
     for (int u = 0; u < kSegSteps; ++u) {
       const uint32_t t = b2_lds_ro(tba);                                           // table offsets of this block: DC | AC << 16
@@ -305,7 +347,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
       const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
       w = __funnelshift_l(w1, w0, p);
       eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-      // a finished lane, and one that waits for the extra slot, step in place: entry 0
+      // a finished lane, and one that waits for the ninth step, step in place: entry 0
       const uint32_t e = (done || eraw >= kHOverflow) ? 0u : eraw;
       uint32_t fn;
       advance(e, fn);
@@ -313,32 +355,53 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
       b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, e);
       b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, fn);
     }
-    // ---- the extra slot: whoever is waiting in front of a symbol the first-level table did not resolve ----
-    const bool stuck = !done && eraw >= kHOverflow;                                // then w, cur and eraw are still those of p
-    uint32_t e = 0, fn = 0;
-    if (__any_sync(0xffffffffu, stuck)) {
-      if (stuck) {
-        const bool is_dc = z == 0;
-        e = eraw;
-        if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
-        if (e & kHOverflow) {
+    B2_SEG_TICK(3);
+    // ---- the ninth step: a step like the others for every lane, plus the table's second level.  A lane that has been
+    //      waiting in front of a long code since some earlier step reads the same first-level entry again and gets its
+    //      symbol here; every other lane simply decodes one more symbol (and, if that one is long, does not wait at all).
+    //      What two levels cannot settle -- kHOverflow, only in tables with more long-code prefixes than kHL2Blocks --
+    //      takes a branch that is uniform for the CTA (ovf_possible); error entries are ordinary entries with flags ----
+    uint32_t e, fn;
+    {
+      const uint32_t t = b2_lds_ro(tba);
+      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));
+      const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
+      const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
+      w = __funnelshift_l(w1, w0, p);
+      eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+      const bool is_dc = z == 0;
+      // (not for a finished or idle lane: what it reads need not be a table entry)
+      eraw = b2_lds_ro_if(!done && (eraw & kHLong) != 0u, cur + 4u * ((eraw & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)), eraw);
+      if (ovf_possible) {
+        if (!done && (eraw & kHOverflow)) {
           const ImageDev &im = imgs[L.img];
           const int blk = (int)((tba - tb_a) >> 7), comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-          e = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
+          eraw = huff_slow(is_dc ? tsets[im.tset].dc[im.td[comp] & 3] : tsets[im.tset].ac[im.ta[comp] & 3], w >> 16, is_dc);
         }
-        if (e & kHBadCode) err |= ST_BAD_CODE;
-        if (e & kHBadSize) err |= is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN;
-        advance(e, fn);
       }
+      e = done ? 0u : eraw;
+      err |= (e & kHBadCode) ? (uint32_t)ST_BAD_CODE : 0u;
+      err |= (e & kHBadSize) ? (uint32_t)(is_dc ? ST_BAD_DC_LEN : ST_BAD_AC_LEN) : 0u;
+      advance(e, fn);
     }
+    B2_SEG_TICK(4);
     const bool fin = __all_sync(0xffffffffu, done);
     b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes, w);
     b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 128u, e);
     b2_sts(slot_a + (uint32_t)kSegSteps * kSegSlotBytes + 256u, fn);
-    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | (fin ? kSegFinFlag : 0u));
+    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << kSegTailNbShift) | ((nb - nb0) << 1) | (fin ? kSegFinFlag : 0u));
     ff.publish(r, lane);
+    B2_SEG_TICK(5);
     if (fin) break;
   }
+#if B2_SEG_DIAG == 7
+  if (lane == 0) {
+    for (int k = 0; k < 6; ++k) atomicAdd(&g_seg_diag[k], diag[k]);
+    atomicAdd(&g_seg_diag[6], (unsigned long long)(r + 1));
+    atomicAdd(&g_seg_diag[7], 1ull);
+    atomicAdd(&g_seg_diag[8], (unsigned long long)nroom);
+  }
+#endif
   // the last block ran past the segment's end (file.hpp:36-40), or more than padding is left: the segment holds more blocks
   if (L.live) err |= p > pend ? (uint32_t)ST_OVERRUN : (pend - p > 7u ? (uint32_t)ST_BLOCK_COUNT : 0u);
   // the AC writers whose turn did not come with the last round each get an empty one that tells them to stop
@@ -347,7 +410,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     ff.wait_room(r);
     const uint32_t slot_a = ff.round_a(r);
     for (int u = 0; u < kSegSlots; ++u) { b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, 0u); b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, 0u); }
-    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << 1) | kSegFinFlag);
+    b2_sts(slot_a + (uint32_t)kSegSlots * kSegSlotBytes, (nb << kSegTailNbShift) | kSegFinFlag);
     ff.publish(r, lane);
   }
 }
@@ -371,10 +434,15 @@ B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {
 // =========================== AC coefficients: stateless, every kSegAcW-th round ===========================
 // magnitude extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store into the block image; everything a symbol
 // needs is in its FIFO entry, so the writers keep no state between symbols and several of them work in parallel.
-B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a, const uint32_t *fl,
-                             uint32_t g0, uint32_t &err) {
+B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a, const uint32_t *fl, const uint32_t *fround,
+                             uint32_t side_a, uint32_t g0, uint32_t &err) {
+#if B2_SEG_DIAG == 7
+  unsigned long long diag[4] = {0, 0, 0, 0};
+  long long tprev = clock64();
+#endif
   for (uint32_t r = (uint32_t)w;; r += (uint32_t)kSegAcW) {
     ff.wait(r);
+    B2_SEG_TICK(0);
     const uint32_t ra = ff.round_a(r);
     uint32_t fw[kSegSlots], fe[kSegSlots], fn[kSegSlots];
 #pragma unroll
@@ -385,8 +453,11 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
     const uint32_t tail = b2_lds(ra + (uint32_t)kSegSlots * kSegSlotBytes);
     ff.release(r, lane);                                          // every lane has read the round before it is handed back
     // the blocks of this round (the highest is the one in progress after it) must fit the ring of images in front of
-    // the flushed ones
-    while (__any_sync(0xffffffffu, (tail >> 1) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm)) b2_backoff(kSegPollNs);
+    // the flushed ones, and the round itself the ring of rounds between the writers and the flusher
+    B2_SEG_TICK(2);
+    while (__any_sync(0xffffffffu, (tail >> kSegTailNbShift) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm ||
+                                       r - b2_ld_acquire_smem(fround) >= (uint32_t)kSegWorkedDepth)) b2_backoff(kSegPollNs);
+    B2_SEG_TICK(1);
     uint32_t bad = 0;
 #pragma unroll
     for (int u = 0; u < (B2_SEG_DIAG == 5 ? 0 : kSegSlots); ++u) {
@@ -406,16 +477,24 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
       bad |= (!two || z2 == 0u) ? 0u : pos2 + (size2 == 0u ? 1u : 0u);    // z2 = 0: EOB
     }
     if (bad > 63u) err |= ST_BAD_RUN;                 // (positions are below 128: OR-ing them keeps "some position > 63")
+    b2_sts_u8(side_a + (r & (uint32_t)(kSegWorkedDepth - 1)) * 32u + (uint32_t)lane, tail & ((1u << kSegTailNbShift) - 1u));
     ff.worked_arrive(r, lane);
+    B2_SEG_TICK(2);
+#if B2_SEG_DIAG == 7
+    ++diag[3];
+#endif
     if (tail & kSegFinFlag) break;
   }
+#if B2_SEG_DIAG == 7
+  if (lane == 0) for (int k = 0; k < 4; ++k) atomicAdd(&g_seg_diag[10 + k], diag[k]);
+#endif
 }
 
 // =========================== the way out ===========================
 // Once a round's writer is through with it, the blocks the round finished leave (DC prediction first): eight threads
 // per block, 16 bytes each -- whole 128-byte lines -- and the image is cleared.
 B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t list_a,
-                           uint32_t *fl, uint4 *__restrict__ coef4, uint32_t &err) {
+                           uint32_t side_a, uint32_t *fl, uint32_t *fround, uint4 *__restrict__ coef4, uint32_t &err) {
   const uint32_t gblk = (uint32_t)L.gb;              // the coefficient buffer holds fewer than 2^32 blocks (512 GB)
   if (__any_sync(0xffffffffu, !L.live && L.bidx < L.bend)) {
     // a scan that is not decoded (stage U found it broken) still gets its blocks: zeros
@@ -428,51 +507,89 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
   int pred0 = L.pred[0], pred1 = L.pred[1], pred2 = L.pred[2];   // DC prediction per component (jpeg.cpp:335-345), restarted with the segment
   int blk = L.blk0;                                  // block-in-MCU of the lane's next block to leave
   uint32_t dcbad = 0;                                // != 0 once an absolute DC left the int16 range
+#if B2_SEG_DIAG == 7
+  unsigned long long diag[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long tprev = clock64();
+#endif
   for (uint32_t r = 0;; ++r) {
-    ff.wait(r);
-    const uint32_t tail = b2_lds(ff.round_a(r) + (uint32_t)kSegSlots * kSegSlotBytes);
-    ff.release(r, lane);
     ff.worked_wait(r);                               // the round's writer is through
-    const uint32_t upto = tail >> 1, cnt = upto - flushed;
+    B2_SEG_TICK(1);
+    const uint32_t tail = b2_lds_u8(side_a + (r & (uint32_t)(kSegWorkedDepth - 1)) * 32u + (uint32_t)lane);
+    const uint32_t cnt = tail >> 1, upto = flushed + cnt;                  // at most kSegMaxFin: a block takes two steps or more
+    // who has a k-th finished block: everything below is counted off these masks (no vote inside a loop, no shuffle chain)
+    uint32_t has[kSegMaxFin], excl = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < kSegMaxFin; ++k) has[k] = __ballot_sync(0xffffffffu, (uint32_t)k < cnt);
+#pragma unroll
+    for (int k = 0; k < kSegMaxFin; ++k) { excl += (uint32_t)__popc(has[k] & ((1u << lane) - 1u)); total += (uint32_t)__popc(has[k]); }
     // DC: the writers left each block's DC DIFFERENCE at position 0 of its image; a lane's blocks leave in order, so
-    // this is where prediction happens -- once per block, two passes per round typically
-    for (uint32_t k = 0; __any_sync(0xffffffffu, k < cnt); ++k) {
-      if (k < cnt) {
-        const uint32_t a = seg_asm_addr(asm_a, gblk + flushed + k, 0u);
-        const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
-        const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + (int)(int16_t)b2_lds_u16(a);
-        pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
-        dcbad |= (uint32_t)(dc + 32768) >> 16;
-        b2_sts_u16(a, (uint32_t)dc);
-        blk = blk + 1 == L.bpm ? 0 : blk + 1;
+    // this is where prediction happens -- once per block; the differences are fetched first, the sums follow
+    int diff[kSegMaxFin];
+#pragma unroll
+    for (int k = 0; k < kSegMaxFin; ++k) {
+      diff[k] = 0;
+      if (B2_SEG_DIAG != 9 && has[k] != 0u) { if ((uint32_t)k < cnt) diff[k] = (int)(int16_t)b2_lds_u16(seg_asm_addr(asm_a, gblk + flushed + (uint32_t)k, 0u)); }
+    }
+#pragma unroll
+    for (int k = 0; k < kSegMaxFin; ++k) {
+      if (B2_SEG_DIAG != 9 && has[k] != 0u) {
+        if ((uint32_t)k < cnt) {
+          const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
+          const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff[k];
+          pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
+          dcbad |= (uint32_t)(dc + 32768) >> 16;
+          b2_sts_u16(seg_asm_addr(asm_a, gblk + flushed + (uint32_t)k, 0u), (uint32_t)dc);
+          blk = blk + 1 == L.bpm ? 0 : blk + 1;
+        }
       }
     }
+    B2_SEG_TICK(4);
     // the round's finished blocks of all lanes as one list (a byte each: lane << 3 | number among the lane's blocks), so
-    // that every pass of the copy loop moves four whole blocks whatever lanes they belong to
-    uint32_t incl = cnt;
+    // that every pass of the copy loop moves whole blocks whatever lanes they belong to
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); incl += lane >= d ? t : 0u; }
-    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31), excl = incl - cnt;
-#pragma unroll
-    for (uint32_t k = 0; k < (uint32_t)(kSegSlots + 1) / 2 + 1; ++k)
+    for (uint32_t k = 0; k < (uint32_t)kSegMaxFin; ++k)
       if (k < cnt) b2_sts_u8(list_a + excl + k, ((uint32_t)lane << 3) | k);
     __syncwarp();
-    for (uint32_t q0 = 0; q0 < total; q0 += 4) {
-      const uint32_t q = q0 + ((uint32_t)lane >> 3);
-      const uint32_t ent = q < total ? b2_lds_u8(list_a + q) : 0u;
-      const uint32_t ls = ent >> 3;
-      const uint32_t gb = __shfl_sync(0xffffffffu, gblk + flushed, (int)ls) + (ent & 7u);   // global block index: its low bits name the image
-      if (q < total) {
-        const uint32_t sa = asm_g + ((gb & (uint32_t)(kSegAsm - 1)) << 12) + (ls << 7) + ((uint32_t)(lane & 7) << 4);
-        coef4[(size_t)gb * 8 + (lane & 7)] = b2_lds_v4(sa);
-        b2_sts_v4(sa, make_uint4(0u, 0u, 0u, 0u));
+    B2_SEG_TICK(5);
+    // eight threads per block and kSegCopyDepth blocks per thread and pass: the loads of a pass are issued before its stores
+    for (uint32_t q0 = 0; q0 < (B2_SEG_DIAG == 8 ? 0u : total); q0 += 4u * (uint32_t)kSegCopyDepth) {
+      uint32_t gbv[kSegCopyDepth], sav[kSegCopyDepth];
+      uint4 v[kSegCopyDepth];
+#pragma unroll
+      for (int j = 0; j < kSegCopyDepth; ++j) {
+        const uint32_t q = q0 + 4u * (uint32_t)j + ((uint32_t)lane >> 3);
+        const uint32_t ent = q < total ? b2_lds_u8(list_a + q) : 0u;
+        const uint32_t ls = ent >> 3;
+        gbv[j] = __shfl_sync(0xffffffffu, gblk + flushed, (int)ls) + (ent & 7u);   // global block index: its low bits name the image
+        sav[j] = asm_g + ((gbv[j] & (uint32_t)(kSegAsm - 1)) << 12) + (ls << 7) + ((uint32_t)(lane & 7) << 4);
       }
+#pragma unroll
+      for (int j = 0; j < kSegCopyDepth; ++j)
+        if (q0 + 4u * (uint32_t)j + ((uint32_t)lane >> 3) < total) v[j] = b2_lds_v4(sav[j]);
+#pragma unroll
+      for (int j = 0; j < kSegCopyDepth; ++j)
+        if (q0 + 4u * (uint32_t)j + ((uint32_t)lane >> 3) < total) {
+          coef4[(size_t)gbv[j] * 8 + (lane & 7)] = v[j];
+          b2_sts_v4(sav[j], make_uint4(0u, 0u, 0u, 0u));
+        }
     }
+    B2_SEG_TICK(6);
+#if B2_SEG_DIAG == 7
+    diag[7] += total;
+#endif
     flushed = upto;
     __syncwarp();                                    // the images are cleared before anybody learns that they are free
     b2_st_release_smem(fl, flushed);
+    if (lane == 0) b2_st_release_smem(fround, r + 1u);
+    B2_SEG_TICK(2);
+#if B2_SEG_DIAG == 7
+    ++diag[3];
+#endif
     if (tail & kSegFinFlag) break;
   }
+#if B2_SEG_DIAG == 7
+  if (lane == 0) for (int k = 0; k < 8; ++k) atomicAdd(&g_seg_diag[16 + k], diag[k]);
+#endif
   if (dcbad) err |= ST_DC_RANGE;
 }
 
@@ -487,12 +604,14 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
               const int32_t *__restrict__ x_unit_base, const int32_t *__restrict__ x_img, int nimg,
               const XUnit *__restrict__ xunits, const uint32_t *__restrict__ segunit) {
   B2_DYN_SMEM(uint32_t, lut);                                   // [8][kHTab], then the groups
+  uint32_t seen = 0;                                            // OR of the table entries this thread copies
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = warp % kSegGroups, role = warp / kSegGroups;    // role 0 decoder, 1 .. kSegAcW writers, kSegAcW + 1 flusher
   uint32_t *const grp = lut + kHTabsPerSet * kHTab + g * kSegGroupWords;
   uint32_t *const ringl = grp + lane;                           // window ring: word j of this lane at ringl[(j & 31) * 32]
   uint32_t *const tb = grp + kSegOffTb;                         // [block-in-MCU][lane]: DC table offset | AC table offset << 16
   uint32_t *const fl = grp + kSegOffFl + lane;                  // blocks of this lane that have left the assembly ring
+  uint32_t *const fround = grp + kSegOffBar + 2 * kSegBars;     // rounds the flusher has finished
   SegFifo ff;
   ff.fifo_a = b2_dsm_addr(grp + kSegOffFifo) + 4u * (uint32_t)lane;
   ff.bar_a = b2_dsm_addr(grp + kSegOffBar);
@@ -505,16 +624,21 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
     for (int t = 0; t < kHTabsPerSet; ++t) {
       const bool used = t < 4 ? tsets[set].dc[t].set : tsets[set].ac[t - 4].set;
       if (!used) continue;
-      for (int k = tid; k < kHTab / 4; k += kSegThreads) dst[t * (kHTab / 4) + k] = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
+      for (int k = tid; k < kHTab / 4; k += kSegThreads) {
+        const uint4 v = b2_ld_nc_v4(src + t * (kHTab / 4) + k);
+        dst[t * (kHTab / 4) + k] = v;
+        seen |= v.x | v.y | v.z | v.w;
+      }
     }
     // block images and flushed counts start at zero
     for (int gg = 0; gg < kSegGroups; ++gg) {
       uint4 *z = reinterpret_cast<uint4 *>(lut + kHTabsPerSet * kHTab + gg * kSegGroupWords + kSegOffAsm);
       for (int k = tid; k < (kSegAsm * 32 * 32 + 32) / 4; k += kSegThreads) z[k] = make_uint4(0u, 0u, 0u, 0u);
     }
-    if (role == 0 && lane == 0) { ff.init(); b2_mbar_init_fence(); }
+    if (role == 0 && lane == 0) { ff.init(); *fround = 0u; b2_mbar_init_fence(); }
   }
-  __syncthreads();
+  // does any table of the set hold codes that neither level resolves (kernels_huff.cuh: kHOverflow)?  uniform for the CTA
+  const bool ovf_possible = __syncthreads_or((int)(seen & kHOverflow)) != 0;
 
   const int slot = (int)blockIdx.x * kSegUnits + g * 32 + lane;
   const SegLane L = units ? seg_lane(units[slot], imgs, out, seg_start)
@@ -523,9 +647,9 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   // the inner loops address shared memory through 32-bit window addresses (register + immediate)
   const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
-  if (role == 0) seg_decode(ff, lane, L, imgs, tsets, d_us, ringl, tb, lut_a, err);
-  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, g0, err);
-  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), fl, reinterpret_cast<uint4 *>(coef), err);
+  if (role == 0) seg_decode(ff, lane, L, imgs, tsets, d_us, ringl, tb, lut_a, ovf_possible, err);
+  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, fround, b2_dsm_addr(grp + kSegOffSide), g0, err);
+  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), b2_dsm_addr(grp + kSegOffSide), fl, fround, reinterpret_cast<uint4 *>(coef), err);
   if (err) atomicOr(&out[L.img].status, err);
 }
 

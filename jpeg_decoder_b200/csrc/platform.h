@@ -152,6 +152,11 @@ B2_DEVICE uint32_t b2_lds_ro(uint32_t a) {
   asm("ld.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(a));
   return v;
 }
+// the same under a predicate: `keep` where the predicate is off (no branch, no select behind the load)
+B2_DEVICE uint32_t b2_lds_ro_if(bool on, uint32_t a, uint32_t keep) {
+  asm("{\n.reg .pred q;\nsetp.ne.u32 q, %2, 0;\n@q ld.shared::cta.u32 %0, [%1];\n}" : "+r"(keep) : "r"(a), "r"((uint32_t)on));
+  return keep;
+}
 B2_DEVICE void b2_sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u16 [%0], %1;" ::"r"(a), "h"((unsigned short)v) : "memory"); }
 B2_DEVICE uint32_t b2_lds_u16(uint32_t a) { unsigned short v; asm volatile("ld.shared::cta.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory"); return v; }
 B2_DEVICE void b2_sts_u8(uint32_t a, uint32_t v) { asm volatile("st.shared::cta.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
@@ -168,6 +173,13 @@ B2_DEVICE void b2_sts_v4(uint32_t a, uint4 v) {
 B2_DEVICE void b2_mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 B2_DEVICE void b2_mbar_init_a(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+// has the phase of that parity completed?  Does not wait: issued early, the answer is there when it is needed
+B2_DEVICE bool b2_mbar_test_a(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+               : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0u;
 }
 B2_DEVICE void b2_mbar_wait_a(uint32_t bar, uint32_t parity) {
   asm volatile(

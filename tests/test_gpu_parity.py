@@ -78,7 +78,7 @@ def test_extreme_content(dec, oracle_mod, harness):
     """Pictures at the ends of the symbol statistics, many restart segments each:
     flat ones (every block is DC + EOB: a lane finishes four to five blocks per FIFO round -- the most the segment
     decoder's ring of block images ever holds, its room check has to wait), white noise at q98 (long codes and large
-    magnitudes in nearly every block: the extra slot of every round is in use), and both alternating MCU by MCU."""
+    magnitudes in nearly every block: the second table level in every round's ninth step), and both alternating MCU by MCU."""
     rng = np.random.default_rng(11)
     w, h = 640, 352
     flat = np.full((h, w, 3), 128, np.uint8)
@@ -185,6 +185,16 @@ def test_zero_padded_restart_segments(dec, oracle_mod, harness):
     st, rgbs, coefs = dec.decode([z, d], want_coef=True)
     assert st == [0, 0]
     assert np.array_equal(coefs[0].astype(np.int32), c0) and np.array_equal(rgbs[0], r0) and np.array_equal(rgbs[1], r0)
+
+
+def test_tables_with_more_long_codes_than_the_second_level_holds(dec, oracle_mod, harness):
+    # 140 twelve-bit AC codes over 35 ten-bit prefixes: beyond the lookup tables' second level, resolved from the DHT data
+    from tests import jpeg_craft as jc
+    datas = [jc.with_ac_code_lengths(harness.synth_jpeg(71, 96, 64, 98, 2, 2, False, 0), jc.OVERFLOW_AC_BITS),
+             jc.with_ac_code_lengths(harness.synth_jpeg(72, 88, 56, 95, 1, 1, False, 5), jc.OVERFLOW_AC_BITS),
+             jc.with_ac_code_lengths(harness.synth_jpeg(74, 160, 120, 99, 2, 1, False, 0), jc.OVERFLOW_AC_BITS),
+             harness.synth_jpeg(73, 64, 64, 90, 2, 2, False, 4)]
+    compare(dec, oracle_mod, datas)
 
 
 def test_spec_superset_component_ids_and_16bit_dqt(dec, oracle_mod, harness):

@@ -47,6 +47,24 @@ def test_port_matches_live_reference_binary(oracle_mod, harness):
         assert info["sizeof_mcu"] == 768
 
 
+def test_port_matches_live_reference_on_transcoded_huffman_tables(oracle_mod, harness):
+    # the same coefficients under AC tables with 140 twelve-bit codes (tests/jpeg_craft.py): the reference's bit-by-bit
+    # getNextSymbol (jpeg.cpp:300-320) and the port agree with each other and with the untranscoded file
+    if not oracle_mod.have_ref():
+        pytest.skip("oracle/_ref/ref_decode not built (reference sources absent)")
+    from tests import jpeg_craft as jc
+    for args in [(71, 96, 64, 98, 2, 2, False, 0), (72, 88, 56, 95, 1, 1, False, 5), (74, 160, 120, 99, 2, 1, False, 0)]:
+        d = harness.synth_jpeg(*args)
+        t = jc.with_ac_code_lengths(d, jc.OVERFLOW_AC_BITS)
+        assert t != d
+        info, coef, rgb = oracle_mod.ref_dump(t)
+        rc, _, pc, pr = oracle_mod.port_decode(t)
+        rc0, _, pc0, pr0 = oracle_mod.port_decode(d)
+        assert rc == 0 and rc0 == 0
+        assert np.array_equal(coef, pc) and np.array_equal(rgb, pr)
+        assert np.array_equal(pc, pc0) and np.array_equal(pr, pr0)
+
+
 def test_idct_constants_bit_patterns(oracle_mod):
     # m0,m1,m2,m3,m4,m5,s0..s7 as the reference's double->float initialisers give them
     want = [0x3fec835e, 0x3fb504f3, 0x3f8a8bd4, 0x3fb504f3, 0x40273d74, 0x3f43ef15,
