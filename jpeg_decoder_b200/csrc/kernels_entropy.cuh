@@ -224,7 +224,8 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
           p = B; tba = tb_a; z = 0u; done = true;
         } else {
           uint32_t e = eraw;
-          if (e & kHLong) e = b2_lds(cur + 4u * ((e & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+          if (e & kHLong) e = b2_lds(cur + 4u * (huff_l2_base(e) + ((w >> (32 - kHLutBits - 6)) & 63u)));
+          else if (huff_is_l1_error(e)) e = huff_l1_error(e);
           if (e & kHOverflow) {
             const int ci = (int)comp;
             e = huff_slow(is_dc ? tsets[I.im->tset].dc[I.im->td[ci] & 3] : tsets[I.im->tset].ac[I.im->ta[ci] & 3], w >> 16, is_dc);

@@ -22,7 +22,12 @@
 //               Two thirds of the symbols of a typical scan pair up, so a decoder that takes both at once makes a third
 //               fewer steps, and whoever places the coefficients has everything about both symbols in the one entry.
 //               bit 28 overflow   bit 29 bad size (jpeg.cpp:330,381)   bit 30 no such code (jpeg.cpp:319)
-//               bit 31 long (level-1 only; [15:0] = level-2 base)
+//               bit 31 long (level-1 only)
+//               A LEVEL-1 entry with any of the bits 28..31 has NOTHING in its low 20 bits: a decoder that adds such an
+//               entry's adv / zinc / adv2 to its state stays where it is, without looking at the flags -- that test was
+//               two links in the segment decoder's dependent chain.  What the entry has to say is in [24:20]: the
+//               level-2 block for a long code (huff_l2_base), the code length for an error entry (huff_l1_error gives
+//               the standard form: advance by the code, end the block, the flag).
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -49,6 +54,14 @@ B2_HD uint32_t huff_adv2(uint32_t e) { return (e >> 16) & 15u; }
 B2_HD uint32_t huff_zinc2_raw(uint32_t e) { return (e >> 20) & 31u; }                                  // 0: the second symbol is EOB
 B2_HD uint32_t huff_zinc2(uint32_t e) { const uint32_t z = huff_zinc2_raw(e); return z ? z : 64u; }   // only if adv2 != 0
 B2_HD uint32_t huff_size2(uint32_t e) { return (e >> 25) & 7u; }
+// level-1 entries with a flag (see above)
+B2_HD uint32_t huff_l1_long(uint32_t blk) { return kHLong | (blk << 20); }
+B2_HD uint32_t huff_l2_base(uint32_t e) { return (uint32_t)kHL1 + ((e >> 20) & 7u) * 64u; }
+B2_HD bool huff_is_l1_error(uint32_t e) { return (e & (kHBadCode | kHBadSize)) != 0u && (e & 0xfffffu) == 0u; }
+B2_HD uint32_t huff_l1_error(uint32_t e) {
+  const uint32_t len = (e >> 20) & 31u;
+  return huff_entry(len, len, 64, (e & (kHBadCode | kHBadSize)) | kHEob);
+}
 // symbol -> entry, following decodeMCUComponent (jpeg.cpp:330-400)
 B2_HD uint32_t huff_symbol_entry(uint32_t sym, uint32_t len, bool is_dc) {
   if (is_dc) {
@@ -110,7 +123,7 @@ B2_GLOBAL void k_build_luts(const TableSet *__restrict__ tsets, uint32_t *__rest
       e = huff_search(spec, canon, (uint32_t)idx << (16 - kHLutBits), 1, kHLutBits, is_dc);
       if (e & kHBadCode) {                                   // no short code: a long one, or none at all
         const uint32_t blk = (uint32_t)idx - p0;
-        if ((uint32_t)idx >= p0 && blk < (uint32_t)kHL2Blocks) e = kHLong | (uint32_t)(kHL1 + blk * 64);
+        if ((uint32_t)idx >= p0 && blk < (uint32_t)kHL2Blocks) e = huff_l1_long(blk);
         else if ((uint32_t)idx >= p0) e = kHOverflow;
       } else if (!is_dc && !(e & (kHSpecial | kHEob)) && huff_adv(e) < (uint32_t)kHLutBits) {
         // a second AC symbol inside the index bits that are left?  its code AND its magnitude bits must fit
@@ -128,6 +141,8 @@ B2_GLOBAL void k_build_luts(const TableSet *__restrict__ tsets, uint32_t *__rest
       e = prefix < (uint32_t)kHL1 ? huff_search(spec, canon, (prefix << 6) | low, kHLutBits + 1, 16, is_dc)
                                   : huff_entry(16, 16, 64, kHBadCode | kHEob);
     }
+    // level 1: an error entry keeps its flag and the code length only
+    if (idx < kHL1 && (e & (kHBadCode | kHBadSize))) e = (e & (kHBadCode | kHBadSize)) | (huff_len(e) << 20);
     lut[idx] = e;
   }
 }

@@ -111,6 +111,10 @@ constexpr int kSegNbShift = 7;
 // last word of a round, per lane: blocks finished after the round << 4 | blocks finished IN the round << 1 | the decoder has finished
 constexpr uint32_t kSegFinFlag = 1u;
 constexpr int kSegTailNbShift = 4;
+// what the flusher publishes per lane (fl): blocks of the lane that have left, low kSegFlBits bits | rounds it has finished
+// above them.  Readers only ever need how far THEY are ahead of it -- a few blocks, a few rounds -- so the low bits of the
+// differences are the differences, however long the unit is.  One word, so that one release (a fence) per round does
+constexpr int kSegFlBits = 24;
 // a writer waits on full[s] by phase parity, so it must see EVERY phase of the slots it reads: a slot belongs to one writer
 static_assert(kSegFifo % kSegAcW == 0, "a FIFO slot always belongs to the same writer (a reader must not skip a barrier phase)");
 static_assert((kSegFifo & (kSegFifo - 1)) == 0 && (kSegAsm & (kSegAsm - 1)) == 0, "ring sizes are powers of two");
@@ -203,10 +207,10 @@ B2_DEVICE SegLane seg_lane_x(int slot, const ImageDev *__restrict__ imgs, const 
 //              in a ring as deep as worked[] (side)
 //   worked[i]  1 arrival: the writer of round r (i = r % kSegWorkedDepth) has put its values into the block images and
 //              its byte into the side ring -- what the flusher waits for.  A writer does not begin round r before the
-//              flusher has finished round r - kSegWorkedDepth (the flusher's round counter, next to the barriers), so
+//              flusher has finished round r - kSegWorkedDepth (the flusher's round counter, in the high bits of its per-lane word: kSegFlBits), so
 //              a phase cannot complete twice before the flusher has looked at it
 constexpr int kSegBars = 2 * kSegFifo + kSegWorkedDepth;
-static_assert(2 * kSegBars + 1 <= 32, "the mbarriers and the flusher's round counter share 32 words");
+static_assert(2 * kSegBars <= 32, "32 words are set aside for the mbarriers");
 struct SegFifo {
   uint32_t fifo_a;           // window address of slot 0 of round 0, this lane
   uint32_t bar_a;            // window address of full[0]
@@ -230,7 +234,9 @@ struct SegFifo {
     if (lane == 0) b2_mbar_arrive_a(full(r));
   }
   // ---- consumers ----
-  B2_MEMBER void wait(uint32_t r) const { b2_mbar_wait_a(full(r), (r / (uint32_t)kSegFifo) & 1u); }
+  B2_MEMBER void wait(uint32_t r) const {
+    b2_mbar_wait_a(full(r), (r / (uint32_t)kSegFifo) & 1u);
+  }
   B2_MEMBER void release(uint32_t r, int lane) const {           // the warp has the round in registers
     __syncwarp();
     if (lane == 0) b2_mbar_arrive_a(empty(r));
@@ -290,10 +296,13 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
   uint32_t z = 0, nb = 0;                          // zig-zag index, blocks finished
   // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
   auto advance = [&](uint32_t e, uint32_t &fn) {
-    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
-    const bool pair = a2 != 0u && z + z1 < 64u;    // an AC entry may describe TWO symbols; both are taken unless the first ends the block
+    // an AC entry may describe TWO symbols; both are taken unless the first could end the block: it moves the index by 16
+    // at most, so below 48 it cannot -- a test on z alone, made while the entry is still on its way (the test on
+    // z + z1 sat between the entry and the next window address: three more links in the chain)
+    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e) & (z < 48u ? 15u : 0u);
+    const bool pair = a2 != 0u;
     fn = z | (pair ? kSegPairBit : 0u) | (nb << kSegNbShift);
-    p += huff_adv(e) + (pair ? a2 : 0u);
+    p += huff_adv(e) + a2;
     z += z1 + (pair ? huff_zinc2(e) : 0u);
     // ---- block end without a branch: some lane ends a block in four steps out of five ----
     const bool end = z >= 64u;
@@ -339,21 +348,29 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     B2_SEG_TICK(2);
     uint32_t w = 0, cur = 0, eraw = 0;
     const uint32_t nb0 = nb;                       // blocks finished before this round
+    // The FIFO stores of a step are issued in the NEXT step, behind its loads: shared-memory stores and loads stay in
+    // program order (the assembler cannot know that FIFO and window ring never overlap), so two stores in front of the
+    // window loads are eight cycles of issue time in the chain; behind them they fall into the loads' shadow.
+    uint32_t e_prev = 0, fn_prev = 0;
 #pragma unroll kSegUnroll
     for (int u = 0; u < kSegSteps; ++u) {
-      const uint32_t t = b2_lds_ro(tba);                                           // table offsets of this block: DC | AC << 16
-      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));                          // chosen while the window is still on its way
-      const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
+      const uint32_t wa = b2_and_x4_add<(uint32_t)((kSegWords - 1) << 5)>(p, ring_a);      // ring_a + 128 * ((p >> 5) & 31)
       const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
+      const uint32_t t = b2_lds_ro(tba);                                           // table offsets of this block: DC | AC << 16
+      if (u > 0) {
+        b2_sts(slot_a + (uint32_t)(u - 1) * kSegSlotBytes + 128u, e_prev);
+        b2_sts(slot_a + (uint32_t)(u - 1) * kSegSlotBytes + 256u, fn_prev);
+      }
+      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));                          // chosen while the window is still on its way
       w = __funnelshift_l(w1, w0, p);
-      eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
-      // a finished lane, and one that waits for the ninth step, step in place: entry 0
-      const uint32_t e = (done || eraw >= kHOverflow) ? 0u : eraw;
+      eraw = b2_lds_ro(b2_shr_x4_add<32 - kHLutBits>(w, cur));
+      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes, w);
+      // a finished lane steps in place: entry 0.  So does one that waits for the ninth step, by itself: the low bits of
+      // a first-level entry with a flag are zero (kernels_huff.cuh), and the consumers find nothing in them either
+      const uint32_t e = done ? 0u : eraw;
       uint32_t fn;
       advance(e, fn);
-      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes, w);
-      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 128u, e);
-      b2_sts(slot_a + (uint32_t)u * kSegSlotBytes + 256u, fn);
+      e_prev = e; fn_prev = fn;
     }
     B2_SEG_TICK(3);
     // ---- the ninth step: a step like the others for every lane, plus the table's second level.  A lane that has been
@@ -363,15 +380,19 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     //      takes a branch that is uniform for the CTA (ovf_possible); error entries are ordinary entries with flags ----
     uint32_t e, fn;
     {
-      const uint32_t t = b2_lds_ro(tba);
-      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));
       const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
       const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
+      const uint32_t t = b2_lds_ro(tba);
+      b2_sts(slot_a + (uint32_t)(kSegSteps - 1) * kSegSlotBytes + 128u, e_prev);
+      b2_sts(slot_a + (uint32_t)(kSegSteps - 1) * kSegSlotBytes + 256u, fn_prev);
+      cur = lut_r + (z == 0 ? (t & 0xffffu) : (t >> 16));
       w = __funnelshift_l(w1, w0, p);
       eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
       const bool is_dc = z == 0;
       // (not for a finished or idle lane: what it reads need not be a table entry)
-      eraw = b2_lds_ro_if(!done && (eraw & kHLong) != 0u, cur + 4u * ((eraw & 0xffffu) + ((w >> (32 - kHLutBits - 6)) & 63u)), eraw);
+      const uint32_t e1 = eraw;
+      eraw = b2_lds_ro_if(!done && (e1 & kHLong) != 0u, cur + 4u * (huff_l2_base(e1) + ((w >> (32 - kHLutBits - 6)) & 63u)), e1);
+      eraw = huff_is_l1_error(e1) ? huff_l1_error(e1) : eraw;
       if (ovf_possible) {
         if (!done && (eraw & kHOverflow)) {
           const ImageDev &im = imgs[L.img];
@@ -434,7 +455,7 @@ B2_DEVICE int seg_extend(uint32_t w, uint32_t len, uint32_t size) {
 // =========================== AC coefficients: stateless, every kSegAcW-th round ===========================
 // magnitude extension (jpeg.cpp:388-397), zig-zag position, one 2-byte store into the block image; everything a symbol
 // needs is in its FIFO entry, so the writers keep no state between symbols and several of them work in parallel.
-B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a, const uint32_t *fl, const uint32_t *fround,
+B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a, const uint32_t *fl,
                              uint32_t side_a, uint32_t g0, uint32_t &err) {
 #if B2_SEG_DIAG == 7
   unsigned long long diag[4] = {0, 0, 0, 0};
@@ -455,8 +476,14 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
     // the blocks of this round (the highest is the one in progress after it) must fit the ring of images in front of
     // the flushed ones, and the round itself the ring of rounds between the writers and the flusher
     B2_SEG_TICK(2);
-    while (__any_sync(0xffffffffu, (tail >> kSegTailNbShift) - b2_ld_acquire_smem(fl) >= (uint32_t)kSegAsm ||
-                                       r - b2_ld_acquire_smem(fround) >= (uint32_t)kSegWorkedDepth)) b2_backoff(kSegPollNs);
+    // (one word says both, kSegFlBits: both differences are small, so their low bits are the differences)
+    for (;;) {
+      const uint32_t f = b2_ld_acquire_smem(fl);
+      const bool wait = (((tail >> kSegTailNbShift) - f) & ((1u << kSegFlBits) - 1u)) >= (uint32_t)kSegAsm ||
+                        ((r - (f >> kSegFlBits)) & ((1u << (32 - kSegFlBits)) - 1u)) >= (uint32_t)kSegWorkedDepth;
+      if (!__any_sync(0xffffffffu, wait)) break;
+      b2_backoff(kSegPollNs);
+    }
     B2_SEG_TICK(1);
     uint32_t bad = 0;
 #pragma unroll
@@ -494,7 +521,7 @@ B2_DEVICE void seg_ac_writer(const SegFifo &ff, int w, int lane, uint32_t asm_a,
 // Once a round's writer is through with it, the blocks the round finished leave (DC prediction first): eight threads
 // per block, 16 bytes each -- whole 128-byte lines -- and the image is cleared.
 B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32_t asm_g /*image 0, lane 0*/, uint32_t list_a,
-                           uint32_t side_a, uint32_t *fl, uint32_t *fround, uint4 *__restrict__ coef4, uint32_t &err) {
+                           uint32_t side_a, uint32_t *fl, uint4 *__restrict__ coef4, uint32_t &err) {
   const uint32_t gblk = (uint32_t)L.gb;              // the coefficient buffer holds fewer than 2^32 blocks (512 GB)
   if (__any_sync(0xffffffffu, !L.live && L.bidx < L.bend)) {
     // a scan that is not decoded (stage U found it broken) still gets its blocks: zeros
@@ -502,6 +529,8 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
       for (uint32_t b = 0; b < (uint32_t)(L.bend - L.bidx); ++b)
         for (int c = 0; c < 8; ++c) coef4[(size_t)(gblk + b) * 8 + c] = make_uint4(0u, 0u, 0u, 0u);
   }
+  char *cbase = reinterpret_cast<char *>(coef4) + ((lane & 7) << 4);   // this thread's sixteen bytes of block 0
+  b2_keep(cbase);                                    // (kept in registers: the compiler would rather rebuild it in every pass)
   uint32_t flushed = 0;                              // blocks of this lane that have left
   const uint32_t asm_a = asm_g + ((uint32_t)lane << 7);
   int pred0 = L.pred[0], pred1 = L.pred[1], pred2 = L.pred[2];   // DC prediction per component (jpeg.cpp:335-345), restarted with the segment
@@ -537,7 +566,7 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
           const int comp = blk < L.nluma ? 0 : blk - L.nluma + 1;
           const int dc = (comp == 0 ? pred0 : (comp == 1 ? pred1 : pred2)) + diff[k];
           pred0 = comp == 0 ? dc : pred0; pred1 = comp == 1 ? dc : pred1; pred2 = comp == 2 ? dc : pred2;
-          dcbad |= (uint32_t)(dc + 32768) >> 16;
+          dcbad |= (uint32_t)(dc + 32768);           // a bit above the low sixteen: the value is outside int16
           b2_sts_u16(seg_asm_addr(asm_a, gblk + flushed + (uint32_t)k, 0u), (uint32_t)dc);
           blk = blk + 1 == L.bpm ? 0 : blk + 1;
         }
@@ -569,7 +598,7 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
 #pragma unroll
       for (int j = 0; j < kSegCopyDepth; ++j)
         if (q0 + 4u * (uint32_t)j + ((uint32_t)lane >> 3) < total) {
-          coef4[(size_t)gbv[j] * 8 + (lane & 7)] = v[j];
+          b2_stg_v4(cbase + ((size_t)gbv[j] << 7), v[j]);                        // one multiply-add wide per address
           b2_sts_v4(sav[j], make_uint4(0u, 0u, 0u, 0u));
         }
     }
@@ -579,8 +608,7 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
 #endif
     flushed = upto;
     __syncwarp();                                    // the images are cleared before anybody learns that they are free
-    b2_st_release_smem(fl, flushed);
-    if (lane == 0) b2_st_release_smem(fround, r + 1u);
+    b2_st_release_smem(fl, (flushed & ((1u << kSegFlBits) - 1u)) | ((r + 1u) << kSegFlBits));
     B2_SEG_TICK(2);
 #if B2_SEG_DIAG == 7
     ++diag[3];
@@ -590,7 +618,7 @@ B2_DEVICE void seg_flusher(const SegFifo &ff, int lane, const SegLane &L, uint32
 #if B2_SEG_DIAG == 7
   if (lane == 0) for (int k = 0; k < 8; ++k) atomicAdd(&g_seg_diag[16 + k], diag[k]);
 #endif
-  if (dcbad) err |= ST_DC_RANGE;
+  if (dcbad >> 16) err |= ST_DC_RANGE;
 }
 
 // units[u] = (image, segment); the units of one CTA share a table set (the planner pads each table-set group to a
@@ -611,7 +639,6 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   uint32_t *const ringl = grp + lane;                           // window ring: word j of this lane at ringl[(j & 31) * 32]
   uint32_t *const tb = grp + kSegOffTb;                         // [block-in-MCU][lane]: DC table offset | AC table offset << 16
   uint32_t *const fl = grp + kSegOffFl + lane;                  // blocks of this lane that have left the assembly ring
-  uint32_t *const fround = grp + kSegOffBar + 2 * kSegBars;     // rounds the flusher has finished
   SegFifo ff;
   ff.fifo_a = b2_dsm_addr(grp + kSegOffFifo) + 4u * (uint32_t)lane;
   ff.bar_a = b2_dsm_addr(grp + kSegOffBar);
@@ -635,7 +662,7 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
       uint4 *z = reinterpret_cast<uint4 *>(lut + kHTabsPerSet * kHTab + gg * kSegGroupWords + kSegOffAsm);
       for (int k = tid; k < (kSegAsm * 32 * 32 + 32) / 4; k += kSegThreads) z[k] = make_uint4(0u, 0u, 0u, 0u);
     }
-    if (role == 0 && lane == 0) { ff.init(); *fround = 0u; b2_mbar_init_fence(); }
+    if (role == 0 && lane == 0) { ff.init(); b2_mbar_init_fence(); }
   }
   // does any table of the set hold codes that neither level resolves (kernels_huff.cuh: kHOverflow)?  uniform for the CTA
   const bool ovf_possible = __syncthreads_or((int)(seen & kHOverflow)) != 0;
@@ -648,8 +675,8 @@ k_entropy_seg(const uint2 *__restrict__ units, const ImageDev *__restrict__ imgs
   const uint32_t lut_a = b2_dsm_addr(lut), asm_g = b2_dsm_addr(grp + kSegOffAsm);
   const uint32_t g0 = (uint32_t)L.gb & 7u;           // block n of the segment: coefficient pos at pos ^ key(n), key(n) = ((g0 + n) & 7) << 3
   if (role == 0) seg_decode(ff, lane, L, imgs, tsets, d_us, ringl, tb, lut_a, ovf_possible, err);
-  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, fround, b2_dsm_addr(grp + kSegOffSide), g0, err);
-  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), b2_dsm_addr(grp + kSegOffSide), fl, fround, reinterpret_cast<uint4 *>(coef), err);
+  else if (role <= kSegAcW) seg_ac_writer(ff, role - 1, lane, asm_g + ((uint32_t)lane << 7), fl, b2_dsm_addr(grp + kSegOffSide), g0, err);
+  else seg_flusher(ff, lane, L, asm_g, b2_dsm_addr(grp + kSegOffList), b2_dsm_addr(grp + kSegOffSide), fl, reinterpret_cast<uint4 *>(coef), err);
   if (err) atomicOr(&out[L.img].status, err);
 }
 

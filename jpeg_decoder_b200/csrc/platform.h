@@ -192,6 +192,22 @@ B2_DEVICE void b2_mbar_wait_a(uint32_t bar, uint32_t parity) {
       "B2_DONEA:\n"
       "}" ::"r"(bar), "r"(parity) : "memory");
 }
+// base + 4 * ((v & MASK) >> SHIFT) as two instructions (AND or shift, then multiply-add): written in C the compiler turns
+// it back into shift, AND and add -- one more link in a dependent chain
+template <uint32_t MASK> B2_DEVICE uint32_t b2_and_x4_add(uint32_t v, uint32_t base) {
+  uint32_t r;
+  asm("{\n.reg .b32 t;\nand.b32 t, %1, %2;\nmad.lo.u32 %0, t, 4, %3;\n}" : "=r"(r) : "r"(v), "n"(MASK), "r"(base));
+  return r;
+}
+template <int SHIFT> B2_DEVICE uint32_t b2_shr_x4_add(uint32_t v, uint32_t base) {
+  uint32_t r;
+  asm("{\n.reg .b32 t;\nshr.u32 t, %1, %2;\nmad.lo.u32 %0, t, 4, %3;\n}" : "=r"(r) : "r"(v), "n"(SHIFT), "r"(base));
+  return r;
+}
+B2_DEVICE void b2_stg_v4(void *p, uint4 v) {          // a store the compiler cannot take for a generic one
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+template <class T> B2_DEVICE void b2_keep(T *&p) { asm volatile("" : "+l"(p)); }
 B2_DEVICE uint32_t b2_launder(uint32_t v) { asm volatile("" : "+r"(v) :: "memory"); return v; }
 // shifts that give 0 for counts >= 32 (PTX semantics; undefined in C++)
 B2_DEVICE uint32_t b2_shr(uint32_t v, uint32_t n) { uint32_t r; asm("shr.u32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }

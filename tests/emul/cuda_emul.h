@@ -290,7 +290,11 @@ static inline void b2_sts_u8(uint32_t a, uint32_t v) { *b2_dsm_at(a, 1, "st.shar
 static inline uint32_t b2_lds_u8(uint32_t a) { return *b2_dsm_at(a, 1, "ld.shared.u8"); }
 static inline uint4 b2_lds_v4(uint32_t a) { uint4 v; memcpy(&v, b2_dsm_at(a, 16, "ld.shared.v4"), 16); return v; }
 static inline void b2_sts_v4(uint32_t a, uint4 v) { memcpy(b2_dsm_at(a, 16, "st.shared.v4"), &v, 16); }
+static inline void b2_stg_v4(void *p, uint4 v) { memcpy(p, &v, 16); }
+template <class T> static inline void b2_keep(T *&) {}
 static inline uint32_t b2_launder(uint32_t v) { return v; }
+template <uint32_t MASK> static inline uint32_t b2_and_x4_add(uint32_t v, uint32_t base) { return base + 4u * (v & MASK); }
+template <int SHIFT> static inline uint32_t b2_shr_x4_add(uint32_t v, uint32_t base) { return base + 4u * (v >> SHIFT); }
 // mbarriers by window address (arrival counts only): [63:32] completed phases, [31:16] arrivals a phase takes, [15:0] arrivals so far
 static inline uint64_t *b2_mbar_ptr(uint32_t a) { return reinterpret_cast<uint64_t *>(b2_dsm_at(a, 8, "mbarrier")); }
 static inline void b2_mbar_init_a(uint32_t a, uint32_t count) { __atomic_store_n(b2_mbar_ptr(a), (uint64_t)count << 16, __ATOMIC_SEQ_CST); }
