@@ -30,6 +30,7 @@
 // symbol one magnitude extension for the sums, nothing for AC symbols.
 // Algorithmic bytes: (1 + overlap / sub size) x scan bytes in (sync) + 36 B per sub of state.
 #pragma once
+#include <type_traits>
 #include "platform.h"
 #include "dev_types.h"
 #include "kernels_unstuff.cuh"   // find_owner
@@ -160,26 +161,34 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
   uint32_t tba = tb_a + (I.active ? I.blk : 0u) * 128u;
   uint32_t sp = p, sba = tba;
   // what one symbol does to the lane's state (entry e; two symbols when the entry pairs them)
-  auto advance = [&](uint32_t e, uint32_t w, bool is_dc, uint32_t comp) {
+  // (run_in: a std::true_type while some lane of the warp is still before its sub's first block -- the bookkeeping of
+  //  that moment is a sixth of a step's instructions, and three rounds in four no lane needs it)
+  auto advance = [&](uint32_t e, uint32_t w, bool is_dc, uint32_t comp, auto run_in) {
     const uint32_t size = huff_size(e);
     int diff = seg_extend(w, huff_adv(e) - size, size);            // jpeg.cpp:335-343; 0 for size 0
     diff = is_dc ? diff : 0;
-    dsum += diff; d1 += comp == 1u ? diff : 0; d2 += comp == 2u ? diff : 0;
-    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e);
-    const bool pair = a2 != 0u && z + z1 < 64u;
-    p += huff_adv(e) + (pair ? a2 : 0u);
+    // per component by multiply-add (comp is 0, 1 or 2: its two bits are the factors) -- on the FMA pipe, which this
+    // kernel leaves idle, instead of a compare and a select on the integer pipe, which it fills
+    dsum += diff; d1 += diff * (int)(comp & 1u); d2 += diff * (int)(comp >> 1);
+    // both symbols of a paired entry unless the first could end the block (kernels_segdec.cuh: a test on z alone)
+    const uint32_t z1 = huff_zinc(e), a2 = huff_adv2(e) & (z < 48u ? 15u : 0u);
+    const bool pair = a2 != 0u;
+    p += huff_adv(e) + a2;
     z += z1 + (pair ? huff_zinc2(e) : 0u);
     const bool end = z >= 64u;
     const uint32_t tbn = tba + 128u == tb_end ? tb_a : tba + 128u;
     z = end ? 0u : z;
     tba = end ? tbn : tba;
     nb += (end && p <= B) ? 1u : 0u;                               // a "block" that runs past the segment's end is padding
-    const bool ns = end && !started && p >= lo;                    // the run-in is over: the block that starts here is the sub's first
-    started = started || ns;
-    sp = ns ? p : sp; sba = ns ? tba : sba;
-    nb = ns ? 0u : nb; dsum = ns ? 0 : dsum; d1 = ns ? 0 : d1; d2 = ns ? 0 : d2;
+    if (decltype(run_in)::value) {
+      const bool ns = end && !started && p >= lo;                  // the run-in is over: the block that starts here is the sub's first
+      started = started || ns;
+      sp = ns ? p : sp; sba = ns ? tba : sba;
+      nb = ns ? 0u : nb; dsum = ns ? 0 : dsum; d1 = ns ? 0 : d1; d2 = ns ? 0 : d2;
+    }
     done = done || (end && p >= hi);
   };
+  bool all_started = false;                            // warp-uniform: every lane is past its run-in (or has nothing to walk)
   for (;;) {
     // top-up, once per round: the same instructions for every lane, predicated per lane (kernels_segdec.cuh)
     const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8) && rw <= (I.usbits >> 5) + 8u;
@@ -192,21 +201,26 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
     b2_cp_async_wait<2>();
     uint32_t w = 0, cur = 0, eraw = 0, comp = 0;
     bool is_dc = false, nearf = false;
+    auto steps = [&](auto run_in) {
 #pragma unroll
     for (int u = 0; u < kXSteps; ++u) {
       const uint32_t t = b2_lds_ro(tba);
       comp = b2_lds_ro(tba + kXTb2Off);
       is_dc = z == 0u;
       cur = lut_r + (is_dc ? (t & 0xffffu) : (t >> 16));
-      const uint32_t wa = ring_a + ((p << 2) & (uint32_t)((kSegWords - 1) << 7));
+      const uint32_t wa = b2_and_x4_add<(uint32_t)((kSegWords - 1) << 5)>(p, ring_a);      // ring_a + 128 * ((p >> 5) & 31)
       const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
       w = __funnelshift_l(w1, w0, p);
-      eraw = b2_lds_ro(cur + ((w >> (30 - kHLutBits)) & (uint32_t)((kHL1 - 1) * 4)));
+      eraw = b2_lds_ro(b2_shr_x4_add<32 - kHLutBits>(w, cur));
       // a block start inside the segment's last seven bits: padding or a very short block -- the extra slot decides
       nearf = is_dc && p + 7u >= B;
-      const uint32_t e = (done || nearf || eraw >= kHOverflow) ? 0u : eraw;
-      advance(e, w, is_dc, comp);
+      // (an entry the first table level cannot resolve stands still by itself: kernels_huff.cuh)
+      const uint32_t e = (done || nearf) ? 0u : eraw;
+      advance(e, w, is_dc, comp, run_in);
     }
+    };
+    if (!all_started) all_started = __all_sync(0xffffffffu, started || done);
+    if (all_started) steps(std::false_type()); else steps(std::true_type());
     // ---- the extra slot: lanes waiting in front of something the steps do not handle ----
     const bool stuck = !done && (nearf || eraw >= kHOverflow);
     if (__any_sync(0xffffffffu, stuck)) {
@@ -230,7 +244,7 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
             const int ci = (int)comp;
             e = huff_slow(is_dc ? tsets[I.im->tset].dc[I.im->td[ci] & 3] : tsets[I.im->tset].ac[I.im->ta[ci] & 3], w >> 16, is_dc);
           }
-          advance(e, w, is_dc, comp);
+          advance(e, w, is_dc, comp, std::true_type());
         }
       }
     }

@@ -155,23 +155,35 @@ B2_GLOBAL void k_unstuff_count(const ImageDev *__restrict__ imgs, const int32_t 
   if (threadIdx.x == 0) tile_cnt[blockIdx.x] = tot;   // emits in the low half, RSTs in the high half
 }
 
-// U2: one warp per image turns tile counts into exclusive prefixes (emits and RSTs separately).
+// U2: one warp per image turns tile counts into exclusive prefixes (emits and RSTs separately).  A lane takes kUScanPer
+// consecutive tiles per pass -- their loads are independent, the warp-wide scan runs over the lanes' sums -- so a scan of
+// several thousand tiles (one 8192 x 8192 image: 7,000) is some thirty dependent passes, not two hundred.
+constexpr int kUScanPer = 8;
 B2_GLOBAL void k_unstuff_scan(const ImageDev *__restrict__ imgs, int nimg, const uint32_t *__restrict__ tile_cnt,
                               uint2 *__restrict__ tile_pre) {
   const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (i >= nimg) return;
   const int t0 = imgs[i].tile_base, nt = imgs[i].ntiles;
   uint32_t carry_e = 0, carry_r = 0;
-  for (int b = 0; b < nt; b += 32) {
-    const int t = b + lane;
-    const uint32_t c = t < nt ? tile_cnt[t0 + t] : 0;
-    uint32_t e = c & 0xffffu, r = c >> 16;
+  for (int b = 0; b < nt; b += 32 * kUScanPer) {
+    const int t = b + lane * kUScanPer;
+    uint32_t c[kUScanPer];
+#pragma unroll
+    for (int k = 0; k < kUScanPer; ++k) c[k] = t + k < nt ? tile_cnt[t0 + t + k] : 0u;
+    uint32_t e = 0, r = 0;                                   // this lane's sums
+#pragma unroll
+    for (int k = 0; k < kUScanPer; ++k) { e += c[k] & 0xffffu; r += c[k] >> 16; }
     const uint32_t e0 = e, r0 = r;
     for (int d = 1; d < 32; d <<= 1) {
       const uint32_t oe = __shfl_up_sync(0xffffffffu, e, d), orr = __shfl_up_sync(0xffffffffu, r, d);
       if (lane >= d) { e += oe; r += orr; }
     }
-    if (t < nt) tile_pre[t0 + t] = make_uint2(carry_e + e - e0, carry_r + r - r0);
+    uint32_t pe = carry_e + e - e0, pr = carry_r + r - r0;   // exclusive prefixes of the lane's first tile
+#pragma unroll
+    for (int k = 0; k < kUScanPer; ++k) {
+      if (t + k < nt) tile_pre[t0 + t + k] = make_uint2(pe, pr);
+      pe += c[k] & 0xffffu; pr += c[k] >> 16;
+    }
     carry_e += __shfl_sync(0xffffffffu, e, 31);
     carry_r += __shfl_sync(0xffffffffu, r, 31);
   }
