@@ -14,6 +14,9 @@
 // valid stream both put the boundary at the same bit).
 //
 // HBM traffic: reads raw twice (count, scatter), writes it once: 3 B per scan byte.
+// (Tried and dropped, profiles/r02_experiments.md: count and scatter as ONE pass with decoupled look-back between the
+// tiles of an image.  Correct, but at 4 KiB per tile the look-back's trips through L2 cost more than the second
+// classification saves: 0.43 ms instead of 0.34 ms for C2.)
 #pragma once
 #include "platform.h"
 #include "dev_types.h"
@@ -131,6 +134,50 @@ B2_DEVICE bool u_count_fast(const uint8_t *__restrict__ raw, uint32_t pos, uint3
   return other == 0u && raw_len - pos >= 16u;
 }
 
+// A thread's emitted bytes into the tile's staging buffer (byte stores, already word-swapped); q = where they start.
+B2_DEVICE void u_stage(const UClass &c, uint32_t q, uint8_t *sbuf, uint32_t *sbuf32) {
+  if (c.emit_mask == 0xffffu) {
+    // all sixteen bytes pass (no FF near: 94 % of the threads): whole big-endian words, ragged ends as bytes
+    const uint32_t sh = q & 3u, wb = q >> 2;
+    uint32_t B[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) B[j] = __byte_perm(c.ow[j], 0, 0x0123);
+    if (sh == 0) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sbuf32[wb + j] = B[j];
+    } else {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) sbuf32[wb + j] = __funnelshift_r(B[j], B[j - 1], 8u * sh);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if ((uint32_t)k < 4u - sh) sbuf[(q + k) ^ 3u] = (uint8_t)(c.ow[0] >> (8 * k));
+        if ((uint32_t)k < sh) sbuf[(q + 16u - sh + k) ^ 3u] = (uint8_t)(c.ow[3] >> (8u * (4u - sh + k)));
+      }
+    }
+  } else {
+    uint32_t ee = q;
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      if (c.emit_mask & (1u << k)) { sbuf[ee ^ 3u] = (uint8_t)(c.ow[k >> 2] >> (8 * (k & 3))); ++ee; }
+  }
+}
+// The tile's output is the contiguous byte range [lo, hi) of the unstuffed scan, staged from the 16-byte aligned
+// position a: whole 16-byte chunks leave as 128-bit stores, the ragged first and last bytes (which neighbouring tiles
+// share) byte by byte.
+B2_DEVICE void u_drain(uint8_t *us, const uint8_t *sbuf, uint32_t a, uint32_t lo, uint32_t hi) {
+  const uint32_t c0 = (lo + 15u) & ~15u, c1 = hi & ~15u;           // whole 16-byte chunks inside it
+  for (uint32_t g = c0 + threadIdx.x * 16u; g < c1; g += kUThreads * 16u)
+    *reinterpret_cast<uint4 *>(us + g) = *reinterpret_cast<const uint4 *>(sbuf + (g - a));
+  if (threadIdx.x < 32) {                                          // ragged edges: at most 15 bytes each
+    const uint32_t head_end = c0 < hi ? c0 : hi;
+    const uint32_t g0 = lo + threadIdx.x;
+    if (g0 < head_end) us[g0 ^ 3u] = sbuf[(g0 - a) ^ 3u];
+    const uint32_t tail0 = c1 > head_end ? c1 : head_end;
+    const uint32_t g1 = tail0 + threadIdx.x;
+    if (g1 < hi) us[g1 ^ 3u] = sbuf[(g1 - a) ^ 3u];
+  }
+}
+
 // U1: per-tile counts and the first EOI / first illegal marker of each image.
 B2_GLOBAL void k_unstuff_count(const ImageDev *__restrict__ imgs, const int32_t *__restrict__ tile_base, int nimg,
                                const uint8_t *__restrict__ d_raw, uint32_t *__restrict__ tile_cnt,
@@ -215,30 +262,7 @@ B2_GLOBAL void k_unstuff_scatter(const ImageDev *__restrict__ imgs, const int32_
   const uint32_t a = tp.x & ~15u;                 // 16-byte aligned start of the range in the scan
   uint32_t *sbuf32 = reinterpret_cast<uint32_t *>(sbuf4);
   const uint32_t q = e - a;                       // where this thread's bytes start in the staging buffer
-  if (c.emit_mask == 0xffffu) {
-    // all sixteen bytes pass (no FF near: 94 % of the threads): whole big-endian words, ragged ends as bytes
-    const uint32_t sh = q & 3u, wb = q >> 2;
-    uint32_t B[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) B[j] = __byte_perm(c.ow[j], 0, 0x0123);
-    if (sh == 0) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) sbuf32[wb + j] = B[j];
-    } else {
-#pragma unroll
-      for (int j = 1; j < 4; ++j) sbuf32[wb + j] = __funnelshift_r(B[j], B[j - 1], 8u * sh);
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        if ((uint32_t)k < 4u - sh) sbuf[(q + k) ^ 3u] = (uint8_t)(c.ow[0] >> (8 * k));
-        if ((uint32_t)k < sh) sbuf[(q + 16u - sh + k) ^ 3u] = (uint8_t)(c.ow[3] >> (8u * (4u - sh + k)));
-      }
-    }
-  } else {
-    uint32_t ee = q;
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-      if (c.emit_mask & (1u << k)) { sbuf[ee ^ 3u] = (uint8_t)(c.ow[k >> 2] >> (8 * (k & 3))); ++ee; }
-  }
+  u_stage(c, q, sbuf, sbuf32);
   for (uint32_t m = c.rst_mask; m; m &= m - 1) {  // rare: a restart marker ends at byte k
     const int k = __ffs((int)m) - 1;
     const uint32_t before = (uint32_t)__popc(c.rst_mask & ((1u << k) - 1u));
@@ -255,19 +279,7 @@ B2_GLOBAL void k_unstuff_scatter(const ImageDev *__restrict__ imgs, const int32_
     }
   }
   __syncthreads();
-  uint8_t *us = d_us + im.raw_off;
-  const uint32_t lo = tp.x, hi = tp.x + (tot & 0xffffu);          // byte range this tile owns
-  const uint32_t c0 = (lo + 15u) & ~15u, c1 = hi & ~15u;           // whole 16-byte chunks inside it
-  for (uint32_t g = c0 + threadIdx.x * 16u; g < c1; g += kUThreads * 16u)
-    *reinterpret_cast<uint4 *>(us + g) = *reinterpret_cast<const uint4 *>(sbuf + (g - a));
-  if (threadIdx.x < 32) {                                          // ragged edges: at most 15 bytes each
-    const uint32_t head_end = c0 < hi ? c0 : hi;
-    const uint32_t g0 = lo + threadIdx.x;
-    if (g0 < head_end) us[g0 ^ 3u] = sbuf[(g0 - a) ^ 3u];
-    const uint32_t tail0 = c1 > head_end ? c1 : head_end;
-    const uint32_t g1 = tail0 + threadIdx.x;
-    if (g1 < hi) us[g1 ^ 3u] = sbuf[(g1 - a) ^ 3u];
-  }
+  u_drain(d_us + im.raw_off, sbuf, a, tp.x, tp.x + (tot & 0xffffu));
 }
 
 // U4: close the segment tables and raise the stream-level status bits.
