@@ -402,7 +402,8 @@ def run_gpu_arm(args, rank, world, local_rank):
         entropy_dom = dom != "pixel"
         roofline = {"kernel": d["name"], "bound": "hbm", "achieved": d["gbs"], "peak": peak, "unit": "GB/s", "frac": d["frac"],
                     "traffic": d.get("traffic"), "peak_source": peak_src,
-                    "real_bound": "integer issue (one dependent chain per stream: position -> window -> table -> position)"
+                    "real_bound": "integer (ALU) pipe of the SM sub-partitions, one warp instruction per two cycles -- "
+                                  "see issue.alu_pipe_pct; one dependent chain per stream: position -> window -> table -> position"
                                   if entropy_dom else "hbm, then fp32 issue of the mandated operation order",
                     "issue": dict(d.get("issue", {}), unit="warp instructions per cycle and SM", peak=4.0,
                                   frac=(d["issue"]["ipc"] / 4.0 if d.get("issue", {}).get("ipc") else None)),

@@ -123,6 +123,15 @@ def test_zero_padded_restart_segments_decode_on_both_paths(emul, oracle_mod, har
         assert np.array_equal(rgbs[1], r0)
 
 
+def test_extreme_aspect_ratios_and_tiny_restart_intervals(emul, oracle_mod, harness):
+    # one MCU wide / one MCU high, a restart marker after every MCU; both entropy paths
+    cases = [(8, 600, 90, 1, 1, 0, 1), (600, 8, 90, 1, 1, 0, 1), (16, 401, 85, 2, 2, 0, 1), (520, 16, 85, 2, 2, 0, 0),
+             (9, 333, 92, 1, 2, 0, 7), (5, 300, 80, 1, 1, 1, 3)]
+    datas = [harness.synth_jpeg(900 + i, *c) for i, c in enumerate(cases)]
+    check(emul, oracle_mod, datas, flags=1, path=1)
+    check(emul, oracle_mod, datas, flags=1, path=2)
+
+
 def test_tables_with_more_long_codes_than_the_second_level_holds(emul, oracle_mod, harness):
     # AC tables whose 140 twelve-bit codes cover 35 ten-bit prefixes (kernels_huff.cuh provides a second level for 8):
     # the codes beyond them are resolved from the DHT data (huff_slow) -- in the ninth step of the segment decoder's

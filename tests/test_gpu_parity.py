@@ -74,6 +74,15 @@ def test_mixed_batch_all_sampling_formats(dec, oracle_mod, harness):
     compare(dec, oracle_mod, datas, flags=1)
 
 
+def test_extreme_aspect_ratios_and_tiny_restart_intervals(dec, oracle_mod, harness):
+    # one MCU wide or one MCU high, a restart marker after every MCU (thousands of segments of a few bytes), and a
+    # restart interval that does not divide the MCU count
+    cases = [(8, 3001, 90, 1, 1, 0, 1), (3001, 8, 90, 1, 1, 0, 1), (16, 2049, 85, 2, 2, 0, 1), (4100, 16, 85, 2, 2, 0, 0),
+             (2047, 9, 92, 2, 1, 0, 1), (9, 1999, 92, 1, 2, 0, 7), (5, 4000, 80, 1, 1, 1, 3), (4000, 3, 80, 1, 1, 1, 0)]
+    datas = [harness.synth_jpeg(900 + i, *c) for i, c in enumerate(cases)]
+    compare(dec, oracle_mod, datas, flags=1)
+
+
 def test_extreme_content(dec, oracle_mod, harness):
     """Pictures at the ends of the symbol statistics, many restart segments each:
     flat ones (every block is DC + EOB: a lane finishes four to five blocks per FIFO round -- the most the segment
