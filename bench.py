@@ -330,15 +330,17 @@ def run_gpu_arm(args, rank, world, local_rank):
     assert all(s == 0 for s in st), "decode status not clean: %r" % st[:8]
     stage = {k: 0.0 for k in ("unstuff", "sync", "write", "pixel", "total")}
     barrier()
-    with ClockSampler(local_rank) as clocks:
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            dec.run()
-            dec.fetch(None, None)          # waits on the stream, reads the convergence flag + per-image status
-            for k, v in dec.last_timing().items():
-                stage[k] += v
-        barrier()
-        t_res = time.perf_counter() - t0
+    # clocks and throttle reasons are sampled through BOTH timed regions (device-resident and host -> host): ten
+    # device-resident steps of a few ms are shorter than one sampling period of nvidia-smi
+    clocks = ClockSampler(local_rank).__enter__()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        dec.run()
+        dec.fetch(None, None)          # waits on the stream, reads the convergence flag + per-image status
+        for k, v in dec.last_timing().items():
+            stage[k] += v
+    barrier()
+    t_res = time.perf_counter() - t0
     t_res = max_over_ranks(t_res)
     stats = dec.stats()
     launches = stats["kernel_launches"] * args.steps
@@ -357,6 +359,7 @@ def run_gpu_arm(args, rank, world, local_rank):
         st = e2e_step()
     barrier()
     t_e2e = max_over_ranks(time.perf_counter() - t0)
+    clocks.__exit__(None, None, None)
     stats_e = dec.stats()
     assert all(s == 0 for s in st)
     # the same copies, same chunks, same buffers, no kernels: the PCIe floor under the call at this N
