@@ -101,7 +101,7 @@ constexpr int kSegSlots = kSegSteps + 1;      // FIFO slots per round: the steps
 constexpr int kSegSlotBytes = 3 * 128;        // one slot: (window, entry, zig-zag index | block number) x 32 lanes
 constexpr int kSegRoundBytes = kSegSlots * kSegSlotBytes + 128;   // + the round's last word per lane (kSegTailNbShift)
 constexpr int kSegMaxFin = (kSegSlots + 1) / 2;   // blocks a lane can FINISH in one round: a block is a DC symbol and at least one more
-constexpr int kSegCopyDepth = 3;              // blocks per thread-octet and pass of the flusher's copy loop (2, 3, 4: the same time)
+constexpr int kSegCopyDepth = 3;              // blocks per thread-octet and pass of the flusher's copy loop (2, 3, 4: the same time; 6: 2-4 % slower)
 constexpr int kSegAsm = 8;                    // block images per lane in the assembly ring; a round touches at most 6 blocks of a lane
 constexpr int kSegUnroll = B2_SEG_UNROLL;     // how far the decoder's step loop is unrolled (instruction-cache footprint)
 constexpr unsigned kSegPollNs = B2_SEG_POLL_NS;   // a warp that finds nothing to do sleeps this long before it looks again
@@ -317,7 +317,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
 #if B2_SEG_DIAG == 7
   unsigned long long diag[6] = {0, 0, 0, 0, 0, 0};
   long long tprev = clock64();
-  uint32_t nroom = 0;
+  uint32_t nroom = 0, lane_rounds = 0;     // lane_rounds: rounds in which THIS lane still had something to decode
 #endif
   for (;; ++r) {
     const bool room = ff.has_room(r);     // asked before the top-up, needed after it: the barrier's answer takes ~90 cycles
@@ -339,6 +339,7 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     if (!room) ff.wait_room(r);
 #if B2_SEG_DIAG == 7
     nroom += room ? 0u : 1u;
+    lane_rounds += done ? 0u : 1u;
 #endif
     B2_SEG_TICK(1);
     const uint32_t slot_a = ff.round_a(r);
@@ -421,6 +422,11 @@ B2_DEVICE void seg_decode(const SegFifo &ff, int lane, const SegLane &L, const I
     atomicAdd(&g_seg_diag[6], (unsigned long long)(r + 1));
     atomicAdd(&g_seg_diag[7], 1ull);
     atomicAdd(&g_seg_diag[8], (unsigned long long)nroom);
+  }
+  {
+    unsigned long long lr = lane_rounds;       // sum over the warp's lanes
+    for (int d = 16; d > 0; d >>= 1) lr += __shfl_xor_sync(0xffffffffu, lr, d);
+    if (lane == 0) atomicAdd(&g_seg_diag[9], lr);
   }
 #endif
   // the last block ran past the segment's end (file.hpp:36-40), or more than padding is left: the segment holds more blocks

@@ -39,6 +39,7 @@ rounds, warps = v[6], v[7]
 print(json.dumps({"lib": os.path.basename(jd.LIB_SO), "write_ms": round(t["write"], 4), "decoder_warps": warps, "rounds_per_warp": round(rounds / warps, 1),
                   "cycles_per_round": {n: round(v[i] / rounds, 1) for i, n in enumerate(names)}, "total_per_round": round(sum(v[:6]) / rounds, 1),
                   "rounds_without_room": round(v[8] / rounds, 3),
+                  "lanes_busy": round(v[9] / (32.0 * rounds), 3),   # share of (lane, round) slots in which the lane still had work
                   "writer_per_own_round": {n: round(v[10 + i] / max(v[13], 1), 1) for i, n in enumerate(["wait_full", "wait_asm_room", "read+compute"])},
                   "flusher_per_round": {n: round(v[16 + i] / max(v[19], 1), 1) for i, n in [(0, "wait_full"), (1, "wait_worked"), (4, "masks+dc"), (5, "list"), (6, "copy"), (2, "release"), (7, "blocks")]}}))
 dec.close()
