@@ -90,7 +90,7 @@ B2_DEVICE XLoc x_locate(int gsub, const XParams &xp, const int32_t *__restrict__
 }
 
 // ---------------------------------------------------------------- plan: subs and units per segment (one warp per image)
-B2_GLOBAL void k_xplan(XParams xp, const ImageDev *__restrict__ imgs, const ImageOut *__restrict__ out,
+B2_GLOBAL void k_xplan(XParams xp, const ImageDev *__restrict__ imgs, ImageOut *__restrict__ out,
                        const uint32_t *__restrict__ seg_start, uint32_t *__restrict__ segsub, uint32_t *__restrict__ segunit) {
   const int i = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (i >= xp.nimg) return;
@@ -103,6 +103,9 @@ B2_GLOBAL void k_xplan(XParams xp, const ImageDev *__restrict__ imgs, const Imag
     uint32_t ns = 0, nu = 0;
     if (k < im.nseg && !dead) {
       const uint32_t len = seg[k + 1] - seg[k];
+      // a segment without a single bit (a file cut right behind an RSTn) has no sub, and so nobody who would count its
+      // blocks: the header promises at least one MCU here
+      if (len == 0u) atomicOr(&out[i].status, (uint32_t)ST_BLOCK_COUNT);
       ns = (len + (1u << xp.sub_shift) - 1u) >> xp.sub_shift;
       nu = (ns + (uint32_t)xp.unit_subs - 1u) / (uint32_t)xp.unit_subs;
     }
@@ -129,6 +132,7 @@ struct XWalkIn {
   const ImageDev *im;        // for the per-length search of pathological tables only
 };
 struct XWalkOut { uint32_t sp, sblk, ep, eblk; int nb, d0, d1, d2; };
+constexpr int kXOverNb = 1 << 28;            // "blocks" of a sub whose walk ran past its segment's end (see x_walk)
 
 // All 32 lanes of a warp together.  ringl: this lane's column of the warp's window ring; tbl: this lane's column of the
 // warp's table-offset entries, already filled for the lane's image ([blk] = DC table byte offset | AC << 16, and at
@@ -189,6 +193,7 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
     done = done || (end && p >= hi);
   };
   bool all_started = false;                            // warp-uniform: every lane is past its run-in (or has nothing to walk)
+  bool padblk = false;                                 // the segment's last bits (at most seven) were taken for a block start
   for (;;) {
     // top-up, once per round: the same instructions for every lane, predicated per lane (kernels_segdec.cuh)
     const bool need = !done && rw - (p >> 5) <= (uint32_t)(kSegWords - 8) && rw <= (I.usbits >> 5) + 8u;
@@ -237,6 +242,7 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
           if (!started) { started = true; nb = 0u; dsum = d1 = d2 = 0; sp = B; sba = tb_a; }
           p = B; tba = tb_a; z = 0u; done = true;
         } else {
+          padblk = padblk || nearf;
           uint32_t e = eraw;
           if (e & kHLong) e = b2_lds(cur + 4u * (huff_l2_base(e) + ((w >> (32 - kHLutBits - 6)) & 63u)));
           else if (huff_is_l1_error(e)) e = huff_l1_error(e);
@@ -256,6 +262,12 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
   if (O.sp >= B) { O.sp = B; O.sblk = 0; }           // the segment is over: the next block is the next segment's first
   if (O.ep >= B) { O.ep = B; O.eblk = 0; }
   O.nb = (int)nb; O.d1 = d1; O.d2 = d2; O.d0 = dsum - d1 - d2;
+  // A block that began more than padding before the segment's end and ran past it is not one of the blocks counted above
+  // -- if the header's count is already complete without it, nobody would notice that more than padding is left over
+  // (the segment decoder says ST_BLOCK_COUNT to this; found by scripts/dev/soak.py).  A count no segment can reach makes
+  // k_xunits say the same; its clamps keep every unit inside the segment's blocks.  Only a walk that met a block start
+  // inside its own sub (sp < hi) knows what follows that start: a run-in that never synchronised says nothing.
+  if (I.active && p > B && !padblk && sp < hi) O.nb = kXOverNb;
   if (!I.active) { O.sp = O.ep = I.p; O.sblk = O.eblk = I.blk; O.nb = O.d0 = O.d1 = O.d2 = 0; }
 }
 

@@ -1,0 +1,101 @@
+#!/usr/bin/env python
+"""Dev tool: randomised soak of both entropy paths on the GPU -- clean pictures of random shape / sampling / quality /
+restart interval next to corrupted copies of them (byte flips, truncation, runs of FF 00 / 00 / FF FF, chunks moved),
+in mixed batches.  Checks: no hang (run it under `timeout`), clean pictures bit-exact against the oracle (a sample) and
+identical between the two paths (all), every corrupted picture either flagged or decoded to the oracle's result.
+    timeout 600 python scripts/dev/soak.py [rounds] [seed]  -> one JSON line"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+import jpeg_decoder_b200 as jd  # noqa: E402
+from jpeg_decoder_b200 import abi, harness  # noqa: E402
+from oracle import oracle  # noqa: E402
+
+rounds = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+harness.build_harness(); oracle.build()
+
+
+def corrupt(d):
+    m = bytearray(d)
+    body = d.find(b"\xff\xda") + 14
+    n = len(d) - 2 - body
+    if n < 16:
+        return bytes(m)
+    kind = int(rng.integers(0, 7))
+    at = body + int(rng.integers(0, n - 8))
+    ln = int(rng.integers(1, min(n - (at - body), 400)))
+    if kind == 0:
+        for p in rng.integers(body, len(d) - 2, size=int(rng.integers(1, 30))):
+            m[p] = int(rng.integers(0, 255))
+    elif kind == 1:
+        m = m[:at] + b"\xff\xd9"
+    elif kind == 2:
+        m[at:at + ln] = (b"\xff\x00" * ln)[:ln]
+    elif kind == 3:
+        m[at:at + ln] = bytes(ln)
+    elif kind == 4:
+        m[at:at + ln] = b"\xff" * ln
+    elif kind == 5:
+        src = body + int(rng.integers(0, n - 8))
+        m[at:at + ln] = m[src:src + ln]
+    else:
+        m[at:at + 2] = bytes([0xff, int(rng.integers(0xd0, 0xd8))])
+    return bytes(m)
+
+
+decs = {p: jd.Decoder(0) for p in ("segment", "sync")}
+decs["segment"].set_entropy_path(abi.ENTROPY_SEGMENT); decs["sync"].set_entropy_path(abi.ENTROPY_SYNC)
+stat = {"batches": 0, "clean": 0, "corrupt": 0, "corrupt_flagged": 0, "oracle_checked": 0, "unflagged_same_as_oracle": 0,
+        "unflagged_but_oracle_rejects": 0}
+for r in range(rounds):
+    datas, clean = [], []
+    for i in range(int(rng.integers(4, 24))):
+        w, h = int(rng.integers(1, 700)), int(rng.integers(1, 500))
+        hs, vs = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
+        gray = bool(rng.integers(0, 6) == 0)
+        if gray:
+            hs = vs = 1
+        q = int(rng.integers(20, 100))
+        ri = int([0, 0, -1, 1, 2, 5, 17][int(rng.integers(0, 7))])
+        d = harness.synth_jpeg(int(rng.integers(0, 1 << 30)), w, h, q, hs, vs, gray, ri)
+        datas.append(d); clean.append(True)
+        for _ in range(int(rng.integers(0, 3))):
+            datas.append(corrupt(d)); clean.append(False)
+    order = rng.permutation(len(datas))
+    datas = [datas[k] for k in order]; clean = [clean[k] for k in order]
+    res = {p: decs[p].decode(datas, flags=1, want_coef=True) for p in decs}
+    stat["batches"] += 1
+    for i, d in enumerate(datas):
+        st_s, st_x = res["segment"][0][i], res["sync"][0][i]
+        if clean[i]:
+            stat["clean"] += 1
+            assert st_s == 0 and st_x == 0, (r, i, st_s, st_x)
+            assert np.array_equal(res["segment"][1][i], res["sync"][1][i]) and np.array_equal(res["segment"][2][i], res["sync"][2][i])
+            if i % 5 == 0:
+                rc, _, oc, orgb = oracle.port_decode(d, flags=1)
+                assert rc == 0 and np.array_equal(res["segment"][2][i].astype(np.int32), oc) and np.array_equal(res["segment"][1][i], orgb)
+                stat["oracle_checked"] += 1
+        else:
+            stat["corrupt"] += 1
+            for p, st in (("segment", st_s), ("sync", st_x)):
+                if st != 0:
+                    stat["corrupt_flagged"] += 1
+                    continue
+                rc, _, oc, orgb = oracle.port_decode(d, flags=1)      # not flagged: then it must be what the reference logic makes of it
+                if rc == 0:
+                    assert np.array_equal(res[p][2][i].astype(np.int32), oc), (r, i, p, "unflagged corrupt stream differs from the oracle")
+                    stat["unflagged_same_as_oracle"] += 1
+                else:
+                    stat["unflagged_but_oracle_rejects"] += 1
+                    os.makedirs(os.path.join(ROOT, "gpurun_out", "soak"), exist_ok=True)
+                    name = os.path.join(ROOT, "gpurun_out", "soak", "case_%s_r%d_i%d.jpg" % (p, r, i))
+                    open(name, "wb").write(d)
+                    print(json.dumps({"oracle_rc": rc, "path": p, "status": 0, "round": r, "image": i, "file": name}), flush=True)
+print(json.dumps(stat))
+assert stat["unflagged_but_oracle_rejects"] == 0, "a stream the reference's logic rejects went through unflagged"

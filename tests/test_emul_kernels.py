@@ -123,6 +123,36 @@ def test_zero_padded_restart_segments_decode_on_both_paths(emul, oracle_mod, har
         assert np.array_equal(rgbs[1], r0)
 
 
+def test_file_cut_right_behind_a_restart_marker_is_flagged_on_both_paths(emul, harness):
+    # the last restart segment holds no bit at all (found by scripts/dev/soak.py): the self-synchronising path has no
+    # sub-sequence there, so the planner itself has to say that the segment's blocks are missing
+    from jpeg_decoder_b200 import abi
+    from tests import jpeg_craft as jc
+    good = harness.synth_jpeg(81, 200, 120, 85, 2, 2, False, 1)
+    marks = jc.restart_markers(good)
+    cut = good[:marks[-1] + 2] + b"\xff\xd9"                   # ... RSTn FF D9
+    mid = good[:marks[len(marks) // 2] + 2] + good[marks[len(marks) // 2 + 1]:]   # a segment's bytes removed: RSTn RSTn+1 in a row
+    for path in (1, 2):
+        st, rgbs, _, _ = emul.decode([good, cut, mid, good], flags=1, path=path)
+        assert st[0] == 0 and st[3] == 0 and np.array_equal(rgbs[0], rgbs[3])
+        assert st[1] != 0 and st[2] != 0, (path, st)
+        assert not rgbs[1].any() or (st[1] & (abi.ST_BLOCK_COUNT | abi.ST_OVERRUN | abi.ST_BAD_RST_COUNT))
+
+
+def test_streams_the_soak_found_are_flagged_on_both_paths(emul, oracle_mod):
+    # scripts/dev/soak.py (random corruption, both entropy paths against the oracle) found two kinds of stream that the
+    # reference's logic rejects and the self-synchronising path let through: a file cut right behind an RSTn, and a
+    # restart segment with more than padding left over behind its last block.  The files are kept as fixtures.
+    import os
+    from tests.conftest import GOLDEN_DIR
+    for name in ("soak_cut_behind_rst.jpg", "soak_leftover_behind_last_block.jpg"):
+        d = open(os.path.join(GOLDEN_DIR, name), "rb").read()
+        assert oracle_mod.port_decode(d, flags=1)[0] != 0
+        for path in (1, 2):
+            st, _, _, _ = emul.decode([d], flags=1, path=path)
+            assert st[0] != 0, (name, path)
+
+
 def test_extreme_aspect_ratios_and_tiny_restart_intervals(emul, oracle_mod, harness):
     # one MCU wide / one MCU high, a restart marker after every MCU; both entropy paths
     cases = [(8, 600, 90, 1, 1, 0, 1), (600, 8, 90, 1, 1, 0, 1), (16, 401, 85, 2, 2, 0, 1), (520, 16, 85, 2, 2, 0, 0),

@@ -74,6 +74,31 @@ def test_mixed_batch_all_sampling_formats(dec, oracle_mod, harness):
     compare(dec, oracle_mod, datas, flags=1)
 
 
+def test_file_cut_right_behind_a_restart_marker_is_flagged(dec, harness):
+    # an EMPTY restart segment (file cut behind an RSTn, or two RSTn in a row): flagged by both entropy paths, black
+    # pixels, neighbours untouched
+    from tests import jpeg_craft as jc
+    good = harness.synth_jpeg(81, 200, 120, 85, 2, 2, False, 1)
+    marks = jc.restart_markers(good)
+    cut = good[:marks[-1] + 2] + b"\xff\xd9"
+    mid = good[:marks[len(marks) // 2] + 2] + good[marks[len(marks) // 2 + 1]:]
+    st, rgbs, _ = dec.decode([good, cut, mid, good], flags=1)
+    assert st[0] == 0 and st[3] == 0 and np.array_equal(rgbs[0], rgbs[3])
+    assert st[1] != 0 and st[2] != 0, st
+    assert not rgbs[1].any() and not rgbs[2].any()
+
+
+def test_streams_the_soak_found_are_flagged(dec, oracle_mod):
+    # tests/golden/soak_*.jpg: what scripts/dev/soak.py found (see test_emul_kernels.py); flagged, black, by both paths
+    import os
+    from tests.conftest import GOLDEN_DIR
+    datas = [open(os.path.join(GOLDEN_DIR, n), "rb").read() for n in ("soak_cut_behind_rst.jpg", "soak_leftover_behind_last_block.jpg")]
+    st, rgbs, _ = dec.decode(datas, flags=1)
+    for i, d in enumerate(datas):
+        assert oracle_mod.port_decode(d, flags=1)[0] != 0
+        assert st[i] != 0 and not rgbs[i].any()
+
+
 def test_extreme_aspect_ratios_and_tiny_restart_intervals(dec, oracle_mod, harness):
     # one MCU wide or one MCU high, a restart marker after every MCU (thousands of segments of a few bytes), and a
     # restart interval that does not divide the MCU count
