@@ -49,11 +49,13 @@ struct ProgBits {
   uint32_t cidx;
   uint32_t buf;         // left-aligned: the next bit is bit 31
   int cnt;              // valid bits in buf
+  uint32_t fake;        // zero bytes fed since the last restart because the data had run out (end of the scan, or a marker)
+  bool over;            // ... and some of their bits were USED, not just looked at: file.hpp:36-40 "unavailable data"
   B2_MEMBER void init(const uint8_t *b, uint32_t len) {
     const uintptr_t a = reinterpret_cast<uintptr_t>(b);
     base = reinterpret_cast<const uint4 *>(a & ~(uintptr_t)15);
     pos = (uint32_t)(a & 15); end = pos + len;
-    cidx = 0xffffffffu; buf = 0; cnt = 0;
+    cidx = 0xffffffffu; buf = 0; cnt = 0; fake = 0; over = false;
     c = make_uint4(0, 0, 0, 0);
   }
   B2_MEMBER uint32_t byte_at(uint32_t q) {            // q < end (the scan buffer has slack behind the last image)
@@ -65,14 +67,17 @@ struct ProgBits {
   B2_MEMBER void fill() {
     while (cnt <= 24) {
       uint32_t byte = 0;
+      bool real = false;
       if (pos < end) {
         byte = byte_at(pos);
+        real = true;
         if (byte == 0xffu) {
           const uint32_t nx = pos + 1 < end ? byte_at(pos + 1) : 0xd9u;
           if (nx == 0u) pos += 2;                     // stuffed zero (file.hpp:78-82)
-          else byte = 0;                              // a marker (RSTn or the end of the scan): feed zeros, stay in front of it
+          else { byte = 0; real = false; }            // a marker (RSTn or the end of the scan): feed zeros, stay in front of it
         } else ++pos;
       }
+      fake += real ? 0u : 1u;
       buf |= byte << (24 - cnt);
       cnt += 8;
     }
@@ -87,9 +92,20 @@ struct ProgBits {
     return v;
   }
   B2_MEMBER uint32_t bit() { return bits(1); }
-  B2_MEMBER void restart() {                          // byte-align (BitStream::align, file.hpp:161-164) and step over RSTn
-    buf = 0; cnt = 0;
-    if (pos + 1 < end && byte_at(pos) == 0xffu) { const uint32_t m = byte_at(pos + 1); if (m >= 0xd0u && m <= 0xd7u) pos += 2; }
+  // the fed zeros are the newest bytes of the buffer: if more of them were fed than bits are left, some were consumed
+  B2_MEMBER void account() { over = over || (int)(fake * 8u) > cnt; }
+  B2_MEMBER void restart() {
+    // BitStream::align (file.hpp:161-164): on to the next byte boundary of what has been USED.  Bytes come in whole, so the
+    // bits to drop are cnt mod 8; what is left are whole bytes looked at ahead of time -- the newest `fake` of them zeros fed
+    // in front of the marker, which go; real ones (there is no marker here: a damaged file) stay, as the reference, which has
+    // dropped the markers wherever they stood (file.hpp:84-86), would read on from the same byte
+    account();
+    skip(cnt & 7);
+    const int drop = (int)fake * 8 < cnt ? (int)fake * 8 : cnt;
+    cnt -= drop;
+    buf = cnt ? buf & ~(0xffffffffu >> cnt) : 0u;
+    fake = 0;
+    if (cnt == 0 && pos + 1 < end && byte_at(pos) == 0xffu) { const uint32_t m = byte_at(pos + 1); if (m >= 0xd0u && m <= 0xd7u) pos += 2; }
   }
 };
 
@@ -263,6 +279,8 @@ k_prog_scan(const ImageDev *__restrict__ imgs, const ProgImageDev *__restrict__ 
         err |= prog_block(B, S, coef, im.coef_base + block_of(by, bx), pred[c], &T[0], &T[0], eobrun);
       }
   }
+  B.account();
+  if (B.over) err |= ST_OVERRUN;                      // the scan (or a restart interval of it) ended before its blocks did
   if (err) atomicOr(&out[i].status, err);
 }
 

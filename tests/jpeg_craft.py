@@ -236,3 +236,16 @@ def with_ac_code_lengths(data, bits):
 
 # 22 codes of 2..8 bits, 140 codes of 12 bits: the long codes cover 35 ten-bit prefixes
 OVERFLOW_AC_BITS = [0, 1, 1, 2, 2, 4, 4, 8, 0, 0, 0, 140, 0, 0, 0, 0]
+
+
+def damaged_progressive(data):
+    """Two damaged copies of a progressive file with restart markers (what scripts/dev/soak_progressive.py found):
+    (zeros over a stretch of the LAST scan that holds one RSTn -- the reference's logic reads on over it and so must we,
+     the file cut in the middle of the last scan -- the scan ends before its blocks do)."""
+    sos = [i for i in range(len(data) - 1) if data[i] == 0xFF and data[i + 1] == 0xDA][-1]
+    marks = [i for i in range(sos + 14, len(data) - 2) if data[i] == 0xFF and 0xD0 <= data[i + 1] <= 0xD7]
+    m = marks[len(marks) // 2]
+    zeroed = bytearray(data)
+    zeroed[m - 60:m + 60] = bytes(120)
+    cut = data[:m - 30] + b"\xff\xd9"
+    return bytes(zeroed), cut

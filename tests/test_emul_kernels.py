@@ -206,3 +206,11 @@ def test_progressive_scans_against_reference_digests(emul, oracle_mod, golden_pr
         assert sha(c.astype(np.int32)) == golden_prog[n]["coef_sha256"] and sha(r) == golden_prog[n]["rgb_sha256"], n
     rc, _, oc, orgb = oracle_mod.port_decode_progressive(datas[-1])
     assert rc == 0 and np.array_equal(coefs[-1].astype(np.int32), oc) and np.array_equal(rgbs[-1], orgb)
+    # damaged files: around a destroyed RSTn the result is the reference's reading of the file or a status; a scan that ends early is flagged
+    from tests import jpeg_craft as jc
+    zeroed, cut = jc.damaged_progressive(open(os.path.join(GOLDEN_DIR, "prog", "p420_320x240_q90_rst.jpg"), "rb").read())
+    st, rgbs, coefs = emul.decode_progressive([zeroed, cut])
+    rc, _, oc, orgb = oracle_mod.port_decode_progressive(zeroed)
+    assert st[0] != 0 or (rc == 0 and np.array_equal(coefs[0].astype(np.int32), oc) and np.array_equal(rgbs[0], orgb))   # flagged, or the reference's reading
+    assert oracle_mod.port_decode_progressive(cut)[0] != 0 and st[1] != 0
+

@@ -323,5 +323,14 @@ def test_progressive_files(lib_so, oracle_mod, golden_prog):
         bad = bytearray(datas[0]); k = bad.rfind(b"\xff\xda"); bad[k + 20:k + 60] = bytes(40)
         st, _, _ = dec.decode_progressive([bytes(bad), datas[1]])
         assert st[1] == 0
+        # what scripts/dev/soak_progressive.py found: around a destroyed RSTn the result is the reference's reading of the file
+        # (BitStream::align, then on from the same byte) or a status; a scan that ends before its blocks do is flagged and black
+        from tests import jpeg_craft as jc
+        zeroed, cut = jc.damaged_progressive(open(os.path.join(GOLDEN_DIR, "prog", "p420_320x240_q90_rst.jpg"), "rb").read())
+        st, rgbs, coefs = dec.decode_progressive([zeroed, cut, datas[1]], want_coef=True)
+        rc, _, oc, orgb = oracle_mod.port_decode_progressive(zeroed)
+        assert st[0] != 0 or (rc == 0 and np.array_equal(coefs[0].astype(np.int32), oc) and np.array_equal(rgbs[0], orgb))   # flagged, or the reference's reading
+        assert oracle_mod.port_decode_progressive(cut)[0] != 0 and st[1] != 0 and not rgbs[1].any()
+        assert st[2] == 0
     finally:
         dec.close()
