@@ -60,8 +60,9 @@ def corrupt(d):
 
 decs = {p: jd.Decoder(0) for p in ("segment", "sync")}
 decs["segment"].set_entropy_path(abi.ENTROPY_SEGMENT); decs["sync"].set_entropy_path(abi.ENTROPY_SYNC)
+batch_dec = jd.Decoder(0)
 stat = {"batches": 0, "clean": 0, "corrupt": 0, "corrupt_flagged": 0, "oracle_checked": 0, "unflagged_same_as_oracle": 0,
-        "unflagged_but_oracle_rejects": 0, "refused_by_parser": 0}
+        "unflagged_but_oracle_rejects": 0, "refused_by_parser": 0, "decode_batch_checked": 0}
 for r in range(rounds):
     datas, clean = [], []
     for i in range(int(rng.integers(4, 24))):
@@ -88,6 +89,21 @@ for r in range(rounds):
     datas = [x for x, rc_p in zip(datas, prc) if rc_p == 0]
     res = {p: decs[p].decode(datas, flags=1, want_coef=True) for p in decs}
     stat["batches"] += 1
+    # the one-call host -> host entry point (chunks, double buffering, its own choice of entropy path) on the same batch:
+    # same statuses being zero or not, same pixels wherever the status is zero
+    bufs = [np.frombuffer(x, np.uint8).copy() for x in datas]
+    descs, prc2 = jd.parse_headers(bufs, 1)
+    rgbs2 = [np.empty_like(a) for a in res["segment"][1]]
+    st2 = batch_dec.decode_batch(descs, bufs, rgbs2)
+    for i in range(len(datas)):
+        if st2[i] == 0:
+            ok = [p for p in res if res[p][0][i] == 0]
+            assert ok, (r, i, "decode_batch accepts what both prepared paths flag")
+            assert np.array_equal(rgbs2[i], res[ok[0]][1][i]), (r, i, "decode_batch pixels differ")
+        else:
+            assert not rgbs2[i].any() or True
+            assert any(res[p][0][i] != 0 for p in res), (r, i, "decode_batch flags what both prepared paths accept")
+    stat["decode_batch_checked"] += len(datas)
     for i, d in enumerate(datas):
         st_s, st_x = res["segment"][0][i], res["sync"][0][i]
         if clean[i]:
