@@ -3,7 +3,7 @@
 restart interval next to corrupted copies of them (byte flips, truncation, runs of FF 00 / 00 / FF FF, chunks moved),
 in mixed batches.  Checks: no hang (run it under `timeout`), clean pictures bit-exact against the oracle (a sample) and
 identical between the two paths (all), every corrupted picture either flagged or decoded to the oracle's result.
-    timeout 600 python scripts/dev/soak.py [rounds] [seed]  -> one JSON line"""
+    timeout 600 python scripts/dev/soak.py [rounds] [seed] [max width] [max height]  -> one JSON line"""
 import json
 import os
 import sys
@@ -18,6 +18,7 @@ from oracle import oracle  # noqa: E402
 
 rounds = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+MAXW, MAXH = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (700, 500)   # larger: several CTAs of subs per scan
 harness.build_harness(); oracle.build()
 
 
@@ -65,8 +66,8 @@ stat = {"batches": 0, "clean": 0, "corrupt": 0, "corrupt_flagged": 0, "oracle_ch
         "unflagged_but_oracle_rejects": 0, "refused_by_parser": 0, "decode_batch_checked": 0}
 for r in range(rounds):
     datas, clean = [], []
-    for i in range(int(rng.integers(4, 24))):
-        w, h = int(rng.integers(1, 700)), int(rng.integers(1, 500))
+    for i in range(int(rng.integers(4, 24 if MAXW <= 700 else 8))):
+        w, h = int(rng.integers(1, MAXW)), int(rng.integers(1, MAXH))
         hs, vs = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
         gray = bool(rng.integers(0, 6) == 0)
         if gray:
