@@ -214,3 +214,41 @@ def test_progressive_scans_against_reference_digests(emul, oracle_mod, golden_pr
     assert st[0] != 0 or (rc == 0 and np.array_equal(coefs[0].astype(np.int32), oc) and np.array_equal(rgbs[0], orgb))   # flagged, or the reference's reading
     assert oracle_mod.port_decode_progressive(cut)[0] != 0 and st[1] != 0
 
+
+
+def test_mini_soak_of_both_paths_against_the_oracle(emul, oracle_mod, harness):
+    # a small fixed-seed edition of scripts/dev/soak.py (which runs thousands of batches on the GPU): random pictures and
+    # corrupted copies of them through both entropy paths -- a clean one is bit-exact, a corrupted one is flagged or
+    # decoded to what the reference's logic makes of it, and whatever the oracle rejects is flagged
+    rng = np.random.default_rng(5)
+    datas, clean = [], []
+    for i in range(10):
+        w, h = int(rng.integers(8, 160)), int(rng.integers(8, 120))
+        hs, vs = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
+        d = harness.synth_jpeg(600 + i, w, h, int(rng.integers(30, 99)), hs, vs, False, int([0, -1, 1, 3][int(rng.integers(0, 4))]))
+        datas.append(d); clean.append(True)
+        m = bytearray(d)
+        body = d.find(b"\xff\xda") + 14
+        at = body + int(rng.integers(0, max(1, len(d) - 2 - body - 8)))
+        ln = int(rng.integers(1, 60))
+        kind = i % 5
+        if kind == 0:
+            m[at:at + ln] = bytes(ln)
+        elif kind == 1:
+            m = m[:at] + b"\xff\xd9"
+        elif kind == 2:
+            m[at:at + ln] = (b"\xff\x00" * ln)[:ln]
+        elif kind == 3:
+            m[at:at + ln] = b"\xff" * ln
+        else:
+            for p in rng.integers(body, len(d) - 2, size=6):
+                m[p] = int(rng.integers(0, 255))
+        datas.append(bytes(m)); clean.append(False)
+    for path in (1, 2):
+        st, rgbs, coefs, _ = emul.decode(datas, flags=1, path=path)
+        for i, d in enumerate(datas):
+            rc, _, oc, orgb = oracle_mod.port_decode(d, flags=1)
+            if clean[i]:
+                assert rc == 0 and st[i] == 0 and np.array_equal(coefs[i].astype(np.int32), oc) and np.array_equal(rgbs[i], orgb), (path, i)
+            elif st[i] == 0:
+                assert rc == 0 and np.array_equal(coefs[i].astype(np.int32), oc), (path, i, rc)
