@@ -47,7 +47,7 @@ def encode_rgb(rgb, quality=90, hs=2, vs=2, gray=False, restart=0):
     """restart: 0 none, >0 DRI value in MCUs, -1 one MCU row."""
     rgb = np.ascontiguousarray(rgb, np.uint8)
     h, w = rgb.shape[:2]
-    buf = np.empty(w * h * 3 + 65536, np.uint8)
+    buf = np.empty(w * h * 8 + 65536, np.uint8)      # white noise at quality 100 takes more bytes than the pixels it encodes
     n = _load().b200enc_encode_rgb(rgb.ctypes.data, w, h, quality, hs, vs, int(gray), restart, buf.ctypes.data, len(buf))
     if n < 0:
         raise RuntimeError("encoder output buffer too small")

@@ -126,7 +126,11 @@ def test_extreme_content(dec, oracle_mod, harness):
     datas = [harness.encode_rgb(flat, 90, 2, 2, False, -1), harness.encode_rgb(black, 50, 2, 2, False, 1),
              harness.encode_rgb(noise, 98, 2, 2, False, -1), harness.encode_rgb(noise, 98, 1, 1, False, 3),
              harness.encode_rgb(mixed, 95, 2, 2, False, -1), harness.encode_rgb(mixed, 90, 2, 1, False, 2),
-             harness.encode_rgb(flat, 90, 1, 1, True, 5), harness.encode_rgb(noise, 98, 1, 1, True, -1)]
+             harness.encode_rgb(flat, 90, 1, 1, True, 5), harness.encode_rgb(noise, 98, 1, 1, True, -1),
+             # q100: quantisers of 1, 99 % of all coefficients non-zero -- a block takes eight rounds of a lane, the ring
+             # of rounds between the writers and the flusher is what bounds them then
+             harness.encode_rgb(noise, 100, 1, 1, False, -1), harness.encode_rgb(noise, 100, 1, 1, False, 0),
+             harness.encode_rgb(noise, 100, 2, 2, False, 7)]
     compare(dec, oracle_mod, datas, flags=1)
 
 
