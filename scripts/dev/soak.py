@@ -15,6 +15,7 @@ sys.path.insert(0, ROOT)
 import jpeg_decoder_b200 as jd  # noqa: E402
 from jpeg_decoder_b200 import abi, harness  # noqa: E402
 from oracle import oracle  # noqa: E402
+from tests import jpeg_craft as jc  # noqa: E402
 
 rounds = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
@@ -63,7 +64,7 @@ decs = {p: jd.Decoder(0) for p in ("segment", "sync")}
 decs["segment"].set_entropy_path(abi.ENTROPY_SEGMENT); decs["sync"].set_entropy_path(abi.ENTROPY_SYNC)
 batch_dec = jd.Decoder(0)
 stat = {"batches": 0, "clean": 0, "corrupt": 0, "corrupt_flagged": 0, "oracle_checked": 0, "unflagged_same_as_oracle": 0,
-        "unflagged_but_oracle_rejects": 0, "refused_by_parser": 0, "decode_batch_checked": 0}
+        "unflagged_but_oracle_rejects": 0, "refused_by_parser": 0, "decode_batch_checked": 0, "transcoded": 0}
 for r in range(rounds):
     datas, clean = [], []
     for i in range(int(rng.integers(4, 24 if MAXW <= 700 else 8))):
@@ -75,6 +76,11 @@ for r in range(rounds):
         q = int(rng.integers(20, 100))
         ri = int([0, 0, -1, 1, 2, 5, 17][int(rng.integers(0, 7))])
         d = harness.synth_jpeg(int(rng.integers(0, 1 << 30)), w, h, q, hs, vs, gray, ri)
+        if w * h < 60000 and rng.integers(0, 4) == 0:
+            # the same picture under random Huffman code lengths (1 to 16 bits, whatever a Huffman tree over skewed weights
+            # gives): pairs, long codes and second-level overflow of the lookup tables in proportions no encoder produces
+            d = jc.with_ac_code_lengths(d, jc.random_code_lengths(rng))
+            stat["transcoded"] += 1
         datas.append(d); clean.append(True)
         for _ in range(int(rng.integers(0, 3))):
             datas.append(corrupt(d)); clean.append(False)

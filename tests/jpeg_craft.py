@@ -3,6 +3,8 @@ emits: arbitrary component identifiers (T.81 B.2.2), 16-bit quantisation tables 
 segments padded with 0-bits instead of 1-bits (F.1.2.3)."""
 import struct
 
+import numpy as np
+
 
 def segments(data):
     """[(marker, payload offset, payload length)] of the header segments up to and including SOS."""
@@ -249,3 +251,27 @@ def damaged_progressive(data):
     zeroed[m - 60:m + 60] = bytes(120)
     cut = data[:m - 30] + b"\xff\xd9"
     return bytes(zeroed), cut
+
+
+def random_code_lengths(rng, nsym=162):
+    """16 counts of a random prefix code over nsym symbols: lengths of a Huffman tree over random (skewed) weights, one
+    extra symbol reserving the all-ones code (T.81 Annex K.2), no code longer than 16 bits."""
+    import heapq
+    while True:
+        lam = float(rng.uniform(0.01, 0.35))           # geometric weights: from nearly flat to 1-bit-to-16-bit codes
+        w = list(np.exp(-lam * np.arange(nsym + 1)) * (0.5 + rng.random(nsym + 1)))
+        w[-1] = 1e-12                                  # the reserved code point: the lightest, so it ends up all ones
+        heap = [(x, i, (i,)) for i, x in enumerate(w)]
+        heapq.heapify(heap)
+        depth = [0] * (nsym + 1)
+        nxt = nsym + 1
+        while len(heap) > 1:
+            a = heapq.heappop(heap); b = heapq.heappop(heap)
+            for i in a[2] + b[2]:
+                depth[i] += 1
+            heapq.heappush(heap, (a[0] + b[0], nxt, a[2] + b[2])); nxt += 1
+        if max(depth) <= 16:
+            bits = [0] * 16
+            for d in sorted(depth[:-1]):
+                bits[d - 1] += 1
+            return bits
