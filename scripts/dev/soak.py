@@ -79,7 +79,7 @@ for r in range(rounds):
         if w * h < 60000 and rng.integers(0, 4) == 0:
             # the same picture under random Huffman code lengths (1 to 16 bits, whatever a Huffman tree over skewed weights
             # gives): pairs, long codes and second-level overflow of the lookup tables in proportions no encoder produces
-            d = jc.with_ac_code_lengths(d, jc.random_code_lengths(rng))
+            d = jc.with_ac_code_lengths(d, jc.random_code_lengths(rng), jc.random_code_lengths(rng, 12) if rng.integers(0, 2) else None)
             stat["transcoded"] += 1
         datas.append(d); clean.append(True)
         for _ in range(int(rng.integers(0, 3))):

@@ -158,9 +158,10 @@ class _Out:
             self.put((1 << (8 - self.n)) - 1, 8 - self.n)
 
 
-def with_ac_code_lengths(data, bits):
+def with_ac_code_lengths(data, bits, dc_bits=None):
     """The same picture with every AC table's code LENGTHS replaced by `bits` (16 counts; sum = the table's symbol
-    count, symbols keep their order) and the scan transcoded to the new codes.  Baseline, one scan, RSTn allowed."""
+    count, symbols keep their order) and the scan transcoded to the new codes; dc_bits: the same for every DC table.
+    Baseline, one scan, RSTn allowed."""
     segs = segments(data)
     tabs, frame, scan, ri = {}, None, None, 0
     for m, off, n in segs:
@@ -186,7 +187,7 @@ def with_ac_code_lengths(data, bits):
     for (cid, hs, vs), (sid, td, ta) in zip(comps, scan):
         assert cid == sid
         blocks += [(td, 0x10 | ta)] * (hs * vs if len(comps) > 1 else 1)
-    new_tabs = {k: ((list(bits), v[1]) if k >> 4 else v) for k, v in tabs.items()}
+    new_tabs = {k: ((list(bits), v[1]) if k >> 4 else ((list(dc_bits), v[1]) if dc_bits else v)) for k, v in tabs.items()}
     for k, (b, v) in new_tabs.items():
         assert sum(b) == len(v), (k, sum(b), len(v))
     dec = {k: _canon(*v)[1] for k, v in tabs.items()}
@@ -258,7 +259,7 @@ def random_code_lengths(rng, nsym=162):
     extra symbol reserving the all-ones code (T.81 Annex K.2), no code longer than 16 bits."""
     import heapq
     while True:
-        lam = float(rng.uniform(0.01, 0.35))           # geometric weights: from nearly flat to 1-bit-to-16-bit codes
+        lam = float(rng.uniform(0.01, 0.35)) * 162.0 / nsym    # geometric weights: from nearly flat to 1-bit-to-16-bit codes
         w = list(np.exp(-lam * np.arange(nsym + 1)) * (0.5 + rng.random(nsym + 1)))
         w[-1] = 1e-12                                  # the reserved code point: the lightest, so it ends up all ones
         heap = [(x, i, (i,)) for i, x in enumerate(w)]
