@@ -86,7 +86,9 @@ namespace b2 {
 #define B2_SEG_POLL_NS 200
 #endif
 #ifndef B2_SEG_DIAG
-#define B2_SEG_DIAG 0     // measurements only: 5 = the writers do not compute
+#define B2_SEG_DIAG 0     // measurements only (scripts/build_variant.sh): 7 = cycle counters per role and part of a round
+                          // (scripts/dev/seg_diag.py); wrong results on purpose: 5 = the writers do not compute, 8 = the flusher
+                          // does not copy, 9 = no DC prediction
 #endif
 constexpr int kSegGroups = B2_SEG_GROUPS;     // groups (32 segments: one decoder warp + its consumers) per CTA
 constexpr int kSegAcW = B2_SEG_ACW;           // AC writer warps per group: writer w takes the rounds r with r % kSegAcW == w
