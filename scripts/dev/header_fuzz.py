@@ -19,7 +19,7 @@ cases = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
 harness.build_harness(); oracle.build()
 stat = {"cases": 0, "both_accept": 0, "both_refuse": 0, "parser_accepts_oracle_fails_later": 0, "mismatch": 0}
-bad, later, keep = [], {}, []
+bad, later = [], {}
 for c in range(cases):
     w, h = int(rng.integers(1, 200)), int(rng.integers(1, 150))
     hs, vs = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
@@ -52,12 +52,9 @@ for c in range(cases):
         elif rc_o != 0 and rc_p == 0:
             stat["parser_accepts_oracle_fails_later"] += 1     # allowed: the failure may lie in the scan
             later[rc_o] = later.get(rc_o, 0) + 1
-            if len(keep) < 400:
-                keep.append((flags, rc_o, d))
         else:
             stat["mismatch"] += 1
             bad.append((c, flags, rc_o, rc_p))
-            open("/tmp/hfuzz_%d_%d.jpg" % (c, flags), "wb").write(d)
+            os.makedirs(os.path.join(ROOT, "gpurun_out", "hfuzz"), exist_ok=True)
+            open(os.path.join(ROOT, "gpurun_out", "hfuzz", "case_%d_%d.jpg" % (c, flags)), "wb").write(d)
 print(json.dumps(stat), bad[:10], "oracle codes where the parser accepted:", later)
-import pickle
-pickle.dump(keep, open("/tmp/hfuzz_keep.pkl", "wb"))
