@@ -190,7 +190,10 @@ B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, 
       const int r = (int)(rs >> 4), sz = (int)(rs & 15u);
       if (sz) {
         k += r;
-        if (k > 63) return ST_BAD_RUN;
+        // a run that leaves the scan's BAND is an error, not only one that leaves the block: scans of one component with
+        // disjoint bands run side by side (same dependency level), and a write outside the band would race with the
+        // neighbour's (found by scripts/dev/soak_progressive.py: GPU and emulation disagreed on two damaged files)
+        if (k > S.se) return ST_BAD_RUN;
         *prog_coef(coef, gb, k) = (int16_t)(prog_extend(B.bits(sz), sz) * (1 << S.al));
       } else if (r == 15) k += 15;
       else { eobrun = 1 << r; if (r) eobrun += (int)B.bits(r); --eobrun; break; }
@@ -215,7 +218,10 @@ B2_DEVICE uint32_t prog_block(ProgBits &B, const ProgScanDev &S, int16_t *coef, 
         } else if (--r < 0) break;
         ++k;
       } while (k <= S.se);
-      if (sz && k <= 63) *prog_coef(coef, gb, k) = (int16_t)sz;
+      if (sz) {
+        if (k > S.se) return ST_BAD_RUN;                // the new coefficient's place lies behind the band (see above)
+        *prog_coef(coef, gb, k) = (int16_t)sz;
+      }
     }
   }
   if (eobrun > 0) {                                   // rest of the band: correction bits only
