@@ -46,10 +46,11 @@ constexpr int kChunkWords = 64 + 8;          // read-ahead slack past the end of
 constexpr int kXMinShift = 9, kXMaxShift = 16;
 
 // dynamic shared memory (32-bit words): the table set's used tables (compacted), then per warp the window ring
-// [word][lane] (+ the slot that repeats slot 0) and two [block-in-MCU][lane] columns: table offsets, component
+// [word][lane] (+ the slot that repeats slot 0) and a [block-in-MCU][lane] column: DC table offset | component in its low two
+// bits | AC table offset << 16
 constexpr int kXRingWords = (kSegWords + 1) * 32;
-constexpr int kXWarpWords = kXRingWords + 2 * kMaxBpm * 32;
-constexpr uint32_t kXTb2Off = (uint32_t)kMaxBpm * 128u;   // bytes from a lane's table-offset entry to its component entry
+constexpr int kXWarpWords = kXRingWords + kMaxBpm * 32;
+static_assert((kHTab * 4) % 4 == 0 && kHTab * 4 >= 4, "the low two bits of a table's byte offset are free: they carry the component");
 B2_HD size_t xsync_smem_bytes(int nslots) {
   return sizeof(uint32_t) * ((size_t)nslots * kHTab + (size_t)kXWarps * kXWarpWords);
 }
@@ -135,8 +136,7 @@ struct XWalkOut { uint32_t sp, sblk, ep, eblk; int nb, d0, d1, d2; };
 constexpr int kXOverNb = 1 << 28;            // "blocks" of a sub whose walk ran past its segment's end (see x_walk)
 
 // All 32 lanes of a warp together.  ringl: this lane's column of the warp's window ring; tbl: this lane's column of the
-// warp's table-offset entries, already filled for the lane's image ([blk] = DC table byte offset | AC << 16, and at
-// +kXTb2Off the component).  Counts the blocks that start in [sp, ep), sp = first block start >= lo, ep = first block
+// warp's table-offset entries, already filled for the lane's image ([blk] = DC table byte offset | component | AC << 16).  Counts the blocks that start in [sp, ep), sp = first block start >= lo, ep = first block
 // start >= hi (or the segment's end), and sums their DC differences (jpeg.cpp:335-345) per component.
 B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, const XWalkIn &I,
                       const TableSet *__restrict__ tsets, XWalkOut &O) {
@@ -154,7 +154,7 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
     }
     rw += kSegWords;
   } else {                                              // an idle lane steps in place over entry 0 of table 0: keep its reads inside the CTA's shared memory
-    tbl[0] = 0u; tbl[kMaxBpm * 32] = 0u;
+    tbl[0] = 0u;
   }
   b2_cp_async_commit();
   b2_cp_async_wait<0>();
@@ -210,9 +210,9 @@ B2_DEVICE void x_walk(int lane, uint32_t *ringl, uint32_t *tbl, uint32_t lut_a, 
 #pragma unroll
     for (int u = 0; u < kXSteps; ++u) {
       const uint32_t t = b2_lds_ro(tba);
-      comp = b2_lds_ro(tba + kXTb2Off);
+      comp = t & 3u;
       is_dc = z == 0u;
-      cur = lut_r + (is_dc ? (t & 0xffffu) : (t >> 16));
+      cur = lut_r + (is_dc ? (t & 0xfffcu) : (t >> 16));
       const uint32_t wa = b2_and_x4_add<(uint32_t)((kSegWords - 1) << 5)>(p, ring_a);      // ring_a + 128 * ((p >> 5) & 31)
       const uint32_t w0 = b2_lds_ro(wa), w1 = b2_lds_ro(wa + 128u);
       w = __funnelshift_l(w1, w0, p);
@@ -345,8 +345,7 @@ B2_DEVICE void x_set_tb(uint32_t *tbl, const ImageDev &im, const int32_t *tabslo
   for (int b = 0; b < im.bpm; ++b) {
     const int c = b < nluma ? 0 : b - nluma + 1;
     const int sd = tabslot[im.td[c] & 3], sa = tabslot[4 + (im.ta[c] & 3)];
-    tbl[b * 32] = (uint32_t)(sd < 0 ? 0 : sd) * (kHTab * 4) | ((uint32_t)(sa < 0 ? 0 : sa) * (kHTab * 4)) << 16;
-    tbl[kMaxBpm * 32 + b * 32] = (uint32_t)c;
+    tbl[b * 32] = (uint32_t)(sd < 0 ? 0 : sd) * (kHTab * 4) | (uint32_t)c | ((uint32_t)(sa < 0 ? 0 : sa) * (kHTab * 4)) << 16;
   }
 }
 
